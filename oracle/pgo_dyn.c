@@ -28,6 +28,11 @@ struct pgo_arm {
   double residual_thr;
   double max_coord_vel;
   double q[PGO_MAXD], qd[PGO_MAXD];
+  /* joint positions behind btMultiBody's m_cachedWorldTransform, i.e. what getLinkState() reports without
+   * computeForwardKinematics: forwardKinematics() runs at the START of each stepSimulation, so link poses
+   * lag the joint state by one substep.  Pinned by test/pybullet_test.py:139-170 (orientation/velocity KATs
+   * match q_19, not q_20).  resetJointState refreshes it. */
+  double q_fk[PGO_MAXD];
   int motor_mode[PGO_MAXD];
   double motor_target[PGO_MAXD], motor_maximp[PGO_MAXD];
   double ik_damping, ik_residual;
@@ -111,12 +116,13 @@ int pgo_arm_nlinks(const pgo_arm* a) { return a->nl; }
 void pgo_arm_set_damping(pgo_arm* a, double lin, double ang) { a->lin_damp = lin; a->ang_damp = ang; }
 void pgo_arm_set_solver(pgo_arm* a, int iters, double thr) { a->solver_iters = iters; a->residual_thr = thr; }
 void pgo_arm_set_ik(pgo_arm* a, double damping, int iters, double thr) { a->ik_damping = damping; a->ik_iters = iters; a->ik_residual = thr; }
-void pgo_arm_reset_joint(pgo_arm* a, int d, double q) { a->q[d] = q; a->qd[d] = 0; }
+void pgo_arm_reset_joint(pgo_arm* a, int d, double q) { a->q[d] = q; a->qd[d] = 0; memcpy(a->q_fk, a->q, sizeof a->q); }
 void pgo_arm_get_q(const pgo_arm* a, double* q, double* qd) {
   for (int d = 0; d < a->nd; d++) { if (q) q[d] = a->q[d]; if (qd) qd[d] = a->qd[d]; }
 }
 void pgo_arm_set_q(pgo_arm* a, const double* q, const double* qd) {
   for (int d = 0; d < a->nd; d++) { if (q) a->q[d] = q[d]; if (qd) a->qd[d] = qd[d]; }
+  memcpy(a->q_fk, a->q, sizeof a->q);
 }
 void pgo_arm_set_motor(pgo_arm* a, int d, int mode, double target, double max_force) {
   a->motor_mode[d] = mode; a->motor_target[d] = target; a->motor_maximp[d] = max_force * a->dt;
@@ -180,10 +186,19 @@ void pgo_arm_link_state(const pgo_arm* a0, int link, double pos[3], double quat[
   fk(a);
   double w[PGO_MAXL][3], vc[PGO_MAXL][3];
   link_vel(a, a->Rw, a->ow, a->comw, w, vc);
-  for (int k = 0; k < 3; k++) { if (pos) pos[k] = a->comw[link][k]; if (lin) lin[k] = vc[link][k]; if (ang) ang[k] = w[link][k]; }
-  if (quat) R_to_quat_xyzw(a->Rw[link], quat); /* inertial rpy = 0: COM frame shares the link orientation */
+  /* pose from the cached (one-substep-old) transforms; velocities = compTreeLinkVelocities (link-local,
+   * current q/qd) rotated to world by the CACHED basis */
+  double Rc[PGO_MAXL][9], oc[PGO_MAXL][3], cc[PGO_MAXL][3], vl[3], wl[3];
+  fk_q(a, a->q_fk, Rc, oc, cc);
+  m3Tvec(a->Rw[link], vc[link], vl);
+  m3Tvec(a->Rw[link], w[link], wl);
+  if (lin) m3vec(Rc[link], vl, lin);
+  if (ang) m3vec(Rc[link], wl, ang);
+  for (int k = 0; k < 3; k++) if (pos) pos[k] = cc[link][k];
+  if (quat) R_to_quat_xyzw(Rc[link], quat); /* inertial rpy = 0: COM frame shares the link orientation */
 }
 void pgo_arm_link_frame(const pgo_arm* a0, int link, double R[9], double p[3]) {
+  /* CURRENT-q frame of the URDF link (what the colliders / getClosestPoints see) */
   pgo_arm* a = (pgo_arm*)a0;
   fk(a);
   memcpy(R, a->Rw[link], sizeof(m3));
@@ -372,6 +387,7 @@ typedef struct { int dof; double sign, rhs, lo, hi, applied, dinv, resp[PGO_MAXD
 int pgo_arm_substep(pgo_arm* a) {
   int nd = a->nd;
   double qdd[PGO_MAXD];
+  memcpy(a->q_fk, a->q, sizeof a->q); /* btMultiBodyDynamicsWorld::solveConstraints -> forwardKinematics() */
   /* 1. forward dynamics with gravity/damping, velocity update (solveExternalForces) */
   aba(a, qdd);
   for (int d = 0; d < nd; d++) {
@@ -527,4 +543,5 @@ int pgo__arm_prims(const pgo_arm* a, const pgo_prim_t** P) { *P = a->P; return a
 void pgo__arm_fk(pgo_arm* a) { fk(a); }
 const double* pgo__arm_Rw(const pgo_arm* a, int link) { return a->Rw[link]; }
 const double* pgo__arm_ow(const pgo_arm* a, int link) { return a->ow[link]; }
+const double* pgo__arm_base(const pgo_arm* a) { return a->base_pos; }
 const pgo_link_t* pgo__arm_links(const pgo_arm* a) { return a->L; }

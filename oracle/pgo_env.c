@@ -1,0 +1,523 @@
+/* oracle/pgo_env.c -- CPU restatement of the reference's Python env layer for the hot path:
+ *   RobotTaskEnv.reset/step/_get_obs        panda_gym/envs/core.py:286-308, 352-368
+ *   Panda.set_action / get_obs / reset      panda_gym/envs/robots/panda.py:120-172, 226-312
+ *   Reach                                   panda_gym/envs/tasks/reach.py
+ *   ReachAO                                 panda_gym/envs/tasks/reach_ao.py:182-198, 518-722, 896-1264, 1308-1383
+ *   distance()                              panda_gym/utils.py:4-16
+ * TEST INFRASTRUCTURE ONLY (see oracle/pgo.h).  The pyb_utils-fork distance aggregation behind
+ * check_collided / get_obs is reconstructed from its call sites: PARITY UNPINNED.
+ */
+#define _GNU_SOURCE
+#include "pgo.h"
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define N_ARM 7
+static const double NEUTRAL[7] = {0.0, -0.3, 0.0, -2.2, 0.0, 2.0, 0.78539816339744830962}; /* panda.py:67 */
+static const double FORCES[7] = {87.0, 87.0, 87.0, 87.0, 12.0, 120.0, 120.0};              /* panda.py:63 */
+static const int COLL_LINKS[PGO_NCL] = {0, 1, 2, 3, 4, 5, 6, 7, 9};                        /* reach_ao.py:98-99 */
+#define EE_LINK 11                                                                          /* panda.py:68 */
+#define NPRIM_ALL 36
+
+struct pgo_env {
+  pgo_env_config cfg;
+  pgo_arm* arm;
+  double goal[3];
+  pgo_obstacle obs[PGO_MAXOBS];
+  int nobs;
+  int is_collided, goal_reached, steps;
+  double d_link[PGO_NCL];
+  int have_recent, have_prev;
+  float recent[8], prev[8];
+  double cur_vel[7], prev_vel[7], cur_acc[7], prev_acc[7], jerk[7];
+  pgo_pcg64 rng;
+  double dummy[3]; /* the collidable r=0.05 probe sphere (reach_ao.py:284-290) */
+  /* scenario parameter block */
+  int goal_sampler;        /* 0 box, 1 hollow sphere */
+  double goal_lo[3], goal_hi[3];
+  double goal_rmin, goal_rmax; int goal_upper, goal_front, goal_34;
+  int obs_sampler;         /* 0 goal box, 1 wang (70/20/10), 2 experimental (50/50), 3 wang-N (70/30) */
+  int randomize_obstacles, allow_overlap, random_num_obs, size_lo, size_hi;
+  double table_pos[3], table_half[3];
+};
+
+/* ------------------------------------------------------------------ helpers */
+static float f32_distance(const float* a, const float* b) {
+  /* utils.distance on float32 inputs: norm in float32 (no FMA), np.round(., 6) in float32 */
+  volatile float dx = a[0] - b[0], dy = a[1] - b[1], dz = a[2] - b[2];
+  volatile float xx = dx * dx, yy = dy * dy, zz = dz * dz;
+  volatile float s = xx + yy; s = s + zz;
+  volatile float d = sqrtf(s);
+  volatile float m = d * 1e6f;
+  m = rintf(m);
+  return m / 1e6f;
+}
+
+void pgo_env_default_config(pgo_env_config* c, int task) {
+  memset(c, 0, sizeof *c);
+  c->task = task;
+  c->control = 0; c->reward_type = 0; c->goal_condition = 0; c->action_limiter = 0;
+  c->n_substeps = 20; c->collision_reward = -100.0; c->ee_error_threshold = 0.05; c->speed_threshold = 0.1;
+  c->safety_distance = 0.0; c->max_episode_steps = 50;
+  if (task == 0) { /* PandaReach*: Panda(obs_type=("ee",)), base (-0.6,0,0) (panda_tasks.py:81-88) */
+    c->obs_js = 0; c->obstacle_obs = 0; c->truncate_on_collision = 0; c->terminate_on_success = 0;
+    c->base_pos[0] = -0.6; c->scenario = PGO_SCN_NONE;
+  } else {         /* PandaReachAO-v3 with TrainConfig() defaults (train_config.py) */
+    c->obs_js = 1; c->obstacle_obs = 1; c->truncate_on_collision = 1; c->terminate_on_success = 1;
+    c->scenario = PGO_SCN_REACHAO1;
+  }
+}
+
+static void add_sphere(pgo_env* e, double r) {
+  pgo_obstacle* o = &e->obs[e->nobs++];
+  o->type = 0; o->pos[0] = 0.1; o->pos[1] = 0; o->pos[2] = 0.1; o->size[0] = r; o->size[1] = o->size[2] = 0; /* reach_ao.py:819 */
+}
+static void add_cuboid(pgo_env* e, double h) {
+  pgo_obstacle* o = &e->obs[e->nobs++];
+  o->type = 1; o->pos[0] = 0.1; o->pos[1] = 0; o->pos[2] = 0.1; o->size[0] = o->size[1] = o->size[2] = h;    /* reach_ao.py:841 */
+}
+static void goal_box(pgo_env* e, double xl, double xh, double yl, double yh, double zl, double zh) {
+  e->goal_sampler = 0;
+  e->goal_lo[0] = xl; e->goal_lo[1] = yl; e->goal_lo[2] = zl; e->goal_hi[0] = xh; e->goal_hi[1] = yh; e->goal_hi[2] = zh;
+}
+static void goal_shell(pgo_env* e, double rmin, double rmax, int upper, int front, int q34) {
+  e->goal_sampler = 1; e->goal_rmin = rmin; e->goal_rmax = rmax; e->goal_upper = upper; e->goal_front = front; e->goal_34 = q34;
+}
+
+static void setup_scenario(pgo_env* e) {
+  const pgo_env_config* c = &e->cfg;
+  e->nobs = 0;
+  if (c->task == 0) { /* Reach: goal_range 0.3 (reach.py:24-25); table 1.1x0.7x0.4 at x=-0.3 (reach.py:33) */
+    goal_box(e, -0.15, 0.15, -0.15, 0.15, 0.0, 0.3);
+    e->table_pos[0] = -0.3; e->table_pos[1] = 0; e->table_pos[2] = -0.2;
+    e->table_half[0] = 0.55; e->table_half[1] = 0.35; e->table_half[2] = 0.2;
+    return;
+  }
+  /* ReachAO: table 2.0x1.3x0.4 (reach_ao.py:272); default goal range (reach_ao.py:78-82) */
+  e->table_pos[0] = 0; e->table_pos[1] = 0; e->table_pos[2] = -0.2;
+  e->table_half[0] = 1.0; e->table_half[1] = 0.65; e->table_half[2] = 0.2;
+  goal_box(e, -0.3 / 2.5 + 0.6, 0.3 / 2.5 + 0.6, -0.3 / 1.5, 0.3 / 1.5, 0.0, 0.3);
+  e->obs_sampler = 0; e->randomize_obstacles = 0; e->allow_overlap = 0; e->random_num_obs = 0;
+  switch (c->scenario) {
+    case PGO_SCN_REACH1: goal_box(e, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4); break;       /* :518-522 */
+    case PGO_SCN_REACH2: case PGO_SCN_REACH3: goal_shell(e, 0.5, 0.85, 1, 0, 1); break;                      /* :524-539 */
+    case PGO_SCN_REACHAO1:                                                                                   /* :541-545 */
+      goal_box(e, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4);
+      e->randomize_obstacles = 1; add_sphere(e, 0.04); break;
+    case PGO_SCN_REACHAO2:                                                                                   /* :547-564 */
+      goal_shell(e, 0.5, 0.8, 1, 1, 0); e->randomize_obstacles = 1; e->obs_sampler = 1;
+      add_sphere(e, 0.05); add_sphere(e, 0.05); break;
+    case PGO_SCN_REACHAO3:                                                                                   /* :573-585 */
+      goal_shell(e, 0.5, 0.8, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 1;
+      for (int i = 0; i < 3; i++) add_sphere(e, 0.05);
+      break;
+    case PGO_SCN_REACHAO_RAND:                                                                               /* :587-599 */
+      goal_shell(e, 0.5, 0.8, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 2;
+      for (int i = 0; i < 3; i++) add_sphere(e, 0.05);
+      for (int i = 0; i < 3; i++) add_cuboid(e, 0.05);
+      e->random_num_obs = 1; e->allow_overlap = 1; e->size_lo = 4; e->size_hi = 6; break;
+    case PGO_SCN_WANG:                                                                                       /* :646-699 */
+      goal_shell(e, 0.4, 0.95, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 3;
+      for (int i = 0; i < c->n_obstacles; i++) add_sphere(e, 0.05);
+      break;
+    case PGO_SCN_WANGEXP:                                                                                    /* :701-722 */
+      goal_shell(e, 0.5, 0.8, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 1;
+      for (int i = 0; i < c->n_obstacles; i++) add_sphere(e, 0.05);
+      break;
+    default: break;
+  }
+}
+
+pgo_env* pgo_env_create(const pgo_env_config* c) {
+  pgo_env* e = (pgo_env*)calloc(1, sizeof *e);
+  e->cfg = *c;
+  e->arm = pgo_arm_create(0, c->base_pos);
+  setup_scenario(e);
+  for (int k = 0; k < PGO_NCL; k++) e->d_link[k] = 0.0; /* reach_ao.py:110 np.zeros */
+  for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, 0.0);
+  return e;
+}
+void pgo_env_destroy(pgo_env* e) { if (e) { pgo_arm_destroy(e->arm); free(e); } }
+pgo_arm* pgo_env_arm(pgo_env* e) { return e->arm; }
+int pgo_env_is_collided(const pgo_env* e) { return e->is_collided; }
+void pgo_env_set_goal(pgo_env* e, const double g[3]) { memcpy(e->goal, g, 24); }
+void pgo_env_get_goal(const pgo_env* e, double g[3]) { memcpy(g, e->goal, 24); }
+void pgo_env_set_obstacles(pgo_env* e, int n, const pgo_obstacle* o) { e->nobs = n; memcpy(e->obs, o, n * sizeof *o); }
+int pgo_env_get_obstacles(const pgo_env* e, pgo_obstacle* o) { memcpy(o, e->obs, e->nobs * sizeof *o); return e->nobs; }
+
+static int task_obs_dim(const pgo_env* e) {
+  if (e->cfg.task == 0 || e->cfg.obstacle_obs == 0) return 0;
+  if (e->nobs == 0) return 27; /* reach_ao.py:904: np.ones(27) whatever the mode */
+  switch (e->cfg.obstacle_obs) { case 1: return 36; case 2: return 27; case 3: return 9; default: return 1; }
+}
+int pgo_env_obs_dim(const pgo_env* e) { return 6 + (e->cfg.obs_js ? 14 : 0) + task_obs_dim(e); }
+int pgo_env_act_dim(const pgo_env* e) { return e->cfg.control == 1 ? 3 : 7; } /* block_gripper=True */
+
+/* ------------------------------------------------------------------ collision queries */
+int pgo_env_check_collided(pgo_env* e, double* d_link, double* d_table_min) {
+  /* reach_ao.py:896-900 */
+  pgo_obstacle table; table.type = 1; memcpy(table.pos, e->table_pos, 24); memcpy(table.size, e->table_half, 24);
+  double mn = 1e300, tmn = 1e300;
+  for (int i = 0; i < PGO_NCL; i++) {
+    double best = 999.0; /* pyb_utils saturates at max_distance */
+    for (int j = 0; j < e->nobs; j++) {
+      double d = pgo_link_obstacle_distance(e->arm, COLL_LINKS[i], &e->obs[j], 0, 0);
+      if (d < best) best = d;
+    }
+    e->d_link[i] = best;
+    if (d_link) d_link[i] = best;
+    if (best < mn) mn = best;
+    if (i >= 1) { /* table: ignore panda_link0, panda_link1 */
+      double d = pgo_link_obstacle_distance(e->arm, COLL_LINKS[i], &table, 0, 0);
+      if (d < tmn) tmn = d;
+    }
+  }
+  if (d_table_min) *d_table_min = tmn;
+  return (mn <= 0.0 || tmn <= 0.0) ? 1 : 0;
+}
+
+/* body-level getClosestPoints(robot, body) min distance (reach_ao.py:1169-1181): every link incl. base */
+static double robot_body_distance(pgo_env* e, const pgo_obstacle* o) {
+  double best = 1e300;
+  for (int p = 0; p < NPRIM_ALL; p++) { double d = pgo_prim_obstacle_distance(e->arm, p, o, 0, 0); if (d < best) best = d; }
+  return best;
+}
+/* sphere body vs sphere / box body; box-box: Bullet's SAT box detector only reports overlapping boxes */
+static int body_body_collision(const pgo_obstacle* a, const pgo_obstacle* b, double margin) {
+  if (a->type == 0 && b->type == 0) {
+    double d[3] = {a->pos[0] - b->pos[0], a->pos[1] - b->pos[1], a->pos[2] - b->pos[2]};
+    return margin >= sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]) - a->size[0] - b->size[0];
+  }
+  if (a->type == 1 && b->type == 1) {
+    for (int k = 0; k < 3; k++) if (fabs(a->pos[k] - b->pos[k]) > a->size[k] + b->size[k]) return 0;
+    return 1;
+  }
+  const pgo_obstacle* s = a->type == 0 ? a : b;
+  const pgo_obstacle* bx = a->type == 0 ? b : a;
+  double m = pgo_box_margin(bx->size), v[3], d2 = 0, rel[3];
+  for (int k = 0; k < 3; k++) {
+    double ek = bx->size[k] - m;
+    rel[k] = s->pos[k] - bx->pos[k];
+    double cl = rel[k] > ek ? ek : (rel[k] < -ek ? -ek : rel[k]);
+    v[k] = rel[k] - cl; d2 += v[k] * v[k];
+  }
+  double d;
+  if (d2 <= 1.1920929e-07) {
+    double best = 1e300;
+    for (int k = 0; k < 3; k++) { double ek = bx->size[k] - m; if (ek - rel[k] < best) best = ek - rel[k]; if (ek + rel[k] < best) best = ek + rel[k]; }
+    d = -best;
+  } else d = sqrt(d2);
+  return margin >= d - m - s->size[0];
+}
+
+/* ------------------------------------------------------------------ samplers (reach_ao.py:1183-1211, 610-644) */
+static void sample_hollow(pgo_env* e, double rmin, double rmax, int upper, int front, int q34, double out[3]) {
+  double phi = pgo_pcg64_uniform(&e->rng, 0, 2 * M_PI);
+  double theta = upper ? pgo_pcg64_uniform(&e->rng, 0, 0.5 * M_PI) : pgo_pcg64_uniform(&e->rng, 0, M_PI);
+  if (front) phi = pgo_pcg64_uniform(&e->rng, -0.5 * M_PI, 0.5 * M_PI);
+  if (q34) phi = pgo_pcg64_uniform(&e->rng, -0.75 * M_PI, 0.75 * M_PI);
+  double r = cbrt(pgo_pcg64_uniform(&e->rng, rmin * rmin * rmin, rmax * rmax * rmax));
+  out[0] = r * sin(theta) * cos(phi); out[1] = r * sin(theta) * sin(phi); out[2] = r * cos(theta);
+}
+static void sample_goal(pgo_env* e, double out[3]) {
+  if (e->goal_sampler == 0) for (int k = 0; k < 3; k++) out[k] = pgo_pcg64_uniform(&e->rng, e->goal_lo[k], e->goal_hi[k]);
+  else sample_hollow(e, e->goal_rmin, e->goal_rmax, e->goal_upper, e->goal_front, e->goal_34, out);
+}
+static void ee_position(pgo_env* e, double p[3]) { pgo_arm_link_state(e->arm, EE_LINK, p, 0, 0, 0); }
+static void sample_obstacle(pgo_env* e, double out[3]) {
+  double s[3], c[3];
+  switch (e->obs_sampler) {
+    case 0: for (int k = 0; k < 3; k++) out[k] = pgo_pcg64_uniform(&e->rng, e->goal_lo[k], e->goal_hi[k]); return;
+    case 1: { /* sample_obstacle_wang */
+      double r = pgo_pcg64_double(&e->rng);
+      if (r > 0.3) { sample_hollow(e, 0.1, 0.5, 0, 0, 0, s); memcpy(c, e->goal, 24); }
+      else if (r > 0.1) { sample_hollow(e, 0.1, 0.4, 0, 0, 0, s); ee_position(e, c); }
+      else { sample_hollow(e, 0.3, 0.6, 1, 0, 0, s); pgo_arm_link_state(e->arm, 0, c, 0, 0, 0); }
+      break; }
+    case 2: { /* sample_obstacle_experimental */
+      double r = pgo_pcg64_double(&e->rng);
+      sample_hollow(e, 0.1, 0.5, 0, 0, 0, s);
+      if (r > 0.5) memcpy(c, e->goal, 24); else ee_position(e, c);
+      break; }
+    default: { /* create_scenario_wang.sample_wang_obstacle */
+      double r = pgo_pcg64_double(&e->rng);
+      if (r > 0.3) { sample_hollow(e, 0.2, 0.6, 0, 0, 0, s); memcpy(c, e->goal, 24); }
+      else { sample_hollow(e, 0.2, 0.4, 0, 0, 0, s); ee_position(e, c); }
+      break; }
+  }
+  for (int k = 0; k < 3; k++) out[k] = s[k] + c[k];
+}
+
+/* Generator.integers / shuffle pieces (reach_ao.py:1062-1082), 32-bit draws with PCG64's buffered half */
+typedef struct { int has; uint32_t val; } u32buf;
+static uint32_t next_u32(pgo_env* e, u32buf* b) {
+  if (b->has) { b->has = 0; return b->val; }
+  uint64_t n = pgo_pcg64_next(&e->rng);
+  b->has = 1; b->val = (uint32_t)(n >> 32);
+  return (uint32_t)n;
+}
+static uint32_t lemire_u32(pgo_env* e, u32buf* b, uint32_t rng) {
+  uint32_t excl = rng + 1;
+  uint64_t m = (uint64_t)next_u32(e, b) * excl;
+  uint32_t left = (uint32_t)m;
+  if (left < excl) {
+    uint32_t thr = (0xFFFFFFFFu - rng) % excl;
+    while (left < thr) { m = (uint64_t)next_u32(e, b) * excl; left = (uint32_t)m; }
+  }
+  return (uint32_t)(m >> 32);
+}
+static uint32_t interval_u32(pgo_env* e, u32buf* b, uint32_t max) {
+  if (max == 0) return 0;
+  uint32_t mask = max, v;
+  mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
+  while ((v = (next_u32(e, b) & mask)) > max) {}
+  return v;
+}
+
+/* ------------------------------------------------------------------ reset (reach_ao.py:965-1033) */
+static int set_coll_free_goal(pgo_env* e, int with_obstacles, double margin) {
+  pgo_obstacle table; table.type = 1; memcpy(table.pos, e->table_pos, 24); memcpy(table.size, e->table_half, 24);
+  int i = 0, status = 0;
+  for (;;) {
+    sample_goal(e, e->goal);
+    if (i > 9999) { ee_position(e, e->goal); status = 1; break; }
+    i++;
+    pgo_obstacle probe; probe.type = 0; memcpy(probe.pos, e->goal, 24); probe.size[0] = 0.05;
+    memcpy(e->dummy, e->goal, 24);
+    int coll = 0;
+    if (with_obstacles) for (int j = 0; j < e->nobs; j++) coll |= body_body_collision(&probe, &e->obs[j], margin);
+    coll |= body_body_collision(&probe, &table, margin);
+    coll |= (margin >= robot_body_distance(e, &probe));
+    if (!coll) break;
+  }
+  return status;
+}
+static int set_coll_free_obs(pgo_env* e, double margin) {
+  pgo_obstacle table; table.type = 1; memcpy(table.pos, e->table_pos, 24); memcpy(table.size, e->table_half, 24);
+  for (int j = 0; j < e->nobs; j++) {
+    int i = 0;
+    for (;;) {
+      if (i > 9999) return 2; /* StopIteration escapes in the reference (reach_ao.py:1144-1145) */
+      i++;
+      double pos[3];
+      sample_obstacle(e, pos);
+      memcpy(e->obs[j].pos, pos, 24);
+      pgo_obstacle probe; probe.type = 0; memcpy(probe.pos, e->dummy, 24); probe.size[0] = 0.05;
+      int coll = (margin + e->cfg.safety_distance >= robot_body_distance(e, &e->obs[j]));
+      coll |= body_body_collision(&table, &e->obs[j], margin);
+      coll |= body_body_collision(&probe, &e->obs[j], margin);
+      if (!e->allow_overlap) {
+        for (int k = 0; k < e->nobs; k++) if (k != j) coll |= body_body_collision(&e->obs[k], &e->obs[j], 0.0);
+        e->dummy[0] = e->dummy[1] = e->dummy[2] = 0.0; /* probe moved to the origin and LEFT there */
+        memcpy(probe.pos, e->dummy, 24);
+        coll |= !body_body_collision(&probe, &e->obs[j], 1.0);
+      }
+      if (!coll) break;
+    }
+  }
+  return 0;
+}
+
+static void robot_obs(pgo_env* e, float* o, float* ag) {
+  double p[3], v[3], q[PGO_MAXD], qd[PGO_MAXD];
+  pgo_arm_link_state(e->arm, EE_LINK, p, 0, v, 0);
+  for (int k = 0; k < 3; k++) { o[k] = (float)p[k]; o[3 + k] = (float)v[k]; if (ag) ag[k] = (float)p[k]; }
+  if (e->cfg.obs_js) {
+    pgo_arm_get_q(e->arm, q, qd);
+    for (int d = 0; d < 7; d++) { o[6 + d] = (float)q[d]; o[13 + d] = (float)qd[d]; }
+  }
+}
+
+static void task_obs(pgo_env* e, float* o) {
+  /* reach_ao.py:902-959 */
+  int n = task_obs_dim(e);
+  if (n == 0) return;
+  if (e->nobs == 0) { for (int k = 0; k < 27; k++) o[k] = 1.0f; return; }
+  double dmin[PGO_NCL], u[PGO_NCL][3], all = 1e300;
+  for (int i = 0; i < PGO_NCL; i++) {
+    double best = 1e300, pa[3] = {0, 0, 0}, pb[3] = {0, 0, 0};
+    for (int j = 0; j < e->nobs; j++) {
+      double ta[3], tb[3];
+      double d = pgo_link_obstacle_distance(e->arm, COLL_LINKS[i], &e->obs[j], ta, tb);
+      if (d < best) { best = d; memcpy(pa, ta, 24); memcpy(pb, tb, 24); }
+    }
+    dmin[i] = best < 999.0 ? best : 999.0;
+    if (dmin[i] < all) all = dmin[i];
+    double v[3] = {pb[0] - pa[0], pb[1] - pa[1], pb[2] - pa[2]};
+    double L = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+    for (int k = 0; k < 3; k++) { double x = v[k] / L; u[i][k] = isnan(x) ? 0.0 : x; } /* utils.unit_vector */
+  }
+  switch (e->cfg.obstacle_obs) {
+    case 1: for (int i = 0; i < 9; i++) { o[i] = (float)dmin[i]; for (int k = 0; k < 3; k++) o[9 + 3 * i + k] = (float)u[i][k]; } break;
+    case 2: for (int i = 0; i < 9; i++) for (int k = 0; k < 3; k++) o[3 * i + k] = (float)u[i][k]; break;
+    case 3: for (int i = 0; i < 9; i++) o[i] = (float)dmin[i]; break;
+    default: o[0] = (float)all; break;
+  }
+}
+
+void pgo_env_get_obs(pgo_env* e, float* obs, float* ag, float* dg) {
+  robot_obs(e, obs, ag);
+  task_obs(e, obs + 6 + (e->cfg.obs_js ? 14 : 0));
+  if (dg) for (int k = 0; k < 3; k++) dg[k] = (float)e->goal[k];
+}
+
+static int is_success(pgo_env* e, const float* ag, const float* dg) {
+  float d = f32_distance(ag, dg);
+  float thr = (float)e->cfg.ee_error_threshold;
+  if (e->cfg.task == 1 && e->cfg.goal_condition == 1) { /* "halt": latched (reach_ao.py:1253-1261) */
+    if (!e->goal_reached) {
+      double v[3]; pgo_arm_link_state(e->arm, EE_LINK, 0, 0, v, 0);
+      double sp = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+      e->goal_reached = (d < thr) && (sp < (double)(float)e->cfg.speed_threshold);
+    }
+    return e->goal_reached;
+  }
+  return d < thr;
+}
+
+int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, int* success) {
+  int status = 0;
+  pgo_pcg64_seed(&e->rng, seed);                       /* core.py:302 */
+  for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, NEUTRAL[d]); /* panda.py:290-298 */
+  e->steps = 0;
+  if (e->cfg.task == 0) {
+    for (int k = 0; k < 3; k++) e->goal[k] = pgo_pcg64_uniform(&e->rng, e->goal_lo[k], e->goal_hi[k]); /* reach.py:75-78 */
+  } else {
+    e->goal_reached = 0; e->is_collided = 0;
+    status |= set_coll_free_goal(e, 0, 0.1);           /* fixed_target None */
+    if (e->randomize_obstacles) status |= set_coll_free_obs(e, 0.03);
+    else status |= set_coll_free_goal(e, 1, 0.03);
+    e->dummy[0] = 0; e->dummy[1] = 0; e->dummy[2] = -5.0;
+    if (e->random_num_obs) {                           /* reach_ao.py:1062-1082 */
+      u32buf b = {0, 0};
+      int n = e->nobs;
+      int k = e->size_lo + (e->size_hi - 1 - e->size_lo == 0 ? 0 : (int)lemire_u32(e, &b, (uint32_t)(e->size_hi - 1 - e->size_lo)));
+      int to_move = abs(k - n), order[PGO_MAXOBS];
+      for (int i = 0; i < n; i++) order[i] = i;
+      for (int i = n - 1; i >= 1; i--) { int j = (int)interval_u32(e, &b, (uint32_t)i); int t = order[i]; order[i] = order[j]; order[j] = t; }
+      for (int i = 0; i < n && to_move > 0; i++, to_move--) { e->obs[order[i]].pos[0] = 99.9; e->obs[order[i]].pos[1] = 99.9; e->obs[order[i]].pos[2] = -99.9; }
+    }
+    e->have_recent = e->have_prev = 0;                 /* reach_ao.py:1025-1026 */
+  }
+  float a[3], g[3];
+  pgo_env_get_obs(e, obs, a, g);
+  if (ag) memcpy(ag, a, 12);
+  if (dg) memcpy(dg, g, 12);
+  if (success) *success = is_success(e, a, g);
+  return status;
+}
+
+/* ------------------------------------------------------------------ step */
+static void set_action(pgo_env* e, const float* action) {
+  int na = pgo_env_act_dim(e);
+  float a[8];
+  for (int k = 0; k < na; k++) a[k] = action[k];
+  if (e->cfg.action_limiter == 1) { /* "scale" (panda.py:129-133) */
+    int any = 0; float mx = 0;
+    for (int k = 0; k < na; k++) { if (a[k] < -1 || a[k] > 1) any = 1; if (fabsf(a[k]) > mx) mx = fabsf(a[k]); }
+    if (any) for (int k = 0; k < na; k++) a[k] = a[k] / mx;
+  } else for (int k = 0; k < na; k++) a[k] = a[k] < -1.f ? -1.f : (a[k] > 1.f ? 1.f : a[k]);
+  memcpy(e->prev, e->recent, sizeof e->prev); e->have_prev = e->have_recent;
+  memcpy(e->recent, a, sizeof a); e->have_recent = 1;
+  double q[PGO_MAXD], qd[PGO_MAXD], tgt[7];
+  pgo_arm_get_q(e->arm, q, qd);
+  if (e->cfg.control == 1) { /* ee (panda.py:226-246) */
+    double p[3], ik[PGO_MAXD];
+    ee_position(e, p);
+    for (int k = 0; k < 3; k++) { volatile float s = a[k] * 0.05f; p[k] += (double)s; }
+    if (p[2] < 0) p[2] = 0;
+    const double quat[4] = {1.0, 0.0, 0.0, 0.0};
+    pgo_arm_ik(e->arm, EE_LINK, p, quat, ik);
+    for (int d = 0; d < 7; d++) tgt[d] = ik[d];
+  } else {
+    for (int d = 0; d < 7; d++) { volatile float s = a[d] * 0.05f; tgt[d] = q[d] + (double)s; } /* panda.py:257-261 */
+  }
+  if (e->cfg.control == 2) { for (int d = 0; d < 7; d++) pgo_arm_set_motor(e->arm, d, 0, (double)a[d], FORCES[d]); }
+  else if (e->cfg.control == 3) { for (int d = 0; d < 7; d++) pgo_arm_reset_joint(e->arm, d, tgt[d]); }
+  else { for (int d = 0; d < 7; d++) pgo_arm_set_motor(e->arm, d, 1, tgt[d], FORCES[d]); }
+  /* panda.py:167-172 (velocities sampled AFTER a possible teleport, before the sim step) */
+  pgo_arm_get_q(e->arm, q, qd);
+  for (int d = 0; d < 7; d++) {
+    e->prev_vel[d] = e->cur_vel[d]; e->prev_acc[d] = e->cur_acc[d];
+    e->cur_vel[d] = qd[d];
+    e->cur_acc[d] = e->prev_vel[d] - e->cur_vel[d];
+    e->jerk[d] = fabs(e->prev_acc[d] - e->cur_acc[d]);
+  }
+}
+
+static double norm7(const double* v) { double s = 0; for (int d = 0; d < 7; d++) s += v[d] * v[d]; return sqrt(s); }
+
+static float reward_one(pgo_env* e, const float* ag, const float* dg) {
+  const pgo_env_config* c = &e->cfg;
+  float d = f32_distance(ag, dg);
+  float thr = (float)c->ee_error_threshold;
+  if (c->task == 0) return c->reward_type == 0 ? -(float)(d > thr) : -d; /* reach.py:84-89 */
+  double v[3]; pgo_arm_link_state(e->arm, EE_LINK, 0, 0, v, 0);
+  double speed = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+  double effort = norm7(e->cur_acc), jerk = norm7(e->jerk);
+  float vthr = (float)c->speed_threshold;
+  double r;
+  switch (c->reward_type) {
+    case 0:
+      if (c->goal_condition == 0) { float ee = d + (float)e->is_collided; r = -1.0 + (double)(ee < thr); }
+      else r = 1.0 - (double)((d < thr) && (speed < (double)vthr));
+      break;
+    case 1: { /* wang */
+      double dd = (double)d, obs = 0;
+      for (int i = 0; i < PGO_NCL; i++) { double t = 1 - e->d_link[i] / 0.05; obs += t > 0 ? t : 0; }
+      r = -(double)(float)(10e-3 * dd * dd + log(dd * dd + 10e-4) + 0.1 * obs);
+      break; }
+    case 2: /* kumar_her */
+      if (c->goal_condition == 0) r = -(double)(float)((double)(d > thr) * jerk);
+      else r = (double)(float)((d < thr) && (speed < (double)vthr)) - jerk;
+      break;
+    case 3: r = -(double)(float)(d > thr) - effort; break; /* kumar_optim */
+    default: { /* kumar */
+      double dd = (double)d, obs = 0;
+      for (int i = 0; i < PGO_NCL; i++) { double t = 1 - e->d_link[i] / 0.05; obs += t > 0 ? t : 0; }
+      r = (double)(float)(exp(-20.0 * dd * dd) - 0.005 * effort - 0.1 * obs);
+      break; }
+  }
+  if (c->truncate_on_collision && (c->reward_type == 0 || c->reward_type == 2 || c->reward_type == 3))
+    r += (double)e->is_collided * c->collision_reward;
+  return (float)r;
+}
+
+void pgo_env_compute_reward(pgo_env* e, const float* ag, const float* dg, int n, float* out) {
+  for (int i = 0; i < n; i++) out[i] = reward_one(e, ag + 3 * i, dg + 3 * i);
+}
+
+void pgo_env_step(pgo_env* e, const float* action, float* obs, float* ag, float* dg, float* reward, int* flags) {
+  set_action(e, action);
+  for (int k = 0; k < e->cfg.n_substeps; k++) {
+    pgo_arm_substep(e->arm);
+    if (e->cfg.task == 1) { /* step_check_collision (reach_ao.py:182-188) */
+      e->is_collided = pgo_env_check_collided(e, 0, 0);
+      if (e->is_collided) break;
+    }
+  }
+  float a[3], g[3];
+  pgo_env_get_obs(e, obs, a, g);
+  if (ag) memcpy(ag, a, 12);
+  if (dg) memcpy(dg, g, 12);
+  int succ = is_success(e, a, g);
+  int terminated = e->cfg.terminate_on_success ? succ : 0;
+  int truncated = (e->cfg.task == 1 && e->cfg.truncate_on_collision) ? e->is_collided : 0;
+  *reward = reward_one(e, a, g);
+  e->steps++;
+  flags[0] = succ; flags[1] = terminated; flags[2] = truncated;
+  flags[3] = e->steps >= e->cfg.max_episode_steps; /* gymnasium TimeLimit */
+}
+
+/* test hook: after `skip` Generator.random() draws, k = Generator.integers(lo, hi) then Generator.shuffle(list(range(n))) */
+int pgo_test_integers_shuffle(uint64_t seed, int skip, int lo, int hi, int n, int* perm) {
+  pgo_env e; memset(&e, 0, sizeof e);
+  pgo_pcg64_seed(&e.rng, seed);
+  for (int i = 0; i < skip; i++) pgo_pcg64_double(&e.rng);
+  u32buf b = {0, 0};
+  int k = lo + (hi - 1 - lo == 0 ? 0 : (int)lemire_u32(&e, &b, (uint32_t)(hi - 1 - lo)));
+  for (int i = 0; i < n; i++) perm[i] = i;
+  for (int i = n - 1; i >= 1; i--) { int j = (int)interval_u32(&e, &b, (uint32_t)i); int t = perm[i]; perm[i] = perm[j]; perm[j] = t; }
+  return k;
+}

@@ -1,0 +1,263 @@
+"""ctypes binding of the CPU oracle (oracle/_build/liboracle.so).  TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+LIB_PATH = os.path.join(ORACLE_DIR, "_build", "liboracle.so")
+
+c_int, c_double, c_void_p, c_u64, c_float = ctypes.c_int, ctypes.c_double, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_float
+
+
+class EnvConfig(ctypes.Structure):
+    _fields_ = [
+        ("task", c_int), ("control", c_int), ("reward_type", c_int), ("goal_condition", c_int),
+        ("action_limiter", c_int), ("obs_js", c_int), ("obstacle_obs", c_int), ("n_substeps", c_int),
+        ("truncate_on_collision", c_int), ("terminate_on_success", c_int),
+        ("collision_reward", c_double), ("ee_error_threshold", c_double), ("speed_threshold", c_double),
+        ("safety_distance", c_double), ("max_episode_steps", c_int), ("scenario", c_int), ("n_obstacles", c_int),
+        ("base_pos", c_double * 3),
+    ]
+
+
+class Obstacle(ctypes.Structure):
+    _fields_ = [("type", c_int), ("pos", c_double * 3), ("size", c_double * 3)]
+
+
+class Pcg64(ctypes.Structure):
+    _fields_ = [("s_hi", c_u64), ("s_lo", c_u64), ("inc_hi", c_u64), ("inc_lo", c_u64)]
+
+
+SCENARIOS = {"none": 0, "reach1": 1, "reach2": 2, "reach3": 3, "reachao1": 4, "reachao2": 5, "reachao3": 6,
+             "reachao_rand": 7, "wang": 8, "wangexp": 9}
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR], check=True)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        build()
+    L = ctypes.CDLL(LIB_PATH)
+    P = c_void_p
+
+    def sig(name, res, *args):
+        f = getattr(L, name)
+        f.restype = res
+        f.argtypes = list(args)
+
+    sig("pgo_arm_create", P, c_int, P)
+    sig("pgo_arm_destroy", None, P)
+    sig("pgo_arm_ndof", c_int, P)
+    sig("pgo_arm_nlinks", c_int, P)
+    sig("pgo_arm_set_damping", None, P, c_double, c_double)
+    sig("pgo_arm_set_solver", None, P, c_int, c_double)
+    sig("pgo_arm_reset_joint", None, P, c_int, c_double)
+    sig("pgo_arm_get_q", None, P, P, P)
+    sig("pgo_arm_set_q", None, P, P, P)
+    sig("pgo_arm_set_motor", None, P, c_int, c_int, c_double, c_double)
+    sig("pgo_arm_substep", c_int, P)
+    sig("pgo_arm_link_state", None, P, c_int, P, P, P, P)
+    sig("pgo_arm_link_frame", None, P, c_int, P, P)
+    sig("pgo_arm_minv", None, P, P)
+    sig("pgo_arm_ik", None, P, c_int, P, P, P)
+    sig("pgo_arm_set_ik", None, P, c_double, c_int, c_double)
+    sig("pgo_arm_jacobian", None, P, c_int, P, P)
+    sig("pgo_box_margin", c_double, P)
+    sig("pgo_prim_obstacle_distance", c_double, P, c_int, P, P, P)
+    sig("pgo_link_obstacle_distance", c_double, P, c_int, P, P, P)
+    sig("pgo_gjk_cyl_box", c_double, P, P, c_double, c_double, P, P, P, P)
+    sig("pgo_pcg64_seed", None, P, c_u64)
+    sig("pgo_pcg64_next", c_u64, P)
+    sig("pgo_pcg64_double", c_double, P)
+    sig("pgo_pcg64_uniform", c_double, P, c_double, c_double)
+    sig("pgo_env_default_config", None, P, c_int)
+    sig("pgo_env_create", P, P)
+    sig("pgo_env_destroy", None, P)
+    sig("pgo_env_obs_dim", c_int, P)
+    sig("pgo_env_act_dim", c_int, P)
+    sig("pgo_env_reset", c_int, P, c_u64, P, P, P, P)
+    sig("pgo_env_step", None, P, P, P, P, P, P, P)
+    sig("pgo_env_arm", P, P)
+    sig("pgo_env_set_goal", None, P, P)
+    sig("pgo_env_get_goal", None, P, P)
+    sig("pgo_env_set_obstacles", None, P, c_int, P)
+    sig("pgo_env_get_obstacles", c_int, P, P)
+    sig("pgo_env_check_collided", c_int, P, P, P)
+    sig("pgo_env_get_obs", None, P, P, P, P)
+    sig("pgo_env_compute_reward", None, P, P, P, c_int, P)
+    sig("pgo_env_is_collided", c_int, P)
+    _lib = L
+    return L
+
+
+def dp(a):
+    return a.ctypes.data_as(c_void_p) if a is not None else None
+
+
+class Arm:
+    """pybullet-body-like handle on the oracle's multibody (model 0 = custom_0, 1 = stock)."""
+
+    def __init__(self, model=0, base=(0.0, 0.0, 0.0), handle=None):
+        self.L = lib()
+        self._own = handle is None
+        self.h = handle if handle is not None else self.L.pgo_arm_create(model, dp(np.asarray(base, dtype=np.float64)))
+        self.nd = self.L.pgo_arm_ndof(self.h)
+
+    def __del__(self):
+        if getattr(self, "_own", False) and self.h:
+            self.L.pgo_arm_destroy(self.h)
+            self.h = None
+
+    def q(self):
+        q = np.zeros(self.nd); qd = np.zeros(self.nd)
+        self.L.pgo_arm_get_q(self.h, dp(q), dp(qd))
+        return q, qd
+
+    def set_q(self, q=None, qd=None):
+        q = None if q is None else np.ascontiguousarray(q, dtype=np.float64)
+        qd = None if qd is None else np.ascontiguousarray(qd, dtype=np.float64)
+        self.L.pgo_arm_set_q(self.h, dp(q), dp(qd))
+
+    def reset_joint(self, d, v):
+        self.L.pgo_arm_reset_joint(self.h, d, float(v))
+
+    def set_motor(self, d, mode, target, force):
+        self.L.pgo_arm_set_motor(self.h, d, mode, float(target), float(force))
+
+    def substep(self):
+        return self.L.pgo_arm_substep(self.h)
+
+    def link_state(self, link):
+        p = np.zeros(3); q = np.zeros(4); v = np.zeros(3); w = np.zeros(3)
+        self.L.pgo_arm_link_state(self.h, link, dp(p), dp(q), dp(v), dp(w))
+        return p, q, v, w
+
+    def link_frame(self, link):
+        R = np.zeros(9); p = np.zeros(3)
+        self.L.pgo_arm_link_frame(self.h, link, dp(R), dp(p))
+        return R.reshape(3, 3), p
+
+    def minv(self):
+        M = np.zeros((self.nd, self.nd))
+        self.L.pgo_arm_minv(self.h, dp(M))
+        return M
+
+    def ik(self, link, pos, quat=None):
+        out = np.zeros(self.nd)
+        pos = np.asarray(pos, dtype=np.float64)
+        quat = None if quat is None else np.asarray(quat, dtype=np.float64)
+        self.L.pgo_arm_ik(self.h, link, dp(pos), dp(quat), dp(out))
+        return out
+
+    def jacobian(self, link):
+        Jt = np.zeros((3, self.nd)); Jr = np.zeros((3, self.nd))
+        self.L.pgo_arm_jacobian(self.h, link, dp(Jt), dp(Jr))
+        return Jt, Jr
+
+    def link_obstacle_distance(self, link, obstacle):
+        pa = np.zeros(3); pb = np.zeros(3)
+        d = self.L.pgo_link_obstacle_distance(self.h, link, ctypes.byref(obstacle), dp(pa), dp(pb))
+        return d, pa, pb
+
+
+def make_obstacle(kind, pos, size):
+    o = Obstacle()
+    o.type = 0 if kind == "sphere" else 1
+    for k in range(3):
+        o.pos[k] = float(pos[k])
+    if kind == "sphere":
+        o.size[0] = float(size); o.size[1] = 0.0; o.size[2] = 0.0
+    else:
+        for k in range(3):
+            o.size[k] = float(size[k])
+    return o
+
+
+class Env:
+    """Single reference-shaped env (RobotTaskEnv semantics) on the oracle."""
+
+    def __init__(self, task=1, **kw):
+        self.L = lib()
+        self.cfg = EnvConfig()
+        self.L.pgo_env_default_config(ctypes.byref(self.cfg), task)
+        for k, v in kw.items():
+            if k == "scenario" and isinstance(v, str):
+                name, _, n = v.partition("-")
+                self.cfg.scenario = SCENARIOS[name]
+                if n:
+                    self.cfg.n_obstacles = int(n)
+            elif k == "base_pos":
+                for i in range(3):
+                    self.cfg.base_pos[i] = float(v[i])
+            else:
+                setattr(self.cfg, k, v)
+        self.h = self.L.pgo_env_create(ctypes.byref(self.cfg))
+        self.obs_dim = self.L.pgo_env_obs_dim(self.h)
+        self.act_dim = self.L.pgo_env_act_dim(self.h)
+        self.arm = Arm(handle=self.L.pgo_env_arm(self.h))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.pgo_env_destroy(self.h)
+            self.h = None
+
+    def reset(self, seed):
+        obs = np.zeros(self.obs_dim, np.float32); ag = np.zeros(3, np.float32); dg = np.zeros(3, np.float32)
+        succ = c_int(0)
+        status = self.L.pgo_env_reset(self.h, int(seed), dp(obs), dp(ag), dp(dg), ctypes.byref(succ))
+        return dict(observation=obs, achieved_goal=ag, desired_goal=dg), dict(is_success=bool(succ.value), status=status)
+
+    def step(self, action):
+        a = np.ascontiguousarray(action, dtype=np.float32)
+        obs = np.zeros(self.obs_dim, np.float32); ag = np.zeros(3, np.float32); dg = np.zeros(3, np.float32)
+        r = c_float(0); flags = (c_int * 4)()
+        self.L.pgo_env_step(self.h, dp(a), dp(obs), dp(ag), dp(dg), ctypes.byref(r), flags)
+        return (dict(observation=obs, achieved_goal=ag, desired_goal=dg), float(r.value),
+                dict(is_success=bool(flags[0]), terminated=bool(flags[1]), truncated=bool(flags[2]), time_limit=bool(flags[3])))
+
+    def get_obs(self):
+        obs = np.zeros(self.obs_dim, np.float32); ag = np.zeros(3, np.float32); dg = np.zeros(3, np.float32)
+        self.L.pgo_env_get_obs(self.h, dp(obs), dp(ag), dp(dg))
+        return dict(observation=obs, achieved_goal=ag, desired_goal=dg)
+
+    def goal(self):
+        g = np.zeros(3)
+        self.L.pgo_env_get_goal(self.h, dp(g))
+        return g
+
+    def set_goal(self, g):
+        self.L.pgo_env_set_goal(self.h, dp(np.asarray(g, dtype=np.float64)))
+
+    def obstacles(self):
+        arr = (Obstacle * 8)()
+        n = self.L.pgo_env_get_obstacles(self.h, arr)
+        return [(arr[i].type, np.array(arr[i].pos[:]), np.array(arr[i].size[:])) for i in range(n)]
+
+    def set_obstacles(self, obs_list):
+        arr = (Obstacle * max(1, len(obs_list)))(*obs_list)
+        self.L.pgo_env_set_obstacles(self.h, len(obs_list), arr)
+
+    def check_collided(self):
+        d = np.zeros(9); t = c_double(0)
+        c = self.L.pgo_env_check_collided(self.h, dp(d), ctypes.byref(t))
+        return bool(c), d, t.value
+
+    def compute_reward(self, ag, dg):
+        ag = np.ascontiguousarray(ag, dtype=np.float32).reshape(-1, 3); dg = np.ascontiguousarray(dg, dtype=np.float32).reshape(-1, 3)
+        out = np.zeros(len(ag), np.float32)
+        self.L.pgo_env_compute_reward(self.h, dp(ag), dp(dg), len(ag), dp(out))
+        return out

@@ -1,0 +1,96 @@
+"""Pin the CPU oracle against every known-answer vector the reference's own tests hold for the path
+(reference test/pybullet_test.py, all atol 1e-3) plus the golden vectors recovered from shipped artefacts
+(SURVEY.md section 4 / 8c)."""
+import numpy as np
+
+
+def test_dt():
+    # test/pybullet_test.py:30-35: dt == timestep * n_substeps == 0.04
+    assert (1.0 / 500) * 20 == 0.04
+
+
+def test_link_position_stock(oracle):
+    # test/pybullet_test.py:124-136: stock URDF, q = 0, getLinkState(1)[0]
+    arm = oracle.Arm(model=1)
+    assert np.allclose(arm.link_state(1)[0], [0.000, 0.060, 0.373], atol=1e-3)
+
+
+def _motor_kat(oracle):
+    arm = oracle.Arm(model=1)
+    arm.set_motor(5, 1, 0.3, 5.0)  # control_joints("panda", [5], [0.3], [5.0]) -> POSITION_CONTROL
+    for _ in range(20):
+        arm.substep()
+    return arm
+
+
+def test_joint_angle_kat(oracle):
+    # test/pybullet_test.py:190-204
+    arm = _motor_kat(oracle)
+    assert np.allclose(arm.q()[0][5], 0.063, atol=1e-3)
+
+
+def test_link_orientation_kat(oracle):
+    # test/pybullet_test.py:139-153
+    arm = _motor_kat(oracle)
+    assert np.allclose(arm.link_state(5)[1], [0.707, -0.02, 0.02, 0.707], atol=1e-3)
+
+
+def test_link_velocity_kat(oracle):
+    # test/pybullet_test.py:156-170
+    arm = _motor_kat(oracle)
+    assert np.allclose(arm.link_state(5)[2], [-0.0068, 0.0000, 0.1186], atol=1e-3)
+
+
+def test_link_angular_velocity_kat(oracle):
+    # test/pybullet_test.py:173-187 -- this one pins the inertia-from-AABB rule (mesh + 4 margins) and the
+    # btMultiBody damping 0.04: 3 margins give 2.9835, 5 give 2.9545, damping 0 gives 2.9727.
+    arm = _motor_kat(oracle)
+    w = arm.link_state(5)[3]
+    assert np.allclose(w, [0.000, -2.969, 0.000], atol=1e-3)
+    assert abs(w[1] + 2.969) < 2e-4
+
+
+def test_set_joint_angles(oracle):
+    # test/pybullet_test.py:220-251
+    arm = oracle.Arm(model=1)
+    arm.reset_joint(3, 0.4)
+    arm.reset_joint(4, 0.5)
+    q, qd = arm.q()
+    assert np.allclose(q[3:5], [0.4, 0.5], atol=1e-3) and np.all(qd == 0)
+
+
+def test_inverse_kinematics_kat(oracle):
+    # test/pybullet_test.py:254-266 -- pins: DLS with joint damping 0.5, 20 iterations, URDF link frame
+    # (not COM), normalised target quaternion.
+    arm = oracle.Arm(model=1)
+    out = arm.ik(6, [0.4, 0.5, 0.6], [0.707, -0.02, 0.02, 0.707])
+    assert np.allclose(out, [1.000, 1.223, -1.113, -0.021, -0.917, 0.666, -0.499, 0.0, 0.0], atol=1e-3)
+
+
+def test_free_fall():
+    # test/pybullet_test.py:56-64: semi-implicit Euler, g = 9.81, 20 substeps of 1/500 -> v_z = -0.392
+    v = 0.0
+    for _ in range(20):
+        v += -9.81 * (1.0 / 500)
+    assert np.allclose(v, -0.392, atol=1e-3)
+
+
+def test_neutral_pose_golden(oracle):
+    # shipped checkpoints (training/run_data/wandb/deep-frog-298 ... best_model.zip::_last_obs.achieved_goal):
+    # real PyBullet FK of panda_grasptarget (link 12 of custom_0) at the neutral pose, float32
+    arm = oracle.Arm(model=0)
+    for d, v in enumerate([0, -0.3, 0, -2.2, 0, 2.0, np.pi / 4]):
+        arm.reset_joint(d, v)
+    assert np.allclose(arm.link_state(12)[0], [0.48420656, -5.19e-12, 0.41103777], atol=2e-6)
+    # the current code's end-effector = COM of link 11 (rightfinger)
+    assert np.allclose(arm.link_state(11)[0], [0.4816, 0.0100, 0.4375], atol=1e-4)
+
+
+def test_minv_symmetric_positive(oracle):
+    arm = oracle.Arm(model=0)
+    rng = np.random.default_rng(0)
+    for _ in range(5):
+        arm.set_q(rng.uniform(-1, 1, 7), np.zeros(7))
+        M = arm.minv()
+        assert np.allclose(M, M.T, atol=1e-9)
+        assert np.all(np.linalg.eigvalsh(M) > 0)

@@ -179,10 +179,7 @@ def emit_model(tag, urdf_path, out):
     JT = {"fixed": 0, "revolute": 1, "continuous": 1, "prismatic": 2}
     prim_rows = []
     link_rows = []
-    for idx, (name, j, parent) in enumerate(order):
-        L = links[name]
-        R = rpy_to_R(*j["rpy"])
-        first = len(prim_rows)
+    def add_prims(L, idx):
         for p in L["prims"]:
             if p["type"] == "mesh":
                 continue  # meshes only feed the inertia rule (stock model); no distance queries on them
@@ -190,11 +187,18 @@ def emit_model(tag, urdf_path, out):
             axis = [Rp[0][2], Rp[1][2], Rp[2][2]]  # cylinder z-axis in link frame
             prim_rows.append("  {%d, %d, %s, %s, %r, %r}" % (
                 idx, 0 if p["type"] == "sphere" else 1, fmt(p["xyz"]), fmt(axis), p["r"], p["L"] / 2))
+
+    for idx, (name, j, parent) in enumerate(order):
+        L = links[name]
+        R = rpy_to_R(*j["rpy"])
+        first = len(prim_rows)
+        add_prims(L, idx)
         inertia = bullet_inertia(L)
         link_rows.append("  {/*%2d %s*/ %d, %d, %s, %s, %s, %d, %r, %r, %s, %r, %s, %d, %d}" % (
             idx, name, parent, JT[j["type"]], fmt(j["xyz"]), fmt([x for row in R for x in row]), fmt(j["axis"]),
             j["has_limit"], j["lower"], j["upper"], fmt(L["com"]), L["mass"], fmt(inertia), first,
             len(prim_rows) - first))
+    add_prims(links[root], -1)  # base link (fixed): only body-level closest-point queries see it
     out.append("/* %s : %s */" % (tag, urdf_path.replace("/root/reference/", "")))
     out.append("static const pgo_link_t %s_LINKS[%d] = {" % (tag, len(link_rows)))
     out.append(",\n".join(link_rows))
