@@ -1,0 +1,178 @@
+/* panda_b200.h -- C ABI of the B200-native batched Panda simulator (libpanda_b200.so).
+ *
+ * Drop-in boundary for the env-step hot path of RaikoPipe/panda-gym.  Every entry point names the reference
+ * interface it replaces (file:line into the reference repo).  Conventions: plain pointers and sizes, no C++ /
+ * torch types; every call returns 0 on success or a negative pg_status, with a thread-local message available
+ * from pg_last_error(); no exception crosses the boundary.  The library owns all device memory; callers get
+ * non-owning device pointers through pg_get_view().  A handle is bound to one CUDA device and must be used from
+ * one host thread at a time.  `stream` arguments are cudaStream_t passed as void* (NULL = default stream); all
+ * work is stream-ordered and asynchronous unless stated otherwise.
+ *
+ * There is no CPU fallback: pg_create() fails when no CUDA device is usable.
+ */
+#ifndef PANDA_B200_H
+#define PANDA_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pg_env_s* pg_handle;
+
+enum pg_status { PG_OK = 0, PG_ERR_ARG = -1, PG_ERR_CUDA = -2, PG_ERR_STATE = -3, PG_ERR_UNSUPPORTED = -4 };
+
+enum pg_task { PG_TASK_REACH = 0, PG_TASK_REACH_AO = 1 };                       /* envs/tasks/reach.py, reach_ao.py */
+enum pg_control { PG_CTRL_JOINTS = 0, PG_CTRL_EE = 1, PG_CTRL_JSD = 2, PG_CTRL_PCC = 3 }; /* panda.py:141-165 */
+enum pg_reward { PG_REW_SPARSE = 0, PG_REW_DENSE_OR_WANG = 1, PG_REW_KUMAR_HER = 2, PG_REW_KUMAR_OPTIM = 3, PG_REW_KUMAR = 4 };
+enum pg_obstacle_obs { PG_OOBS_NONE = 0, PG_OOBS_VECTORS_CLOSEST_PER_LINK = 1, PG_OOBS_VECTORS = 2,
+                       PG_OOBS_CLOSEST_PER_LINK = 3, PG_OOBS_CLOSEST = 4 };      /* reach_ao.py:908-932 */
+enum pg_goal_sampler { PG_GOAL_BOX = 0, PG_GOAL_SHELL = 1 };                     /* reach_ao.py:1183-1211 */
+enum pg_obstacle_sampler { PG_OSMP_GOAL_BOX = 0, PG_OSMP_WANG = 1, PG_OSMP_EXPERIMENTAL = 2, PG_OSMP_WANG_N = 3 }; /* :610-644, 650-660 */
+
+#define PG_MAX_OBSTACLES 8
+
+/* Scenario ("curriculum stage") parameter block.  Replaces ReachAO._create_scenario + the create_scenario_*
+ * builders (reach_ao.py:225-266, 518-722) and Reach's goal range (reach.py:24-25).  Swapping it with
+ * pg_set_stage() is what setup_training.py:233-252 does by rebuilding the SubprocVecEnv per stage. */
+typedef struct {
+  int goal_sampler;                 /* pg_goal_sampler */
+  double goal_lo[3], goal_hi[3];    /* PG_GOAL_BOX */
+  double goal_rmin, goal_rmax;      /* PG_GOAL_SHELL (sample_within_hollow_sphere) */
+  int goal_upper_half, goal_front_half, goal_three_quarter_front;
+  int n_obstacles;                  /* <= PG_MAX_OBSTACLES */
+  int obstacle_type[PG_MAX_OBSTACLES];      /* 0 sphere, 1 cuboid */
+  double obstacle_size[PG_MAX_OBSTACLES][3];/* sphere: [0] = radius; cuboid: half extents */
+  int obstacle_sampler;             /* pg_obstacle_sampler */
+  int randomize_obstacle_position;  /* reach_ao.py:987-992 */
+  int allow_overlapping_obstacles;  /* reach_ao.py:1150 */
+  int random_num_obs, sample_size_lo, sample_size_hi; /* reach_ao.py:1062-1082 */
+  int max_episode_steps;            /* gymnasium TimeLimit (panda_gym/__init__.py:15-20) */
+  double ee_error_threshold;        /* reach_ao.py:71 / reach.py:15 */
+  double speed_threshold;           /* reach_ao.py:72 */
+} pg_stage;
+
+/* Environment configuration.  Replaces the constructor arguments of PandaReachAOEnv / PandaReachEnv
+ * (panda_tasks.py:72-88, 142-159) and the TrainConfig fields they read (classes/train_config.py:26-59). */
+typedef struct {
+  int n_envs;                /* environments on this device */
+  int task;                  /* pg_task */
+  int control;               /* pg_control  (TrainConfig.control_type) */
+  int reward_type;           /* pg_reward   (TrainConfig.reward_type) */
+  int goal_condition;        /* 0 "reach", 1 "halt" */
+  int action_limiter;        /* 0 "clip", 1 "scale" (panda.py:129-135) */
+  int obs_js;                /* "js" in obs_type (panda.py:273-279) */
+  int obstacle_obs;          /* pg_obstacle_obs (TrainConfig.task_observations["obstacles"]) */
+  int n_substeps;            /* 20 (train_config.py:44) */
+  int truncate_on_collision; /* train_config.py:27 */
+  int terminate_on_success;  /* train_config.py:28 */
+  double collision_reward;   /* -100 (train_config.py:33) */
+  double safety_distance;    /* train_config.py:39 */
+  double base_position[3];   /* panda_tasks.py:82 / :148 */
+  int auto_reset;            /* 1: done environments are reset inside pg_step (SB3 VecEnv semantics) */
+  pg_stage stage;
+} pg_config;
+
+/* fill cfg with the reference defaults: task PG_TASK_REACH -> PandaReachJoints-v3 (sparse);
+ * PG_TASK_REACH_AO -> PandaReachAO-v3 with TrainConfig() defaults.  scenario: name accepted by
+ * ReachAO._create_scenario ("reachao1", "reachao3", "wangexp-3", "reach1", ... ) or NULL. */
+int pg_default_config(pg_config* cfg, int task, const char* scenario);
+/* scenario name -> stage block (reach_ao.py:229-260); returns PG_ERR_ARG for unknown names */
+int pg_stage_from_scenario(pg_stage* stage, const char* scenario);
+
+int pg_create(const pg_config* cfg, int device, pg_handle* out);
+int pg_destroy(pg_handle h);                                   /* RobotTaskEnv.close (core.py:370-371) */
+int pg_set_stage(pg_handle h, const pg_stage* stage);          /* setup_training.py:233-252 */
+/* VecEnv.seed(seed): environment i draws its first reset from numpy-compatible PCG64(seed + first_env_index + i) */
+int pg_seed(pg_handle h, uint64_t base_seed, uint64_t first_env_index);
+
+/* RobotTaskEnv.reset (core.py:298-308).  mask_dev: NULL = all environments, else uint8[n] on the device.
+ * seeds_dev: NULL = next seed of each environment's own stream, else uint64[n] explicit seeds (reset(seed=s)). */
+int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, void* stream);
+/* RobotTaskEnv.step (core.py:352-368) for all environments + TimeLimit + (optional) SB3 auto-reset.
+ * actions_dev: float32 [n][act_dim] row-major on the device. */
+int pg_step(pg_handle h, const float* actions_dev, void* stream);
+
+/* Host-buffer form of the step (what a SubprocVecEnv.step call is to its caller): copies actions_host
+ * [n][act_dim] to the device, steps, copies the results back and synchronises the stream.  Any output pointer
+ * may be NULL.  Buffers should be page-locked for full PCIe speed. */
+typedef struct {
+  float* observation;    /* [n][obs_dim] */
+  float* achieved_goal;  /* [n][3] */
+  float* desired_goal;   /* [n][3] */
+  float* reward;         /* [n] */
+  uint8_t* done;         /* [n] terminated | truncated | time limit */
+  uint8_t* flags;        /* [n] bit0 is_success, bit1 terminated, bit2 truncated (collision), bit3 TimeLimit.truncated */
+} pg_host_out;
+int pg_step_host(pg_handle h, const float* actions_host, const pg_host_out* out, void* stream);
+int pg_reset_host(pg_handle h, const pg_host_out* out, void* stream);
+
+/* Task.compute_reward(achieved_goal, desired_goal, info) vectorised over n rows (core.py:282; the HER relabel
+ * entry).  Like the reference (reach_ao.py:1319,1336,1377) collision / jerk / effort terms read the LIVE state
+ * of environment `env_index` (SB3 passes indices=[0]). */
+int pg_compute_reward(pg_handle h, const float* ag_dev, const float* dg_dev, float* out_dev, int64_t n, int env_index, void* stream);
+
+/* synthetic rollouts: fill actions_dev [n][act_dim] with U(-1, 1) from a counter-based generator */
+int pg_random_actions(pg_handle h, uint64_t seed, uint64_t counter, float* actions_dev, void* stream);
+
+/* RobotTaskEnv.save_state / restore_state / remove_state (core.py:310-336; pybullet.py:79-102) */
+int pg_save_state(pg_handle h, int* state_id, void* stream);
+int pg_restore_state(pg_handle h, int state_id, void* stream);
+int pg_remove_state(pg_handle h, int state_id);
+
+/* non-owning views of device buffers */
+enum pg_view_id {
+  PG_V_OBSERVATION = 0,   /* f32 [n][obs_dim]  RobotTaskEnv._get_obs()["observation"] (core.py:286-296) */
+  PG_V_ACHIEVED_GOAL,     /* f32 [n][3] */
+  PG_V_DESIRED_GOAL,      /* f32 [n][3] */
+  PG_V_REWARD,            /* f32 [n] */
+  PG_V_DONE,              /* u8  [n] */
+  PG_V_FLAGS,             /* u8  [n] bit0 success, bit1 terminated, bit2 truncated, bit3 time limit */
+  PG_V_TERMINAL_OBSERVATION, /* f32 [n][obs_dim] infos[i]["terminal_observation"] (valid where done) */
+  PG_V_TERMINAL_ACHIEVED, /* f32 [n][3] */
+  PG_V_EP_RETURN,         /* f32 [n] Monitor "r" of the episode that just ended */
+  PG_V_EP_LENGTH,         /* i32 [n] Monitor "l" */
+  PG_V_Q,                 /* f32 [7][n] joint angles (SoA) */
+  PG_V_QD,                /* f32 [7][n] joint velocities */
+  PG_V_GOAL,              /* f64 [3][n] */
+  PG_V_OBSTACLE_POS,      /* f64 [PG_MAX_OBSTACLES][3][n] */
+  PG_V_STATS,             /* f64 [8] episodes, successes, collisions, timeouts, sum_return, sum_length, reset_failures, - */
+  PG_V_STEP_COUNT,        /* i32 [n] */
+  PG_V_D_LINK,            /* f32 [9][n] distances_closest_obstacles (reach_ao.py:897) */
+  PG_V_COUNT
+};
+typedef struct { void* ptr; int dtype; /* 0 f32, 1 u8, 2 i32, 3 f64, 4 u64 */ int ndim; int64_t shape[3]; } pg_view;
+int pg_get_view(pg_handle h, int view_id, pg_view* out);
+int pg_obs_dim(pg_handle h);
+int pg_act_dim(pg_handle h);
+int pg_num_envs(pg_handle h);
+/* number of kernels this library launched on behalf of the handle so far */
+int64_t pg_launch_count(pg_handle h);
+
+/* ---- matched-state entry points used by the parity tests (pybullet getters/setters of pybullet.py) ---- */
+/* resetJointState for every env (pybullet.py:427-435): q_dev f32 [7][n]; velocities zeroed unless qd_dev given */
+int pg_set_joint_state(pg_handle h, const float* q_dev, const float* qd_dev, void* stream);
+int pg_set_goal(pg_handle h, const double* goal_dev /* [3][n] */, void* stream);
+int pg_set_obstacles(pg_handle h, const double* pos_dev /* [n_obstacles][3][n] */, void* stream);
+/* recompute observation / flags at the current state without stepping (RobotTaskEnv._get_obs) */
+int pg_observe(pg_handle h, void* stream);
+/* n_sub raw stepSimulation() calls with POSITION_CONTROL targets / max forces, no task logic:
+ * q, qd f32 [7][n] in/out, target f32 [7][n], max_force f32 [7] (host) */
+int pg_debug_substeps(int device, int n, float* q_dev, float* qd_dev, const float* target_dev, const float* max_force_host,
+                      int n_sub, int velocity_mode, void* stream);
+/* joint-space inverse mass matrix: q f32 [7][n] -> minv f32 [28][n] packed lower (row-major i*(i+1)/2+j) */
+int pg_debug_minv(int device, int n, const float* q_dev, float* minv_dev, void* stream);
+/* calculateInverseKinematics (pybullet.py:465-493) for link 11 with quaternion (1,0,0,0): q f32 [7][n],
+ * target f32 [3][n] -> out f32 [7][n] */
+int pg_debug_ik(int device, int n, const float* q_dev, const float* target_dev, const float* base, float* out_dev, void* stream);
+
+/* roofline denominator: FP32 FMA issue-rate micro-benchmark (8 independent FFMA chains per thread, all SMs).
+ * Runs `iters` x 8 x 2 flops per thread on `blocks` x 256 threads; *tflops_out = achieved TFLOP/s (CUDA events). */
+int pg_debug_fma_peak(int device, int blocks, int iters, double* tflops_out);
+
+const char* pg_last_error(void);
+const char* pg_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

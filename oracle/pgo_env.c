@@ -521,3 +521,23 @@ int pgo_test_integers_shuffle(uint64_t seed, int skip, int lo, int hi, int n, in
   for (int i = n - 1; i >= 1; i--) { int j = (int)interval_u32(&e, &b, (uint32_t)i); int t = perm[i]; perm[i] = perm[j]; perm[j] = t; }
   return k;
 }
+
+/* CPU baseline driver: `steps` env-steps of one environment with U(-1,1) actions from PCG64(seed) and
+ * SB3-style auto-reset (fresh seed per episode).  Returns the number of episodes finished. */
+int pgo_bench_rollout(const pgo_env_config* cfg, uint64_t seed, int steps, double* checksum) {
+  pgo_env* e = pgo_env_create(cfg);
+  pgo_pcg64 ar; pgo_pcg64_seed(&ar, seed ^ 0xabcdef);
+  float obs[64], ag[3], dg[3], r, a[8];
+  int flags[4], succ, episodes = 0;
+  double cs = 0;
+  pgo_env_reset(e, seed, obs, ag, dg, &succ);
+  for (int s = 0; s < steps; s++) {
+    for (int k = 0; k < 7; k++) a[k] = (float)(2.0 * pgo_pcg64_double(&ar) - 1.0);
+    pgo_env_step(e, a, obs, ag, dg, &r, flags);
+    cs += r;
+    if (flags[1] || flags[2] || flags[3]) { episodes++; pgo_env_reset(e, seed + 7919u * (uint64_t)episodes, obs, ag, dg, &succ); }
+  }
+  if (checksum) *checksum = cs;
+  pgo_env_destroy(e);
+  return episodes;
+}

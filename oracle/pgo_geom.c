@@ -148,7 +148,7 @@ double pgo_gjk_cyl_box(const double c[3], const double a[3], double r, double h,
     } else { /* tetrahedron: origin inside => overlap; else closest face */
       static const int F[4][3] = {{0, 1, 2}, {0, 1, 3}, {0, 2, 3}, {1, 2, 3}};
       static const int O[4] = {3, 2, 1, 0};
-      double best = 1e300, bl[3]; int bmask = 0, bf = -1, outside_any = 0;
+      double best = 1e300, bl[3]; int bmask = 0, bf = -1, inside = 1;
       for (int f = 0; f < 4; f++) {
         const double *p0 = W[F[f][0]], *p1 = W[F[f][1]], *p2 = W[F[f][2]], *po = W[O[f]];
         double e1[3], e2[3], nn[3], t0[3], t1[3];
@@ -156,17 +156,17 @@ double pgo_gjk_cyl_box(const double c[3], const double a[3], double r, double h,
         sub3(po, p0, t0);
         for (int k = 0; k < 3; k++) t1[k] = -p0[k];
         double so = dot3(nn, t0), sp = dot3(nn, t1);
-        if (so * sp < 0 || (so == 0 && sp != 0)) { /* origin on the outer side of this face */
-          outside_any = 1;
-          double l[3]; int mask;
-          closest_triangle(p0, p1, p2, l, &mask);
-          double q[3] = {0, 0, 0};
-          for (int k = 0; k < 3; k++) for (int x = 0; x < 3; x++) q[x] += l[k] * W[F[f][k]][x];
-          double d2 = dot3(q, q);
-          if (d2 < best) { best = d2; bf = f; bmask = mask; memcpy(bl, l, sizeof bl); }
-        }
+        /* the origin is inside only if it lies strictly on the opposite-vertex side of every face of a
+         * NON-degenerate tetrahedron; the closest face is searched over all four regardless */
+        if (!(so * sp > 0) || fabs(so) <= 1e-10 * sqrt(dot3(nn, nn) * dot3(t0, t0))) inside = 0;
+        double l[3]; int mask;
+        closest_triangle(p0, p1, p2, l, &mask);
+        double q[3] = {0, 0, 0};
+        for (int k = 0; k < 3; k++) for (int x = 0; x < 3; x++) q[x] += l[k] * W[F[f][k]][x];
+        double d2 = dot3(q, q);
+        if (d2 < best) { best = d2; bf = f; bmask = mask; memcpy(bl, l, sizeof bl); }
       }
-      if (!outside_any) { /* cores overlap */
+      if (inside) { /* cores overlap */
         for (int k = 0; k < 3; k++) { pa[k] = c[k]; pb[k] = c[k]; }
         return 0.0;
       }

@@ -1,0 +1,469 @@
+// pg_api.cu -- C ABI (include/panda_b200.h) over the kernels of pg_kernels.cuh.  Host side only: handle
+// bookkeeping, device allocations (the library owns every buffer), parameter blocks, launches.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/panda_b200.h"
+#include "pg_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define PG_CUDA(call)                                                                                         \
+  do {                                                                                                        \
+    cudaError_t _e = (call);                                                                                  \
+    if (_e != cudaSuccess) return fail(PG_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(_e));      \
+  } while (0)
+
+struct Buffer { void** slot; size_t bytes; };
+
+}  // namespace
+
+struct pg_env_s {
+  pg_config cfg;
+  int device;
+  pg::Params P;
+  std::vector<Buffer> state_bufs;   // everything save_state snapshots
+  std::vector<void*> all_bufs;
+  std::map<int, std::vector<void*>> saved;
+  uint64_t first_env;
+  int64_t launches;
+  float* d_actions;                 // staging for the host-buffer step
+  int grid() const { return (P.n + pg::kBlock - 1) / pg::kBlock; }
+};
+
+namespace {
+
+template <typename T>
+int alloc(pg_env_s* h, T** p, size_t count, bool is_state) {
+  size_t bytes = count * sizeof(T);
+  PG_CUDA(cudaMalloc((void**)p, bytes));
+  PG_CUDA(cudaMemset(*p, 0, bytes));
+  h->all_bufs.push_back(*p);
+  if (is_state) h->state_bufs.push_back(Buffer{(void**)p, bytes});
+  return PG_OK;
+}
+
+double box_margin(const double* s) { double m = fmin(s[0], fmin(s[1], s[2])); return fmin(0.04, 0.1 * m); }
+
+void fill_stage(pg_env_s* h, const pg_stage* s) {
+  pg::Params& P = h->P;
+  pg::StageDev& d = P.st;
+  d.goal_sampler = s->goal_sampler;
+  for (int k = 0; k < 3; k++) { d.goal_lo[k] = s->goal_lo[k]; d.goal_hi[k] = s->goal_hi[k]; }
+  d.goal_rmin = s->goal_rmin; d.goal_rmax = s->goal_rmax;
+  d.goal_upper = s->goal_upper_half; d.goal_front = s->goal_front_half; d.goal_34 = s->goal_three_quarter_front;
+  d.nobs = s->n_obstacles;
+  P.scene.nobs = s->n_obstacles;
+  for (int j = 0; j < pg::kMaxObst; j++) {
+    d.obs_type[j] = j < s->n_obstacles ? s->obstacle_type[j] : 0;
+    for (int k = 0; k < 3; k++) d.obs_size[j][k] = j < s->n_obstacles ? s->obstacle_size[j][k] : 0.0;
+    pg::Obst& o = P.scene.obst[j];
+    o.type = d.obs_type[j];
+    o.sx = (float)d.obs_size[j][0]; o.sy = (float)d.obs_size[j][1]; o.sz = (float)d.obs_size[j][2];
+    o.margin = o.type == 1 ? (float)box_margin(d.obs_size[j]) : 0.f;
+    P.scene.obst_bound[j] = o.type == 1 ? sqrtf(o.sx * o.sx + o.sy * o.sy + o.sz * o.sz) : o.sx;
+  }
+  d.obs_sampler = s->obstacle_sampler; d.randomize_obstacles = s->randomize_obstacle_position;
+  d.allow_overlap = s->allow_overlapping_obstacles; d.random_num_obs = s->random_num_obs;
+  d.size_lo = s->sample_size_lo; d.size_hi = s->sample_size_hi;
+  d.max_episode_steps = s->max_episode_steps;
+  d.ee_thr = (float)s->ee_error_threshold; d.speed_thr = (float)s->speed_threshold;
+  // observation width (reach_ao.py:902-932: np.ones(27) when the scenario has no obstacles)
+  int t = 0;
+  if (P.task == 1 && P.obstacle_obs != 0) {
+    if (s->n_obstacles == 0) t = 27;
+    else t = P.obstacle_obs == 1 ? 36 : (P.obstacle_obs == 2 ? 27 : (P.obstacle_obs == 3 ? 9 : 1));
+  }
+  P.task_obs_dim = t;
+  P.obs_dim = 6 + (P.obs_js ? 14 : 0) + t;
+}
+
+void set_goal_box(pg_stage* s, double xl, double xh, double yl, double yh, double zl, double zh) {
+  s->goal_sampler = PG_GOAL_BOX;
+  s->goal_lo[0] = xl; s->goal_lo[1] = yl; s->goal_lo[2] = zl; s->goal_hi[0] = xh; s->goal_hi[1] = yh; s->goal_hi[2] = zh;
+}
+void set_goal_shell(pg_stage* s, double rmin, double rmax, int upper, int front, int q34) {
+  s->goal_sampler = PG_GOAL_SHELL; s->goal_rmin = rmin; s->goal_rmax = rmax;
+  s->goal_upper_half = upper; s->goal_front_half = front; s->goal_three_quarter_front = q34;
+}
+void add_sphere(pg_stage* s, double r) { int j = s->n_obstacles++; s->obstacle_type[j] = 0; s->obstacle_size[j][0] = r; s->obstacle_size[j][1] = s->obstacle_size[j][2] = 0; }
+void add_cuboid(pg_stage* s, double hx) { int j = s->n_obstacles++; s->obstacle_type[j] = 1; s->obstacle_size[j][0] = s->obstacle_size[j][1] = s->obstacle_size[j][2] = hx; }
+
+}  // namespace
+
+extern "C" {
+
+const char* pg_last_error(void) { return g_err.c_str(); }
+const char* pg_version(void) { return "panda_b200 0.1 (sm_100a)"; }
+
+int pg_stage_from_scenario(pg_stage* s, const char* scenario) {
+  if (!s) return fail(PG_ERR_ARG, "stage is NULL");
+  memset(s, 0, sizeof *s);
+  s->max_episode_steps = 50; s->ee_error_threshold = 0.05; s->speed_threshold = 0.1;
+  // ReachAO defaults (reach_ao.py:73-82): goal box x 0.6 +- 0.12, y +- 0.2, z [0, 0.3]
+  set_goal_box(s, -0.3 / 2.5 + 0.6, 0.3 / 2.5 + 0.6, -0.3 / 1.5, 0.3 / 1.5, 0.0, 0.3);
+  if (!scenario || !*scenario) return PG_OK;
+  std::string full(scenario), name = full;
+  int count = 0;
+  size_t dash = full.find('-');  // reach_ao.py:226-227
+  if (dash != std::string::npos) { name = full.substr(0, dash); count = atoi(full.c_str() + dash + 1); }
+  if (name == "reach_classic") {          // Reach (reach.py:24-25), goal_range 0.3
+    set_goal_box(s, -0.15, 0.15, -0.15, 0.15, 0.0, 0.3);
+  } else if (name == "reach1") {          // reach_ao.py:518-522
+    set_goal_box(s, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4);
+  } else if (name == "reach2" || name == "reach3") {  // :524-539
+    set_goal_shell(s, 0.5, 0.85, 1, 0, 1);
+  } else if (name == "reachao1") {        // :541-545
+    set_goal_box(s, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4);
+    s->randomize_obstacle_position = 1; add_sphere(s, 0.04);
+  } else if (name == "reachao2") {        // :547-564
+    set_goal_shell(s, 0.5, 0.8, 1, 1, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG;
+    add_sphere(s, 0.05); add_sphere(s, 0.05);
+  } else if (name == "reachao3") {        // :573-585
+    set_goal_shell(s, 0.5, 0.8, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG;
+    for (int i = 0; i < 3; i++) add_sphere(s, 0.05);
+  } else if (name == "reachao_rand") {    // :587-599
+    set_goal_shell(s, 0.5, 0.8, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_EXPERIMENTAL;
+    for (int i = 0; i < 3; i++) add_sphere(s, 0.05);
+    for (int i = 0; i < 3; i++) add_cuboid(s, 0.05);
+    s->random_num_obs = 1; s->allow_overlapping_obstacles = 1; s->sample_size_lo = 4; s->sample_size_hi = 6;
+  } else if (name == "wang") {            // :646-699
+    if (count < 0 || count > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "wang-N: N out of range");
+    set_goal_shell(s, 0.4, 0.95, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG_N;
+    for (int i = 0; i < count; i++) add_sphere(s, 0.05);
+  } else if (name == "wangexp") {         // :701-722
+    if (count < 0 || count > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "wangexp-N: N out of range");
+    set_goal_shell(s, 0.5, 0.8, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG;
+    for (int i = 0; i < count; i++) add_sphere(s, 0.05);
+  } else {
+    return fail(PG_ERR_ARG, std::string("Scenario ") + scenario + " not found!");  // reach_ao.py:262-264
+  }
+  return PG_OK;
+}
+
+int pg_default_config(pg_config* c, int task, const char* scenario) {
+  if (!c) return fail(PG_ERR_ARG, "cfg is NULL");
+  memset(c, 0, sizeof *c);
+  c->n_envs = 1; c->task = task; c->control = PG_CTRL_JOINTS; c->reward_type = PG_REW_SPARSE;
+  c->n_substeps = 20; c->collision_reward = -100.0; c->auto_reset = 1;
+  if (task == PG_TASK_REACH) {  // PandaReachEnv (panda_tasks.py:72-88): obs_type ("ee",), base (-0.6, 0, 0), no termination
+    c->obs_js = 0; c->obstacle_obs = PG_OOBS_NONE; c->base_position[0] = -0.6;
+    return pg_stage_from_scenario(&c->stage, "reach_classic");
+  }
+  if (task != PG_TASK_REACH_AO) return fail(PG_ERR_ARG, "unknown task");
+  c->obs_js = 1; c->obstacle_obs = PG_OOBS_VECTORS_CLOSEST_PER_LINK; c->truncate_on_collision = 1; c->terminate_on_success = 1;
+  return pg_stage_from_scenario(&c->stage, scenario ? scenario : "reachao1");
+}
+
+int pg_create(const pg_config* cfg, int device, pg_handle* out) {
+  if (!cfg || !out) return fail(PG_ERR_ARG, "NULL argument");
+  if (cfg->n_envs <= 0) return fail(PG_ERR_ARG, "n_envs must be positive");
+  if (cfg->stage.n_obstacles < 0 || cfg->stage.n_obstacles > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "n_obstacles out of range");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev == 0) return fail(PG_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+  if (device < 0 || device >= ndev) return fail(PG_ERR_ARG, "bad device index");
+  PG_CUDA(cudaSetDevice(device));
+  pg_env_s* h = new pg_env_s();
+  h->cfg = *cfg; h->device = device; h->launches = 0; h->first_env = 0; h->d_actions = nullptr;
+  pg::Params& P = h->P;
+  memset(&P, 0, sizeof P);
+  const int n = cfg->n_envs;
+  P.n = n; P.task = cfg->task; P.control = cfg->control; P.reward_type = cfg->reward_type; P.goal_condition = cfg->goal_condition;
+  P.action_limiter = cfg->action_limiter; P.obs_js = cfg->obs_js; P.obstacle_obs = cfg->obstacle_obs;
+  P.act_dim = cfg->control == PG_CTRL_EE ? 3 : 7;  // block_gripper = True for Reach / ReachAO
+  P.n_substeps = cfg->n_substeps; P.truncate_on_collision = cfg->truncate_on_collision; P.terminate_on_success = cfg->terminate_on_success;
+  P.auto_reset = cfg->auto_reset; P.collision_reward = (float)cfg->collision_reward; P.safety_distance = cfg->safety_distance;
+  for (int k = 0; k < 3; k++) { P.base[k] = (float)cfg->base_position[k]; P.based[k] = cfg->base_position[k]; }
+  if (cfg->task == PG_TASK_REACH) {  // table 1.1 x 0.7 x 0.4 at x = -0.3 (reach.py:33); never queried
+    P.table_pos[0] = -0.3; P.table_half[0] = 0.55; P.table_half[1] = 0.35;
+  } else {                           // table 2.0 x 1.3 x 0.4 (reach_ao.py:272)
+    P.table_pos[0] = 0.0; P.table_half[0] = 1.0; P.table_half[1] = 0.65;
+  }
+  P.table_pos[1] = 0.0; P.table_pos[2] = -0.2; P.table_half[2] = 0.2;
+  double tm = box_margin(P.table_half);
+  P.scene.has_table = cfg->task == PG_TASK_REACH_AO;
+  P.scene.table_margin = (float)tm;
+  for (int k = 0; k < 3; k++) { P.scene.table_pos[k] = (float)P.table_pos[k]; P.scene.table_core[k] = (float)(P.table_half[k] - tm); }
+  fill_stage(h, &cfg->stage);
+  // observation width is fixed at creation (gym spaces); allocate for the widest layout
+  const int max_obs = 6 + 14 + 36;
+  int rc = PG_OK;
+#define A(ptr, count, st) if ((rc = alloc(h, &ptr, (size_t)(count), st)) != PG_OK) { pg_destroy(h); return rc; }
+  A(P.q, 7 * n, true) A(P.qd, 7 * n, true) A(P.goal, 3 * n, true) A(P.obs_pos, (size_t)pg::kMaxObst * 3 * n, true)
+  A(P.recent, 7 * n, true) A(P.prev, 7 * n, true) A(P.cur_vel, 7 * n, true) A(P.cur_acc, 7 * n, true) A(P.jerk, 7 * n, true)
+  A(P.d_link, 9 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
+  A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
+  A(P.rng, 4 * n, true) A(P.episode, n, true)
+  A(P.obs, (size_t)max_obs * n, true) A(P.achieved, 3 * n, true) A(P.desired, 3 * n, true) A(P.reward, n, true)
+  A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true) A(P.done, n, true) A(P.flags, n, true)
+  A(P.stats, 8, false)
+  A(h->d_actions, 7 * n, false)
+#undef A
+  // obstacles start where create_obstacle_* puts them: (0.1, 0, 0.1) (reach_ao.py:819, 841)
+  {
+    std::vector<double> init((size_t)pg::kMaxObst * 3 * n);
+    for (int j = 0; j < pg::kMaxObst; j++)
+      for (int e = 0; e < n; e++) { init[(size_t)(j * 3 + 0) * n + e] = 0.1; init[(size_t)(j * 3 + 1) * n + e] = 0.0; init[(size_t)(j * 3 + 2) * n + e] = 0.1; }
+    cudaError_t e2 = cudaMemcpy(P.obs_pos, init.data(), init.size() * sizeof(double), cudaMemcpyHostToDevice);
+    if (e2 != cudaSuccess) { pg_destroy(h); return fail(PG_ERR_CUDA, cudaGetErrorString(e2)); }
+  }
+  P.base_seed = 0;
+  *out = h;
+  return PG_OK;
+}
+
+int pg_destroy(pg_handle h) {
+  if (!h) return PG_OK;
+  cudaSetDevice(h->device);
+  for (void* p : h->all_bufs) cudaFree(p);
+  for (auto& kv : h->saved) for (void* p : kv.second) cudaFree(p);
+  delete h;
+  return PG_OK;
+}
+
+int pg_set_stage(pg_handle h, const pg_stage* s) {
+  if (!h || !s) return fail(PG_ERR_ARG, "NULL argument");
+  if (s->n_obstacles < 0 || s->n_obstacles > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "n_obstacles out of range");
+  h->cfg.stage = *s;
+  fill_stage(h, s);
+  return PG_OK;
+}
+
+int pg_seed(pg_handle h, uint64_t base_seed, uint64_t first_env_index) {
+  if (!h) return fail(PG_ERR_ARG, "NULL handle");
+  PG_CUDA(cudaSetDevice(h->device));
+  h->P.base_seed = base_seed; h->first_env = first_env_index;
+  PG_CUDA(cudaMemset(h->P.episode, 0, sizeof(uint32_t) * h->P.n));
+  return PG_OK;
+}
+
+int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, void* stream) {
+  if (!h) return fail(PG_ERR_ARG, "NULL handle");
+  PG_CUDA(cudaSetDevice(h->device));
+  pg::k_reset<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, mask_dev, seeds_dev, 0, h->first_env);
+  h->launches++;
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_step(pg_handle h, const float* actions_dev, void* stream) {
+  if (!h || !actions_dev) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  pg::k_step<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
+  h->launches++;
+  if (h->P.auto_reset) {
+    pg::k_reset<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, nullptr, nullptr, 1, h->first_env);
+    h->launches++;
+  }
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+static int copy_out(pg_handle h, const pg_host_out* o, cudaStream_t s) {
+  const pg::Params& P = h->P;
+  const size_t n = P.n;
+  if (o->observation) PG_CUDA(cudaMemcpyAsync(o->observation, P.obs, n * P.obs_dim * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (o->achieved_goal) PG_CUDA(cudaMemcpyAsync(o->achieved_goal, P.achieved, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (o->desired_goal) PG_CUDA(cudaMemcpyAsync(o->desired_goal, P.desired, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (o->reward) PG_CUDA(cudaMemcpyAsync(o->reward, P.reward, n * sizeof(float), cudaMemcpyDeviceToHost, s));
+  if (o->done) PG_CUDA(cudaMemcpyAsync(o->done, P.done, n, cudaMemcpyDeviceToHost, s));
+  if (o->flags) PG_CUDA(cudaMemcpyAsync(o->flags, P.flags, n, cudaMemcpyDeviceToHost, s));
+  PG_CUDA(cudaStreamSynchronize(s));
+  return PG_OK;
+}
+
+int pg_step_host(pg_handle h, const float* actions_host, const pg_host_out* out, void* stream) {
+  if (!h || !actions_host) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  PG_CUDA(cudaMemcpyAsync(h->d_actions, actions_host, (size_t)h->P.n * h->P.act_dim * sizeof(float), cudaMemcpyHostToDevice, s));
+  int rc = pg_step(h, h->d_actions, stream);
+  if (rc != PG_OK) return rc;
+  if (out) return copy_out(h, out, s);
+  PG_CUDA(cudaStreamSynchronize(s));
+  return PG_OK;
+}
+
+int pg_reset_host(pg_handle h, const pg_host_out* out, void* stream) {
+  int rc = pg_reset(h, nullptr, nullptr, stream);
+  if (rc != PG_OK) return rc;
+  if (out) return copy_out(h, out, (cudaStream_t)stream);
+  PG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return PG_OK;
+}
+
+int pg_compute_reward(pg_handle h, const float* ag, const float* dg, float* out, int64_t n, int env_index, void* stream) {
+  if (!h || !ag || !dg || !out) return fail(PG_ERR_ARG, "NULL argument");
+  if (env_index < 0 || env_index >= h->P.n) return fail(PG_ERR_ARG, "env_index out of range");
+  if (n <= 0) return PG_OK;
+  PG_CUDA(cudaSetDevice(h->device));
+  pg::k_reward<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h->P, ag, dg, out, n, env_index);
+  h->launches++;
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_random_actions(pg_handle h, uint64_t seed, uint64_t counter, float* actions_dev, void* stream) {
+  if (!h || !actions_dev) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  int64_t m = (int64_t)h->P.n * h->P.act_dim;
+  pg::k_random_actions<<<(unsigned)((m + 255) / 256), 256, 0, (cudaStream_t)stream>>>(actions_dev, m, seed, counter);
+  h->launches++;
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_save_state(pg_handle h, int* state_id, void* stream) {
+  if (!h || !state_id) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  int id = 0;
+  while (h->saved.count(id)) id++;  // first free non-negative integer, like Bullet's saveState
+  std::vector<void*> copies;
+  for (const Buffer& b : h->state_bufs) {
+    void* p = nullptr;
+    PG_CUDA(cudaMalloc(&p, b.bytes));
+    copies.push_back(p);
+    PG_CUDA(cudaMemcpyAsync(p, *b.slot, b.bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  }
+  h->saved[id] = copies;
+  *state_id = id;
+  return PG_OK;
+}
+int pg_restore_state(pg_handle h, int state_id, void* stream) {
+  if (!h) return fail(PG_ERR_ARG, "NULL handle");
+  auto it = h->saved.find(state_id);
+  if (it == h->saved.end()) return fail(PG_ERR_STATE, "Couldn't restore state.");  // pybullet.error text
+  PG_CUDA(cudaSetDevice(h->device));
+  for (size_t i = 0; i < h->state_bufs.size(); i++)
+    PG_CUDA(cudaMemcpyAsync(*h->state_bufs[i].slot, it->second[i], h->state_bufs[i].bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return PG_OK;
+}
+int pg_remove_state(pg_handle h, int state_id) {
+  if (!h) return fail(PG_ERR_ARG, "NULL handle");
+  auto it = h->saved.find(state_id);
+  if (it == h->saved.end()) return fail(PG_ERR_STATE, "unknown state id");
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (void* p : it->second) cudaFree(p);
+  h->saved.erase(it);
+  return PG_OK;
+}
+
+int pg_get_view(pg_handle h, int id, pg_view* v) {
+  if (!h || !v) return fail(PG_ERR_ARG, "NULL argument");
+  const pg::Params& P = h->P;
+  const int64_t n = P.n;
+  memset(v, 0, sizeof *v);
+  auto set = [&](void* p, int dt, int nd, int64_t a, int64_t b, int64_t c) { v->ptr = p; v->dtype = dt; v->ndim = nd; v->shape[0] = a; v->shape[1] = b; v->shape[2] = c; };
+  switch (id) {
+    case PG_V_OBSERVATION: set(P.obs, 0, 2, n, P.obs_dim, 0); break;
+    case PG_V_ACHIEVED_GOAL: set(P.achieved, 0, 2, n, 3, 0); break;
+    case PG_V_DESIRED_GOAL: set(P.desired, 0, 2, n, 3, 0); break;
+    case PG_V_REWARD: set(P.reward, 0, 1, n, 0, 0); break;
+    case PG_V_DONE: set(P.done, 1, 1, n, 0, 0); break;
+    case PG_V_FLAGS: set(P.flags, 1, 1, n, 0, 0); break;
+    case PG_V_TERMINAL_OBSERVATION: set(P.term_obs, 0, 2, n, P.obs_dim, 0); break;
+    case PG_V_TERMINAL_ACHIEVED: set(P.term_achieved, 0, 2, n, 3, 0); break;
+    case PG_V_EP_RETURN: set(P.last_ret, 0, 1, n, 0, 0); break;
+    case PG_V_EP_LENGTH: set(P.last_len, 2, 1, n, 0, 0); break;
+    case PG_V_Q: set(P.q, 0, 2, 7, n, 0); break;
+    case PG_V_QD: set(P.qd, 0, 2, 7, n, 0); break;
+    case PG_V_GOAL: set(P.goal, 3, 2, 3, n, 0); break;
+    case PG_V_OBSTACLE_POS: set(P.obs_pos, 3, 3, pg::kMaxObst, 3, n); break;
+    case PG_V_STATS: set(P.stats, 3, 1, 8, 0, 0); break;
+    case PG_V_STEP_COUNT: set(P.steps, 2, 1, n, 0, 0); break;
+    case PG_V_D_LINK: set(P.d_link, 0, 2, 9, n, 0); break;
+    default: return fail(PG_ERR_ARG, "unknown view id");
+  }
+  return PG_OK;
+}
+int pg_obs_dim(pg_handle h) { return h ? h->P.obs_dim : PG_ERR_ARG; }
+int pg_act_dim(pg_handle h) { return h ? h->P.act_dim : PG_ERR_ARG; }
+int pg_num_envs(pg_handle h) { return h ? h->P.n : PG_ERR_ARG; }
+int64_t pg_launch_count(pg_handle h) { return h ? h->launches : 0; }
+
+int pg_set_joint_state(pg_handle h, const float* q_dev, const float* qd_dev, void* stream) {
+  if (!h || !q_dev) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  size_t bytes = (size_t)7 * h->P.n * sizeof(float);
+  PG_CUDA(cudaMemcpyAsync(h->P.q, q_dev, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  if (qd_dev) PG_CUDA(cudaMemcpyAsync(h->P.qd, qd_dev, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  else PG_CUDA(cudaMemsetAsync(h->P.qd, 0, bytes, (cudaStream_t)stream));
+  return PG_OK;
+}
+int pg_set_goal(pg_handle h, const double* goal_dev, void* stream) {
+  if (!h || !goal_dev) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  PG_CUDA(cudaMemcpyAsync(h->P.goal, goal_dev, (size_t)3 * h->P.n * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return PG_OK;
+}
+int pg_set_obstacles(pg_handle h, const double* pos_dev, void* stream) {
+  if (!h || !pos_dev) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  PG_CUDA(cudaMemcpyAsync(h->P.obs_pos, pos_dev, (size_t)h->P.st.nobs * 3 * h->P.n * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return PG_OK;
+}
+int pg_observe(pg_handle h, void* stream) {
+  if (!h) return fail(PG_ERR_ARG, "NULL handle");
+  PG_CUDA(cudaSetDevice(h->device));
+  pg::k_observe<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P);
+  h->launches++;
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_debug_substeps(int device, int n, float* q, float* qd, const float* tgt, const float* f, int n_sub, int velocity_mode, void* stream) {
+  if (!q || !qd || !tgt || !f || n <= 0) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(device));
+  pg::k_debug_substeps<<<(n + pg::kBlock - 1) / pg::kBlock, pg::kBlock, 0, (cudaStream_t)stream>>>(n, q, qd, tgt, f[0], f[1], f[2], f[3], f[4], f[5], f[6], n_sub, velocity_mode);
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+int pg_debug_minv(int device, int n, const float* q, float* out, void* stream) {
+  if (!q || !out || n <= 0) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(device));
+  pg::k_debug_minv<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, q, out);
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+int pg_debug_ik(int device, int n, const float* q, const float* tgt, const float* base, float* out, void* stream) {
+  if (!q || !tgt || !out || !base || n <= 0) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(device));
+  pg::k_debug_ik<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, q, tgt, base[0], base[1], base[2], out);
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_debug_fma_peak(int device, int blocks, int iters, double* tflops_out) {
+  if (!tflops_out || blocks <= 0 || iters <= 0) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(device));
+  float* d = nullptr;
+  PG_CUDA(cudaMalloc(&d, 4));
+  cudaEvent_t e0, e1;
+  PG_CUDA(cudaEventCreate(&e0)); PG_CUDA(cudaEventCreate(&e1));
+  pg::k_fma_peak<<<blocks, 256>>>(d, iters, 0.999f, 0.001f);  // warm-up
+  float best = 1e30f;
+  for (int r = 0; r < 5; r++) {
+    PG_CUDA(cudaEventRecord(e0));
+    pg::k_fma_peak<<<blocks, 256>>>(d, iters, 0.999f, 0.001f);
+    PG_CUDA(cudaEventRecord(e1));
+    PG_CUDA(cudaEventSynchronize(e1));
+    float ms = 0; PG_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    if (ms < best) best = ms;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  *tflops_out = (double)blocks * 256.0 * (double)iters * 16.0 / (best * 1e-3) / 1e12;
+  return PG_OK;
+}
+
+}  // extern "C"

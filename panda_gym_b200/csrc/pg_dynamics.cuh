@@ -1,0 +1,367 @@
+// pg_dynamics.cuh -- one Bullet stepSimulation() of the 7-DoF Panda arm, one environment per thread, fp32.
+//
+// Replaces pybullet.stepSimulation behind panda_gym/pybullet.py:68-71 (reference) for the robot the fork
+// loads (franka_panda_custom_0, panda.py:54).  Same mathematics as the oracle (oracle/pgo_dyn.c), different
+// algorithm: instead of Bullet's articulated-body pass plus seven impulse-response passes, the thread builds
+//   tau_b = RNEA(q, qd, qdd = 0)  (gravity + Coriolis + btMultiBody per-link damping), link-local frames
+//   M     = CRBA(q)               (7x7, 28 unique entries, registers)
+//   M^-1  = (L L^T)^-1            (Cholesky, explicit inverse: the PGS rows need its columns)
+// and then runs Bullet's projected Gauss-Seidel over joint-limit + motor rows exactly as
+// btMultiBodyConstraintSolver does (50 sweeps, alternating direction, residual early-out 1e-7), followed by
+// the semi-implicit Euler position update.  All 7 joints are revolute about their local z axis and every
+// joint origin is Rx(0 / +-90 deg), which the templates below fold into sign flips.
+#pragma once
+#include "pg_model.cuh"
+
+namespace pg {
+
+template <typename T> struct V3T { T x, y, z; };
+using V3 = V3T<float>;
+using D3 = V3T<double>;
+template <typename T> __host__ __device__ __forceinline__ V3T<T> v3t(T x, T y, T z) { V3T<T> r; r.x = x; r.y = y; r.z = z; return r; }
+__host__ __device__ __forceinline__ V3 v3(float x, float y, float z) { return v3t<float>(x, y, z); }
+template <typename T> __host__ __device__ __forceinline__ V3T<T> operator+(V3T<T> a, V3T<T> b) { return v3t<T>(a.x + b.x, a.y + b.y, a.z + b.z); }
+template <typename T> __host__ __device__ __forceinline__ V3T<T> operator-(V3T<T> a, V3T<T> b) { return v3t<T>(a.x - b.x, a.y - b.y, a.z - b.z); }
+template <typename T> __host__ __device__ __forceinline__ V3T<T> operator*(T s, V3T<T> a) { return v3t<T>(s * a.x, s * a.y, s * a.z); }
+template <typename T> __host__ __device__ __forceinline__ V3T<T> cross(V3T<T> a, V3T<T> b) { return v3t<T>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+template <typename T> __host__ __device__ __forceinline__ T dot(V3T<T> a, V3T<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ float norm(V3 a) { return sqrtf(dot(a, a)); }
+__host__ __device__ __forceinline__ double norm(D3 a) { return sqrt(dot(a, a)); }
+
+// child -> parent:  E = Rx(ROT*90deg) * Rz(q)
+template <int ROT>
+__device__ __forceinline__ V3 to_parent(V3 v, float c, float s) {
+  float x = c * v.x - s * v.y, y = s * v.x + c * v.y, z = v.z;
+  if (ROT == 1) return v3(x, -z, y);
+  if (ROT == -1) return v3(x, z, -y);
+  return v3(x, y, z);
+}
+// parent -> child:  E^T
+template <int ROT>
+__device__ __forceinline__ V3 to_child(V3 v, float c, float s) {
+  V3 u = v;
+  if (ROT == 1) u = v3(v.x, v.z, -v.y);
+  if (ROT == -1) u = v3(v.x, -v.z, v.y);
+  return v3(c * u.x + s * u.y, -s * u.x + c * u.y, u.z);
+}
+
+constexpr float kDt = 1.0f / 500.0f;      // pybullet.py:50
+constexpr float kGravity = 9.81f;         // pybullet.py:54
+constexpr float kDamp = 0.04f;            // btMultiBody linear/angular damping (pinned by the KAT, see oracle)
+constexpr float kMaxCoordVel = 100.0f;    // btMultiBody m_maxCoordinateVelocity
+constexpr float kLimitErp = 0.2f;         // solverInfo.m_erp on joint-limit rows
+constexpr float kLimitMaxImpulse = 100.f; // btMultiBodyConstraint m_maxAppliedImpulse
+constexpr int kSolverIters = 50;          // PyBullet numSolverIterations
+constexpr float kResidualThr = 1e-7f;     // PyBullet solverResidualThreshold
+
+// kinematic state of a link frame, expressed in that frame
+struct Kin { V3 w, al, a, v; };
+
+// wrench (about the frame origin) of one rigid body riding on a frame with state k:
+// Newton-Euler with qdd = 0 plus btMultiBody's velocity damping  m v (k + k|v|),  I w (k + k|w|).
+__device__ __forceinline__ void body_wrench(const Kin& k, float m, V3 c, float ixx, float iyy, float izz, float ixy, float ixz,
+                                            float iyz, V3& f, V3& n) {
+  V3 wc = cross(k.w, c);
+  V3 vc = k.v + wc;
+  V3 ac = k.a + cross(k.al, c) + cross(k.w, wc);
+  float dl = kDamp + kDamp * norm(vc);
+  V3 F = m * (ac + dl * vc);
+  V3 Iw = v3(ixx * k.w.x + ixy * k.w.y + ixz * k.w.z, ixy * k.w.x + iyy * k.w.y + iyz * k.w.z, ixz * k.w.x + iyz * k.w.y + izz * k.w.z);
+  V3 Ia = v3(ixx * k.al.x + ixy * k.al.y + ixz * k.al.z, ixy * k.al.x + iyy * k.al.y + iyz * k.al.z, ixz * k.al.x + iyz * k.al.y + izz * k.al.z);
+  float da = kDamp + kDamp * norm(k.w);
+  V3 N = Ia + cross(k.w, Iw) + da * Iw;
+  f = f + F;
+  n = n + N + cross(c, F);
+}
+
+template <int I>
+__device__ __forceinline__ Kin kin_step(const Kin& p, float c, float s, float qd) {
+  using L = pgm::Link<I>;
+  const V3 pp = v3(L::px, L::py, L::pz);
+  Kin k;
+  V3 wc = to_child<L::rot>(p.w, c, s);
+  k.w = v3(wc.x, wc.y, wc.z + qd);
+  V3 alc = to_child<L::rot>(p.al, c, s);
+  k.al = v3(alc.x + wc.y * qd, alc.y - wc.x * qd, alc.z);
+  V3 wxp = cross(p.w, pp);
+  k.a = to_child<L::rot>(p.a + cross(p.al, pp) + cross(p.w, wxp), c, s);
+  k.v = to_child<L::rot>(p.v + wxp, c, s);
+  return k;
+}
+
+template <int I>
+__device__ __forceinline__ void link_wrench(const Kin& k, V3& f, V3& n) {
+  using L = pgm::Link<I>;
+  f = v3(0, 0, 0); n = v3(0, 0, 0);
+  body_wrench(k, L::m, v3(L::cx, L::cy, L::cz), L::ixx, L::iyy, L::izz, 0.f, 0.f, 0.f, f, n);
+}
+template <int K>
+__device__ __forceinline__ void sub_wrench(const Kin& k, V3& f, V3& n) {
+  using S = pgm::Sub<K>;
+  body_wrench(k, S::m, v3(S::cx, S::cy, S::cz), S::ixx, S::iyy, S::izz, S::ixy, S::ixz, S::iyz, f, n);
+}
+
+// child wrench -> parent frame, accumulated
+template <int I>
+__device__ __forceinline__ void wrench_up(V3 fc, V3 nc, float c, float s, V3& f, V3& n) {
+  using L = pgm::Link<I>;
+  V3 fp = to_parent<L::rot>(fc, c, s);
+  V3 np = to_parent<L::rot>(nc, c, s);
+  f = f + fp;
+  n = n + np + cross(v3(L::px, L::py, L::pz), fp);
+}
+
+// tau_b[i] = joint torque needed to hold qdd = 0  (== C(q,qd) qd + g(q) + damping)
+__device__ __forceinline__ void rnea_bias(const float* cq, const float* sq, const float* qd, float* tau) {
+  Kin k0;
+  k0.w = v3(0, 0, 0); k0.al = v3(0, 0, 0); k0.v = v3(0, 0, 0);
+  k0.a = v3(0, 0, kGravity);  // gravity as base acceleration
+  V3 f1, n1, f2, n2, f3, n3, f4, n4, f5, n5, f6, n6, f7, n7;
+  Kin k1 = kin_step<1>(k0, cq[0], sq[0], qd[0]); link_wrench<1>(k1, f1, n1);
+  Kin k2 = kin_step<2>(k1, cq[1], sq[1], qd[1]); link_wrench<2>(k2, f2, n2);
+  Kin k3 = kin_step<3>(k2, cq[2], sq[2], qd[2]); link_wrench<3>(k3, f3, n3);
+  Kin k4 = kin_step<4>(k3, cq[3], sq[3], qd[3]); link_wrench<4>(k4, f4, n4);
+  Kin k5 = kin_step<5>(k4, cq[4], sq[4], qd[4]); link_wrench<5>(k5, f5, n5);
+  Kin k6 = kin_step<6>(k5, cq[5], sq[5], qd[5]); link_wrench<6>(k6, f6, n6);
+  Kin k7 = kin_step<7>(k6, cq[6], sq[6], qd[6]); link_wrench<7>(k7, f7, n7);
+  sub_wrench<0>(k7, f7, n7); sub_wrench<1>(k7, f7, n7); sub_wrench<2>(k7, f7, n7);
+  tau[6] = n7.z; wrench_up<7>(f7, n7, cq[6], sq[6], f6, n6);
+  tau[5] = n6.z; wrench_up<6>(f6, n6, cq[5], sq[5], f5, n5);
+  tau[4] = n5.z; wrench_up<5>(f5, n5, cq[4], sq[4], f4, n4);
+  tau[3] = n4.z; wrench_up<4>(f4, n4, cq[3], sq[3], f3, n3);
+  tau[2] = n3.z; wrench_up<3>(f3, n3, cq[2], sq[2], f2, n2);
+  tau[1] = n2.z; wrench_up<2>(f2, n2, cq[1], sq[1], f1, n1);
+  tau[0] = n1.z;
+}
+
+// ---------------------------------------------------------------------------------------------- CRBA
+// spatial inertia about a frame origin: mass, first moment h = m c, rotational inertia about the origin
+struct SI { float m; V3 h; float xx, yy, zz, xy, xz, yz; };
+
+__device__ __forceinline__ void si_add_body(SI& S, float m, V3 c, float ixx, float iyy, float izz, float ixy, float ixz, float iyz) {
+  S.m += m;
+  S.h = S.h + m * c;
+  float cc = dot(c, c);
+  S.xx += ixx + m * (cc - c.x * c.x); S.yy += iyy + m * (cc - c.y * c.y); S.zz += izz + m * (cc - c.z * c.z);
+  S.xy += ixy - m * c.x * c.y; S.xz += ixz - m * c.x * c.z; S.yz += iyz - m * c.y * c.z;
+}
+template <int I>
+__device__ __forceinline__ SI si_link() {
+  using L = pgm::Link<I>;
+  SI S; S.m = 0; S.h = v3(0, 0, 0); S.xx = S.yy = S.zz = S.xy = S.xz = S.yz = 0;
+  si_add_body(S, L::m, v3(L::cx, L::cy, L::cz), L::ixx, L::iyy, L::izz, 0.f, 0.f, 0.f);
+  return S;
+}
+template <int K>
+__device__ __forceinline__ void si_add_sub(SI& S) {
+  using B = pgm::Sub<K>;
+  si_add_body(S, B::m, v3(B::cx, B::cy, B::cz), B::ixx, B::iyy, B::izz, B::ixy, B::ixz, B::iyz);
+}
+// express child composite inertia (frame I) in the parent frame (I-1) and add it to P
+template <int I>
+__device__ __forceinline__ void si_up(const SI& C, float c, float s, SI& P) {
+  using L = pgm::Link<I>;
+  // rotate about z by q:  T = Rz I Rz^T
+  float xx = c * c * C.xx - 2.f * c * s * C.xy + s * s * C.yy;
+  float yy = s * s * C.xx + 2.f * c * s * C.xy + c * c * C.yy;
+  float xy = c * s * (C.xx - C.yy) + (c * c - s * s) * C.xy;
+  float xz = c * C.xz - s * C.yz;
+  float yz = s * C.xz + c * C.yz;
+  float zz = C.zz;
+  // then Rx(+-90): (x,y,z) -> (x,-z,y) / (x,z,-y)
+  float Xx = xx, Yy = yy, Zz = zz, Xy = xy, Xz = xz, Yz = yz;
+  if (L::rot == 1) { Yy = zz; Zz = yy; Xy = -xz; Xz = xy; Yz = -yz; }
+  if (L::rot == -1) { Yy = zz; Zz = yy; Xy = xz; Xz = -xy; Yz = -yz; }
+  V3 g = to_parent<L::rot>(C.h, c, s);
+  const V3 p = v3(L::px, L::py, L::pz);
+  float pg2 = 2.f * dot(p, g), pp = dot(p, p);
+  P.m += C.m;
+  P.h = P.h + g + C.m * p;
+  P.xx += Xx - 2.f * g.x * p.x + pg2 - C.m * p.x * p.x + C.m * pp;
+  P.yy += Yy - 2.f * g.y * p.y + pg2 - C.m * p.y * p.y + C.m * pp;
+  P.zz += Zz - 2.f * g.z * p.z + pg2 - C.m * p.z * p.z + C.m * pp;
+  P.xy += Xy - (g.x * p.y + p.x * g.y) - C.m * p.x * p.y;
+  P.xz += Xz - (g.x * p.z + p.x * g.z) - C.m * p.x * p.z;
+  P.yz += Yz - (g.y * p.z + p.y * g.z) - C.m * p.y * p.z;
+}
+// force produced by unit acceleration of a z-axis joint on composite inertia C: n = I[:,z], f = z x h
+__device__ __forceinline__ void si_col(const SI& C, V3& f, V3& n) { f = v3(-C.h.y, C.h.x, 0.f); n = v3(C.xz, C.yz, C.zz); }
+template <int I>
+__device__ __forceinline__ void col_up(V3& f, V3& n, float c, float s) {
+  using L = pgm::Link<I>;
+  V3 fp = to_parent<L::rot>(f, c, s);
+  V3 np = to_parent<L::rot>(n, c, s);
+  n = np + cross(v3(L::px, L::py, L::pz), fp);
+  f = fp;
+}
+
+// packed symmetric index, i >= j
+__host__ __device__ constexpr int sym(int i, int j) { return i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i; }
+
+// joint-space mass matrix, 28 packed entries
+__device__ __forceinline__ void crba(const float* cq, const float* sq, float* M) {
+  V3 f7, n7, f6, n6, f5, n5, f4, n4, f3, n3, f2, n2, f1, n1;
+  SI C = si_link<7>();
+  si_add_sub<0>(C); si_add_sub<1>(C); si_add_sub<2>(C);
+  si_col(C, f7, n7); M[sym(6, 6)] = n7.z;
+  SI P = si_link<6>(); si_up<7>(C, cq[6], sq[6], P); C = P;
+  col_up<7>(f7, n7, cq[6], sq[6]); M[sym(6, 5)] = n7.z;
+  si_col(C, f6, n6); M[sym(5, 5)] = n6.z;
+  P = si_link<5>(); si_up<6>(C, cq[5], sq[5], P); C = P;
+  col_up<6>(f7, n7, cq[5], sq[5]); M[sym(6, 4)] = n7.z;
+  col_up<6>(f6, n6, cq[5], sq[5]); M[sym(5, 4)] = n6.z;
+  si_col(C, f5, n5); M[sym(4, 4)] = n5.z;
+  P = si_link<4>(); si_up<5>(C, cq[4], sq[4], P); C = P;
+  col_up<5>(f7, n7, cq[4], sq[4]); M[sym(6, 3)] = n7.z;
+  col_up<5>(f6, n6, cq[4], sq[4]); M[sym(5, 3)] = n6.z;
+  col_up<5>(f5, n5, cq[4], sq[4]); M[sym(4, 3)] = n5.z;
+  si_col(C, f4, n4); M[sym(3, 3)] = n4.z;
+  P = si_link<3>(); si_up<4>(C, cq[3], sq[3], P); C = P;
+  col_up<4>(f7, n7, cq[3], sq[3]); M[sym(6, 2)] = n7.z;
+  col_up<4>(f6, n6, cq[3], sq[3]); M[sym(5, 2)] = n6.z;
+  col_up<4>(f5, n5, cq[3], sq[3]); M[sym(4, 2)] = n5.z;
+  col_up<4>(f4, n4, cq[3], sq[3]); M[sym(3, 2)] = n4.z;
+  si_col(C, f3, n3); M[sym(2, 2)] = n3.z;
+  P = si_link<2>(); si_up<3>(C, cq[2], sq[2], P); C = P;
+  col_up<3>(f7, n7, cq[2], sq[2]); M[sym(6, 1)] = n7.z;
+  col_up<3>(f6, n6, cq[2], sq[2]); M[sym(5, 1)] = n6.z;
+  col_up<3>(f5, n5, cq[2], sq[2]); M[sym(4, 1)] = n5.z;
+  col_up<3>(f4, n4, cq[2], sq[2]); M[sym(3, 1)] = n4.z;
+  col_up<3>(f3, n3, cq[2], sq[2]); M[sym(2, 1)] = n3.z;
+  si_col(C, f2, n2); M[sym(1, 1)] = n2.z;
+  P = si_link<1>(); si_up<2>(C, cq[1], sq[1], P); C = P;
+  col_up<2>(f7, n7, cq[1], sq[1]); M[sym(6, 0)] = n7.z;
+  col_up<2>(f6, n6, cq[1], sq[1]); M[sym(5, 0)] = n6.z;
+  col_up<2>(f5, n5, cq[1], sq[1]); M[sym(4, 0)] = n5.z;
+  col_up<2>(f4, n4, cq[1], sq[1]); M[sym(3, 0)] = n4.z;
+  col_up<2>(f3, n3, cq[1], sq[1]); M[sym(2, 0)] = n3.z;
+  col_up<2>(f2, n2, cq[1], sq[1]); M[sym(1, 0)] = n2.z;
+  si_col(C, f1, n1); M[sym(0, 0)] = n1.z;
+}
+
+// M (packed, SPD) -> M^-1 (packed), in place, via Cholesky
+__device__ __forceinline__ void spd_inverse7(float* A) {
+  // L L^T = A  (lower, packed)
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+    float d = A[sym(j, j)];
+#pragma unroll
+    for (int k = 0; k < j; k++) d -= A[sym(j, k)] * A[sym(j, k)];
+    float inv = rsqrtf(d);
+    A[sym(j, j)] = inv;  // store 1 / L_jj
+#pragma unroll
+    for (int i = j + 1; i < 7; i++) {
+      float v = A[sym(i, j)];
+#pragma unroll
+      for (int k = 0; k < j; k++) v -= A[sym(i, k)] * A[sym(j, k)];
+      A[sym(i, j)] = v * inv;
+    }
+  }
+  // W = L^-1 (lower), in place; diagonal already holds 1/L_jj
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+#pragma unroll
+    for (int i = j + 1; i < 7; i++) {
+      float v = 0.f;
+#pragma unroll
+      for (int k = j; k < i; k++) v -= A[sym(i, k)] * (k == j ? A[sym(j, j)] : A[sym(k, j)]);
+      // note: entries A[sym(k, j)] for j < k < i already hold W_kj (computed earlier in this i-loop)
+      A[sym(i, j)] = v * A[sym(i, i)];
+    }
+  }
+  // A^-1 = W^T W:  out_ij = sum_{k >= max(i,j)} W_ki W_kj ; ascending (i, j<=i) order only reads W rows >= i
+#pragma unroll
+  for (int i = 0; i < 7; i++) {
+#pragma unroll
+    for (int j = 0; j <= i; j++) {
+      float v = 0.f;
+#pragma unroll
+      for (int k = i; k < 7; k++) v += A[sym(k, i)] * A[sym(k, j)];
+      A[sym(i, j)] = v;
+    }
+  }
+}
+
+// One stepSimulation().  q, qd updated in place; cq/sq hold cos/sin of the CURRENT q on entry and of the new q
+// on exit.  tgt = POSITION_CONTROL targets (or velocity targets when VELOCITY is true), fmax = max force.
+template <bool VELOCITY>
+__device__ __forceinline__ void substep(float* q, float* qd, float* cq, float* sq, const float* tgt, const float* max_imp) {
+  float tau[7], Mi[28];
+  rnea_bias(cq, sq, qd, tau);
+  crba(cq, sq, Mi);
+  spd_inverse7(Mi);
+  // 1. unconstrained velocity update  qd += dt * M^-1 (-tau_b)
+#pragma unroll
+  for (int i = 0; i < 7; i++) {
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 7; j++) acc -= Mi[sym(i, j)] * tau[j];
+    qd[i] = fminf(fmaxf(qd[i] + acc * kDt, -kMaxCoordVel), kMaxCoordVel);
+  }
+  // 2. rows.  Motor row d: unit Jacobian on dof d.  Limit row d (at most one side active): sign sg[d].
+  float rhs[7], dinv[7], app[7], dv[7];
+  float lrhs[7], lsg[7], lapp[7];
+  bool any_limit = false;
+  const float lo[7] = {pgm::Link<1>::lo, pgm::Link<2>::lo, pgm::Link<3>::lo, pgm::Link<4>::lo, pgm::Link<5>::lo, pgm::Link<6>::lo, pgm::Link<7>::lo};
+  const float hi[7] = {pgm::Link<1>::hi, pgm::Link<2>::hi, pgm::Link<3>::hi, pgm::Link<4>::hi, pgm::Link<5>::hi, pgm::Link<6>::hi, pgm::Link<7>::hi};
+#pragma unroll
+  for (int d = 0; d < 7; d++) {
+    float denom = Mi[sym(d, d)];
+    dinv[d] = denom > 1.1920929e-07f ? 1.0f / denom : 0.f;
+    float want = VELOCITY ? tgt[d] : 50.0f * (tgt[d] - q[d]);  // kp (q* - q)/dt + v + kd (0 - v): kp .1, kd 1, dt 1/500
+    rhs[d] = (want - qd[d]) * dinv[d];
+    app[d] = 0.f; dv[d] = 0.f;
+    float pl = q[d] - lo[d], pu = hi[d] - q[d];
+    lsg[d] = 0.f; lrhs[d] = 0.f; lapp[d] = 0.f;
+    if (pl <= 0.f) { lsg[d] = 1.f; lrhs[d] = (-pl * kLimitErp / kDt - qd[d]) * dinv[d]; any_limit = true; }
+    else if (pu <= 0.f) { lsg[d] = -1.f; lrhs[d] = (-pu * kLimitErp / kDt + qd[d]) * dinv[d]; any_limit = true; }
+  }
+  // 3. projected Gauss-Seidel, Bullet order: rows = [limits (dof order), motors (dof order)];
+  //    even iterations sweep backward, odd forward; stop when max residual^2 <= 1e-7
+#define PG_MOTOR_ROW(d)                                                     \
+  if (max_imp[d] != 0.f) {                                                  \
+    float delta = rhs[d] - dv[d] * dinv[d];                                 \
+    float cl = fminf(fmaxf(app[d] + delta, -max_imp[d]), max_imp[d]);       \
+    delta = live ? cl - app[d] : 0.f;                                       \
+    app[d] += delta;                                                        \
+    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] += Mi[sym(i, d)] * delta; \
+    float res = delta * Mi[sym(d, d)];                                      \
+    lsq = fmaxf(lsq, res * res);                                            \
+  }
+#define PG_LIMIT_ROW(d)                                                     \
+  if (lsg[d] != 0.f && live) {                                              \
+    float delta = lrhs[d] - lsg[d] * dv[d] * dinv[d];                       \
+    float sum = lapp[d] + delta;                                            \
+    if (sum < 0.f) { delta = -lapp[d]; lapp[d] = 0.f; }                     \
+    else if (sum > kLimitMaxImpulse) { delta = kLimitMaxImpulse - lapp[d]; lapp[d] = kLimitMaxImpulse; } \
+    else lapp[d] = sum;                                                     \
+    float sd = lsg[d] * delta;                                              \
+    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] += Mi[sym(i, d)] * sd; \
+    float res = delta * Mi[sym(d, d)];                                      \
+    lsq = fmaxf(lsq, res * res);                                            \
+  }
+  bool live = true;
+  for (int it = 0; it < kSolverIters; it += 2) {
+    float lsq = 0.f;  // even iteration: backward sweep (motors 6..0, then limits 6..0)
+    PG_MOTOR_ROW(6) PG_MOTOR_ROW(5) PG_MOTOR_ROW(4) PG_MOTOR_ROW(3) PG_MOTOR_ROW(2) PG_MOTOR_ROW(1) PG_MOTOR_ROW(0)
+    if (any_limit) { PG_LIMIT_ROW(6) PG_LIMIT_ROW(5) PG_LIMIT_ROW(4) PG_LIMIT_ROW(3) PG_LIMIT_ROW(2) PG_LIMIT_ROW(1) PG_LIMIT_ROW(0) }
+    if (lsq <= kResidualThr) live = false;
+    if (!__any_sync(__activemask(), live)) break;
+    lsq = 0.f;        // odd iteration: forward sweep (limits 0..6, then motors 0..6)
+    if (any_limit) { PG_LIMIT_ROW(0) PG_LIMIT_ROW(1) PG_LIMIT_ROW(2) PG_LIMIT_ROW(3) PG_LIMIT_ROW(4) PG_LIMIT_ROW(5) PG_LIMIT_ROW(6) }
+    PG_MOTOR_ROW(0) PG_MOTOR_ROW(1) PG_MOTOR_ROW(2) PG_MOTOR_ROW(3) PG_MOTOR_ROW(4) PG_MOTOR_ROW(5) PG_MOTOR_ROW(6)
+    if (lsq <= kResidualThr) live = false;
+    if (!__any_sync(__activemask(), live)) break;
+  }
+#undef PG_MOTOR_ROW
+#undef PG_LIMIT_ROW
+  // 4. apply, clamp, integrate
+#pragma unroll
+  for (int d = 0; d < 7; d++) {
+    qd[d] = fminf(fmaxf(qd[d] + dv[d], -kMaxCoordVel), kMaxCoordVel);
+    q[d] += qd[d] * kDt;
+    sincosf(q[d], &sq[d], &cq[d]);
+  }
+}
+
+}  // namespace pg

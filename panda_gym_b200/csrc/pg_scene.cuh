@@ -1,0 +1,127 @@
+// pg_scene.cuh -- per-environment collision / observation pass over the 9 ReachAO collision links.
+//
+// Replaces (reference) ReachAO.check_collided (reach_ao.py:896-900) in its flag-only form and
+// ReachAO.get_obs / get_vector_obs (reach_ao.py:902-959) in its full form; both go through the pyb_utils-fork
+// CollisionDetector in the reference, i.e. 9 links x M obstacles getClosestPoints calls per query.
+#pragma once
+#include "pg_geom.cuh"
+
+namespace pg {
+
+struct SceneParams {
+  int nobs;
+  Obst obst[kMaxObst];
+  float obst_bound[kMaxObst];  // bounding radius of each obstacle shape
+  float table_pos[3], table_core[3], table_margin;
+  int has_table;
+};
+
+// primitives of collision-link slot S: [first, first + count)
+__host__ __device__ constexpr int slot_first(int s) { return s <= 4 ? 3 * s : 3 * s + 3; }
+__host__ __device__ constexpr int slot_count(int s) { return s == 4 ? 6 : 3; }
+__host__ __device__ constexpr float cabs(float x) { return x < 0 ? -x : x; }
+__host__ __device__ constexpr float cmax(float a, float b) { return a > b ? a : b; }
+
+// conservative bounding sphere of a slot: centre = its first primitive, radius via L1 offsets
+template <int K0, int K> struct BoundAcc {
+  using A = pgm::Prim<K0>; using B = pgm::Prim<K>;
+  static constexpr float ext = B::r + (B::type == 1 ? B::h : 0.f);
+  static constexpr float off = cabs(B::x - A::x) + cabs(B::y - A::y) + cabs(B::z - A::z);
+  static constexpr float value = off + ext;
+};
+template <int K0, int N> struct SlotBound { static constexpr float value = cmax(SlotBound<K0, N - 1>::value, BoundAcc<K0, K0 + N - 1>::value); };
+template <int K0> struct SlotBound<K0, 0> { static constexpr float value = 0.f; };
+
+template <int K>
+__device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obst& ob, float& best, V3& bdir) {
+  using Pm = pgm::Prim<K>;
+  V3 c = frame_point(F, Pm::x, Pm::y, Pm::z);
+  Closest k;
+  if (Pm::type == 0) {
+    if (ob.type == 0) k = sphere_sphere<float>(c, Pm::r, o, ob.sx);
+    else k = sphere_box<float>(c, Pm::r, o, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
+  } else {
+    V3 a = frame_dir(F, Pm::ax, Pm::ay, Pm::az);
+    if (ob.type == 0) k = cyl_sphere<float>(c, a, Pm::r, Pm::h, o, ob.sx);
+    else k = cyl_box<float>(c, a, Pm::r, Pm::h, o, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
+  }
+  if (k.d < best) { best = k.d; bdir = k.dir; }
+}
+template <int K>
+__device__ __forceinline__ float prim_vs_table(const Frame& F, const SceneParams& S) {
+  using Pm = pgm::Prim<K>;
+  V3 c = frame_point(F, Pm::x, Pm::y, Pm::z);
+  V3 b = v3(S.table_pos[0], S.table_pos[1], S.table_pos[2]), e = v3(S.table_core[0], S.table_core[1], S.table_core[2]);
+  if (Pm::type == 0) return sphere_box<float>(c, Pm::r, b, e, S.table_margin).d;
+  return cyl_table_distance(c, frame_dir(F, Pm::ax, Pm::ay, Pm::az), Pm::r, Pm::h, b, e, S.table_margin);
+}
+
+template <int K0, int N> struct PrimLoop {
+  static __device__ __forceinline__ void obstacle(const Frame& F, V3 o, const Obst& ob, float& best, V3& dir) {
+    PrimLoop<K0, N - 1>::obstacle(F, o, ob, best, dir);
+    prim_vs_obstacle<K0 + N - 1>(F, o, ob, best, dir);
+  }
+  static __device__ __forceinline__ float table(const Frame& F, const SceneParams& S) {
+    return fminf(PrimLoop<K0, N - 1>::table(F, S), prim_vs_table<K0 + N - 1>(F, S));
+  }
+};
+template <int K0> struct PrimLoop<K0, 0> {
+  static __device__ __forceinline__ void obstacle(const Frame&, V3, const Obst&, float&, V3&) {}
+  static __device__ __forceinline__ float table(const Frame&, const SceneParams&) { return 3.0e38f; }
+};
+
+// One collision link.  FULL: exact per-link minimum distance + closest pair (observation); otherwise only
+// "is any distance <= 0", with bounding-sphere culling.  obs_pos: f64 [kMaxObst][3][n] (SoA), e = env.
+template <int S, bool FULL>
+__device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __restrict__ obs_pos, int n, int e, const Frame& F,
+                                          bool& hit, float& d_out, V3& u_out) {
+  constexpr int K0 = slot_first(S), N = slot_count(S);
+  using P0 = pgm::Prim<K0>;
+  constexpr float R = SlotBound<K0, N>::value + 0.002f;
+  float best = 999.0f;  // pyb_utils saturates at max_distance
+  V3 dir = v3(0, 0, 0);
+  V3 ctr = frame_point(F, P0::x, P0::y, P0::z);
+  for (int j = 0; j < P.nobs; j++) {
+    V3 o = v3((float)obs_pos[(size_t)(j * 3 + 0) * n + e], (float)obs_pos[(size_t)(j * 3 + 1) * n + e], (float)obs_pos[(size_t)(j * 3 + 2) * n + e]);
+    if (!FULL) {
+      V3 d = o - ctr;
+      float rr = R + P.obst_bound[j];
+      if (dot(d, d) > rr * rr) continue;
+    }
+    PrimLoop<K0, N>::obstacle(F, o, P.obst[j], best, dir);
+  }
+  if (best <= 0.f) hit = true;
+  if (S >= 1 && P.has_table) {  // table: panda_link0 / panda_link1 ignored (reach_ao.py:898)
+    bool near = true;
+    if (!FULL) near = (ctr.z - R) <= (P.table_pos[2] + P.table_core[2] + P.table_margin + 0.002f) ||
+                      fabsf(ctr.x - P.table_pos[0]) + R > P.table_core[0] || fabsf(ctr.y - P.table_pos[1]) + R > P.table_core[1];
+    if (near && PrimLoop<K0, N>::table(F, P) <= 0.f) hit = true;
+  }
+  if (FULL) {
+    d_out = best;
+    // utils.unit_vector(pA, pB) = nan_to_num((pB - pA) / |pB - pA|) with pB - pA = d * dir
+    u_out = best > 0.f ? dir : (best < 0.f ? v3(-dir.x, -dir.y, -dir.z) : v3(0, 0, 0));
+  }
+}
+
+// all 9 collision links at joint cosines/sines (cq, sq).  FULL fills d_link[9], u_link[9].
+template <bool FULL>
+__device__ __forceinline__ bool scene_pass(const SceneParams& P, const double* __restrict__ obs_pos, int n, int e, V3 base, const float* cq,
+                                           const float* sq, float* d_link, V3* u_link) {
+  bool hit = false;
+  float d; V3 u;
+  Frame F = base_frame(base);
+  F = frame_step<1>(F, cq[0], sq[0]); slot_eval<0, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[0] = d; u_link[0] = u; }
+  F = frame_step<2>(F, cq[1], sq[1]); slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[1] = d; u_link[1] = u; }
+  F = frame_step<3>(F, cq[2], sq[2]); slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[2] = d; u_link[2] = u; }
+  F = frame_step<4>(F, cq[3], sq[3]); slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[3] = d; u_link[3] = u; }
+  F = frame_step<5>(F, cq[4], sq[4]); slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[4] = d; u_link[4] = u; }
+  F = frame_step<6>(F, cq[5], sq[5]); slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[5] = d; u_link[5] = u; }
+  F = frame_step<7>(F, cq[6], sq[6]);
+  slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[6] = d; u_link[6] = u; }
+  slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[7] = d; u_link[7] = u; }
+  slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[8] = d; u_link[8] = u; }
+  return hit;
+}
+
+}  // namespace pg

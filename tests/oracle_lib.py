@@ -100,6 +100,7 @@ def lib():
     sig("pgo_env_get_obs", None, P, P, P, P)
     sig("pgo_env_compute_reward", None, P, P, P, c_int, P)
     sig("pgo_env_is_collided", c_int, P)
+    sig("pgo_bench_rollout", c_int, P, c_u64, c_int, P)
     _lib = L
     return L
 
@@ -261,3 +262,30 @@ class Env:
         out = np.zeros(len(ag), np.float32)
         self.L.pgo_env_compute_reward(self.h, dp(ag), dp(dg), len(ag), dp(out))
         return out
+
+
+def cpu_rollout(steps_per_env, n_threads, scenario="reachao3", max_episode_steps=100, seed=0):
+    """Time the oracle as a CPU baseline: one environment per host thread (ctypes releases the GIL)."""
+    import threading
+    import time
+    L = lib()
+    cfg = EnvConfig()
+    L.pgo_env_default_config(ctypes.byref(cfg), 1)
+    name, _, n = scenario.partition("-")
+    cfg.scenario = SCENARIOS[name]
+    if n:
+        cfg.n_obstacles = int(n)
+    cfg.max_episode_steps = max_episode_steps
+    res = [0] * n_threads
+
+    def work(i):
+        res[i] = L.pgo_bench_rollout(ctypes.byref(cfg), seed + 1000003 * i, steps_per_env, None)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(n_threads)]
+    t0 = time.perf_counter()
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    return steps_per_env * n_threads / dt, dt, sum(res)

@@ -176,6 +176,7 @@ def fmt(v):
 
 def emit_model(tag, urdf_path, out):
     links, root, order = parse(urdf_path)
+    links["__root__"] = root
     JT = {"fixed": 0, "revolute": 1, "continuous": 1, "prismatic": 2}
     prim_rows = []
     link_rows = []
@@ -212,6 +213,172 @@ def emit_model(tag, urdf_path, out):
     return links, order
 
 
+def mat_vec(R, v):
+    return [sum(R[i][k] * v[k] for k in range(3)) for i in range(3)]
+
+
+def mat_mul(A, B):
+    return [[sum(A[i][k] * B[k][j] for k in range(3)) for j in range(3)] for i in range(3)]
+
+
+def snap(x):
+    """Joint-origin rotations of the Panda are multiples of 90 deg written with 11 digits; snap |x| < 1e-9."""
+    for t in (0.0, 1.0, -1.0):
+        if abs(x - t) < 1e-9:
+            return t
+    return x
+
+
+def ff(x):
+    return repr(float(x)) + "f"
+
+
+def emit_cuda(links, order, path):
+    """Specialised constants of franka_panda_custom_0 for the sm_100a kernels: 7 revolute z-axis joints whose
+    origins are Rx(0 / +-90 deg); everything rigidly attached to link7 (link8, hand, ee, fingers) is expressed
+    in the link7 frame."""
+    o = [
+        "// GENERATED by tools/gen_model.py from the reference's franka_panda_custom_0/panda.urdf (numbers only).",
+        "// Link i (1..7) = child of revolute joint i; frames are the URDF link frames (origin on the joint axis).",
+        "#pragma once",
+        "namespace pgm {",
+        "template <int I> struct Link;   // kinematic + inertial constants of moving link I (1..7)",
+        "template <int K> struct Sub;    // rigid bodies fixed to link7 (own mass / COM / inertia; Bullet damps each)",
+        "template <int K> struct Prim;   // collision primitives of the 9 ReachAO collision links",
+    ]
+    names = [n for n, _, _ in order]
+    # transforms of links 7.. relative to link7 (index 6)
+    rel = {6: ([[1, 0, 0], [0, 1, 0], [0, 0, 1]], [0.0, 0.0, 0.0])}
+    for idx in range(7, len(order)):
+        name, j, parent = order[idx]
+        assert j["type"] == "fixed"
+        Rp, pp = rel[parent]
+        R = rpy_to_R(*j["rpy"])
+        rel[idx] = (mat_mul(Rp, R), [pp[k] + mat_vec(Rp, j["xyz"])[k] for k in range(3)])
+    for i in range(7):
+        name, j, parent = order[i]
+        L = links[name]
+        R = [[snap(x) for x in row] for row in rpy_to_R(*j["rpy"])]
+        if R == [[1, 0, 0], [0, 1, 0], [0, 0, 1]]:
+            rot = 0
+        elif R == [[1, 0, 0], [0, 0, -1], [0, 1, 0]]:
+            rot = 1   # Rx(+90): (x, y, z) -> (x, -z, y)
+        elif R == [[1, 0, 0], [0, 0, 1], [0, -1, 0]]:
+            rot = -1  # Rx(-90): (x, y, z) -> (x, z, -y)
+        else:
+            raise ValueError("unexpected joint origin rotation %r" % R)
+        assert j["axis"] == [0.0, 0.0, 1.0] and j["type"] == "revolute"
+        I = bullet_inertia(L)
+        o.append("template <> struct Link<%d> {  // %s" % (i + 1, name))
+        o.append("  static constexpr int rot = %d;  // joint origin = Rx(rot * 90 deg)" % rot)
+        o.append("  static constexpr float px = %s, py = %s, pz = %s;  // joint origin in the parent frame" % tuple(ff(x) for x in j["xyz"]))
+        o.append("  static constexpr float cx = %s, cy = %s, cz = %s;  // COM" % tuple(ff(x) for x in L["com"]))
+        o.append("  static constexpr float m = %s, ixx = %s, iyy = %s, izz = %s;  // Bullet AABB-box inertia" % (ff(L["mass"]), ff(I[0]), ff(I[1]), ff(I[2])))
+        o.append("  static constexpr float lo = %s, hi = %s;  // joint limits" % (ff(j["lower"]), ff(j["upper"])))
+        o.append("};")
+    # sub-bodies on link7 with mass
+    k = 0
+    for idx in range(7, len(order)):
+        L = links[names[idx]]
+        if L["mass"] == 0.0:
+            continue
+        R, p = rel[idx]
+        c = [p[t] + mat_vec(R, L["com"])[t] for t in range(3)]
+        I = bullet_inertia(L)
+        D = [[I[0], 0, 0], [0, I[1], 0], [0, 0, I[2]]]
+        Rt = [[R[j2][i2] for j2 in range(3)] for i2 in range(3)]
+        IR = mat_mul(mat_mul(R, D), Rt)
+        o.append("template <> struct Sub<%d> {  // %s, in the link7 frame" % (k, names[idx]))
+        o.append("  static constexpr float cx = %s, cy = %s, cz = %s, m = %s;" % (ff(c[0]), ff(c[1]), ff(c[2]), ff(L["mass"])))
+        o.append("  static constexpr float ixx = %s, iyy = %s, izz = %s, ixy = %s, ixz = %s, iyz = %s;" % (
+            ff(IR[0][0]), ff(IR[1][1]), ff(IR[2][2]), ff(IR[0][1]), ff(IR[0][2]), ff(IR[1][2])))
+        o.append("};")
+        k += 1
+    o.append("constexpr int kNumSub = %d;" % k)
+    # end-effector = COM of link 11 (panda.py:68), in the link7 frame, + its orientation
+    R, p = rel[11]
+    c = [p[t] + mat_vec(R, links[names[11]]["com"])[t] for t in range(3)]
+    o.append("// end-effector = COM of link 11 (%s), link7 frame; link-11 frame origin (IK drives this point)" % names[11])
+    o.append("constexpr float kEEx = %s, kEEy = %s, kEEz = %s;" % tuple(ff(x) for x in c))
+    o.append("constexpr float kEEox = %s, kEEoy = %s, kEEoz = %s;" % tuple(ff(x) for x in p))
+    o.append("constexpr float kEErot_c = %s, kEErot_s = %s;  // link11 axes = Rz(angle) * link7 axes: cos, sin" % (ff(R[0][0]), ff(R[1][0])))
+    # COM of link index 0 (sample_obstacle_wang uses get_link_position(0))
+    # collision primitives: 9 collision links, link8 / ee expressed in the link7 frame
+    coll = [0, 1, 2, 3, 4, 5, 6, 7, 9]
+    k = 0
+    o.append("// collision primitives: slot = index into the 9 ReachAO collision links (link1..link8, panda_ee);")
+    o.append("// frame = moving link whose frame the numbers are in (1..7); type 0 sphere, 1 cylinder")
+    for slot, idx in enumerate(coll):
+        L = links[names[idx]]
+        frame = min(idx, 6)
+        R, p = rel[idx] if idx >= 6 else ([[1, 0, 0], [0, 1, 0], [0, 0, 1]], [0, 0, 0])
+        for pr in L["prims"]:
+            Rp = rpy_to_R(*pr["rpy"])
+            axis = mat_vec(R, [Rp[0][2], Rp[1][2], Rp[2][2]])
+            ctr = [p[t] + mat_vec(R, pr["xyz"])[t] for t in range(3)]
+            axis = [0.0 if abs(x) < 1e-12 else x for x in axis]
+            o.append("template <> struct Prim<%d> { static constexpr int slot = %d, frame = %d, type = %d; "
+                     "static constexpr float x = %s, y = %s, z = %s, ax = %s, ay = %s, az = %s, r = %s, h = %s; };" % (
+                         k, slot, frame + 1, 0 if pr["type"] == "sphere" else 1, ff(ctr[0]), ff(ctr[1]), ff(ctr[2]),
+                         ff(axis[0]), ff(axis[1]), ff(axis[2]), ff(pr["r"]), ff(pr["L"] / 2)))
+            k += 1
+    o.append("constexpr int kNumPrim = %d;" % k)
+    o.append("}  // namespace pgm")
+    with open(path, "w") as f:
+        f.write("\n".join(o) + "\n")
+    print("wrote", path)
+
+
+def emit_neutral(links, root, order, path):
+    """World placement (base at the origin) of all 36 collision primitives with the arm at Panda's neutral pose
+    (panda.py:67), in double: the reset path's rejection sampling (reach_ao.py:1101-1181) only ever queries the
+    robot at this pose (randomize_robot_pose=False)."""
+    neutral = [0.0, -0.3, 0.0, -2.2, 0.0, 2.0, math.pi / 4]
+    I3 = [[1.0, 0, 0], [0, 1.0, 0], [0, 0, 1.0]]
+    Rw = {-1: I3}
+    ow = {-1: [0.0, 0.0, 0.0]}
+    rows = []
+    names = [n for n, _, _ in order]
+
+    def add(L, R, o):
+        for pr in L["prims"]:
+            Rp = rpy_to_R(*pr["rpy"])
+            ax = mat_vec(R, [Rp[0][2], Rp[1][2], Rp[2][2]])
+            c = [o[k] + mat_vec(R, pr["xyz"])[k] for k in range(3)]
+            rows.append("  {%d, {%r, %r, %r}, {%r, %r, %r}, %r, %r}" % (
+                0 if pr["type"] == "sphere" else 1, c[0], c[1], c[2], ax[0], ax[1], ax[2], pr["r"], pr["L"] / 2))
+
+    for idx, (name, j, parent) in enumerate(order):
+        R = rpy_to_R(*j["rpy"])
+        if j["type"] == "revolute":
+            q = neutral[idx]
+            c, s = math.cos(q), math.sin(q)
+            R = mat_mul(R, [[c, -s, 0], [s, c, 0], [0, 0, 1]])
+        Rw[idx] = mat_mul(Rw[parent], R)
+        ow[idx] = [ow[parent][k] + mat_vec(Rw[parent], j["xyz"])[k] for k in range(3)]
+        add(links[name], Rw[idx], ow[idx])
+    add(links[root], I3, [0.0, 0.0, 0.0])
+    ee = [ow[11][k] + mat_vec(Rw[11], links[names[11]]["com"])[k] for k in range(3)]
+    l0 = [ow[0][k] + mat_vec(Rw[0], links[names[0]]["com"])[k] for k in range(3)]
+    o = [
+        "// GENERATED by tools/gen_model.py: robot collision primitives at the neutral pose, base at the origin (double).",
+        "#pragma once",
+        "namespace pgm {",
+        "struct NeutralPrim { int type; double c[3]; double a[3]; double r, h; };  // type 0 sphere, 1 cylinder",
+        "constexpr int kNumNeutralPrim = %d;" % len(rows),
+        "static __device__ __constant__ NeutralPrim kNeutralPrims[%d] = {" % len(rows),
+        ",\n".join(rows),
+        "};",
+        "static __device__ __constant__ double kNeutralEE[3] = {%r, %r, %r};     // COM of link 11 (get_ee_position)" % tuple(ee),
+        "static __device__ __constant__ double kNeutralLink0[3] = {%r, %r, %r};  // COM of link 0 (get_link_position(0))" % tuple(l0),
+        "static __device__ __constant__ double kNeutralQ[7] = {%s};" % ", ".join(repr(x) for x in neutral),
+        "}  // namespace pgm",
+    ]
+    with open(path, "w") as f:
+        f.write("\n".join(o) + "\n")
+    print("wrote", path)
+
+
 def main():
     out = [
         "/* GENERATED by tools/gen_model.py -- do not edit. Numbers only (link frames, masses, Bullet-rule",
@@ -237,7 +404,10 @@ def main():
         "} pgo_prim_t;",
         "",
     ]
-    emit_model("PGO_CUSTOM0", os.path.join(REF, "franka_panda_custom_0/panda.urdf"), out)
+    links0, order0 = emit_model("PGO_CUSTOM0", os.path.join(REF, "franka_panda_custom_0/panda.urdf"), out)
+    csrc = os.path.join(os.path.dirname(os.path.dirname(OUT)), "panda_gym_b200", "csrc")
+    emit_cuda(links0, order0, os.path.join(csrc, "pg_model.cuh"))
+    emit_neutral(links0, links0["__root__"], order0, os.path.join(csrc, "pg_neutral.h"))
     emit_model("PGO_STOCK", os.path.join(REF, "franka_panda/panda.urdf"), out)
     out.append("#endif")
     with open(OUT, "w") as f:
