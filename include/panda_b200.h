@@ -169,6 +169,10 @@ int pg_debug_ik(int device, int n, const float* q_dev, const float* target_dev, 
  * Runs `iters` x 8 x 2 flops per thread on `blocks` x 256 threads; *tflops_out = achieved TFLOP/s (CUDA events). */
 int pg_debug_fma_peak(int device, int blocks, int iters, double* tflops_out);
 
+/* launch shape of the step kernel: out[6] = registers/thread, maxThreadsPerBlock, static smem bytes, local bytes,
+ * block size, resident blocks per SM */
+int pg_debug_step_kernel_attrs(int device, int* out);
+
 const char* pg_last_error(void);
 const char* pg_version(void);
 

@@ -10,7 +10,7 @@ c_int, c_double, c_void_p, c_u64, c_i64, c_float, c_u8 = (ctypes.c_int, ctypes.c
                                                           ctypes.c_uint64, ctypes.c_int64, ctypes.c_float, ctypes.c_uint8)
 PG_MAX_OBSTACLES = 8
 LIB_NAME = "libpanda_b200.so"
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+LIB_PATH = os.environ.get("PANDA_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)  # override: tuning variants
 
 
 class Stage(ctypes.Structure):
@@ -82,6 +82,7 @@ SYMBOLS = [
     ("pg_debug_minv", c_int, [c_int, c_int, P, P, P]),
     ("pg_debug_ik", c_int, [c_int, c_int, P, P, P, P, P]),
     ("pg_debug_fma_peak", c_int, [c_int, c_int, c_int, P]),
+    ("pg_debug_step_kernel_attrs", c_int, [c_int, P]),
     ("pg_last_error", ctypes.c_char_p, []),
     ("pg_version", ctypes.c_char_p, []),
 ]

@@ -206,7 +206,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   A(P.rng, 4 * n, true) A(P.episode, n, true)
   A(P.obs, (size_t)max_obs * n, true) A(P.achieved, 3 * n, true) A(P.desired, 3 * n, true) A(P.reward, n, true)
   A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true) A(P.done, n, true) A(P.flags, n, true)
-  A(P.stats, 8, false)
+  A(P.stats, 8, false) A(P.reset_list, n, false) A(P.reset_count, 1, false)
   A(h->d_actions, 7 * n, false)
 #undef A
   // obstacles start where create_obstacle_* puts them: (0.1, 0, 0.1) (reach_ao.py:819, 841)
@@ -259,7 +259,8 @@ int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, vo
 int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   if (!h || !actions_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
-  pg::k_step<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
+  if (h->P.auto_reset) PG_CUDA(cudaMemsetAsync(h->P.reset_count, 0, sizeof(int), (cudaStream_t)stream));
+  pg::k_step<<<(h->P.n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
   h->launches++;
   if (h->P.auto_reset) {
     pg::k_reset<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, nullptr, nullptr, 1, h->first_env);
@@ -424,8 +425,10 @@ int pg_observe(pg_handle h, void* stream) {
 
 int pg_debug_substeps(int device, int n, float* q, float* qd, const float* tgt, const float* f, int n_sub, int velocity_mode, void* stream) {
   if (!q || !qd || !tgt || !f || n <= 0) return fail(PG_ERR_ARG, "bad argument");
+  static const float kForces[7] = {87.f, 87.f, 87.f, 87.f, 12.f, 120.f, 120.f};  // panda.py:63, compiled into the kernels
+  for (int d = 0; d < 7; d++) if (f[d] != kForces[d]) return fail(PG_ERR_UNSUPPORTED, "max_force must equal Panda.joint_forces (panda.py:63)");
   PG_CUDA(cudaSetDevice(device));
-  pg::k_debug_substeps<<<(n + pg::kBlock - 1) / pg::kBlock, pg::kBlock, 0, (cudaStream_t)stream>>>(n, q, qd, tgt, f[0], f[1], f[2], f[3], f[4], f[5], f[6], n_sub, velocity_mode);
+  pg::k_debug_substeps<<<(n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(n, q, qd, tgt, f[0], f[1], f[2], f[3], f[4], f[5], f[6], n_sub, velocity_mode);
   PG_CUDA(cudaGetLastError());
   return PG_OK;
 }
@@ -441,6 +444,18 @@ int pg_debug_ik(int device, int n, const float* q, const float* tgt, const float
   PG_CUDA(cudaSetDevice(device));
   pg::k_debug_ik<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, q, tgt, base[0], base[1], base[2], out);
   PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_debug_step_kernel_attrs(int device, int* out /* [6]: regs, maxThreadsPerBlock, static smem, local bytes, block, blocks/SM */) {
+  if (!out) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(device));
+  cudaFuncAttributes a;
+  PG_CUDA(cudaFuncGetAttributes(&a, pg::k_step));
+  int occ = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pg::k_step, pg::kStepBlock, 0);
+  out[0] = a.numRegs; out[1] = a.maxThreadsPerBlock; out[2] = (int)a.sharedSizeBytes; out[3] = (int)a.localSizeBytes;
+  out[4] = pg::kStepBlock; out[5] = occ;
   return PG_OK;
 }
 

@@ -282,86 +282,152 @@ __device__ __forceinline__ void spd_inverse7(float* A) {
   }
 }
 
-// One stepSimulation().  q, qd updated in place; cq/sq hold cos/sin of the CURRENT q on entry and of the new q
-// on exit.  tgt = POSITION_CONTROL targets (or velocity targets when VELOCITY is true), fmax = max force.
-template <bool VELOCITY>
-__device__ __forceinline__ void substep(float* q, float* qd, float* cq, float* sq, const float* tgt, const float* max_imp) {
-  float tau[7], Mi[28];
-  rnea_bias(cq, sq, qd, tau);
-  crba(cq, sq, Mi);
-  spd_inverse7(Mi);
-  // 1. unconstrained velocity update  qd += dt * M^-1 (-tau_b)
-#pragma unroll
-  for (int i = 0; i < 7; i++) {
-    float acc = 0.f;
-#pragma unroll
-    for (int j = 0; j < 7; j++) acc -= Mi[sym(i, j)] * tau[j];
-    qd[i] = fminf(fmaxf(qd[i] + acc * kDt, -kMaxCoordVel), kMaxCoordVel);
-  }
-  // 2. rows.  Motor row d: unit Jacobian on dof d.  Limit row d (at most one side active): sign sg[d].
-  float rhs[7], dinv[7], app[7], dv[7];
-  float lrhs[7], lsg[7], lapp[7];
-  bool any_limit = false;
+// Generic projected Gauss-Seidel (cold path): joint-limit rows present and / or non-standard motor impulse
+// limits.  Bullet order: rows = [limits (dof order), motors (dof order)]; even iterations sweep backward, odd
+// forward; stop when max |residual| <= sqrt(1e-7).  Arrays live in local memory; this is rare.
+__device__ __noinline__ void pgs_generic(const float* Mi, const float* q, const float* qd, const float* rhs, const float* dinv,
+                                         const float* max_imp, float* dv_out) {
   const float lo[7] = {pgm::Link<1>::lo, pgm::Link<2>::lo, pgm::Link<3>::lo, pgm::Link<4>::lo, pgm::Link<5>::lo, pgm::Link<6>::lo, pgm::Link<7>::lo};
   const float hi[7] = {pgm::Link<1>::hi, pgm::Link<2>::hi, pgm::Link<3>::hi, pgm::Link<4>::hi, pgm::Link<5>::hi, pgm::Link<6>::hi, pgm::Link<7>::hi};
-#pragma unroll
+  float app[7], dv[7], lrhs[7], lsg[7], lapp[7];
   for (int d = 0; d < 7; d++) {
-    float denom = Mi[sym(d, d)];
-    dinv[d] = denom > 1.1920929e-07f ? 1.0f / denom : 0.f;
-    float want = VELOCITY ? tgt[d] : 50.0f * (tgt[d] - q[d]);  // kp (q* - q)/dt + v + kd (0 - v): kp .1, kd 1, dt 1/500
-    rhs[d] = (want - qd[d]) * dinv[d];
-    app[d] = 0.f; dv[d] = 0.f;
-    float pl = q[d] - lo[d], pu = hi[d] - q[d];
-    lsg[d] = 0.f; lrhs[d] = 0.f; lapp[d] = 0.f;
-    if (pl <= 0.f) { lsg[d] = 1.f; lrhs[d] = (-pl * kLimitErp / kDt - qd[d]) * dinv[d]; any_limit = true; }
-    else if (pu <= 0.f) { lsg[d] = -1.f; lrhs[d] = (-pu * kLimitErp / kDt + qd[d]) * dinv[d]; any_limit = true; }
+    app[d] = 0.f; dv[d] = 0.f; lsg[d] = 0.f; lrhs[d] = 0.f; lapp[d] = 0.f;
+    float pl = q[d] - lo[d], pu = hi[d] - q[d];  // btMultiBodyJointLimitConstraint: row only when at / over the limit
+    if (pl <= 0.f) { lsg[d] = 1.f; lrhs[d] = (-pl * kLimitErp / kDt - qd[d]) * dinv[d]; }
+    else if (pu <= 0.f) { lsg[d] = -1.f; lrhs[d] = (-pu * kLimitErp / kDt + qd[d]) * dinv[d]; }
   }
-  // 3. projected Gauss-Seidel, Bullet order: rows = [limits (dof order), motors (dof order)];
-  //    even iterations sweep backward, odd forward; stop when max residual^2 <= 1e-7
+  for (int it = 0; it < kSolverIters; it++) {
+    float res = 0.f;
+    const bool fwd = (it & 1) != 0;
+    for (int r = 0; r < 14; r++) {
+      int row = fwd ? r : 13 - r;       // rows 0..6 = limits, 7..13 = motors
+      int d = row < 7 ? row : row - 7;
+      float delta, sd;
+      if (row < 7) {
+        if (lsg[d] == 0.f) continue;
+        delta = lrhs[d] - lsg[d] * dv[d] * dinv[d];
+        float sum = lapp[d] + delta;
+        if (sum < 0.f) { delta = -lapp[d]; lapp[d] = 0.f; }
+        else if (sum > kLimitMaxImpulse) { delta = kLimitMaxImpulse - lapp[d]; lapp[d] = kLimitMaxImpulse; }
+        else lapp[d] = sum;
+        sd = lsg[d] * delta;
+      } else {
+        if (max_imp[d] == 0.f) continue;
+        float t = fmaf(-dv[d], dinv[d], app[d] + rhs[d]);
+        float cl = fminf(fmaxf(t, -max_imp[d]), max_imp[d]);
+        delta = cl - app[d]; app[d] = cl; sd = delta;
+      }
+      for (int i = 0; i < 7; i++) dv[i] = fmaf(Mi[sym(i, d)], sd, dv[i]);
+      res = fmaxf(res, fabsf(delta * Mi[sym(d, d)]));
+    }
+    if (res <= 3.1622777e-4f) break;
+  }
+  for (int d = 0; d < 7; d++) dv_out[d] = dv[d];
+}
+
+// One stepSimulation().  q, qd updated in place; cq/sq hold cos/sin of the CURRENT q on entry and of the new q
+// on exit (incrementally rotated).  tgt = POSITION_CONTROL targets (velocity targets when `velocity`), read
+// through tgt[d * tgt_stride] (shared memory in the step kernel); unit_imp: every motor's impulse limit is 1
+// (load-time default motors, "pcc" control) instead of panda.py:63 joint_forces * dt.
+//
+// SYNC: every thread of the block calls this (inactive ones with active = false) and the block re-converges at
+// a barrier after each phase.  The step kernel is ~40k SASS instructions of mostly straight-line code, far beyond
+// the 32 KB L1.5 instruction cache: un-synchronised warps each stream the code from L2 on their own and the
+// kernel becomes instruction-fetch bound (ncu: 43 % stall_no_inst).  Keeping the warps of an SM within one cache
+// window of each other turns those fetches into hits.
+__device__ __forceinline__ constexpr float motor_imp(int d) { return (d < 4 ? 87.0f : (d == 4 ? 12.0f : 120.0f)) * kDt; }  // panda.py:63
+
+template <bool SYNC>
+__device__ __forceinline__ void substep(bool active, bool velocity, bool unit_imp, float* q, float* qd, float* cq, float* sq,
+                                        const float* tgt, int stride) {
+  // q and tgt are touched twice per substep: the step kernel keeps them in shared memory (element d at [d * stride])
+  float tau[7], Mi[28];
+  float rhs[7], dinv[7], dv[7];
+  if (active) rnea_bias(cq, sq, qd, tau);
+  if (SYNC) __syncthreads();
+  if (active) crba(cq, sq, Mi);
+  if (SYNC) __syncthreads();
+  bool slow = unit_imp;
+  if (active) {
+    spd_inverse7(Mi);
+    // 1. unconstrained velocity update  qd += dt * M^-1 (-tau_b)
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 7; j++) acc -= Mi[sym(i, j)] * tau[j];
+      qd[i] = fminf(fmaxf(qd[i] + acc * kDt, -kMaxCoordVel), kMaxCoordVel);
+    }
+    // 2. motor rows: unit Jacobian on dof d, rhs = (v* - v) / (M^-1)_dd
+    const float lo[7] = {pgm::Link<1>::lo, pgm::Link<2>::lo, pgm::Link<3>::lo, pgm::Link<4>::lo, pgm::Link<5>::lo, pgm::Link<6>::lo, pgm::Link<7>::lo};
+    const float hi[7] = {pgm::Link<1>::hi, pgm::Link<2>::hi, pgm::Link<3>::hi, pgm::Link<4>::hi, pgm::Link<5>::hi, pgm::Link<6>::hi, pgm::Link<7>::hi};
+#pragma unroll
+    for (int d = 0; d < 7; d++) {
+      float denom = Mi[sym(d, d)];
+      dinv[d] = denom > 1.1920929e-07f ? 1.0f / denom : 0.f;
+      float t = tgt[d * stride];
+      float qv = q[d * stride];
+      float want = velocity ? t : 50.0f * (t - qv);  // kp (q* - q)/dt + v + kd (0 - v): kp .1, kd 1, dt 1/500
+      rhs[d] = (want - qd[d]) * dinv[d];
+      dv[d] = 0.f;
+      slow |= (qv - lo[d] <= 0.f) || (hi[d] - qv <= 0.f);
+    }
+  }
+  if (SYNC) __syncthreads();
+  if (active) {
+    // 3. projected Gauss-Seidel exactly as btMultiBodyConstraintSolver: 50 sweeps, even backward / odd forward,
+    //    residual early-out.  A lane whose residual test fired stays masked off by divergence; the warp leaves
+    //    when all lanes are done.
+    if (slow) {
+      float mi[7], ql[7];
+#pragma unroll
+      for (int d = 0; d < 7; d++) { mi[d] = unit_imp ? 1.0f : motor_imp(d); ql[d] = q[d * stride]; }
+      pgs_generic(Mi, ql, qd, rhs, dinv, mi, dv);
+    } else {
+      float app[7];
+#pragma unroll
+      for (int d = 0; d < 7; d++) app[d] = 0.f;
 #define PG_MOTOR_ROW(d)                                                     \
-  if (max_imp[d] != 0.f) {                                                  \
-    float delta = rhs[d] - dv[d] * dinv[d];                                 \
-    float cl = fminf(fmaxf(app[d] + delta, -max_imp[d]), max_imp[d]);       \
-    delta = live ? cl - app[d] : 0.f;                                       \
-    app[d] += delta;                                                        \
-    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] += Mi[sym(i, d)] * delta; \
-    float res = delta * Mi[sym(d, d)];                                      \
-    lsq = fmaxf(lsq, res * res);                                            \
+  {                                                                         \
+    float t = fmaf(-dv[d], dinv[d], app[d] + rhs[d]);                       \
+    float cl = fminf(fmaxf(t, -motor_imp(d)), motor_imp(d));                \
+    float delta = cl - app[d];                                              \
+    app[d] = cl;                                                            \
+    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] = fmaf(Mi[sym(i, d)], delta, dv[i]); \
+    res = fmaxf(res, fabsf(delta * Mi[sym(d, d)]));                         \
   }
-#define PG_LIMIT_ROW(d)                                                     \
-  if (lsg[d] != 0.f && live) {                                              \
-    float delta = lrhs[d] - lsg[d] * dv[d] * dinv[d];                       \
-    float sum = lapp[d] + delta;                                            \
-    if (sum < 0.f) { delta = -lapp[d]; lapp[d] = 0.f; }                     \
-    else if (sum > kLimitMaxImpulse) { delta = kLimitMaxImpulse - lapp[d]; lapp[d] = kLimitMaxImpulse; } \
-    else lapp[d] = sum;                                                     \
-    float sd = lsg[d] * delta;                                              \
-    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] += Mi[sym(i, d)] * sd; \
-    float res = delta * Mi[sym(d, d)];                                      \
-    lsq = fmaxf(lsq, res * res);                                            \
-  }
-  bool live = true;
-  for (int it = 0; it < kSolverIters; it += 2) {
-    float lsq = 0.f;  // even iteration: backward sweep (motors 6..0, then limits 6..0)
-    PG_MOTOR_ROW(6) PG_MOTOR_ROW(5) PG_MOTOR_ROW(4) PG_MOTOR_ROW(3) PG_MOTOR_ROW(2) PG_MOTOR_ROW(1) PG_MOTOR_ROW(0)
-    if (any_limit) { PG_LIMIT_ROW(6) PG_LIMIT_ROW(5) PG_LIMIT_ROW(4) PG_LIMIT_ROW(3) PG_LIMIT_ROW(2) PG_LIMIT_ROW(1) PG_LIMIT_ROW(0) }
-    if (lsq <= kResidualThr) live = false;
-    if (!__any_sync(__activemask(), live)) break;
-    lsq = 0.f;        // odd iteration: forward sweep (limits 0..6, then motors 0..6)
-    if (any_limit) { PG_LIMIT_ROW(0) PG_LIMIT_ROW(1) PG_LIMIT_ROW(2) PG_LIMIT_ROW(3) PG_LIMIT_ROW(4) PG_LIMIT_ROW(5) PG_LIMIT_ROW(6) }
-    PG_MOTOR_ROW(0) PG_MOTOR_ROW(1) PG_MOTOR_ROW(2) PG_MOTOR_ROW(3) PG_MOTOR_ROW(4) PG_MOTOR_ROW(5) PG_MOTOR_ROW(6)
-    if (lsq <= kResidualThr) live = false;
-    if (!__any_sync(__activemask(), live)) break;
-  }
+      const float kResAbs = 3.1622777e-4f;  // sqrt(1e-7): compare |residual| instead of residual^2
+      bool live = true;
+      for (int it = 0; it < kSolverIters; it += 2) {
+        if (live) {  // even iteration: backward sweep
+          float res = 0.f;
+          PG_MOTOR_ROW(6) PG_MOTOR_ROW(5) PG_MOTOR_ROW(4) PG_MOTOR_ROW(3) PG_MOTOR_ROW(2) PG_MOTOR_ROW(1) PG_MOTOR_ROW(0)
+          if (res <= kResAbs) live = false;
+        }
+        if (live) {  // odd iteration: forward sweep
+          float res = 0.f;
+          PG_MOTOR_ROW(0) PG_MOTOR_ROW(1) PG_MOTOR_ROW(2) PG_MOTOR_ROW(3) PG_MOTOR_ROW(4) PG_MOTOR_ROW(5) PG_MOTOR_ROW(6)
+          if (res <= kResAbs) live = false;
+        }
+        if (!__any_sync(__activemask(), live)) break;
+      }
 #undef PG_MOTOR_ROW
-#undef PG_LIMIT_ROW
-  // 4. apply, clamp, integrate
+    }
+    // 4. apply, clamp, integrate
 #pragma unroll
-  for (int d = 0; d < 7; d++) {
-    qd[d] = fminf(fmaxf(qd[d] + dv[d], -kMaxCoordVel), kMaxCoordVel);
-    q[d] += qd[d] * kDt;
-    sincosf(q[d], &sq[d], &cq[d]);
+    for (int d = 0; d < 7; d++) {
+      qd[d] = fminf(fmaxf(qd[d] + dv[d], -kMaxCoordVel), kMaxCoordVel);
+      float dq = qd[d] * kDt;  // |dq| <= 0.2 (velocity clamp): rotate (cos, sin) by dq with a 5th-order series,
+      q[d * stride] += dq;     // error < 1e-7; the caller re-evaluates sincosf(q) at every env step
+      float d2 = dq * dq;
+      float cd = fmaf(d2, fmaf(d2, 1.0f / 24.0f, -0.5f), 1.0f);
+      float sd = dq * fmaf(d2, fmaf(d2, 1.0f / 120.0f, -1.0f / 6.0f), 1.0f);
+      float c0 = cq[d], s0 = sq[d];
+      cq[d] = c0 * cd - s0 * sd;
+      sq[d] = s0 * cd + c0 * sd;
+    }
   }
+  if (SYNC) __syncthreads();
 }
 
 }  // namespace pg

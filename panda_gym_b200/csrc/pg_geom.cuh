@@ -211,6 +211,17 @@ template <typename T> __host__ __device__ __forceinline__ ClosestT<T> cyl_box(V3
   GjkIn<T> g; g.c = c; g.a = a; g.b = b; g.e = e; g.r = r; g.h = h;
   V3T<T> qa, qb;
   T d = gjk_cyl_box(g, &qa, &qb);
+  if (sizeof(T) == 4 && d > T(0)) {
+    // GJK's stop rule bounds the DISTANCE error by eps but the closest-point / direction error only by
+    // sqrt(eps) (~1e-3 in fp32): polish with alternating exact projections (box clamp <-> solid cylinder).
+#pragma unroll
+    for (int it = 0; it < 3; it++) {
+      V3T<T> rel = qa - b;
+      qb = b + v3t<T>(tmin<T>(tmax<T>(rel.x, -e.x), e.x), tmin<T>(tmax<T>(rel.y, -e.y), e.y), tmin<T>(tmax<T>(rel.z, -e.z), e.z));
+      T dd = point_cylinder<T>(qb, c, a, r, h, qa);
+      d = dd > T(0) ? dd : T(0);
+    }
+  }
   V3T<T> v = qb - qa;
   T L = tnorm(v);
   V3T<T> n = L > T(1e-30) ? (T(1.0) / L) * v : v3t<T>(T(0), T(0), T(0));

@@ -9,6 +9,26 @@
 namespace pg {
 
 constexpr int kBlock = 128;
+// k_step launch shape.  BASELINE configs[1] runs 65 536 environments per GPU = 443 threads per SM on 148 SMs: the
+// kernel must keep >= 14 warps resident per SM or a second, nearly empty wave doubles its latency-bound runtime.
+// Default: 448 threads (14 warps) x 128 registers = one block per SM, 148 x 448 = 66 304 >= 65 536 -> a single
+// wave.  (Each SM sub-partition owns 16 K registers: 4 resident warps per sub-partition cap a thread at 128.)
+#ifndef PG_STEP_BLOCK
+#define PG_STEP_BLOCK 448
+#endif
+#ifndef PG_STEP_MINB
+#define PG_STEP_MINB 1
+#endif
+constexpr int kStepBlock = PG_STEP_BLOCK;
+#ifdef PG_STEP_MAXREG
+#define PG_STEP_BOUNDS __maxnreg__(PG_STEP_MAXREG)
+#else
+#define PG_STEP_BOUNDS __launch_bounds__(PG_STEP_BLOCK, PG_STEP_MINB)
+#endif
+#ifndef PG_STEP_SYNC
+#define PG_STEP_SYNC 1
+#endif
+constexpr bool kStepSync = PG_STEP_SYNC != 0;  // block barriers between the phases of a substep (I-cache locality)
 
 struct StageDev {  // device copy of pg_stage (scenario parameter block)
   int goal_sampler;
@@ -48,6 +68,7 @@ struct Params {
   float *obs, *achieved, *desired, *reward, *term_obs, *term_achieved;
   uint8_t *done, *flags;
   double* stats;                 // [8]
+  int *reset_list, *reset_count;   // compacted indices of environments that finished in the last step
 };
 
 // panda.py:63 joint_forces
@@ -179,7 +200,7 @@ __device__ __forceinline__ void observe(const Params& P, int e, const float* q, 
       for (int k = 0; k < 27; k++) o[off + k] = 1.0f;
     } else {
       float dl[9]; V3 ul[9];
-      scene_pass<true>(P.scene, P.obs_pos, n, e, base, cq, sq, dl, ul);
+      scene_pass<true, false>(true, P.scene, P.obs_pos, n, e, base, cq, sq, dl, ul);
       float mn = dl[0];
 #pragma unroll
       for (int i = 0; i < 9; i++) { P.d_link[(size_t)i * n + e] = dl[i]; mn = fminf(mn, dl[i]); }
@@ -325,11 +346,16 @@ __device__ __forceinline__ void ik_dls(V3 base, const float* q0, V3 target, floa
 // RobotTaskEnv.step (core.py:352-368): Panda.set_action (panda.py:120-172) -> sim.step()
 // (pybullet.py:68-71 / reach_ao.py:182-188) -> _get_obs -> is_success / is_truncated / compute_reward,
 // then gymnasium TimeLimit and Monitor bookkeeping.
-__global__ void __launch_bounds__(kBlock, 3) k_step(const Params P, const float* __restrict__ actions) {
+__global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ actions) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = P.n;
-  if (e >= n) return;
-  float q[7], qd[7], a[7], tgt[7], mimp[7], cq[7], sq[7], q_fk[7];
+  const bool valid = e < n;  // every thread of the block stays for the barriers of the substep loop
+  __shared__ float s_tgt[7 * kStepBlock], s_q[7 * kStepBlock];  // touched twice per substep: kept out of the register file
+  float* tgt = s_tgt + threadIdx.x;
+  float* qs = s_q + threadIdx.x;
+  float q[7], qd[7], a[7], cq[7], sq[7], q_fk[7];
+  bool velocity_mode = false, unit_imp = false;
+  if (valid) {
 #pragma unroll
   for (int d = 0; d < 7; d++) { q[d] = P.q[(size_t)d * n + e]; qd[d] = P.qd[(size_t)d * n + e]; a[d] = 0.f; }
   // --- set_action: limiter
@@ -348,25 +374,25 @@ __global__ void __launch_bounds__(kBlock, 3) k_step(const Params P, const float*
   for (int k = 0; k < 7; k++) { P.prev[(size_t)k * n + e] = P.recent[(size_t)k * n + e]; P.recent[(size_t)k * n + e] = a[k]; }
   P.have_prev[e] = P.have_recent[e]; P.have_recent[e] = 1;
   // --- targets
-  bool velocity_mode = false;
   if (P.control == 1) {
     // ee_displacement_to_target_arm_angles (panda.py:226-246): uses the CACHED end-effector position (last observation)
     const float* lo = P.achieved + (size_t)e * 3;
     V3 t = v3(lo[0] + __fmul_rn(a[0], 0.05f), lo[1] + __fmul_rn(a[1], 0.05f), fmaxf(0.f, lo[2] + __fmul_rn(a[2], 0.05f)));
-    ik_dls(v3(P.base[0], P.base[1], P.base[2]), q, t, tgt);
+    float tq[7];
+    ik_dls(v3(P.base[0], P.base[1], P.base[2]), q, t, tq);
+#pragma unroll
+    for (int d = 0; d < 7; d++) tgt[d * kStepBlock] = tq[d];
   } else {
 #pragma unroll
-    for (int d = 0; d < 7; d++) tgt[d] = q[d] + __fmul_rn(a[d], 0.05f);  // panda.py:257-261
+    for (int d = 0; d < 7; d++) tgt[d * kStepBlock] = q[d] + __fmul_rn(a[d], 0.05f);  // panda.py:257-261
   }
-#pragma unroll
-  for (int d = 0; d < 7; d++) mimp[d] = max_force(d) * kDt;
   if (P.control == 2) { velocity_mode = true;
 #pragma unroll
-    for (int d = 0; d < 7; d++) tgt[d] = a[d]; }
+    for (int d = 0; d < 7; d++) tgt[d * kStepBlock] = a[d]; }
   if (P.control == 3) {  // teleport (resetJointState), motors stay at their load-time default: v* = 0, impulse 1
-    velocity_mode = true;
+    velocity_mode = true; unit_imp = true;
 #pragma unroll
-    for (int d = 0; d < 7; d++) { q[d] = tgt[d]; qd[d] = 0.f; tgt[d] = 0.f; mimp[d] = 1.0f; }
+    for (int d = 0; d < 7; d++) { q[d] = tgt[d * kStepBlock]; qd[d] = 0.f; tgt[d * kStepBlock] = 0.f; }
   }
   // --- joint velocity / acceleration / jerk bookkeeping (panda.py:167-172), sampled before the sim step
 #pragma unroll
@@ -375,20 +401,24 @@ __global__ void __launch_bounds__(kBlock, 3) k_step(const Params P, const float*
     float ca = pv - qd[d];
     P.cur_vel[(size_t)d * n + e] = qd[d]; P.cur_acc[(size_t)d * n + e] = ca; P.jerk[(size_t)d * n + e] = fabsf(pa - ca);
   }
-  // --- sim.step(): n_substeps x stepSimulation, collision check after each (ReachAO)
 #pragma unroll
-  for (int d = 0; d < 7; d++) { sincosf(q[d], &sq[d], &cq[d]); q_fk[d] = q[d]; }
-  bool collided = P.task == 1 ? (P.collided[e] != 0) : false;
+  for (int d = 0; d < 7; d++) { sincosf(q[d], &sq[d], &cq[d]); qs[d * kStepBlock] = q[d]; }
+  }
+  // --- sim.step(): n_substeps x stepSimulation, collision check after each (ReachAO); a collided environment
+  //     stops simulating (reach_ao.py:186-188) but its thread keeps meeting the block barriers
+  bool collided = false, active = valid;
   const V3 base = v3(P.base[0], P.base[1], P.base[2]);
   for (int k = 0; k < P.n_substeps; k++) {
-#pragma unroll
-    for (int d = 0; d < 7; d++) q_fk[d] = q[d];
-    if (velocity_mode) substep<true>(q, qd, cq, sq, tgt, mimp); else substep<false>(q, qd, cq, sq, tgt, mimp);
+    substep<kStepSync>(active, velocity_mode, unit_imp, qs, qd, cq, sq, tgt, kStepBlock);
     if (P.task == 1) {
-      collided = scene_pass<false>(P.scene, P.obs_pos, n, e, base, cq, sq, nullptr, nullptr);
-      if (collided) break;
+      bool hit = scene_pass<false, kStepSync>(active, P.scene, P.obs_pos, n, e, base, cq, sq, nullptr, nullptr);
+      if (active && hit) { collided = true; active = false; }
     }
   }
+  if (!valid) return;
+  // joint angles behind PyBullet's cached link transforms = q at the start of the last simulated substep
+#pragma unroll
+  for (int d = 0; d < 7; d++) { q[d] = qs[d * kStepBlock]; q_fk[d] = q[d] - qd[d] * kDt; sincosf(q[d], &sq[d], &cq[d]); }
 #pragma unroll
   for (int d = 0; d < 7; d++) { P.q[(size_t)d * n + e] = q[d]; P.qd[(size_t)d * n + e] = qd[d]; }
   if (P.task == 1) P.collided[e] = collided;
@@ -416,6 +446,7 @@ __global__ void __launch_bounds__(kBlock, 3) k_step(const Params P, const float*
     for (int k = 0; k < P.obs_dim; k++) t[k] = o[k];
     P.term_achieved[(size_t)e * 3] = ag[0]; P.term_achieved[(size_t)e * 3 + 1] = ag[1]; P.term_achieved[(size_t)e * 3 + 2] = ag[2];
     P.need_reset[e] = 1;
+    if (P.auto_reset) P.reset_list[atomicAdd(P.reset_count, 1)] = e;
     atomicAdd(&P.stats[0], 1.0);
     if (succ) atomicAdd(&P.stats[1], 1.0);
     if (truncated) atomicAdd(&P.stats[2], 1.0);
@@ -508,11 +539,13 @@ __device__ inline Body obstacle_body(const Params& P, int j, int e) {
 // ReachAO.reset (reach_ao.py:965-1033) with its rejection-sampling helpers (:1101-1181)
 __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
                                                   int use_need_reset, uint64_t first_env) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = P.n;
   if (e >= n) return;
-  if (use_need_reset) { if (!P.need_reset[e]) return; }
-  else if (mask && !mask[e]) return;
+  if (use_need_reset) {  // auto-reset: only the (few) environments k_step appended to the compact list
+    if (e >= *P.reset_count) return;
+    e = P.reset_list[e];
+  } else if (mask && !mask[e]) return;
   P.need_reset[e] = 0;
   uint32_t ep = P.episode[e];
   P.episode[e] = ep + 1;
@@ -604,7 +637,7 @@ __global__ void __launch_bounds__(kBlock) k_observe(const Params P) {
   for (int d = 0; d < 7; d++) { q[d] = P.q[(size_t)d * P.n + e]; qd[d] = P.qd[(size_t)d * P.n + e]; sincosf(q[d], &sq[d], &cq[d]); }
   observe(P, e, q, qd, q, cq, sq, ag);
   if (P.task == 1) {
-    bool hit = scene_pass<false>(P.scene, P.obs_pos, P.n, e, v3(P.base[0], P.base[1], P.base[2]), cq, sq, nullptr, nullptr);
+    bool hit = scene_pass<false, false>(true, P.scene, P.obs_pos, P.n, e, v3(P.base[0], P.base[1], P.base[2]), cq, sq, nullptr, nullptr);
     P.flags[e] = (uint8_t)((P.flags[e] & ~4) | (hit ? 4 : 0));
   }
 }
@@ -624,17 +657,29 @@ __global__ void k_random_actions(float* __restrict__ out, int64_t m, uint64_t se
 }
 
 // ------------------------------------------------------------------------------------------------ debug / parity kernels
-__global__ void __launch_bounds__(kBlock, 3) k_debug_substeps(int n, float* q_io, float* qd_io, const float* tgt_in, float f0, float f1, float f2,
+__global__ void PG_STEP_BOUNDS k_debug_substeps(int n, float* q_io, float* qd_io, const float* tgt_in, float f0, float f1, float f2,
                                                            float f3, float f4, float f5, float f6, int nsub, int velocity) {
   int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n) return;
-  float q[7], qd[7], t[7], c[7], s[7];
-  float mi[7] = {f0 * kDt, f1 * kDt, f2 * kDt, f3 * kDt, f4 * kDt, f5 * kDt, f6 * kDt};
+  const bool valid = e < n;
+  __shared__ float s_tgt[7 * kStepBlock], s_q[7 * kStepBlock];
+  float* t = s_tgt + threadIdx.x;
+  float* q = s_q + threadIdx.x;  // element d at q[d * kStepBlock]
+  float qd[7], c[7], s[7];
+  if (valid) {
 #pragma unroll
-  for (int d = 0; d < 7; d++) { q[d] = q_io[(size_t)d * n + e]; qd[d] = qd_io[(size_t)d * n + e]; t[d] = tgt_in[(size_t)d * n + e]; sincosf(q[d], &s[d], &c[d]); }
-  for (int k = 0; k < nsub; k++) { if (velocity) substep<true>(q, qd, c, s, t, mi); else substep<false>(q, qd, c, s, t, mi); }
+    for (int d = 0; d < 7; d++) { q[d * kStepBlock] = q_io[(size_t)d * n + e]; qd[d] = qd_io[(size_t)d * n + e]; t[d * kStepBlock] = tgt_in[(size_t)d * n + e]; sincosf(q[d * kStepBlock], &s[d], &c[d]); }
+  }
+  for (int k = 0; k < nsub; k++) {
+    // parity kernel: re-evaluate cos/sin exactly every 20 substeps like the env step does
+    if (valid && k > 0 && (k % 20) == 0) {
 #pragma unroll
-  for (int d = 0; d < 7; d++) { q_io[(size_t)d * n + e] = q[d]; qd_io[(size_t)d * n + e] = qd[d]; }
+      for (int d = 0; d < 7; d++) sincosf(q[d * kStepBlock], &s[d], &c[d]);
+    }
+    substep<kStepSync>(valid, velocity != 0, false, q, qd, c, s, t, kStepBlock);
+  }
+  if (!valid) return;
+#pragma unroll
+  for (int d = 0; d < 7; d++) { q_io[(size_t)d * n + e] = q[d * kStepBlock]; qd_io[(size_t)d * n + e] = qd[d]; }
 }
 __global__ void k_debug_minv(int n, const float* q_in, float* out) {
   int e = blockIdx.x * blockDim.x + threadIdx.x;

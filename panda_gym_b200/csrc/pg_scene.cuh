@@ -105,22 +105,35 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __
 }
 
 // all 9 collision links at joint cosines/sines (cq, sq).  FULL fills d_link[9], u_link[9].
-template <bool FULL>
-__device__ __forceinline__ bool scene_pass(const SceneParams& P, const double* __restrict__ obs_pos, int n, int e, V3 base, const float* cq,
-                                           const float* sq, float* d_link, V3* u_link) {
+// SYNC: called by every thread of the block (see substep) with block barriers between groups of links.
+template <bool FULL, bool SYNC>
+__device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, const double* __restrict__ obs_pos, int n, int e, V3 base,
+                                           const float* cq, const float* sq, float* d_link, V3* u_link) {
   bool hit = false;
   float d; V3 u;
   Frame F = base_frame(base);
-  F = frame_step<1>(F, cq[0], sq[0]); slot_eval<0, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[0] = d; u_link[0] = u; }
-  F = frame_step<2>(F, cq[1], sq[1]); slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[1] = d; u_link[1] = u; }
-  F = frame_step<3>(F, cq[2], sq[2]); slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[2] = d; u_link[2] = u; }
-  F = frame_step<4>(F, cq[3], sq[3]); slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[3] = d; u_link[3] = u; }
-  F = frame_step<5>(F, cq[4], sq[4]); slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[4] = d; u_link[4] = u; }
-  F = frame_step<6>(F, cq[5], sq[5]); slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[5] = d; u_link[5] = u; }
-  F = frame_step<7>(F, cq[6], sq[6]);
-  slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[6] = d; u_link[6] = u; }
-  slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[7] = d; u_link[7] = u; }
-  slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[8] = d; u_link[8] = u; }
+  if (active) {
+    F = frame_step<1>(F, cq[0], sq[0]); slot_eval<0, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[0] = d; u_link[0] = u; }
+    F = frame_step<2>(F, cq[1], sq[1]); slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[1] = d; u_link[1] = u; }
+    F = frame_step<3>(F, cq[2], sq[2]); slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[2] = d; u_link[2] = u; }
+  }
+  if (SYNC && FULL) __syncthreads();
+  if (active) {
+    F = frame_step<4>(F, cq[3], sq[3]); slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[3] = d; u_link[3] = u; }
+    F = frame_step<5>(F, cq[4], sq[4]); slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[4] = d; u_link[4] = u; }
+  }
+  if (SYNC && FULL) __syncthreads();
+  if (active) {
+    F = frame_step<6>(F, cq[5], sq[5]); slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[5] = d; u_link[5] = u; }
+    F = frame_step<7>(F, cq[6], sq[6]);
+    slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[6] = d; u_link[6] = u; }
+  }
+  if (SYNC && FULL) __syncthreads();
+  if (active) {
+    slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[7] = d; u_link[7] = u; }
+    slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[8] = d; u_link[8] = u; }
+  }
+  if (SYNC) __syncthreads();
   return hit;
 }
 
