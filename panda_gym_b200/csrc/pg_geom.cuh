@@ -149,12 +149,12 @@ template <typename T> __host__ __device__ __noinline__ T gjk_cyl_box(const GjkIn
   int n = 0;
   V3T<T> v = g.c - g.b;
   if (dot(v, v) < (sizeof(T) == 8 ? T(1e-24) : T(1e-12))) v = v3t<T>(T(1), T(0), T(0));
-  for (int it = 0; it < (sizeof(T) == 8 ? 100 : 32); it++) {
+  for (int it = 0; it < (sizeof(T) == 8 ? 100 : 20); it++) {
     V3T<T> sa, sb;
     gjk_support(g, v3t<T>(-v.x, -v.y, -v.z), sa, sb);
     V3T<T> w = sa - sb;
     T vv = dot(v, v);
-    if (n > 0 && vv - dot(v, w) <= (sizeof(T) == 8 ? T(1e-14) : T(1e-6)) * vv + (sizeof(T) == 8 ? T(1e-22) : T(1e-12))) break;
+    if (n > 0 && vv - dot(v, w) <= (sizeof(T) == 8 ? T(1e-14) : T(1e-5)) * vv + (sizeof(T) == 8 ? T(1e-22) : T(1e-12))) break;
     W[n] = w; A[n] = sa; B[n] = sb; n++;
     if (n == 1) { lam[0] = 1; }
     else if (n == 2) {
@@ -215,7 +215,7 @@ template <typename T> __host__ __device__ __forceinline__ ClosestT<T> cyl_box(V3
     // GJK's stop rule bounds the DISTANCE error by eps but the closest-point / direction error only by
     // sqrt(eps) (~1e-3 in fp32): polish with alternating exact projections (box clamp <-> solid cylinder).
 #pragma unroll
-    for (int it = 0; it < 3; it++) {
+    for (int it = 0; it < 4; it++) {
       V3T<T> rel = qa - b;
       qb = b + v3t<T>(tmin<T>(tmax<T>(rel.x, -e.x), e.x), tmin<T>(tmax<T>(rel.y, -e.y), e.y), tmin<T>(tmax<T>(rel.z, -e.z), e.z));
       T dd = point_cylinder<T>(qb, c, a, r, h, qa);

@@ -462,7 +462,8 @@ struct Body { int type; double px, py, pz, sx, sy, sz; };  // sphere (sx = r) or
 __device__ inline double box_margin_d(double sx, double sy, double sz) { double m = fmin(sx, fmin(sy, sz)); return fmin(0.04, 0.1 * m); }
 
 // min distance robot (all 36 primitives at the neutral pose, base offset) vs body: body-level getClosestPoints
-__device__ __noinline__ double robot_body_distance(const Params& P, const Body& b) {
+// cutoff: pairs whose analytic lower bound exceeds it are skipped (the caller only compares the result to it)
+__device__ __noinline__ double robot_body_distance(const Params& P, const Body& b, double cutoff) {
   double best = 1e300;
   D3 o = v3t<double>(b.px - P.based[0], b.py - P.based[1], b.pz - P.based[2]);
   double m = b.type == 1 ? box_margin_d(b.sx, b.sy, b.sz) : 0.0;
@@ -474,7 +475,15 @@ __device__ __noinline__ double robot_body_distance(const Params& P, const Body& 
     if (np.type == 0) d = b.type == 0 ? sphere_sphere<double>(c, np.r, o, b.sx).d : sphere_box<double>(c, np.r, o, core, m).d;
     else {
       D3 a = v3t<double>(np.a[0], np.a[1], np.a[2]);
-      d = b.type == 0 ? cyl_sphere<double>(c, a, np.r, np.h, o, b.sx).d : cyl_box<double>(c, a, np.r, np.h, o, core, m).d;
+      if (b.type == 0) d = cyl_sphere<double>(c, a, np.r, np.h, o, b.sx).d;
+      else {
+        // analytic lower bound: cover the cylinder with ns spheres along its axis
+        int ns = np.h <= np.r ? 1 : (np.h <= 2 * np.r ? 2 : (np.h <= 3 * np.r ? 3 : 4));
+        double seg = np.h / ns, cover = sqrt(np.r * np.r + seg * seg) + (double)kHullMargin, lb = 1e300;
+        for (int i = 0; i < ns; i++) lb = fmin(lb, sphere_box<double>(c + (-np.h + (2 * i + 1) * seg) * a, cover, o, core, m).d);
+        if (lb > cutoff || lb >= best) continue;
+        d = cyl_box<double>(c, a, np.r, np.h, o, core, m).d;
+      }
     }
     best = fmin(best, d);
   }
@@ -578,7 +587,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
         bool coll = false;
         if (pass == 1) for (int j = 0; j < st.nobs; j++) coll |= body_body_collision(probe, obstacle_body(P, j, e), margin);
         coll |= body_body_collision(probe, table, margin);
-        if (!coll) coll |= (margin >= robot_body_distance(P, probe));
+        if (!coll) coll |= (margin >= robot_body_distance(P, probe, margin));
         if (!coll) break;
       }
     }
@@ -600,7 +609,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
             probe.px = probe.py = probe.pz = 0.0;  // the probe sphere is moved to the origin and left there
             coll |= !body_body_collision(probe, ob, 1.0);
           }
-          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance(P, ob));
+          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance(P, ob, margin + P.safety_distance));
           if (!coll) break;
         }
       }

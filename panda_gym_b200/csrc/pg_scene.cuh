@@ -43,7 +43,23 @@ __device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obs
   } else {
     V3 a = frame_dir(F, Pm::ax, Pm::ay, Pm::az);
     if (ob.type == 0) k = cyl_sphere<float>(c, a, Pm::r, Pm::h, o, ob.sx);
-    else k = cyl_box<float>(c, a, Pm::r, Pm::h, o, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
+    else {
+      // cylinder-box needs GJK: first bound it from below (analytically) with a cover of the cylinder by NS
+      // spheres along its axis, radius sqrt(r^2 + (h/NS)^2); a pair that cannot beat the running minimum of this
+      // link is skipped
+      V3 core = v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin);
+      constexpr int NS = Pm::h <= Pm::r ? 1 : (Pm::h <= 2.f * Pm::r ? 2 : (Pm::h <= 3.f * Pm::r ? 3 : 4));
+      constexpr float seg = Pm::h / NS;
+      const float cover = sqrtf(Pm::r * Pm::r + seg * seg) + kHullMargin;
+      float lb = 3.0e38f;
+#pragma unroll
+      for (int i = 0; i < NS; i++) {
+        float t = -Pm::h + (2 * i + 1) * seg;
+        lb = fminf(lb, sphere_box<float>(c + t * a, cover, o, core, ob.margin).d);
+      }
+      if (lb >= best) return;
+      k = cyl_box<float>(c, a, Pm::r, Pm::h, o, core, ob.margin);
+    }
   }
   if (k.d < best) { best = k.d; bdir = k.dir; }
 }
@@ -78,7 +94,7 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __
   constexpr int K0 = slot_first(S), N = slot_count(S);
   using P0 = pgm::Prim<K0>;
   constexpr float R = SlotBound<K0, N>::value + 0.002f;
-  float best = 999.0f;  // pyb_utils saturates at max_distance
+  float best = FULL ? 999.0f : 1e-6f;  // FULL: pyb_utils saturates at max_distance; flag-only: just the sign matters
   V3 dir = v3(0, 0, 0);
   V3 ctr = frame_point(F, P0::x, P0::y, P0::z);
   for (int j = 0; j < P.nobs; j++) {
