@@ -181,14 +181,14 @@ def main():
     # ---- e2e: public host API, pinned host actions in, host numpy results out, every step
     host_actions = [a.cpu().numpy() for a in actions[:8]]
     for k in range(3):
-        env.step(host_actions[k % 8])
+        env.step(host_actions[k % len(host_actions)])
     torch.cuda.synchronize()
     Ke = max(10, K // 2)
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
     for k in range(Ke):
-        obs, rew, dones, infos = env.step(host_actions[k % 8])
+        obs, rew, dones, infos = env.step(host_actions[k % len(host_actions)])
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)

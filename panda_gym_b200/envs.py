@@ -1,0 +1,156 @@
+"""Single-environment, gymnasium-shaped front (N = 1 on the GPU) mirroring the reference's env classes.
+
+Reference: ``panda_gym/envs/core.py::RobotTaskEnv`` (:255-414), ``panda_gym/envs/panda_tasks.py`` (PandaReachEnv
+:72-88, PandaReachAOEnv :133-159) and the registration helpers of ``panda_gym/__init__.py`` (:15-91).
+``make(id, **kwargs)`` plays the role of ``gymnasium.make`` including its ``TimeLimit(max_episode_steps)``
+wrapper.  Semantics follow gymnasium: ``reset(seed) -> (obs, info)``, ``step(a) -> (obs, reward, terminated,
+truncated, info)``; no auto-reset.
+"""
+import numpy as np
+import torch
+
+from . import _lib, sim, spaces
+from .config import TrainConfig
+
+_MAX_EPISODE_STEPS = {"PandaReachAO-v3": 50}
+_REGISTERED = {}
+
+
+def register_reach_ao(max_ep_steps):
+    """panda_gym.register_reach_ao (reference __init__.py:15-20)."""
+    _REGISTERED["PandaReachAO-v3"] = dict(cls="ao", max_episode_steps=max_ep_steps, kwargs={})
+
+
+def register_envs(max_ep_steps):
+    """panda_gym.register_envs (reference __init__.py:23-91) for the env ids on the supported hot path."""
+    for reward_type in ("sparse", "dense"):
+        for control_type in ("ee", "joints"):
+            rs = "Dense" if reward_type == "dense" else ""
+            cs = "Joints" if control_type == "joints" else ""
+            _REGISTERED["PandaReach%s%s-v3" % (cs, rs)] = dict(
+                cls="reach", max_episode_steps=max_ep_steps, kwargs=dict(reward_type=reward_type, control_type=control_type))
+    register_reach_ao(max_ep_steps)
+
+
+def make(env_id, **kwargs):
+    if env_id not in _REGISTERED:
+        raise _lib.PandaB200Error("env id %r is not registered (call register_envs / register_reach_ao first, as with the reference)" % env_id)
+    spec = _REGISTERED[env_id]
+    kw = dict(spec["kwargs"])
+    kw.update(kwargs)
+    cls = PandaReachAOEnv if spec["cls"] == "ao" else PandaReachEnv
+    return cls(max_episode_steps=spec["max_episode_steps"], **kw)
+
+
+class _Namespace:
+    pass
+
+
+class RobotTaskEnv:
+    """Shared implementation; subclasses only build the pg_config."""
+
+    metadata = {"render_modes": ["human", "rgb_array"]}
+
+    def _setup(self, cfg, device, terminate_on_success, max_episode_steps):
+        self.batch = sim.PandaBatch(cfg, device=device)
+        self.terminate_on_success = terminate_on_success
+        self.max_episode_steps = max_episode_steps
+        self._goal_set = False
+        self._saved_goal = {}
+        obs, _ = self.reset()
+        self.observation_space = spaces.Dict(dict(
+            observation=spaces.Box(-10.0, 10.0, shape=obs["observation"].shape, dtype=np.float32),
+            desired_goal=spaces.Box(-10.0, 10.0, shape=obs["achieved_goal"].shape, dtype=np.float32),
+            achieved_goal=spaces.Box(-10.0, 10.0, shape=obs["achieved_goal"].shape, dtype=np.float32)))
+        self.action_space = spaces.Box(-1.0, 1.0, shape=(self.batch.act_dim,), dtype=np.float32)
+        # attribute surface callers poke at (evaluation/evaluate.py uses env.task.* / env.robot.*)
+        self.task = _Namespace()
+        self.task.get_goal = self.get_goal
+        self.task.compute_reward = self.compute_reward
+        self.robot = _Namespace()
+        self.robot.get_joint_angles = lambda: self.batch.view("q")[:, 0].cpu().numpy().astype(np.float64)
+        self.robot.get_joint_velocities = lambda: self.batch.view("qd")[:, 0].cpu().numpy().astype(np.float64)
+        self.sim = _Namespace()
+        self.sim.dt = (1.0 / 500) * self.batch.cfg.n_substeps  # PyBullet.dt (pybullet.py:63-66)
+
+    def _obs(self):
+        v = self.batch.view
+        return {"observation": v("observation")[0].cpu().numpy(), "achieved_goal": v("achieved_goal")[0].cpu().numpy(),
+                "desired_goal": v("desired_goal")[0].cpu().numpy()}
+
+    def get_goal(self):
+        if not self._goal_set:
+            raise RuntimeError("No goal yet, call reset() first")  # core.py:236-237
+        return self.batch.view("goal")[:, 0].cpu().numpy().copy()
+
+    def reset(self, seed=None, options=None):
+        if seed is None:  # core.py:302: a fresh generator from OS entropy on every unseeded reset
+            seed = int(np.random.SeedSequence().generate_state(1, dtype=np.uint64)[0] >> 1)
+        seeds = torch.tensor([int(seed)], dtype=torch.int64, device=self.batch.device)
+        self.batch.reset(seeds=seeds)
+        self._goal_set = True
+        flags = int(self.batch.view("flags")[0])
+        return self._obs(), {"is_success": bool(flags & 1)}
+
+    def step(self, action):
+        a = torch.as_tensor(np.asarray(action, dtype=np.float32).reshape(1, -1), device=self.batch.device)
+        self.batch.step(a)
+        flags = int(self.batch.view("flags")[0])
+        reward = float(self.batch.view("reward")[0])
+        is_success = bool(flags & 1)
+        terminated = bool(flags & 2)
+        truncated = bool(flags & 4) or bool(flags & 8)  # task truncation (collision) or TimeLimit
+        info = {"is_success": is_success, "is_truncated": bool(flags & 4)}
+        if flags & 8:
+            info["TimeLimit.truncated"] = True
+        return self._obs(), reward, terminated, truncated, info
+
+    def compute_reward(self, achieved_goal, desired_goal, info=None):
+        ag = np.asarray(achieved_goal, dtype=np.float32)
+        dg = np.asarray(desired_goal, dtype=np.float32)
+        assert ag.shape == dg.shape
+        dev = self.batch.device
+        out = self.batch.compute_reward(torch.from_numpy(np.ascontiguousarray(ag)).to(dev), torch.from_numpy(np.ascontiguousarray(dg)).to(dev), 0)
+        out = out.cpu().numpy().reshape(ag.shape[:-1])
+        return out if out.shape else np.float32(out)
+
+    def save_state(self):
+        return self.batch.save_state()
+
+    def restore_state(self, state_id):
+        self.batch.restore_state(state_id)
+
+    def remove_state(self, state_id):
+        self.batch.remove_state(state_id)
+
+    def render(self, mode="human", **kwargs):
+        # no graphics stack exists on the target machines: rendering is out of scope
+        return None
+
+    def close(self):
+        self.batch.close()
+
+
+class PandaReachAOEnv(RobotTaskEnv):
+    """reference panda_tasks.py:133-159"""
+
+    def __init__(self, render=False, ee_error_threshold=0.05, speed_threshold=0.1, scenario="reachao1", config=None,
+                 max_episode_steps=50, device=0):
+        config = config if config is not None else TrainConfig()
+        cfg = sim.make_config(1, 1, scenario=scenario, config=config, max_episode_steps=max_episode_steps,
+                              ee_error_threshold=ee_error_threshold, speed_threshold=speed_threshold, auto_reset=False)
+        self.config = config
+        self._setup(cfg, device, config.terminate_on_success, max_episode_steps)
+
+
+class PandaReachEnv(RobotTaskEnv):
+    """reference panda_tasks.py:72-88"""
+
+    def __init__(self, render=False, realtime=False, reward_type="sparse", control_type="js", goal_range=0.3, show_goal_space=False,
+                 max_episode_steps=50, device=0):
+        cfg = sim.make_config(0, 1, control_type=control_type, reward_type=reward_type, max_episode_steps=max_episode_steps,
+                              auto_reset=False)
+        if goal_range != 0.3:
+            for k, (lo, hi) in enumerate(((-goal_range / 2, goal_range / 2), (-goal_range / 2, goal_range / 2), (0.0, goal_range))):
+                cfg.stage.goal_lo[k], cfg.stage.goal_hi[k] = lo, hi
+        self._setup(cfg, device, False, max_episode_steps)
