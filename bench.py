@@ -32,9 +32,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
-# algorithmic FLOPs per env-step of the step kernel as implemented: 20 substeps of
-# RNEA + CRBA + 7x7 Cholesky inverse + 50-sweep PGS + collider FK + link-obstacle tests, + one observation pass
-FLOPS_PER_ENV_STEP = {"reachao3": 0.39e6, "reachao_rand": 0.50e6, "reachao1": 0.37e6, "reachao2": 0.38e6}
+# algorithmic FLOPs per env-step of the step kernel AS IMPLEMENTED: 20 substeps of
+# RNEA + CRBA + 7x7 Cholesky inverse + 50-sweep PGS + collider frames + link-obstacle tests, + one observation pass.
+# Frozen from ncu per-opcode thread-instruction counts of a real rollout launch (2*FFMA + FADD + FMUL), see
+# profiles/r01_k_step_summary.md.  Scenarios without a frozen count fall back to the reachao3 figure.
+FLOPS_PER_ENV_STEP = {"reachao3": 0.191e6}
 BYTES_PER_ENV_STEP = 750.0  # ~308 B read + ~440 B written
 
 
@@ -203,7 +205,7 @@ def main():
     tf = _lib.ctypes.c_double(0.0)
     _lib.check(lib.pg_debug_fma_peak(local, 148 * 8, 1 << 15, _lib.ctypes.byref(tf)))
     fp32_peak = float(tf.value)
-    flops = FLOPS_PER_ENV_STEP.get(args.scenario.split("-")[0], 0.39e6)
+    flops = FLOPS_PER_ENV_STEP.get(args.scenario.split("-")[0], 0.191e6)
     achieved_tflops = flops * N / (ms_per_step * 1e-3) / 1e12
     peaks = {}
     try:

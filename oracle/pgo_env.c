@@ -541,3 +541,8 @@ int pgo_bench_rollout(const pgo_env_config* cfg, uint64_t seed, int steps, doubl
   pgo_env_destroy(e);
   return episodes;
 }
+
+/* test hook: utils.distance on float32 rows (panda_gym/utils.py:4-16) */
+void pgo_test_distance(const float* a, const float* b, int n, float* out) {
+  for (int i = 0; i < n; i++) out[i] = f32_distance(a + 3 * i, b + 3 * i);
+}

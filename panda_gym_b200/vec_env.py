@@ -191,15 +191,10 @@ class PandaVecEnv:
         return {"observation": v("observation"), "achieved_goal": v("achieved_goal"), "desired_goal": v("desired_goal")}
 
     def episode_stats(self, group=None):
-        """{episodes, successes, collisions, timeouts, sum_return, sum_length, reset_failures}; all-reduced over
+        """{episodes, successes, collisions, timeouts, sum_return, sum_length, reset_failures, rates}; summed over
         ``torch.distributed`` ranks when a process group is initialised (the one collective of the path)."""
-        s = self.batch.view("stats").clone()
-        import torch.distributed as dist
-        if dist.is_available() and dist.is_initialized():
-            dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
-        s = s.cpu().numpy()
-        keys = ("episodes", "successes", "collisions", "timeouts", "sum_return", "sum_length", "reset_failures")
-        return {k: float(s[i]) for i, k in enumerate(keys)}
+        from .sharding import allreduce_stats
+        return allreduce_stats(self.batch.view("stats"), group)
 
 
 def make_vec_env(env_id, n_envs=1, seed=None, env_kwargs=None, vec_env_cls=None, **kw):

@@ -101,6 +101,8 @@ def lib():
     sig("pgo_env_compute_reward", None, P, P, P, c_int, P)
     sig("pgo_env_is_collided", c_int, P)
     sig("pgo_bench_rollout", c_int, P, c_u64, c_int, P)
+    sig("pgo_test_distance", None, P, P, c_int, P)
+    sig("pgo_test_integers_shuffle", c_int, c_u64, c_int, c_int, c_int, c_int, P)
     _lib = L
     return L
 

@@ -1,0 +1,38 @@
+"""N > 1 path on CPU: two gloo ranks shard the environments and all-reduce the episode statistics."""
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _worker(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from panda_gym_b200.sharding import allreduce_stats, env_shard, first_reset_seeds
+    n = 1024
+    lo, hi = env_shard(rank, n)
+    seeds = first_reset_seeds(100, rank, n)
+    # local statistics as k_step accumulates them: [episodes, successes, collisions, timeouts, sum_ret, sum_len, fails, -]
+    local = torch.tensor([10.0 + rank, 2.0 * (rank + 1), 5.0, 3.0 + rank - 2 * (rank + 1) + 2 * (rank + 1), -50.0 * (rank + 1), 400.0, 0.0, 0.0], dtype=torch.float64)
+    red = allreduce_stats(local)
+    out[rank] = (lo, hi, seeds[0], seeds[-1], red)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_sharding_and_stats_allreduce():
+    world = 2
+    mgr = mp.Manager(); out = mgr.dict()
+    port = 29650 + os.getpid() % 200
+    mp.spawn(_worker, args=(world, port, out), nprocs=world, join=True)
+    assert out[0][:2] == (0, 1024) and out[1][:2] == (1024, 2048)          # contiguous, disjoint shards
+    assert out[0][2:4] == (100, 1123) and out[1][2:4] == (1124, 2147)      # seed + global env index
+    r0, r1 = out[0][4], out[1][4]
+    assert r0 == r1                                                         # every rank sees the global statistics
+    assert r0["episodes"] == 21.0 and r0["successes"] == 6.0 and r0["collisions"] == 10.0
+    assert abs(r0["success_rate"] - 6.0 / 21.0) < 1e-12 and abs(r0["mean_return"] + 150.0 / 21.0) < 1e-12

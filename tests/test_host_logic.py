@@ -1,0 +1,117 @@
+"""Host-side logic that needs no GPU: the C ABI loads and exports every declared symbol, config / scenario blocks,
+the reference-shaped Python surface, loud failure without a device."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    import __graft_entry__ as ge
+    ge.build_cuda()
+    from panda_gym_b200 import _lib
+    return _lib
+
+
+def test_abi_exports_every_declared_symbol(lib):
+    header = open(os.path.join(ROOT, "include", "panda_b200.h")).read()
+    declared = set(re.findall(r"^\s*(?:int64_t|int|const char\*)\s+(pg_\w+)\s*\(", header, re.M))
+    assert len(declared) >= 28
+    L = ctypes.CDLL(lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), "libpanda_b200.so does not export %s" % name
+    bound = {s[0] for s in lib.SYMBOLS}
+    assert declared == bound, "ctypes table and header differ: %s" % (declared ^ bound)
+    assert b"sm_100a" in lib.load().pg_version()
+
+
+def test_scenario_blocks(lib):
+    L = lib.load()
+    st = lib.Stage()
+    assert L.pg_stage_from_scenario(ctypes.byref(st), b"reachao3") == 0
+    assert st.n_obstacles == 3 and st.goal_sampler == 1 and (st.goal_rmin, st.goal_rmax) == (0.5, 0.8)
+    assert st.obstacle_sampler == 1 and st.randomize_obstacle_position == 1 and st.goal_upper_half == 1
+    assert L.pg_stage_from_scenario(ctypes.byref(st), b"reachao1") == 0
+    assert st.n_obstacles == 1 and st.obstacle_size[0][0] == 0.04 and st.goal_sampler == 0
+    assert np.allclose(st.goal_lo[:], [0.4, -0.2, 0.0]) and np.allclose(st.goal_hi[:], [0.8, 0.2, 0.4])
+    assert L.pg_stage_from_scenario(ctypes.byref(st), b"wangexp-5") == 0 and st.n_obstacles == 5
+    assert L.pg_stage_from_scenario(ctypes.byref(st), b"reachao_rand") == 0
+    assert st.n_obstacles == 6 and list(st.obstacle_type[:6]) == [0, 0, 0, 1, 1, 1] and st.allow_overlapping_obstacles == 1
+    assert (st.sample_size_lo, st.sample_size_hi) == (4, 6)
+    # reach_ao.py:262-264 / SURVEY B.2: "wangexp_3" is not a key
+    assert L.pg_stage_from_scenario(ctypes.byref(st), b"wangexp_3") != 0
+    assert b"not found" in L.pg_last_error()
+
+
+def test_default_configs(lib):
+    L = lib.load()
+    c = lib.Config()
+    assert L.pg_default_config(ctypes.byref(c), 1, None) == 0
+    assert (c.obs_js, c.obstacle_obs, c.truncate_on_collision, c.terminate_on_success, c.n_substeps) == (1, 1, 1, 1, 20)
+    assert c.collision_reward == -100.0 and list(c.base_position[:]) == [0.0, 0.0, 0.0]
+    assert L.pg_default_config(ctypes.byref(c), 0, None) == 0
+    assert c.obs_js == 0 and c.terminate_on_success == 0 and c.base_position[0] == -0.6
+
+
+def test_make_config_maps_trainconfig(lib):
+    from panda_gym_b200 import sim
+    from panda_gym_b200.config import TrainConfig
+    cfg = sim.make_config(1, 16, scenario="reachao2", config=TrainConfig(reward_type="kumar", goal_condition="halt",
+                                                                          action_limiter="scale", collision_reward=-50,
+                                                                          task_observations={"obstacles": "closest_per_link", "prior": None}),
+                          max_episode_steps=75, speed_threshold=0.01)
+    assert (cfg.reward_type, cfg.goal_condition, cfg.action_limiter, cfg.obstacle_obs) == (4, 1, 1, 3)
+    assert cfg.collision_reward == -50 and cfg.stage.max_episode_steps == 75 and cfg.stage.speed_threshold == 0.01
+    with pytest.raises(lib.PandaB200Error):
+        sim.make_config(1, 1, scenario="reachao1", config=TrainConfig(randomize_robot_pose=True))
+    with pytest.raises(lib.PandaB200Error):
+        sim.make_config(1, 1, scenario="no_such_scenario")
+
+
+def test_no_cpu_fallback(lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from panda_gym_b200 import sim
+    cfg = sim.make_config(1, 4, scenario="reachao1")
+    with pytest.raises(lib.PandaB200Error):
+        sim.PandaBatch(cfg)
+    h = ctypes.c_void_p()
+    assert lib.load().pg_create(ctypes.byref(cfg), 0, ctypes.byref(h)) != 0
+    assert b"no CUDA device" in lib.load().pg_last_error() or b"CUDA" in lib.load().pg_last_error()
+
+
+def test_lazy_infos():
+    from panda_gym_b200.vec_env import LazyInfos
+    flags = np.array([0, 1 | 2, 4, 8], np.uint8); done = np.array([0, 1, 1, 1], bool)
+    term = np.arange(4 * 5, dtype=np.float32).reshape(4, 5); ag = np.zeros((4, 3), np.float32)
+    infos = LazyInfos(np.ones((4, 3), np.float32), flags, done, lambda: term, lambda: ag,
+                      lambda: np.array([0, -3, -101, -50], np.float32), lambda: np.array([0, 4, 7, 50]), 1.5)
+    assert len(infos) == 4 and "terminal_observation" not in infos[0]
+    assert infos[1]["is_success"] and infos[1]["episode"] == {"r": -3.0, "l": 4, "t": 1.5}
+    assert infos[2]["is_truncated"] and not infos[2]["TimeLimit.truncated"]
+    assert infos[3]["TimeLimit.truncated"] and np.array_equal(infos[3]["terminal_observation"]["observation"], term[3])
+    assert [i["is_success"] for i in infos] == [False, True, False, False]
+
+
+def test_spaces_and_ids():
+    from panda_gym_b200 import spaces
+    from panda_gym_b200.vec_env import ENV_IDS
+    b = spaces.Box(-1.0, 1.0, shape=(7,), dtype=np.float32)
+    assert b.sample().shape == (7,) and b.sample().dtype == np.float32
+    assert set(ENV_IDS) >= {"PandaReachAO-v3", "PandaReach-v3", "PandaReachJoints-v3", "PandaReachDense-v3", "PandaReachJointsDense-v3"}
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "panda_gym_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle_lib" not in src and "liboracle" not in src, f
+                assert not re.search(r'#include\s+"[^"]*pgo', src) and not re.search(r"\bpgo_\w+\s*\(", src), f

@@ -1,0 +1,97 @@
+"""Oracle env layer: the reference's own smoke / determinism tests restated (test/envs_test.py, test/seed_test.py)
+plus the ReachAO rules of reach_ao.py."""
+import numpy as np
+import pytest
+
+NEUTRAL = np.array([0, -0.3, 0, -2.2, 0, 2.0, np.pi / 4])
+
+
+@pytest.mark.parametrize("scenario,obs_dim,nobs", [("reachao1", 56, 1), ("reachao2", 56, 2), ("reachao3", 56, 3),
+                                                   ("wangexp-3", 56, 3), ("wang-2", 56, 2), ("reachao_rand", 56, 6),
+                                                   ("reach1", 47, 0), ("reach2", 47, 0), ("reach3", 47, 0)])
+def test_scenarios_reset(oracle, scenario, obs_dim, nobs):
+    e = oracle.Env(task=1, scenario=scenario)
+    o, info = e.reset(3)
+    assert info["status"] == 0 and not info["is_success"]
+    assert e.obs_dim == obs_dim and o["observation"].shape == (obs_dim,) and e.act_dim == 7
+    assert len(e.obstacles()) == nobs
+    assert np.allclose(o["observation"][6:13], NEUTRAL, atol=1e-7) and np.all(o["observation"][13:20] == 0)
+    assert np.allclose(o["achieved_goal"], [0.4816, 0.0100, 0.4375], atol=1e-4)   # COM of link 11
+    g = e.goal()
+    assert g[2] - 0.05 > 0.1 - 1e-9, "goal probe (r 0.05) keeps 0.1 clearance above the table (reach_ao.py:1101)"
+    if nobs == 0:
+        assert np.all(o["observation"][20:] == 1.0)  # reach_ao.py:904
+    else:
+        assert not e.check_collided()[0]
+
+
+def test_seed_determinism(oracle):
+    # reference test/seed_test.py: same seed and actions -> identical observations
+    acts = np.random.default_rng(0).uniform(-1, 1, (6, 7)).astype(np.float32)
+    outs = []
+    for _ in range(2):
+        e = oracle.Env(task=1, scenario="reachao3")
+        e.reset(12345)
+        outs.append(np.stack([e.step(a)[0]["observation"] for a in acts]))
+    assert np.array_equal(outs[0], outs[1])
+
+
+def test_random_rollout_smoke(oracle):
+    # reference test/envs_test.py: random steps, nothing numeric
+    for task, kw in ((0, {}), (1, dict(scenario="reachao2"))):
+        e = oracle.Env(task=task, **kw)
+        e.reset(0)
+        rng = np.random.default_rng(1)
+        for i in range(150):
+            o, r, f = e.step(rng.uniform(-1, 1, e.act_dim).astype(np.float32))
+            assert np.isfinite(o["observation"]).all()
+            if f["terminated"] or f["truncated"] or f["time_limit"]:
+                e.reset(i)
+
+
+def test_reward_and_flags_rules(oracle):
+    e = oracle.Env(task=1, scenario="reachao3", max_episode_steps=5)
+    e.reset(0)
+    # success: place the goal on the end-effector
+    ee = e.get_obs()["achieved_goal"].astype(np.float64)
+    e.set_goal(ee)
+    o, r, f = e.step(np.zeros(7, np.float32))
+    assert f["is_success"] and f["terminated"] and r == 0.0
+    # collision: put an obstacle into link 5 -> truncated, reward -1 - 100 (reach_ao.py:1317-1320, 1376-1377)
+    e.reset(1)
+    p = e.arm.link_state(4)[0]
+    e.set_obstacles([oracle.make_obstacle("sphere", p, 0.05)])
+    o, r, f = e.step(np.zeros(7, np.float32))
+    assert f["truncated"] and not f["is_success"] and r == -101.0
+    # time limit
+    e.reset(2)
+    flags = [e.step(np.zeros(7, np.float32))[2] for _ in range(5)]
+    assert not flags[3]["time_limit"] and flags[4]["time_limit"]
+
+
+def test_collision_stops_substeps(oracle):
+    """reach_ao.py:186-188: the substep loop breaks at the first colliding substep."""
+    e1 = oracle.Env(task=1, scenario="reachao1"); e1.reset(5)
+    e2 = oracle.Env(task=1, scenario="reachao1"); e2.reset(5)
+    p = e1.arm.link_state(6)[0] + np.array([0, 0, 0.12])
+    e1.set_obstacles([oracle.make_obstacle("sphere", p, 0.04)])
+    e2.set_obstacles([oracle.make_obstacle("sphere", p + 5.0, 0.04)])
+    a = np.array([0, -1, 0, 1, 0, -1, 0], np.float32)
+    moved1 = moved2 = 0
+    for _ in range(6):
+        q0 = e1.arm.q()[0].copy(); o1, r1, f1 = e1.step(a); moved1 = np.abs(e1.arm.q()[0] - q0).max()
+        q0 = e2.arm.q()[0].copy(); o2, r2, f2 = e2.step(a); moved2 = np.abs(e2.arm.q()[0] - q0).max()
+        if f1["truncated"]:
+            break
+    assert f1["truncated"] and not f2["truncated"]
+    assert moved1 < moved2
+
+
+def test_ee_control_uses_ik(oracle):
+    e = oracle.Env(task=0, control=1)
+    assert e.act_dim == 3
+    o, _ = e.reset(0)
+    z0 = o["achieved_goal"][2]
+    for _ in range(10):
+        o, r, f = e.step(np.array([0, 0, 1.0], np.float32))
+    assert o["achieved_goal"][2] > z0 + 0.1
