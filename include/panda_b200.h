@@ -173,6 +173,37 @@ int pg_debug_fma_peak(int device, int blocks, int iters, double* tflops_out);
  * block size, resident blocks per SM */
 int pg_debug_step_kernel_attrs(int device, int* out);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * On-device Hindsight-Experience-Replay buffer.  Replaces stable_baselines3 HerReplayBuffer (SB3 >= 2.0) as the
+ * reference uses it (classes/train_config.py:2,15; default kwargs n_sampled_goal = 4, strategy "future"):
+ *   add()    -> DictReplayBuffer.add + episode bookkeeping (ep_start / ep_length, overwrite invalidation)
+ *   sample() -> valid = flatnonzero(ep_length > 0); np.random.choice(valid, B); first int(her_ratio * B) samples get a
+ *               future achieved goal t = np.random.randint(cur, ep_len) and a recomputed reward; output order
+ *               cat(real, virtual); dones * (1 - timeouts).
+ * exact_rng = 1 consumes the MT19937 state loaded with pg_her_set_mt_state exactly like numpy's legacy
+ * RandomState does for those two calls (indices bit-identical to SB3 for the same np.random state);
+ * exact_rng = 0 draws from a parallel counter-based generator (same distribution, not the numpy stream). */
+typedef struct pg_her_s* pg_her_handle;
+typedef struct {
+  float *observation, *achieved_goal, *desired_goal;                 /* [batch][obs_dim], [batch][3], [batch][3] */
+  float *next_observation, *next_achieved_goal, *next_desired_goal;
+  float *action, *reward, *done;                                     /* [batch][act_dim], [batch], [batch] */
+  int64_t batch, n_virtual;
+} pg_her_batch;  /* device pointers owned by the buffer, valid until the next pg_her_sample */
+int pg_her_create(int device, int64_t buffer_size, int n_envs, int obs_dim, int act_dim, int n_sampled_goal, int64_t max_batch, pg_her_handle* out);
+int pg_her_destroy(pg_her_handle h);
+/* all inputs are device pointers laid out [n_envs][...]; done / timeout are uint8 (timeout may be NULL) */
+int pg_her_add(pg_her_handle h, const float* obs, const float* ag, const float* dg, const float* next_obs, const float* next_ag,
+               const float* next_dg, const float* action, const float* reward, const uint8_t* done, const uint8_t* timeout, void* stream);
+/* np.random.get_state()[1:3] -> device / back (host arrays) */
+int pg_her_set_mt_state(pg_her_handle h, const uint32_t* key624_host, int pos);
+int pg_her_get_mt_state(pg_her_handle h, uint32_t* key624_host, int* pos);
+/* env: the simulator handle whose compute_reward relabels (reward terms read environment reward_env, SB3 uses 0) */
+int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, uint64_t fast_seed, int reward_env, pg_her_batch* out, void* stream);
+/* (row, env, t) of the last sample() in SB3's draw order (virtual first), for parity tests; synchronises */
+int pg_her_last_indices(pg_her_handle h, int64_t batch, int* row_host, int* env_host, int* t_host, int* n_valid_host, int* status_host);
+int pg_her_info(pg_her_handle h, int* rows, int* pos, int* full, int64_t* launches);
+
 const char* pg_last_error(void);
 const char* pg_version(void);
 

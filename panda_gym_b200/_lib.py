@@ -47,6 +47,11 @@ class HostOut(ctypes.Structure):
                 ("reward", c_void_p), ("done", c_void_p), ("flags", c_void_p)]
 
 
+class HerBatch(ctypes.Structure):
+    _fields_ = [(k, c_void_p) for k in ("observation", "achieved_goal", "desired_goal", "next_observation", "next_achieved_goal",
+                                        "next_desired_goal", "action", "reward", "done")] + [("batch", c_i64), ("n_virtual", c_i64)]
+
+
 VIEW_IDS = {name: i for i, name in enumerate([
     "observation", "achieved_goal", "desired_goal", "reward", "done", "flags", "terminal_observation",
     "terminal_achieved", "ep_return", "ep_length", "q", "qd", "goal", "obstacle_pos", "stats", "step_count", "d_link"])}
@@ -83,6 +88,14 @@ SYMBOLS = [
     ("pg_debug_ik", c_int, [c_int, c_int, P, P, P, P, P]),
     ("pg_debug_fma_peak", c_int, [c_int, c_int, c_int, P]),
     ("pg_debug_step_kernel_attrs", c_int, [c_int, P]),
+    ("pg_her_create", c_int, [c_int, c_i64, c_int, c_int, c_int, c_int, c_i64, P]),
+    ("pg_her_destroy", c_int, [P]),
+    ("pg_her_add", c_int, [P] * 12),
+    ("pg_her_set_mt_state", c_int, [P, P, c_int]),
+    ("pg_her_get_mt_state", c_int, [P, P, P]),
+    ("pg_her_sample", c_int, [P, P, c_i64, c_int, c_u64, c_int, P, P]),
+    ("pg_her_last_indices", c_int, [P, c_i64, P, P, P, P, P]),
+    ("pg_her_info", c_int, [P, P, P, P, P]),
     ("pg_last_error", ctypes.c_char_p, []),
     ("pg_version", ctypes.c_char_p, []),
 ]

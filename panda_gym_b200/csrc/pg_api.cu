@@ -12,6 +12,7 @@
 
 #include "../../include/panda_b200.h"
 #include "pg_kernels.cuh"
+#include "pg_her.cuh"
 
 namespace {
 
@@ -478,6 +479,141 @@ int pg_debug_fma_peak(int device, int blocks, int iters, double* tflops_out) {
   }
   cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
   *tflops_out = (double)blocks * 256.0 * (double)iters * 16.0 / (best * 1e-3) / 1e12;
+  return PG_OK;
+}
+
+}  // extern "C"
+
+// =============================================================================================== HER buffer
+struct pg_her_s {
+  int device;
+  pg::HerParams H;
+  std::vector<void*> bufs;
+  int64_t capacity;      // rows * n_envs
+  int64_t max_batch;
+  pg::HerBatch out;      // library-owned output batch (max_batch rows)
+  int64_t launches;
+  uint64_t fast_counter;
+};
+
+extern "C" {
+
+int pg_her_create(int device, int64_t buffer_size, int n_envs, int obs_dim, int act_dim, int n_sampled_goal, int64_t max_batch, pg_her_handle* out) {
+  if (!out || buffer_size <= 0 || n_envs <= 0 || obs_dim <= 0 || act_dim <= 0 || n_sampled_goal < 0 || max_batch <= 0) return fail(PG_ERR_ARG, "bad argument");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(PG_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
+  PG_CUDA(cudaSetDevice(device));
+  pg_her_s* h = new pg_her_s();
+  h->device = device; h->launches = 0; h->fast_counter = 0; h->max_batch = max_batch;
+  pg::HerParams& H = h->H;
+  memset(&H, 0, sizeof H);
+  H.rows = (int)(buffer_size / n_envs > 0 ? buffer_size / n_envs : 1);  // SB3: buffer_size // n_envs
+  H.n_envs = n_envs; H.obs_dim = obs_dim; H.act_dim = act_dim;
+  H.her_ratio = 1.0f - 1.0f / (float)(n_sampled_goal + 1);
+  h->capacity = (int64_t)H.rows * n_envs;
+  const size_t cap = (size_t)h->capacity;
+  auto A = [&](void** p, size_t bytes) -> int {
+    PG_CUDA(cudaMalloc(p, bytes)); PG_CUDA(cudaMemset(*p, 0, bytes)); h->bufs.push_back(*p); return PG_OK; };
+#define HA(ptr, count, type) { int rc = A((void**)&ptr, (size_t)(count) * sizeof(type)); if (rc != PG_OK) { pg_her_destroy(h); return rc; } }
+  HA(H.obs, cap * obs_dim, float) HA(H.next_obs, cap * obs_dim, float) HA(H.ag, cap * 3, float) HA(H.dg, cap * 3, float)
+  HA(H.next_ag, cap * 3, float) HA(H.next_dg, cap * 3, float) HA(H.action, cap * act_dim, float) HA(H.reward, cap, float)
+  HA(H.done, cap, float) HA(H.timeout, cap, float) HA(H.ep_start, cap, int) HA(H.ep_length, cap, int)
+  HA(H.cur_ep_start, n_envs, int) HA(H.cursor, 2, int) HA(H.valid, cap, int) HA(H.n_valid, 1, int)
+  HA(H.block_counts, (cap + pg::kHerBlock - 1) / pg::kHerBlock + 1, int) HA(H.mt, 625, uint32_t)
+  HA(H.s_row, max_batch, int) HA(H.s_env, max_batch, int) HA(H.s_t, max_batch, int) HA(H.status, 1, int)
+  HA(h->out.obs, max_batch * obs_dim, float) HA(h->out.next_obs, max_batch * obs_dim, float) HA(h->out.ag, max_batch * 3, float)
+  HA(h->out.dg, max_batch * 3, float) HA(h->out.next_ag, max_batch * 3, float) HA(h->out.next_dg, max_batch * 3, float)
+  HA(h->out.action, max_batch * act_dim, float) HA(h->out.reward, max_batch, float) HA(h->out.done, max_batch, float)
+#undef HA
+  // default stream state = np.random.seed(0)-like is NOT assumed: callers load a state with pg_her_set_mt_state
+  *out = h;
+  return PG_OK;
+}
+
+int pg_her_destroy(pg_her_handle h) {
+  if (!h) return PG_OK;
+  cudaSetDevice(h->device);
+  for (void* p : h->bufs) cudaFree(p);
+  delete h;
+  return PG_OK;
+}
+
+int pg_her_set_mt_state(pg_her_handle h, const uint32_t* key624_host, int pos) {
+  if (!h || !key624_host || pos < 0 || pos > 624) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  uint32_t st[625];
+  memcpy(st, key624_host, 624 * sizeof(uint32_t)); st[624] = (uint32_t)pos;
+  PG_CUDA(cudaMemcpy(h->H.mt, st, sizeof st, cudaMemcpyHostToDevice));
+  return PG_OK;
+}
+int pg_her_get_mt_state(pg_her_handle h, uint32_t* key624_host, int* pos) {
+  if (!h || !key624_host || !pos) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  uint32_t st[625];
+  PG_CUDA(cudaMemcpy(st, h->H.mt, sizeof st, cudaMemcpyDeviceToHost));
+  memcpy(key624_host, st, 624 * sizeof(uint32_t)); *pos = (int)st[624];
+  return PG_OK;
+}
+
+int pg_her_add(pg_her_handle h, const float* obs, const float* ag, const float* dg, const float* next_obs, const float* next_ag,
+               const float* next_dg, const float* action, const float* reward, const uint8_t* done, const uint8_t* timeout, void* stream) {
+  if (!h || !obs || !ag || !dg || !next_obs || !next_ag || !next_dg || !action || !reward || !done) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const pg::HerParams& H = h->H;
+  pg::k_her_add_book<<<(H.n_envs + 127) / 128, 128, 0, s>>>(H, done);
+  int64_t tot = (int64_t)H.n_envs * (2 * H.obs_dim + 12 + H.act_dim + 3);
+  pg::k_her_add_data<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(H, obs, ag, dg, next_obs, next_ag, next_dg, action, reward, done, timeout);
+  pg::k_her_advance<<<1, 1, 0, s>>>(H);
+  h->launches += 3;
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, uint64_t fast_seed, int reward_env, pg_her_batch* out, void* stream) {
+  if (!h || !env || !out || batch <= 0 || batch > h->max_batch) return fail(PG_ERR_ARG, "bad argument (batch must be in [1, max_batch])");
+  if (reward_env < 0 || reward_env >= env->P.n) return fail(PG_ERR_ARG, "reward_env out of range");
+  PG_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const pg::HerParams& H = h->H;
+  const int total = (int)h->capacity, nb = (total + pg::kHerBlock - 1) / pg::kHerBlock;
+  const int B = (int)batch, nbv = (int)(H.her_ratio * (float)B);  // int(her_ratio * batch_size)
+  pg::k_her_count<<<nb, pg::kHerBlock, 0, s>>>(H, total);
+  pg::k_her_scan_blocks<<<1, 1024, 0, s>>>(H, nb);
+  pg::k_her_scatter<<<nb, pg::kHerBlock, 0, s>>>(H, total);
+  if (exact_rng) pg::k_her_indices_exact<<<1, 256, 0, s>>>(H, B, nbv);
+  else pg::k_her_indices_fast<<<(B + 255) / 256, 256, 0, s>>>(H, B, nbv, fast_seed, h->fast_counter++);
+  pg::k_her_gather<<<(unsigned)(((int64_t)B * 32 + 255) / 256), 256, 0, s>>>(H, env->P, h->out, B, nbv, reward_env);
+  h->launches += 5;
+  PG_CUDA(cudaGetLastError());
+  out->observation = h->out.obs; out->achieved_goal = h->out.ag; out->desired_goal = h->out.dg;
+  out->next_observation = h->out.next_obs; out->next_achieved_goal = h->out.next_ag; out->next_desired_goal = h->out.next_dg;
+  out->action = h->out.action; out->reward = h->out.reward; out->done = h->out.done;
+  out->batch = batch; out->n_virtual = nbv;
+  return PG_OK;
+}
+
+int pg_her_last_indices(pg_her_handle h, int64_t batch, int* row_host, int* env_host, int* t_host, int* n_valid_host, int* status_host) {
+  if (!h || batch <= 0 || batch > h->max_batch) return fail(PG_ERR_ARG, "bad argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  PG_CUDA(cudaDeviceSynchronize());
+  if (row_host) PG_CUDA(cudaMemcpy(row_host, h->H.s_row, batch * sizeof(int), cudaMemcpyDeviceToHost));
+  if (env_host) PG_CUDA(cudaMemcpy(env_host, h->H.s_env, batch * sizeof(int), cudaMemcpyDeviceToHost));
+  if (t_host) PG_CUDA(cudaMemcpy(t_host, h->H.s_t, batch * sizeof(int), cudaMemcpyDeviceToHost));
+  if (n_valid_host) PG_CUDA(cudaMemcpy(n_valid_host, h->H.n_valid, sizeof(int), cudaMemcpyDeviceToHost));
+  if (status_host) PG_CUDA(cudaMemcpy(status_host, h->H.status, sizeof(int), cudaMemcpyDeviceToHost));
+  return PG_OK;
+}
+
+int pg_her_info(pg_her_handle h, int* rows, int* pos, int* full, int64_t* launches) {
+  if (!h) return fail(PG_ERR_ARG, "NULL handle");
+  PG_CUDA(cudaSetDevice(h->device));
+  int cur[2];
+  PG_CUDA(cudaMemcpy(cur, h->H.cursor, sizeof cur, cudaMemcpyDeviceToHost));
+  if (rows) *rows = h->H.rows;
+  if (pos) *pos = cur[0];
+  if (full) *full = cur[1];
+  if (launches) *launches = h->launches;
   return PG_OK;
 }
 
