@@ -227,6 +227,60 @@ def test_reach_ao_trajectories_and_flags(sim, oracle, scenario):
     assert worst_obs < 2e-3
 
 
+@pytest.mark.parametrize("variant", ["halt_sparse", "wang", "kumar_her", "kumar_her_halt", "kumar_optim", "kumar", "scale_limiter",
+                                     "jsd", "pcc", "closest_per_link", "closest", "vectors", "no_truncate_flags"])
+def test_config_variants(sim, oracle, variant):
+    """Every TrainConfig switch that reaches the env path (train_config.py:26-59): reward types, goal condition, action
+    limiter, control types, obstacle observation modes -- rewards compared to 1e-5 (fp32 kernel vs fp64 oracle terms)."""
+    from panda_gym_b200.config import TrainConfig
+    tc = TrainConfig(); okw = {}
+    if variant == "halt_sparse": tc.goal_condition = "halt"; okw = dict(goal_condition=1, speed_threshold=0.1)
+    if variant == "wang": tc.reward_type = "wang"; okw = dict(reward_type=1)
+    if variant == "kumar_her": tc.reward_type = "kumar_her"; okw = dict(reward_type=2)
+    if variant == "kumar_her_halt": tc.reward_type = "kumar_her"; tc.goal_condition = "halt"; okw = dict(reward_type=2, goal_condition=1)
+    if variant == "kumar_optim": tc.reward_type = "kumar_optim"; okw = dict(reward_type=3)
+    if variant == "kumar": tc.reward_type = "kumar"; okw = dict(reward_type=4)
+    if variant == "scale_limiter": tc.action_limiter = "scale"; okw = dict(action_limiter=1)
+    if variant == "jsd": tc.control_type = "jsd"; okw = dict(control=2)
+    if variant == "pcc": tc.control_type = "pcc"; okw = dict(control=3)
+    if variant == "closest_per_link": tc.task_observations = {"obstacles": "closest_per_link", "prior": None}; okw = dict(obstacle_obs=3)
+    if variant == "closest": tc.task_observations = {"obstacles": "closest", "prior": None}; okw = dict(obstacle_obs=4)
+    if variant == "vectors": tc.task_observations = {"obstacles": "vectors", "prior": None}; okw = dict(obstacle_obs=2)
+    if variant == "no_truncate_flags": tc.truncate_on_collision = False; tc.terminate_on_success = False; okw = dict(truncate_on_collision=0, terminate_on_success=0)
+    n, steps = 24, 25
+    cfg = sim.make_config(1, n, scenario="reachao3", config=tc, max_episode_steps=100, auto_reset=False, speed_threshold=0.1)
+    b = sim.PandaBatch(cfg); b.seed(99); b.reset()
+    envs = [oracle.Env(task=1, scenario="reachao3", max_episode_steps=100, **okw) for _ in range(n)]
+    for i, e in enumerate(envs):
+        e.reset(99 + i)
+    assert b.obs_dim == envs[0].obs_dim
+    rng = np.random.default_rng(3)
+    alive = np.ones(n, bool); compared = 0
+    scale = 2.5 if variant == "scale_limiter" else 1.0
+    for _ in range(steps):
+        A = (scale * rng.uniform(-1, 1, (n, 7))).astype(np.float32)
+        b.step(torch.from_numpy(A).to(dev())); torch.cuda.synchronize()
+        og = b.view("observation").cpu().numpy(); rg = b.view("reward").cpu().numpy(); fg = b.view("flags").cpu().numpy()
+        for i in range(n):
+            if not alive[i]:
+                continue
+            o, r, f = envs[i].step(A[i])
+            compared += 1
+            assert np.abs(o["observation"][:20] - og[i, :20]).max() < 1e-4
+            assert flags_of(f) == fg[i]
+            # jerk / effort terms are norms of joint-velocity differences: fp32-vs-fp64 velocity noise (~1e-5 rad/s) shows
+            rtol = 2e-4 if variant.startswith("kumar") else 1e-5
+            assert abs(r - rg[i]) < rtol * max(1.0, abs(r)), (variant, r, rg[i])
+            if variant == "no_truncate_flags":
+                # physics after a collision is not simulated (DESIGN.md section 3): stop comparing once the oracle collides
+                if envs[i].check_collided()[0]:
+                    alive[i] = False
+            elif flags_of(f) & 14:
+                alive[i] = False
+    assert compared > 200
+    b.close()
+
+
 def test_reach_classic_joints(sim, oracle):
     worst_q, worst_ee, worst_obs, compared, _, _ = _rollout(sim, oracle, None, 32, 50, 31, task=0)
     assert compared == 32 * 50
