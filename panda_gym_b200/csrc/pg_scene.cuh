@@ -63,6 +63,24 @@ __device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obs
   }
   if (k.d < best) { best = k.d; bdir = k.dir; }
 }
+// flag-only form: "is the distance <= 0", squared-distance tests for the sphere pairs (no sqrt / divide)
+template <int K>
+__device__ __forceinline__ bool prim_hits_obstacle(const Frame& F, V3 o, const Obst& ob) {
+  using Pm = pgm::Prim<K>;
+  V3 c = frame_point(F, Pm::x, Pm::y, Pm::z);
+  if (Pm::type == 0) {
+    if (ob.type == 0) { V3 d = o - c; float rr = Pm::r + ob.sx; return dot(d, d) <= rr * rr; }
+    V3 rel = c - o;
+    float ex = ob.sx - ob.margin, ey = ob.sy - ob.margin, ez = ob.sz - ob.margin;
+    V3 v = v3(rel.x - fminf(fmaxf(rel.x, -ex), ex), rel.y - fminf(fmaxf(rel.y, -ey), ey), rel.z - fminf(fmaxf(rel.z, -ez), ez));
+    float rr = Pm::r + ob.margin;
+    return dot(v, v) <= rr * rr;  // centre inside the core gives v = 0: a hit
+  }
+  float best = 1e-6f; V3 dir;
+  prim_vs_obstacle<K>(F, o, ob, best, dir);
+  return best <= 0.f;
+}
+
 template <int K>
 __device__ __forceinline__ float prim_vs_table(const Frame& F, const SceneParams& S) {
   using Pm = pgm::Prim<K>;
@@ -80,10 +98,14 @@ template <int K0, int N> struct PrimLoop {
   static __device__ __forceinline__ float table(const Frame& F, const SceneParams& S) {
     return fminf(PrimLoop<K0, N - 1>::table(F, S), prim_vs_table<K0 + N - 1>(F, S));
   }
+  static __device__ __forceinline__ bool hits(const Frame& F, V3 o, const Obst& ob) {
+    return PrimLoop<K0, N - 1>::hits(F, o, ob) | prim_hits_obstacle<K0 + N - 1>(F, o, ob);
+  }
 };
 template <int K0> struct PrimLoop<K0, 0> {
   static __device__ __forceinline__ void obstacle(const Frame&, V3, const Obst&, float&, V3&) {}
   static __device__ __forceinline__ float table(const Frame&, const SceneParams&) { return 3.0e38f; }
+  static __device__ __forceinline__ bool hits(const Frame&, V3, const Obst&) { return false; }
 };
 
 // One collision link.  FULL: exact per-link minimum distance + closest pair (observation); otherwise only
@@ -103,10 +125,12 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __
       V3 d = o - ctr;
       float rr = R + P.obst_bound[j];
       if (dot(d, d) > rr * rr) continue;
+      if (PrimLoop<K0, N>::hits(F, o, P.obst[j])) hit = true;
+      continue;
     }
     PrimLoop<K0, N>::obstacle(F, o, P.obst[j], best, dir);
   }
-  if (best <= 0.f) hit = true;
+  if (FULL && best <= 0.f) hit = true;
   if (S >= 1 && P.has_table) {  // table: panda_link0 / panda_link1 ignored (reach_ao.py:898)
     bool near = true;
     if (!FULL) near = (ctr.z - R) <= (P.table_pos[2] + P.table_core[2] + P.table_margin + 0.002f) ||

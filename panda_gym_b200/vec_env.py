@@ -26,26 +26,37 @@ ENV_IDS["PandaReachAO-v3"] = dict(task=1)
 
 class LazyInfos:
     """``infos`` list built on demand: SB3 indexes it per env; building 65 536 dicts per step eagerly would cost
-    more than the simulation.  Behaves like a read-only sequence of dicts."""
+    more than the simulation.  Behaves like a read-only sequence of dicts.  Terminal observations / episode
+    statistics of the finished environments are fetched from the device once, on first use, and only their rows."""
 
-    def __init__(self, desired, flags, done, term_obs, term_ag, ep_r, ep_l, t):
+    def __init__(self, desired, flags, done, fetch_terminal, t):
         self._desired, self._flags, self._done = desired, flags, done
-        self._term_obs, self._term_ag, self._ep_r, self._ep_l, self._t = term_obs, term_ag, ep_r, ep_l, t
+        self._fetch, self._t = fetch_terminal, t
+        self._term = None
 
     def __len__(self):
         return len(self._flags)
 
+    def _terminal(self):
+        if self._term is None:
+            idx = np.flatnonzero(self._done)
+            obs, ag, r, l = self._fetch(idx)
+            self._term = ({int(e): k for k, e in enumerate(idx)}, obs, ag, r, l)
+        return self._term
+
     def __getitem__(self, i):
         if isinstance(i, slice):
             return [self[j] for j in range(*i.indices(len(self)))]
+        if i < 0:
+            i += len(self)
         f = int(self._flags[i])
         info = {"is_success": bool(f & 1), "is_truncated": bool(f & 4), "TimeLimit.truncated": bool(f & 8)}
         if self._done[i]:
-            obs, ag = self._term_obs(), self._term_ag()
-            info["terminal_observation"] = {"observation": obs[i].copy(), "achieved_goal": ag[i].copy(),
-                                            "desired_goal": self._desired[i].copy()}
-            r, l = self._ep_r(), self._ep_l()
-            info["episode"] = {"r": float(r[i]), "l": int(l[i]), "t": self._t}
+            pos, obs, ag, r, l = self._terminal()
+            k = pos[int(i)]
+            info["terminal_observation"] = {"observation": obs[k].copy(), "achieved_goal": ag[k].copy(),
+                                            "desired_goal": np.array(self._desired[i], copy=True)}
+            info["episode"] = {"r": float(r[k]), "l": int(l[k]), "t": self._t}
         return info
 
     def __iter__(self):
@@ -54,7 +65,8 @@ class LazyInfos:
 
 class PandaVecEnv:
     def __init__(self, env_id="PandaReachAO-v3", n_envs=8, seed=None, scenario="reachao1", config=None, device=0,
-                 max_episode_steps=50, ee_error_threshold=0.05, speed_threshold=0.1, first_env_index=0, **env_kwargs):
+                 max_episode_steps=50, ee_error_threshold=0.05, speed_threshold=0.1, first_env_index=0, copy_outputs=False,
+                 n_host_buffers=3, **env_kwargs):
         if env_id not in ENV_IDS:
             raise _lib.PandaB200Error("unknown / out-of-scope env id %r (supported: %s)" % (env_id, sorted(ENV_IDS)))
         spec = dict(ENV_IDS[env_id])
@@ -70,22 +82,35 @@ class PandaVecEnv:
         self.first_env_index = int(first_env_index)
         self.batch.seed(0 if seed is None else seed, self.first_env_index)
         self._t0 = time.time()
+        self.copy_outputs = bool(copy_outputs)
+        self.n_host_buffers = max(2, int(n_host_buffers))
         self._alloc_host()
         self._actions = None
 
     # ------------------------------------------------------------------ spaces
     def _alloc_host(self):
+        """Page-locked result buffers.  ``copy_outputs=False`` (default) hands out numpy views of a ring of
+        ``n_host_buffers`` (3) buffer sets: an array returned by step t stays intact until step t + 3 overwrites it --
+        enough for SB3's ``_last_obs`` pattern -- and no 15 MB memcpy is paid per step.  ``copy_outputs=True`` returns
+        fresh arrays like the reference (core.py:287-295)."""
         n, od, ad = self.num_envs, self.batch.obs_dim, self.batch.act_dim
 
         def pinned(shape, dtype):
             return torch.empty(shape, dtype=dtype).pin_memory()
 
-        self._h = dict(observation=pinned((n, od), torch.float32), achieved_goal=pinned((n, 3), torch.float32),
-                       desired_goal=pinned((n, 3), torch.float32), reward=pinned((n,), torch.float32),
-                       done=pinned((n,), torch.uint8), flags=pinned((n,), torch.uint8), actions=pinned((n, ad), torch.float32))
-        self._out = _lib.HostOut(*[ctypes.c_void_p(self._h[k].data_ptr()) for k in
-                                  ("observation", "achieved_goal", "desired_goal", "reward", "done", "flags")])
-        self._np = {k: v.numpy() for k, v in self._h.items()}
+        self._ring = []
+        for _ in range(self.n_host_buffers):
+            h = dict(observation=pinned((n, od), torch.float32), achieved_goal=pinned((n, 3), torch.float32),
+                     desired_goal=pinned((n, 3), torch.float32), reward=pinned((n,), torch.float32),
+                     done=pinned((n,), torch.uint8), flags=pinned((n,), torch.uint8))
+            out = _lib.HostOut(*[ctypes.c_void_p(h[k].data_ptr()) for k in
+                                 ("observation", "achieved_goal", "desired_goal", "reward", "done", "flags")])
+            npv = {k: v.numpy() for k, v in h.items()}
+            npv["done_bool"] = npv["done"].view(np.bool_)
+            self._ring.append((h, out, npv))
+        self._ring_pos = 0
+        self._h_actions = pinned((n, ad), torch.float32)
+        self._np_actions = self._h_actions.numpy()
         self.observation_space = spaces.Dict(dict(
             observation=spaces.Box(-10.0, 10.0, shape=(od,), dtype=np.float32),
             desired_goal=spaces.Box(-10.0, 10.0, shape=(3,), dtype=np.float32),
@@ -93,9 +118,14 @@ class PandaVecEnv:
         self.action_space = spaces.Box(-1.0, 1.0, shape=(ad,), dtype=np.float32)
         self._last_desired = np.zeros((n, 3), np.float32)
 
-    def _obs_dict(self):
-        return {"observation": self._np["observation"].copy(), "achieved_goal": self._np["achieved_goal"].copy(),
-                "desired_goal": self._np["desired_goal"].copy()}
+    def _next_buffers(self):
+        self._ring_pos = (self._ring_pos + 1) % len(self._ring)
+        return self._ring[self._ring_pos]
+
+    def _obs_dict(self, npv):
+        if self.copy_outputs:
+            return {k: npv[k].copy() for k in ("observation", "achieved_goal", "desired_goal")}
+        return {k: npv[k] for k in ("observation", "achieved_goal", "desired_goal")}
 
     # ------------------------------------------------------------------ VecEnv API (host buffers)
     def seed(self, seed=None):
@@ -103,26 +133,36 @@ class PandaVecEnv:
         return [None if seed is None else seed + self.first_env_index + i for i in range(self.num_envs)]
 
     def reset(self):
-        self.batch.reset_host(self._out)
-        self._last_desired = self._np["desired_goal"].copy()
-        return self._obs_dict()
+        _, out, npv = self._next_buffers()
+        self.batch.reset_host(out)
+        self._last_desired = npv["desired_goal"]
+        return self._obs_dict(npv)
 
     def step_async(self, actions):
         self._actions = actions
 
     def step_wait(self):
-        a = np.asarray(self._actions, dtype=np.float32).reshape(self.num_envs, self.batch.act_dim)
-        self._np["actions"][...] = a
+        np.copyto(self._np_actions, np.asarray(self._actions, dtype=np.float32).reshape(self.num_envs, self.batch.act_dim))
         prev_desired = self._last_desired
-        self.batch.step_host(self._np["actions"], self._out)
-        obs = self._obs_dict()
-        rewards = self._np["reward"].copy()
-        dones = self._np["done"].astype(bool)
+        _, out, npv = self._next_buffers()
+        self.batch.step_host(self._np_actions, out)
+        obs = self._obs_dict(npv)
+        if self.copy_outputs:
+            rewards, dones, flags = npv["reward"].copy(), npv["done_bool"].copy(), npv["flags"].copy()
+        else:
+            rewards, dones, flags = npv["reward"], npv["done_bool"], npv["flags"]
         b = self.batch
-        infos = LazyInfos(prev_desired, self._np["flags"].copy(), dones,
-                          lambda: b.view("terminal_observation").cpu().numpy(), lambda: b.view("terminal_achieved").cpu().numpy(),
-                          lambda: b.view("ep_return").cpu().numpy(), lambda: b.view("ep_length").cpu().numpy(),
-                          time.time() - self._t0)
+        # terminal data lives in device buffers that the NEXT step overwrites: snapshot the finished rows now (device
+        # gather, no host copy) and move them to the host only if somebody asks
+        didx = torch.nonzero(b.view("done"), as_tuple=False).flatten()
+        snap = (b.view("terminal_observation").index_select(0, didx), b.view("terminal_achieved").index_select(0, didx),
+                b.view("ep_return").index_select(0, didx), b.view("ep_length").index_select(0, didx))
+
+        def fetch(idx, snap=snap):
+            assert len(idx) == snap[0].shape[0]
+            return tuple(x.cpu().numpy() for x in snap)
+
+        infos = LazyInfos(prev_desired if self.copy_outputs else prev_desired.copy(), flags, dones, fetch, time.time() - self._t0)
         self._last_desired = obs["desired_goal"]
         return obs, rewards, dones, infos
 

@@ -89,14 +89,20 @@ def test_no_cpu_fallback(lib):
 def test_lazy_infos():
     from panda_gym_b200.vec_env import LazyInfos
     flags = np.array([0, 1 | 2, 4, 8], np.uint8); done = np.array([0, 1, 1, 1], bool)
-    term = np.arange(4 * 5, dtype=np.float32).reshape(4, 5); ag = np.zeros((4, 3), np.float32)
-    infos = LazyInfos(np.ones((4, 3), np.float32), flags, done, lambda: term, lambda: ag,
-                      lambda: np.array([0, -3, -101, -50], np.float32), lambda: np.array([0, 4, 7, 50]), 1.5)
-    assert len(infos) == 4 and "terminal_observation" not in infos[0]
+    term = np.arange(3 * 5, dtype=np.float32).reshape(3, 5); ag = np.zeros((3, 3), np.float32)
+    calls = []
+
+    def fetch(idx):
+        calls.append(list(idx))
+        return term, ag, np.array([-3, -101, -50], np.float32), np.array([4, 7, 50])
+
+    infos = LazyInfos(np.ones((4, 3), np.float32), flags, done, fetch, 1.5)
+    assert len(infos) == 4 and "terminal_observation" not in infos[0] and calls == []
     assert infos[1]["is_success"] and infos[1]["episode"] == {"r": -3.0, "l": 4, "t": 1.5}
     assert infos[2]["is_truncated"] and not infos[2]["TimeLimit.truncated"]
-    assert infos[3]["TimeLimit.truncated"] and np.array_equal(infos[3]["terminal_observation"]["observation"], term[3])
+    assert infos[3]["TimeLimit.truncated"] and np.array_equal(infos[3]["terminal_observation"]["observation"], term[2])
     assert [i["is_success"] for i in infos] == [False, True, False, False]
+    assert calls == [[1, 2, 3]], "terminal rows are fetched once, and only for finished environments"
 
 
 def test_spaces_and_ids():
