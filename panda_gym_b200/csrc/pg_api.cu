@@ -251,7 +251,7 @@ int pg_seed(pg_handle h, uint64_t base_seed, uint64_t first_env_index) {
 int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, void* stream) {
   if (!h) return fail(PG_ERR_ARG, "NULL handle");
   PG_CUDA(cudaSetDevice(h->device));
-  pg::k_reset<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, mask_dev, seeds_dev, 0, h->first_env);
+  pg::k_reset<false><<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, mask_dev, seeds_dev, h->first_env);
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -264,7 +264,7 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   pg::k_step<<<(h->P.n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
   h->launches++;
   if (h->P.auto_reset) {
-    pg::k_reset<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, nullptr, nullptr, 1, h->first_env);
+    pg::k_reset<true><<<148 * 8, pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, nullptr, nullptr, h->first_env);  // 4736 warps, grid-stride over the list
     h->launches++;
   }
   PG_CUDA(cudaGetLastError());

@@ -463,12 +463,15 @@ __device__ inline double box_margin_d(double sx, double sy, double sz) { double 
 
 // min distance robot (all 36 primitives at the neutral pose, base offset) vs body: body-level getClosestPoints
 // cutoff: pairs whose analytic lower bound exceeds it are skipped (the caller only compares the result to it)
+// WARP: the 32 lanes of a warp work on the same environment and split the primitives (then min-reduce)
+template <bool WARP>
 __device__ __noinline__ double robot_body_distance(const Params& P, const Body& b, double cutoff) {
   double best = 1e300;
+  const int k0 = WARP ? (threadIdx.x & 31) : 0, kstep = WARP ? 32 : 1;
   D3 o = v3t<double>(b.px - P.based[0], b.py - P.based[1], b.pz - P.based[2]);
   double m = b.type == 1 ? box_margin_d(b.sx, b.sy, b.sz) : 0.0;
   D3 core = v3t<double>(b.sx - m, b.sy - m, b.sz - m);
-  for (int k = 0; k < pgm::kNumNeutralPrim; k++) {
+  for (int k = k0; k < pgm::kNumNeutralPrim; k += kstep) {
     const pgm::NeutralPrim& np = pgm::kNeutralPrims[k];
     D3 c = v3t<double>(np.c[0], np.c[1], np.c[2]);
     double d;
@@ -486,6 +489,10 @@ __device__ __noinline__ double robot_body_distance(const Params& P, const Body& 
       }
     }
     best = fmin(best, d);
+  }
+  if (WARP) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
   }
   return best;
 }
@@ -546,15 +553,23 @@ __device__ inline Body obstacle_body(const Params& P, int j, int e) {
 
 // RobotTaskEnv.reset (core.py:298-308) = Panda.reset (panda.py:290-298) + Reach.reset (reach.py:63-78) /
 // ReachAO.reset (reach_ao.py:965-1033) with its rejection-sampling helpers (:1101-1181)
+//
+// WARP = false: one thread per environment (full / masked resets).  WARP = true: auto-reset of the few environments
+// k_step appended to the compact list, one WARP per environment: every lane runs the same (cheap, serial) sampling
+// code on the same PCG64 state, the 36-primitive robot distance query is split across the lanes.  Grid-stride
+// over the list.
+template <bool WARP>
 __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
-                                                  int use_need_reset, uint64_t first_env) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
+                                                  uint64_t first_env) {
   const int n = P.n;
-  if (e >= n) return;
-  if (use_need_reset) {  // auto-reset: only the (few) environments k_step appended to the compact list
-    if (e >= *P.reset_count) return;
-    e = P.reset_list[e];
-  } else if (mask && !mask[e]) return;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int count = WARP ? *P.reset_count : n;
+  const int stride = WARP ? (gridDim.x * blockDim.x) >> 5 : gridDim.x * blockDim.x;
+  const bool leader = WARP ? (threadIdx.x & 31) == 0 : true;
+  for (int item = WARP ? tid >> 5 : tid; item < count; item += stride) {
+  int e = item;
+  if (WARP) e = P.reset_list[item];
+  else if (mask && !mask[e]) continue;
   P.need_reset[e] = 0;
   uint32_t ep = P.episode[e];
   P.episode[e] = ep + 1;
@@ -587,7 +602,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
         bool coll = false;
         if (pass == 1) for (int j = 0; j < st.nobs; j++) coll |= body_body_collision(probe, obstacle_body(P, j, e), margin);
         coll |= body_body_collision(probe, table, margin);
-        if (!coll) coll |= (margin >= robot_body_distance(P, probe, margin));
+        if (!coll) coll |= (margin >= robot_body_distance<WARP>(P, probe, margin));
         if (!coll) break;
       }
     }
@@ -609,7 +624,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
             probe.px = probe.py = probe.pz = 0.0;  // the probe sphere is moved to the origin and left there
             coll |= !body_body_collision(probe, ob, 1.0);
           }
-          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance(P, ob, margin + P.safety_distance));
+          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance<WARP>(P, ob, margin + P.safety_distance));
           if (!coll) break;
         }
       }
@@ -629,12 +644,13 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
   }
   for (int k = 0; k < 3; k++) P.goal[(size_t)k * n + e] = goal[k];
   P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;
-  if (status) atomicAdd(&P.stats[6], 1.0);
+  if (status && leader) atomicAdd(&P.stats[6], 1.0);
   float ag[3], dg[3];
   observe(P, e, q, qd, q, cq, sq, ag);
   dg[0] = (float)goal[0]; dg[1] = (float)goal[1]; dg[2] = (float)goal[2];
   bool succ = is_success(P, e, ag, dg);
-  if (!use_need_reset) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
+  if (!WARP) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
+  }
 }
 
 // refresh observation / goals at the current state (no stepping)
