@@ -32,8 +32,16 @@ template <int K0, int K> struct BoundAcc {
 template <int K0, int N> struct SlotBound { static constexpr float value = cmax(SlotBound<K0, N - 1>::value, BoundAcc<K0, K0 + N - 1>::value); };
 template <int K0> struct SlotBound<K0, 0> { static constexpr float value = 0.f; };
 
+// Deferred cylinder-box queries of the observation pass.  Which (primitive, box) pairs survive the analytic lower
+// bound differs from lane to lane; calling GJK at each of the 30 call sites would serialise the warp 30 times with a
+// few lanes active.  Instead every lane queues its survivors and the warp drains the queues together, one
+// convergent GJK call per round (rounds = longest queue in the warp, typically 2-4).
+struct CylBoxCand { V3 c, a; float r, h, lb; int j, slot; };
+struct CylBoxQueue { static constexpr int kCap = 12; CylBoxCand q[kCap]; int n; };
+
 template <int K>
-__device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obst& ob, float& best, V3& bdir) {
+__device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obst& ob, float& best, V3& bdir, CylBoxQueue* Q = nullptr,
+                                                 int j = 0) {
   using Pm = pgm::Prim<K>;
   V3 c = frame_point(F, Pm::x, Pm::y, Pm::z);
   Closest k;
@@ -58,6 +66,11 @@ __device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obs
         lb = fminf(lb, sphere_box<float>(c + t * a, cover, o, core, ob.margin).d);
       }
       if (lb >= best) return;
+      if (Q && Q->n < CylBoxQueue::kCap) {
+        CylBoxCand& cd = Q->q[Q->n++];
+        cd.c = c; cd.a = a; cd.r = Pm::r; cd.h = Pm::h; cd.lb = lb; cd.j = j; cd.slot = Pm::slot;
+        return;
+      }
       k = cyl_box<float>(c, a, Pm::r, Pm::h, o, core, ob.margin);
     }
   }
@@ -91,9 +104,10 @@ __device__ __forceinline__ float prim_vs_table(const Frame& F, const SceneParams
 }
 
 template <int K0, int N> struct PrimLoop {
-  static __device__ __forceinline__ void obstacle(const Frame& F, V3 o, const Obst& ob, float& best, V3& dir) {
-    PrimLoop<K0, N - 1>::obstacle(F, o, ob, best, dir);
-    prim_vs_obstacle<K0 + N - 1>(F, o, ob, best, dir);
+  static __device__ __forceinline__ void obstacle(const Frame& F, V3 o, const Obst& ob, float& best, V3& dir, CylBoxQueue* Q, int j) {
+    // spheres first (analytic, they tighten the running minimum), cylinders afterwards
+    PrimLoop<K0, N - 1>::obstacle(F, o, ob, best, dir, Q, j);
+    prim_vs_obstacle<K0 + N - 1>(F, o, ob, best, dir, Q, j);
   }
   static __device__ __forceinline__ float table(const Frame& F, const SceneParams& S) {
     return fminf(PrimLoop<K0, N - 1>::table(F, S), prim_vs_table<K0 + N - 1>(F, S));
@@ -103,7 +117,7 @@ template <int K0, int N> struct PrimLoop {
   }
 };
 template <int K0> struct PrimLoop<K0, 0> {
-  static __device__ __forceinline__ void obstacle(const Frame&, V3, const Obst&, float&, V3&) {}
+  static __device__ __forceinline__ void obstacle(const Frame&, V3, const Obst&, float&, V3&, CylBoxQueue*, int) {}
   static __device__ __forceinline__ float table(const Frame&, const SceneParams&) { return 3.0e38f; }
   static __device__ __forceinline__ bool hits(const Frame&, V3, const Obst&) { return false; }
 };
@@ -112,7 +126,7 @@ template <int K0> struct PrimLoop<K0, 0> {
 // "is any distance <= 0", with bounding-sphere culling.  obs_pos: f64 [kMaxObst][3][n] (SoA), e = env.
 template <int S, bool FULL>
 __device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __restrict__ obs_pos, int n, int e, const Frame& F,
-                                          bool& hit, float& d_out, V3& u_out) {
+                                          bool& hit, float& d_out, V3& u_out, CylBoxQueue* Q) {
   constexpr int K0 = slot_first(S), N = slot_count(S);
   using P0 = pgm::Prim<K0>;
   constexpr float R = SlotBound<K0, N>::value + 0.002f;
@@ -128,20 +142,15 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __
       if (PrimLoop<K0, N>::hits(F, o, P.obst[j])) hit = true;
       continue;
     }
-    PrimLoop<K0, N>::obstacle(F, o, P.obst[j], best, dir);
+    PrimLoop<K0, N>::obstacle(F, o, P.obst[j], best, dir, Q, j);
   }
-  if (FULL && best <= 0.f) hit = true;
   if (S >= 1 && P.has_table) {  // table: panda_link0 / panda_link1 ignored (reach_ao.py:898)
     bool near = true;
     if (!FULL) near = (ctr.z - R) <= (P.table_pos[2] + P.table_core[2] + P.table_margin + 0.002f) ||
                       fabsf(ctr.x - P.table_pos[0]) + R > P.table_core[0] || fabsf(ctr.y - P.table_pos[1]) + R > P.table_core[1];
     if (near && PrimLoop<K0, N>::table(F, P) <= 0.f) hit = true;
   }
-  if (FULL) {
-    d_out = best;
-    // utils.unit_vector(pA, pB) = nan_to_num((pB - pA) / |pB - pA|) with pB - pA = d * dir
-    u_out = best > 0.f ? dir : (best < 0.f ? v3(-dir.x, -dir.y, -dir.z) : v3(0, 0, 0));
-  }
+  if (FULL) { d_out = best; u_out = dir; }  // sign / saturation applied after the deferred queries (scene_pass)
 }
 
 // all 9 collision links at joint cosines/sines (cq, sq).  FULL fills d_link[9], u_link[9].
@@ -151,27 +160,52 @@ __device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, co
                                            const float* cq, const float* sq, float* d_link, V3* u_link) {
   bool hit = false;
   float d; V3 u;
+  CylBoxQueue queue; queue.n = 0;
+  CylBoxQueue* Q = FULL ? &queue : nullptr;
   Frame F = base_frame(base);
   if (active) {
-    F = frame_step<1>(F, cq[0], sq[0]); slot_eval<0, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[0] = d; u_link[0] = u; }
-    F = frame_step<2>(F, cq[1], sq[1]); slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[1] = d; u_link[1] = u; }
-    F = frame_step<3>(F, cq[2], sq[2]); slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[2] = d; u_link[2] = u; }
+    F = frame_step<1>(F, cq[0], sq[0]); slot_eval<0, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[0] = d; u_link[0] = u; }
+    F = frame_step<2>(F, cq[1], sq[1]); slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[1] = d; u_link[1] = u; }
+    F = frame_step<3>(F, cq[2], sq[2]); slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[2] = d; u_link[2] = u; }
   }
   if (SYNC && FULL) __syncthreads();
   if (active) {
-    F = frame_step<4>(F, cq[3], sq[3]); slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[3] = d; u_link[3] = u; }
-    F = frame_step<5>(F, cq[4], sq[4]); slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[4] = d; u_link[4] = u; }
+    F = frame_step<4>(F, cq[3], sq[3]); slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[3] = d; u_link[3] = u; }
+    F = frame_step<5>(F, cq[4], sq[4]); slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[4] = d; u_link[4] = u; }
   }
   if (SYNC && FULL) __syncthreads();
   if (active) {
-    F = frame_step<6>(F, cq[5], sq[5]); slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[5] = d; u_link[5] = u; }
+    F = frame_step<6>(F, cq[5], sq[5]); slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[5] = d; u_link[5] = u; }
     F = frame_step<7>(F, cq[6], sq[6]);
-    slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[6] = d; u_link[6] = u; }
+    slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[6] = d; u_link[6] = u; }
   }
   if (SYNC && FULL) __syncthreads();
   if (active) {
-    slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[7] = d; u_link[7] = u; }
-    slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u); if (FULL) { d_link[8] = d; u_link[8] = u; }
+    slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[7] = d; u_link[7] = u; }
+    slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[8] = d; u_link[8] = u; }
+  }
+  if (FULL && active) {
+    // drain the deferred cylinder-box queries, the whole warp together
+    for (int it = 0;; it++) {
+      const bool has = it < queue.n;
+      if (!__any_sync(__activemask(), has)) break;
+      if (has) {
+        const CylBoxCand cd = queue.q[it];
+        if (cd.lb < d_link[cd.slot]) {
+          const Obst& ob = P.obst[cd.j];
+          V3 o = v3((float)obs_pos[(size_t)(cd.j * 3 + 0) * n + e], (float)obs_pos[(size_t)(cd.j * 3 + 1) * n + e], (float)obs_pos[(size_t)(cd.j * 3 + 2) * n + e]);
+          Closest k = cyl_box<float>(cd.c, cd.a, cd.r, cd.h, o, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
+          if (k.d < d_link[cd.slot]) { d_link[cd.slot] = k.d; u_link[cd.slot] = k.dir; }
+        }
+      }
+    }
+    // utils.unit_vector(pA, pB) = nan_to_num((pB - pA) / |pB - pA|) with pB - pA = d * dir
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+      float b = d_link[i]; V3 dr = u_link[i];
+      u_link[i] = b > 0.f ? dr : (b < 0.f ? v3(-dr.x, -dr.y, -dr.z) : v3(0, 0, 0));
+      if (b <= 0.f) hit = true;
+    }
   }
   if (SYNC) __syncthreads();
   return hit;
