@@ -200,7 +200,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   const int max_obs = 6 + 14 + 36;
   int rc = PG_OK;
 #define A(ptr, count, st) if ((rc = alloc(h, &ptr, (size_t)(count), st)) != PG_OK) { pg_destroy(h); return rc; }
-  A(P.q, 7 * n, true) A(P.qd, 7 * n, true) A(P.goal, 3 * n, true) A(P.obs_pos, (size_t)pg::kMaxObst * 3 * n, true)
+  A(P.q, 7 * n, true) A(P.qd, 7 * n, true) A(P.goal, 3 * n, true) A(P.obs_pos, (size_t)pg::kMaxObst * 3 * n, true) A(P.obs_pos_f, (size_t)pg::kMaxObst * 3 * n, true)
   A(P.recent, 7 * n, true) A(P.prev, 7 * n, true) A(P.cur_vel, 7 * n, true) A(P.cur_acc, 7 * n, true) A(P.jerk, 7 * n, true)
   A(P.d_link, 9 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
   A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
@@ -217,6 +217,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
       for (int e = 0; e < n; e++) { init[(size_t)(j * 3 + 0) * n + e] = 0.1; init[(size_t)(j * 3 + 1) * n + e] = 0.0; init[(size_t)(j * 3 + 2) * n + e] = 0.1; }
     cudaError_t e2 = cudaMemcpy(P.obs_pos, init.data(), init.size() * sizeof(double), cudaMemcpyHostToDevice);
     if (e2 != cudaSuccess) { pg_destroy(h); return fail(PG_ERR_CUDA, cudaGetErrorString(e2)); }
+    pg::k_mirror_obstacles<<<(unsigned)(((size_t)pg::kMaxObst * 3 * n + 255) / 256), 256>>>(P);
   }
   P.base_seed = 0;
   *out = h;
@@ -413,6 +414,7 @@ int pg_set_obstacles(pg_handle h, const double* pos_dev, void* stream) {
   if (!h || !pos_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
   PG_CUDA(cudaMemcpyAsync(h->P.obs_pos, pos_dev, (size_t)h->P.st.nobs * 3 * h->P.n * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  pg::k_mirror_obstacles<<<(unsigned)(((size_t)pg::kMaxObst * 3 * h->P.n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h->P);
   return PG_OK;
 }
 int pg_observe(pg_handle h, void* stream) {

@@ -56,6 +56,7 @@ struct Params {
   float *q, *qd;                 // [7][n]
   double* goal;                  // [3][n]
   double* obs_pos;               // [kMaxObst][3][n]
+  float* obs_pos_f;              // fp32 mirror read by the per-substep collision pass (refreshed by reset / set_obstacles)
   float *recent, *prev;          // [7][n] action history (panda.py:138-139)
   float *cur_vel, *cur_acc, *jerk; // [7][n] (panda.py:167-172)
   float* d_link;                 // [9][n]
@@ -200,7 +201,7 @@ __device__ __forceinline__ void observe(const Params& P, int e, const float* q, 
       for (int k = 0; k < 27; k++) o[off + k] = 1.0f;
     } else {
       float dl[9]; V3 ul[9];
-      scene_pass<true, false>(true, P.scene, P.obs_pos, n, e, base, cq, sq, dl, ul);
+      scene_pass<true, false>(true, P.scene, P.obs_pos_f, n, e, base, cq, sq, dl, ul);
       float mn = dl[0];
 #pragma unroll
       for (int i = 0; i < 9; i++) { P.d_link[(size_t)i * n + e] = dl[i]; mn = fminf(mn, dl[i]); }
@@ -411,7 +412,7 @@ __global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ 
   for (int k = 0; k < P.n_substeps; k++) {
     substep<kStepSync>(active, velocity_mode, unit_imp, qs, qd, cq, sq, tgt, kStepBlock);
     if (P.task == 1) {
-      bool hit = scene_pass<false, kStepSync>(active, P.scene, P.obs_pos, n, e, base, cq, sq, nullptr, nullptr);
+      bool hit = scene_pass<false, kStepSync>(active, P.scene, P.obs_pos_f, n, e, base, cq, sq, nullptr, nullptr);
       if (active && hit) { collided = true; active = false; }
     }
   }
@@ -641,6 +642,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
       }
     }
     P.have_recent[e] = 0; P.have_prev[e] = 0;
+    for (int k = 0; k < st.nobs * 3; k++) P.obs_pos_f[(size_t)k * n + e] = (float)P.obs_pos[(size_t)k * n + e];
   }
   for (int k = 0; k < 3; k++) P.goal[(size_t)k * n + e] = goal[k];
   P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;
@@ -662,9 +664,14 @@ __global__ void __launch_bounds__(kBlock) k_observe(const Params P) {
   for (int d = 0; d < 7; d++) { q[d] = P.q[(size_t)d * P.n + e]; qd[d] = P.qd[(size_t)d * P.n + e]; sincosf(q[d], &sq[d], &cq[d]); }
   observe(P, e, q, qd, q, cq, sq, ag);
   if (P.task == 1) {
-    bool hit = scene_pass<false, false>(true, P.scene, P.obs_pos, P.n, e, v3(P.base[0], P.base[1], P.base[2]), cq, sq, nullptr, nullptr);
+    bool hit = scene_pass<false, false>(true, P.scene, P.obs_pos_f, P.n, e, v3(P.base[0], P.base[1], P.base[2]), cq, sq, nullptr, nullptr);
     P.flags[e] = (uint8_t)((P.flags[e] & ~4) | (hit ? 4 : 0));
   }
+}
+
+__global__ void k_mirror_obstacles(const Params P) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < (int64_t)kMaxObst * 3 * P.n) P.obs_pos_f[i] = (float)P.obs_pos[i];
 }
 
 __global__ void k_reward(const Params P, const float* __restrict__ ag, const float* __restrict__ dg, float* __restrict__ out, int64_t m, int src) {

@@ -123,9 +123,9 @@ template <int K0> struct PrimLoop<K0, 0> {
 };
 
 // One collision link.  FULL: exact per-link minimum distance + closest pair (observation); otherwise only
-// "is any distance <= 0", with bounding-sphere culling.  obs_pos: f64 [kMaxObst][3][n] (SoA), e = env.
+// "is any distance <= 0", with bounding-sphere culling.  obs_pos: f32 [kMaxObst][3][n] (SoA), e = env.
 template <int S, bool FULL>
-__device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __restrict__ obs_pos, int n, int e, const Frame& F,
+__device__ __forceinline__ void slot_eval(const SceneParams& P, const float* __restrict__ obs_pos, int n, int e, const Frame& F,
                                           bool& hit, float& d_out, V3& u_out, CylBoxQueue* Q) {
   constexpr int K0 = slot_first(S), N = slot_count(S);
   using P0 = pgm::Prim<K0>;
@@ -134,7 +134,7 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __
   V3 dir = v3(0, 0, 0);
   V3 ctr = frame_point(F, P0::x, P0::y, P0::z);
   for (int j = 0; j < P.nobs; j++) {
-    V3 o = v3((float)obs_pos[(size_t)(j * 3 + 0) * n + e], (float)obs_pos[(size_t)(j * 3 + 1) * n + e], (float)obs_pos[(size_t)(j * 3 + 2) * n + e]);
+    V3 o = v3(obs_pos[(size_t)(j * 3 + 0) * n + e], obs_pos[(size_t)(j * 3 + 1) * n + e], obs_pos[(size_t)(j * 3 + 2) * n + e]);
     if (!FULL) {
       V3 d = o - ctr;
       float rr = R + P.obst_bound[j];
@@ -156,7 +156,7 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const double* __
 // all 9 collision links at joint cosines/sines (cq, sq).  FULL fills d_link[9], u_link[9].
 // SYNC: called by every thread of the block (see substep) with block barriers between groups of links.
 template <bool FULL, bool SYNC>
-__device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, const double* __restrict__ obs_pos, int n, int e, V3 base,
+__device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, const float* __restrict__ obs_pos, int n, int e, V3 base,
                                            const float* cq, const float* sq, float* d_link, V3* u_link) {
   bool hit = false;
   float d; V3 u;
@@ -193,7 +193,7 @@ __device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, co
         const CylBoxCand cd = queue.q[it];
         if (cd.lb < d_link[cd.slot]) {
           const Obst& ob = P.obst[cd.j];
-          V3 o = v3((float)obs_pos[(size_t)(cd.j * 3 + 0) * n + e], (float)obs_pos[(size_t)(cd.j * 3 + 1) * n + e], (float)obs_pos[(size_t)(cd.j * 3 + 2) * n + e]);
+          V3 o = v3(obs_pos[(size_t)(cd.j * 3 + 0) * n + e], obs_pos[(size_t)(cd.j * 3 + 1) * n + e], obs_pos[(size_t)(cd.j * 3 + 2) * n + e]);
           Closest k = cyl_box<float>(cd.c, cd.a, cd.r, cd.h, o, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
           if (k.d < d_link[cd.slot]) { d_link[cd.slot] = k.d; u_link[cd.slot] = k.dir; }
         }
