@@ -337,6 +337,14 @@ __device__ __noinline__ void pgs_generic(const float* Mi, const float* q, const 
 // window of each other turns those fetches into hits.
 __device__ __forceinline__ constexpr float motor_imp(int d) { return (d < 4 ? 87.0f : (d == 4 ? 12.0f : 120.0f)) * kDt; }  // panda.py:63
 
+#ifndef PG_SYNC_MASK
+#define PG_SYNC_MASK 8   // measured best on B200 (0.795 ms vs 0.843 ms with all five); which of the five per-substep barriers are compiled in (bit 0..3: A..D, bit 4: after the collision pass)
+#endif
+#define PG_SYNC_A ((PG_SYNC_MASK & 1) != 0)
+#define PG_SYNC_B ((PG_SYNC_MASK & 2) != 0)
+#define PG_SYNC_C ((PG_SYNC_MASK & 4) != 0)
+#define PG_SYNC_D ((PG_SYNC_MASK & 8) != 0)
+#define PG_SYNC_E ((PG_SYNC_MASK & 16) != 0)
 template <bool SYNC>
 __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_imp, float* q, float* qd, float* cq, float* sq,
                                         const float* tgt, int stride) {
@@ -344,9 +352,9 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
   float tau[7], Mi[28];
   float rhs[7], dinv[7], dv[7];
   if (active) rnea_bias(cq, sq, qd, tau);
-  if (SYNC) __syncthreads();
+  if (SYNC && PG_SYNC_A) __syncthreads();
   if (active) crba(cq, sq, Mi);
-  if (SYNC) __syncthreads();
+  if (SYNC && PG_SYNC_B) __syncthreads();
   bool slow = unit_imp;
   if (active) {
     spd_inverse7(Mi);
@@ -373,7 +381,7 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
       slow |= (qv - lo[d] <= 0.f) || (hi[d] - qv <= 0.f);
     }
   }
-  if (SYNC) __syncthreads();
+  if (SYNC && PG_SYNC_C) __syncthreads();
   if (active) {
     // 3. projected Gauss-Seidel exactly as btMultiBodyConstraintSolver: 50 sweeps, even backward / odd forward,
     //    residual early-out.  A lane whose residual test fired stays masked off by divergence; the warp leaves
@@ -427,7 +435,7 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
       sq[d] = s0 * cd + c0 * sd;
     }
   }
-  if (SYNC) __syncthreads();
+  if (SYNC && PG_SYNC_D) __syncthreads();
 }
 
 }  // namespace pg

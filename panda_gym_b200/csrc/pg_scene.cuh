@@ -207,7 +207,7 @@ __device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, co
       if (b <= 0.f) hit = true;
     }
   }
-  if (SYNC) __syncthreads();
+  if (SYNC && PG_SYNC_E) __syncthreads();
   return hit;
 }
 
