@@ -281,6 +281,39 @@ def test_config_variants(sim, oracle, variant):
     b.close()
 
 
+@pytest.mark.parametrize("scenario,n,n_substeps", [("reach1", 5, 20), ("reach2", 33, 20), ("wangexp-8", 17, 20), ("wang-1", 1, 20),
+                                                   ("reachao2", 449, 20), ("reachao3", 31, 7), ("reachao3", 9, 40)])
+def test_edge_shapes(sim, oracle, scenario, n, n_substeps):
+    """Ragged / extreme shapes: no obstacles (47-wide observation), all 8 obstacle slots, a single environment, one more
+    environment than a thread block, non-default n_substeps (wandb sweep range 2-50, wandb_sweep_config.yaml:36-39)."""
+    from panda_gym_b200.config import TrainConfig
+    tc = TrainConfig(n_substeps=n_substeps)
+    cfg = sim.make_config(1, n, scenario=scenario, config=tc, max_episode_steps=100, auto_reset=False)
+    b = sim.PandaBatch(cfg); b.seed(11); b.reset()
+    probe = sorted(set([0, n // 2, n - 1]))
+    envs = {i: oracle.Env(task=1, scenario=scenario, max_episode_steps=100, n_substeps=n_substeps) for i in probe}
+    for i, e in envs.items():
+        e.reset(11 + i)
+    assert b.obs_dim == envs[0].obs_dim
+    rng = np.random.default_rng(n)
+    alive = {i: True for i in probe}
+    for _ in range(20):
+        A = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
+        b.step(torch.from_numpy(A).to(dev())); torch.cuda.synchronize()
+        og = b.view("observation").cpu().numpy(); rg = b.view("reward").cpu().numpy(); fg = b.view("flags").cpu().numpy()
+        assert np.isfinite(og).all()
+        for i, e in envs.items():
+            if not alive[i]:
+                continue
+            o, r, f = e.step(A[i])
+            assert np.abs(o["observation"][:29] - og[i, :29]).max() < 5e-5 if o["observation"].shape[0] >= 29 else True
+            assert np.abs(o["observation"][:20] - og[i, :20]).max() < 5e-5
+            assert flags_of(f) == fg[i] and r == rg[i]
+            if flags_of(f) & 14:
+                alive[i] = False
+    b.close()
+
+
 def test_reach_classic_joints(sim, oracle):
     worst_q, worst_ee, worst_obs, compared, _, _ = _rollout(sim, oracle, None, 32, 50, 31, task=0)
     assert compared == 32 * 50
