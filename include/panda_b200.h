@@ -25,7 +25,7 @@ enum pg_task { PG_TASK_REACH = 0, PG_TASK_REACH_AO = 1 };                       
 enum pg_control { PG_CTRL_JOINTS = 0, PG_CTRL_EE = 1, PG_CTRL_JSD = 2, PG_CTRL_PCC = 3 }; /* panda.py:141-165 */
 enum pg_reward { PG_REW_SPARSE = 0, PG_REW_DENSE_OR_WANG = 1, PG_REW_KUMAR_HER = 2, PG_REW_KUMAR_OPTIM = 3, PG_REW_KUMAR = 4 };
 enum pg_obstacle_obs { PG_OOBS_NONE = 0, PG_OOBS_VECTORS_CLOSEST_PER_LINK = 1, PG_OOBS_VECTORS = 2,
-                       PG_OOBS_CLOSEST_PER_LINK = 3, PG_OOBS_CLOSEST = 4 };      /* reach_ao.py:908-932 */
+                       PG_OOBS_CLOSEST_PER_LINK = 3, PG_OOBS_CLOSEST = 4, PG_OOBS_VECTORS_PAST = 5 };      /* reach_ao.py:908-932 */
 enum pg_goal_sampler { PG_GOAL_BOX = 0, PG_GOAL_SHELL = 1 };                     /* reach_ao.py:1183-1211 */
 enum pg_obstacle_sampler { PG_OSMP_GOAL_BOX = 0, PG_OSMP_WANG = 1, PG_OSMP_EXPERIMENTAL = 2, PG_OSMP_WANG_N = 3 }; /* :610-644, 650-660 */
 

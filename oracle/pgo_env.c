@@ -33,6 +33,7 @@ struct pgo_env {
   double cur_vel[7], prev_vel[7], cur_acc[7], prev_acc[7], jerk[7];
   pgo_pcg64 rng;
   double dummy[3]; /* the collidable r=0.05 probe sphere (reach_ao.py:284-290) */
+  float past[3][27]; int npast; /* past_obstacle_observations (reach_ao.py:49-53, 918-922): last three vector observations */
   /* scenario parameter block */
   int goal_sampler;        /* 0 box, 1 hollow sphere */
   double goal_lo[3], goal_hi[3];
@@ -149,7 +150,7 @@ int pgo_env_get_obstacles(const pgo_env* e, pgo_obstacle* o) { memcpy(o, e->obs,
 static int task_obs_dim(const pgo_env* e) {
   if (e->cfg.task == 0 || e->cfg.obstacle_obs == 0) return 0;
   if (e->nobs == 0) return 27; /* reach_ao.py:904: np.ones(27) whatever the mode */
-  switch (e->cfg.obstacle_obs) { case 1: return 36; case 2: return 27; case 3: return 9; default: return 1; }
+  switch (e->cfg.obstacle_obs) { case 1: return 36; case 2: return 27; case 3: return 9; case 5: return 81; default: return 1; }
 }
 int pgo_env_obs_dim(const pgo_env* e) { return 6 + (e->cfg.obs_js ? 14 : 0) + task_obs_dim(e); }
 int pgo_env_act_dim(const pgo_env* e) { return e->cfg.control == 1 ? 3 : 7; } /* block_gripper=True */
@@ -352,6 +353,13 @@ static void task_obs(pgo_env* e, float* o) {
     case 1: for (int i = 0; i < 9; i++) { o[i] = (float)dmin[i]; for (int k = 0; k < 3; k++) o[9 + 3 * i + k] = (float)u[i][k]; } break;
     case 2: for (int i = 0; i < 9; i++) for (int k = 0; k < 3; k++) o[3 * i + k] = (float)u[i][k]; break;
     case 3: for (int i = 0; i < 9; i++) o[i] = (float)dmin[i]; break;
+    case 5: { /* "vectors+past": append the current vectors, return the last three (oldest first) */
+      float cur[27];
+      for (int i = 0; i < 9; i++) for (int k = 0; k < 3; k++) cur[3 * i + k] = (float)u[i][k];
+      if (e->npast == 3) { memcpy(e->past[0], e->past[1], sizeof cur); memcpy(e->past[1], e->past[2], sizeof cur); e->npast = 2; }
+      memcpy(e->past[e->npast++], cur, sizeof cur);
+      for (int h = 0; h < e->npast; h++) memcpy(o + 27 * h, e->past[h], sizeof cur);
+      break; }
     default: o[0] = (float)all; break;
   }
 }
@@ -399,6 +407,8 @@ int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, i
       for (int i = 0; i < n && to_move > 0; i++, to_move--) { e->obs[order[i]].pos[0] = 99.9; e->obs[order[i]].pos[1] = 99.9; e->obs[order[i]].pos[2] = -99.9; }
     }
     e->have_recent = e->have_prev = 0;                 /* reach_ao.py:1025-1026 */
+    e->npast = 0;                                      /* reach_ao.py:1028-1033 */
+    if (e->cfg.obstacle_obs == 5 && e->nobs > 0) { float tmp[81]; task_obs(e, tmp); task_obs(e, tmp); }
   }
   float a[3], g[3];
   pgo_env_get_obs(e, obs, a, g);

@@ -51,4 +51,4 @@ class TrainConfig:
 CONTROL = {"js": 0, "joints": 0, "ee": 1, "jsd": 2, "pcc": 3}
 REWARD_AO = {"sparse": 0, "wang": 1, "kumar_her": 2, "kumar_optim": 3, "kumar": 4}
 REWARD_CLASSIC = {"sparse": 0, "dense": 1}
-OBSTACLE_OBS = {"vectors+closest_per_link": 1, "vectors": 2, "closest_per_link": 3, "closest": 4}
+OBSTACLE_OBS = {"vectors+closest_per_link": 1, "vectors": 2, "closest_per_link": 3, "closest": 4, "vectors+past": 5}

@@ -82,7 +82,7 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   int t = 0;
   if (P.task == 1 && P.obstacle_obs != 0) {
     if (s->n_obstacles == 0) t = 27;
-    else t = P.obstacle_obs == 1 ? 36 : (P.obstacle_obs == 2 ? 27 : (P.obstacle_obs == 3 ? 9 : 1));
+    else t = P.obstacle_obs == 1 ? 36 : (P.obstacle_obs == 2 ? 27 : (P.obstacle_obs == 3 ? 9 : (P.obstacle_obs == 5 ? 81 : 1)));
   }
   P.task_obs_dim = t;
   P.obs_dim = 6 + (P.obs_js ? 14 : 0) + t;
@@ -197,12 +197,12 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   for (int k = 0; k < 3; k++) { P.scene.table_pos[k] = (float)P.table_pos[k]; P.scene.table_core[k] = (float)(P.table_half[k] - tm); }
   fill_stage(h, &cfg->stage);
   // observation width is fixed at creation (gym spaces); allocate for the widest layout
-  const int max_obs = 6 + 14 + 36;
+  const int max_obs = 6 + 14 + 81;
   int rc = PG_OK;
 #define A(ptr, count, st) if ((rc = alloc(h, &ptr, (size_t)(count), st)) != PG_OK) { pg_destroy(h); return rc; }
   A(P.q, 7 * n, true) A(P.qd, 7 * n, true) A(P.goal, 3 * n, true) A(P.obs_pos, (size_t)pg::kMaxObst * 3 * n, true) A(P.obs_pos_f, (size_t)pg::kMaxObst * 3 * n, true)
   A(P.recent, 7 * n, true) A(P.prev, 7 * n, true) A(P.cur_vel, 7 * n, true) A(P.cur_acc, 7 * n, true) A(P.jerk, 7 * n, true)
-  A(P.d_link, 9 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
+  A(P.d_link, 9 * n, true) A(P.past_vec, 54 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
   A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
   A(P.rng, 4 * n, true) A(P.episode, n, true)
   A(P.obs, (size_t)max_obs * n, true) A(P.achieved, 3 * n, true) A(P.desired, 3 * n, true) A(P.reward, n, true)

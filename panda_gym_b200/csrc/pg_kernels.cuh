@@ -60,6 +60,7 @@ struct Params {
   float *recent, *prev;          // [7][n] action history (panda.py:138-139)
   float *cur_vel, *cur_acc, *jerk; // [7][n] (panda.py:167-172)
   float* d_link;                 // [9][n]
+  float* past_vec;               // [2][27][n] previous two vector observations ("vectors+past", reach_ao.py:918-922)
   uint8_t *have_recent, *have_prev, *collided, *goal_reached, *need_reset;
   int *steps, *ep_len, *last_len;
   float *ep_ret, *last_ret;
@@ -170,8 +171,9 @@ struct StepOut { float ag[3]; bool success; };
 // RobotTaskEnv._get_obs (core.py:286-296) + Panda.get_obs (panda.py:264-288) + ReachAO.get_obs (reach_ao.py:902-959).
 // q_fk: joint angles behind PyBullet's cached link transforms (one substep old, see oracle/pgo_dyn.c);
 // cq/sq: cos/sin of the CURRENT q.
+// fresh: first observation of an episode (the reference pre-fills the "vectors+past" history at reset).
 __device__ __forceinline__ void observe(const Params& P, int e, const float* q, const float* qd, const float* q_fk, const float* cq,
-                                        const float* sq, float* ag_out) {
+                                        const float* sq, float* ag_out, bool fresh) {
   const int n = P.n;
   V3 base = v3(P.base[0], P.base[1], P.base[2]);
   // end-effector pose from the cached transforms
@@ -214,6 +216,18 @@ __device__ __forceinline__ void observe(const Params& P, int e, const float* q, 
       } else if (P.obstacle_obs == 3) {
 #pragma unroll
         for (int i = 0; i < 9; i++) o[off + i] = dl[i];
+      } else if (P.obstacle_obs == 5) {  // [v(t-2) | v(t-1) | v(t)], history shifted by one
+#pragma unroll
+        for (int i = 0; i < 9; i++) {
+          const float cur[3] = {ul[i].x, ul[i].y, ul[i].z};
+#pragma unroll
+          for (int k = 0; k < 3; k++) {
+            const int c = 3 * i + k;
+            float h2 = fresh ? cur[k] : P.past_vec[(size_t)c * n + e], h1 = fresh ? cur[k] : P.past_vec[(size_t)(27 + c) * n + e];
+            o[off + c] = h2; o[off + 27 + c] = h1; o[off + 54 + c] = cur[k];
+            P.past_vec[(size_t)c * n + e] = h1; P.past_vec[(size_t)(27 + c) * n + e] = cur[k];
+          }
+        }
       } else o[off] = mn;
     }
   }
@@ -425,7 +439,7 @@ __global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ 
   if (P.task == 1) P.collided[e] = collided;
   // --- observation, success, truncation, reward
   float ag[3], dg[3];
-  observe(P, e, q, qd, q_fk, cq, sq, ag);
+  observe(P, e, q, qd, q_fk, cq, sq, ag, false);
   dg[0] = P.desired[(size_t)e * 3]; dg[1] = P.desired[(size_t)e * 3 + 1]; dg[2] = P.desired[(size_t)e * 3 + 2];
   bool succ = is_success(P, e, ag, dg);
   bool terminated = P.terminate_on_success ? succ : false;
@@ -648,7 +662,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
   P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;
   if (status && leader) atomicAdd(&P.stats[6], 1.0);
   float ag[3], dg[3];
-  observe(P, e, q, qd, q, cq, sq, ag);
+  observe(P, e, q, qd, q, cq, sq, ag, true);
   dg[0] = (float)goal[0]; dg[1] = (float)goal[1]; dg[2] = (float)goal[2];
   bool succ = is_success(P, e, ag, dg);
   if (!WARP) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
@@ -662,7 +676,7 @@ __global__ void __launch_bounds__(kBlock) k_observe(const Params P) {
   float q[7], qd[7], cq[7], sq[7], ag[3];
 #pragma unroll
   for (int d = 0; d < 7; d++) { q[d] = P.q[(size_t)d * P.n + e]; qd[d] = P.qd[(size_t)d * P.n + e]; sincosf(q[d], &sq[d], &cq[d]); }
-  observe(P, e, q, qd, q, cq, sq, ag);
+  observe(P, e, q, qd, q, cq, sq, ag, true);
   if (P.task == 1) {
     bool hit = scene_pass<false, false>(true, P.scene, P.obs_pos_f, P.n, e, v3(P.base[0], P.base[1], P.base[2]), cq, sq, nullptr, nullptr);
     P.flags[e] = (uint8_t)((P.flags[e] & ~4) | (hit ? 4 : 0));

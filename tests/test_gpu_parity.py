@@ -228,7 +228,7 @@ def test_reach_ao_trajectories_and_flags(sim, oracle, scenario):
 
 
 @pytest.mark.parametrize("variant", ["halt_sparse", "wang", "kumar_her", "kumar_her_halt", "kumar_optim", "kumar", "scale_limiter",
-                                     "jsd", "pcc", "closest_per_link", "closest", "vectors", "no_truncate_flags"])
+                                     "jsd", "pcc", "closest_per_link", "closest", "vectors", "vectors_past", "no_truncate_flags"])
 def test_config_variants(sim, oracle, variant):
     """Every TrainConfig switch that reaches the env path (train_config.py:26-59): reward types, goal condition, action
     limiter, control types, obstacle observation modes -- rewards compared to 1e-5 (fp32 kernel vs fp64 oracle terms)."""
@@ -245,6 +245,7 @@ def test_config_variants(sim, oracle, variant):
     if variant == "pcc": tc.control_type = "pcc"; okw = dict(control=3)
     if variant == "closest_per_link": tc.task_observations = {"obstacles": "closest_per_link", "prior": None}; okw = dict(obstacle_obs=3)
     if variant == "closest": tc.task_observations = {"obstacles": "closest", "prior": None}; okw = dict(obstacle_obs=4)
+    if variant == "vectors_past": tc.task_observations = {"obstacles": "vectors+past", "prior": None}; okw = dict(obstacle_obs=5)
     if variant == "vectors": tc.task_observations = {"obstacles": "vectors", "prior": None}; okw = dict(obstacle_obs=2)
     if variant == "no_truncate_flags": tc.truncate_on_collision = False; tc.terminate_on_success = False; okw = dict(truncate_on_collision=0, terminate_on_success=0)
     n, steps = 24, 25
@@ -267,6 +268,8 @@ def test_config_variants(sim, oracle, variant):
             o, r, f = envs[i].step(A[i])
             compared += 1
             assert np.abs(o["observation"][:20] - og[i, :20]).max() < 1e-4
+            if variant == "vectors_past":  # 81 = three stacked vector observations, oldest first
+                assert o["observation"].shape[0] == 101 and np.abs(o["observation"][20:] - og[i, 20:]).max() < 2e-3
             assert flags_of(f) == fg[i]
             # jerk / effort terms are norms of joint-velocity differences: fp32-vs-fp64 velocity noise (~1e-5 rad/s) shows
             rtol = 2e-4 if variant.startswith("kumar") else 1e-5
