@@ -284,44 +284,56 @@ __device__ __forceinline__ void spd_inverse7(float* A) {
 
 // Generic projected Gauss-Seidel (cold path): joint-limit rows present and / or non-standard motor impulse
 // limits.  Bullet order: rows = [limits (dof order), motors (dof order)]; even iterations sweep backward, odd
-// forward; stop when max |residual| <= sqrt(1e-7).  Arrays live in local memory; this is rare.
-__device__ __noinline__ void pgs_generic(const float* Mi, const float* q, const float* qd, const float* rhs, const float* dinv,
-                                         const float* max_imp, float* dv_out) {
+// forward; stop when max |residual| <= sqrt(1e-7).  Not inlined (its register working set is larger than the hot
+// loop's); inputs arrive through local memory and are re-loaded into registers, the sweeps are fully unrolled.
+__device__ __noinline__ void pgs_generic(const float* Mi_in, const float* q, const float* qd, const float* rhs_in, const float* dinv_in,
+                                         const float* max_imp_in, float* dv_out) {
   const float lo[7] = {pgm::Link<1>::lo, pgm::Link<2>::lo, pgm::Link<3>::lo, pgm::Link<4>::lo, pgm::Link<5>::lo, pgm::Link<6>::lo, pgm::Link<7>::lo};
   const float hi[7] = {pgm::Link<1>::hi, pgm::Link<2>::hi, pgm::Link<3>::hi, pgm::Link<4>::hi, pgm::Link<5>::hi, pgm::Link<6>::hi, pgm::Link<7>::hi};
-  float app[7], dv[7], lrhs[7], lsg[7], lapp[7];
+  float Mi[28], rhs[7], dinv[7], max_imp[7], app[7], dv[7], lrhs[7], lsg[7], lapp[7];
+#pragma unroll
+  for (int k = 0; k < 28; k++) Mi[k] = Mi_in[k];
+#pragma unroll
   for (int d = 0; d < 7; d++) {
+    rhs[d] = rhs_in[d]; dinv[d] = dinv_in[d]; max_imp[d] = max_imp_in[d];
     app[d] = 0.f; dv[d] = 0.f; lsg[d] = 0.f; lrhs[d] = 0.f; lapp[d] = 0.f;
     float pl = q[d] - lo[d], pu = hi[d] - q[d];  // btMultiBodyJointLimitConstraint: row only when at / over the limit
     if (pl <= 0.f) { lsg[d] = 1.f; lrhs[d] = (-pl * kLimitErp / kDt - qd[d]) * dinv[d]; }
     else if (pu <= 0.f) { lsg[d] = -1.f; lrhs[d] = (-pu * kLimitErp / kDt + qd[d]) * dinv[d]; }
   }
-  for (int it = 0; it < kSolverIters; it++) {
-    float res = 0.f;
-    const bool fwd = (it & 1) != 0;
-    for (int r = 0; r < 14; r++) {
-      int row = fwd ? r : 13 - r;       // rows 0..6 = limits, 7..13 = motors
-      int d = row < 7 ? row : row - 7;
-      float delta, sd;
-      if (row < 7) {
-        if (lsg[d] == 0.f) continue;
-        delta = lrhs[d] - lsg[d] * dv[d] * dinv[d];
-        float sum = lapp[d] + delta;
-        if (sum < 0.f) { delta = -lapp[d]; lapp[d] = 0.f; }
-        else if (sum > kLimitMaxImpulse) { delta = kLimitMaxImpulse - lapp[d]; lapp[d] = kLimitMaxImpulse; }
-        else lapp[d] = sum;
-        sd = lsg[d] * delta;
-      } else {
-        if (max_imp[d] == 0.f) continue;
-        float t = fmaf(-dv[d], dinv[d], app[d] + rhs[d]);
-        float cl = fminf(fmaxf(t, -max_imp[d]), max_imp[d]);
-        delta = cl - app[d]; app[d] = cl; sd = delta;
-      }
-      for (int i = 0; i < 7; i++) dv[i] = fmaf(Mi[sym(i, d)], sd, dv[i]);
-      res = fmaxf(res, fabsf(delta * Mi[sym(d, d)]));
-    }
+#define PG_GM_ROW(d)                                                        \
+  if (max_imp[d] != 0.f) {                                                  \
+    float t = fmaf(-dv[d], dinv[d], app[d] + rhs[d]);                       \
+    float cl = fminf(fmaxf(t, -max_imp[d]), max_imp[d]);                    \
+    float delta = cl - app[d];                                              \
+    app[d] = cl;                                                            \
+    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] = fmaf(Mi[sym(i, d)], delta, dv[i]); \
+    res = fmaxf(res, fabsf(delta * Mi[sym(d, d)]));                         \
+  }
+#define PG_GL_ROW(d)                                                        \
+  if (lsg[d] != 0.f) {                                                      \
+    float delta = lrhs[d] - lsg[d] * dv[d] * dinv[d];                       \
+    float sum = lapp[d] + delta;                                            \
+    if (sum < 0.f) { delta = -lapp[d]; lapp[d] = 0.f; }                     \
+    else if (sum > kLimitMaxImpulse) { delta = kLimitMaxImpulse - lapp[d]; lapp[d] = kLimitMaxImpulse; } \
+    else lapp[d] = sum;                                                     \
+    float sd = lsg[d] * delta;                                              \
+    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] = fmaf(Mi[sym(i, d)], sd, dv[i]); \
+    res = fmaxf(res, fabsf(delta * Mi[sym(d, d)]));                         \
+  }
+  for (int it = 0; it < kSolverIters; it += 2) {
+    float res = 0.f;  // even iteration: backward (motors 6..0, then limits 6..0)
+    PG_GM_ROW(6) PG_GM_ROW(5) PG_GM_ROW(4) PG_GM_ROW(3) PG_GM_ROW(2) PG_GM_ROW(1) PG_GM_ROW(0)
+    PG_GL_ROW(6) PG_GL_ROW(5) PG_GL_ROW(4) PG_GL_ROW(3) PG_GL_ROW(2) PG_GL_ROW(1) PG_GL_ROW(0)
+    if (res <= 3.1622777e-4f) break;
+    res = 0.f;        // odd iteration: forward (limits 0..6, then motors 0..6)
+    PG_GL_ROW(0) PG_GL_ROW(1) PG_GL_ROW(2) PG_GL_ROW(3) PG_GL_ROW(4) PG_GL_ROW(5) PG_GL_ROW(6)
+    PG_GM_ROW(0) PG_GM_ROW(1) PG_GM_ROW(2) PG_GM_ROW(3) PG_GM_ROW(4) PG_GM_ROW(5) PG_GM_ROW(6)
     if (res <= 3.1622777e-4f) break;
   }
+#undef PG_GM_ROW
+#undef PG_GL_ROW
+#pragma unroll
   for (int d = 0; d < 7; d++) dv_out[d] = dv[d];
 }
 

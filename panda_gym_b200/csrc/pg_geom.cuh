@@ -233,6 +233,10 @@ template <typename T> __host__ __device__ __forceinline__ ClosestT<T> cyl_box(V3
 __device__ __forceinline__ float cyl_table_distance(V3 c, V3 a, float r, float h, V3 b, V3 e, float m) {
   float bound = sqrtf(r * r + h * h);
   float top = b.z + e.z;
+  // only the SIGN of a table distance is ever consumed (collision flag): a cylinder whose bounding sphere clears the
+  // plane of the table top cannot touch the box, wherever it is in x / y
+  float clear = c.z - bound - top - m - kHullMargin;
+  if (clear > 0.f) return clear;
   if (fabsf(c.x - b.x) + bound <= e.x && fabsf(c.y - b.y) + bound <= e.y && c.z >= top) {
     float ext = fabsf(a.z) * h + r * sqrtf(fmaxf(1.f - a.z * a.z, 0.f));
     return (c.z - ext) - top - m - kHullMargin;

@@ -146,8 +146,7 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const float* __r
   }
   if (S >= 1 && P.has_table) {  // table: panda_link0 / panda_link1 ignored (reach_ao.py:898)
     bool near = true;
-    if (!FULL) near = (ctr.z - R) <= (P.table_pos[2] + P.table_core[2] + P.table_margin + 0.002f) ||
-                      fabsf(ctr.x - P.table_pos[0]) + R > P.table_core[0] || fabsf(ctr.y - P.table_pos[1]) + R > P.table_core[1];
+    if (!FULL) near = (ctr.z - R) <= (P.table_pos[2] + P.table_core[2] + P.table_margin + 0.002f);  // else: above the top plane
     if (near && PrimLoop<K0, N>::table(F, P) <= 0.f) hit = true;
   }
   if (FULL) { d_out = best; u_out = dir; }  // sign / saturation applied after the deferred queries (scene_pass)
