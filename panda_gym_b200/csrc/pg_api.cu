@@ -249,6 +249,45 @@ int pg_seed(pg_handle h, uint64_t base_seed, uint64_t first_env_index) {
   return PG_OK;
 }
 
+// Which step kernel runs: 1 = one environment per thread (default), 2 = two environments per thread on the packed
+// fp32 pipe -- an experiment kept for A/B measurements, compiled only with -DPG_PAIR_KERNEL (measured slower on B200:
+// FFMA2 holds the fma pipe for two cycles, so it only saves issue slots, and 7 warps/SM hide less latency than 14;
+// profiles/r01_k_step_summary.md section F).  PANDA_B200_STEP_KERNEL / pg_set_step_kernel() select it.
+static int g_step_kernel = 0;
+static int step_kernel() {
+  if (g_step_kernel == 0) {
+    const char* e = getenv("PANDA_B200_STEP_KERNEL");
+#ifdef PG_PAIR_KERNEL
+    g_step_kernel = (e && e[0] == '2') ? 2 : 1;
+#else
+    (void)e;
+    g_step_kernel = 1;
+#endif
+  }
+  return g_step_kernel;
+}
+#ifdef PG_PAIR_KERNEL
+static cudaError_t pair_kernel_smem() {  // opt in to > 48 KB dynamic shared memory, once per device
+  static bool done[64] = {};
+  int dev = 0;
+  cudaError_t r = cudaGetDevice(&dev);
+  if (r != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return r;
+  r = cudaFuncSetAttribute(pg::k_step2, cudaFuncAttributeMaxDynamicSharedMemorySize, pg::kPairSmemBytes);
+  if (r == cudaSuccess) r = cudaFuncSetAttribute(pg::k_debug_substeps2, cudaFuncAttributeMaxDynamicSharedMemorySize, pg::kPairSmemBytes);
+  if (r == cudaSuccess) done[dev] = true;
+  return r;
+}
+#endif
+int pg_set_step_kernel(int which) {
+  if (which != 1 && which != 2) return fail(PG_ERR_ARG, "step kernel must be 1 or 2");
+#ifndef PG_PAIR_KERNEL
+  if (which == 2) return fail(PG_ERR_UNSUPPORTED, "the packed two-environment kernel is not compiled in (-DPG_PAIR_KERNEL)");
+#endif
+  g_step_kernel = which;
+  return PG_OK;
+}
+int pg_get_step_kernel(void) { return step_kernel(); }
+
 int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, void* stream) {
   if (!h) return fail(PG_ERR_ARG, "NULL handle");
   PG_CUDA(cudaSetDevice(h->device));
@@ -262,6 +301,12 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   if (!h || !actions_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
   if (h->P.auto_reset) PG_CUDA(cudaMemsetAsync(h->P.reset_count, 0, sizeof(int), (cudaStream_t)stream));
+#ifdef PG_PAIR_KERNEL
+  if (step_kernel() == 2) {
+    PG_CUDA(pair_kernel_smem());
+    pg::k_step2<<<(h->P.n + pg::kPairEnvs - 1) / pg::kPairEnvs, pg::kPairBlock, pg::kPairSmemBytes, (cudaStream_t)stream>>>(h->P, actions_dev);
+  } else
+#endif
   pg::k_step<<<(h->P.n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
   h->launches++;
   if (h->P.auto_reset) {
@@ -431,6 +476,12 @@ int pg_debug_substeps(int device, int n, float* q, float* qd, const float* tgt, 
   static const float kForces[7] = {87.f, 87.f, 87.f, 87.f, 12.f, 120.f, 120.f};  // panda.py:63, compiled into the kernels
   for (int d = 0; d < 7; d++) if (f[d] != kForces[d]) return fail(PG_ERR_UNSUPPORTED, "max_force must equal Panda.joint_forces (panda.py:63)");
   PG_CUDA(cudaSetDevice(device));
+#ifdef PG_PAIR_KERNEL
+  if (step_kernel() == 2) {
+    PG_CUDA(pair_kernel_smem());
+    pg::k_debug_substeps2<<<(n + pg::kPairEnvs - 1) / pg::kPairEnvs, pg::kPairBlock, pg::kPairSmemBytes, (cudaStream_t)stream>>>(n, q, qd, tgt, n_sub, velocity_mode);
+  } else
+#endif
   pg::k_debug_substeps<<<(n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(n, q, qd, tgt, f[0], f[1], f[2], f[3], f[4], f[5], f[6], n_sub, velocity_mode);
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -454,11 +505,22 @@ int pg_debug_step_kernel_attrs(int device, int* out /* [6]: regs, maxThreadsPerB
   if (!out) return fail(PG_ERR_ARG, "bad argument");
   PG_CUDA(cudaSetDevice(device));
   cudaFuncAttributes a;
-  PG_CUDA(cudaFuncGetAttributes(&a, pg::k_step));
   int occ = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pg::k_step, pg::kStepBlock, 0);
-  out[0] = a.numRegs; out[1] = a.maxThreadsPerBlock; out[2] = (int)a.sharedSizeBytes; out[3] = (int)a.localSizeBytes;
-  out[4] = pg::kStepBlock; out[5] = occ;
+#ifdef PG_PAIR_KERNEL
+  if (step_kernel() == 2) {
+    PG_CUDA(pair_kernel_smem());
+    PG_CUDA(cudaFuncGetAttributes(&a, pg::k_step2));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pg::k_step2, pg::kPairBlock, pg::kPairSmemBytes);
+    out[2] = (int)a.sharedSizeBytes + pg::kPairSmemBytes; out[4] = pg::kPairBlock;
+  } else
+#endif
+  {
+    PG_CUDA(cudaFuncGetAttributes(&a, pg::k_step));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pg::k_step, pg::kStepBlock, 0);
+    out[2] = (int)a.sharedSizeBytes; out[4] = pg::kStepBlock;
+  }
+  out[0] = a.numRegs; out[1] = a.maxThreadsPerBlock; out[3] = (int)a.localSizeBytes;
+  out[5] = occ;
   return PG_OK;
 }
 

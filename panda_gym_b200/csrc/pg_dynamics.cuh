@@ -12,37 +12,47 @@
 // joint origin is Rx(0 / +-90 deg), which the templates below fold into sign flips.
 #pragma once
 #include "pg_model.cuh"
+#include "pg_packed.cuh"
 
 namespace pg {
 
 template <typename T> struct V3T { T x, y, z; };
 using V3 = V3T<float>;
 using D3 = V3T<double>;
+using V3P = V3T<P2>;
+template <typename T> struct ident { using type = T; };
 template <typename T> __host__ __device__ __forceinline__ V3T<T> v3t(T x, T y, T z) { V3T<T> r; r.x = x; r.y = y; r.z = z; return r; }
 __host__ __device__ __forceinline__ V3 v3(float x, float y, float z) { return v3t<float>(x, y, z); }
 template <typename T> __host__ __device__ __forceinline__ V3T<T> operator+(V3T<T> a, V3T<T> b) { return v3t<T>(a.x + b.x, a.y + b.y, a.z + b.z); }
 template <typename T> __host__ __device__ __forceinline__ V3T<T> operator-(V3T<T> a, V3T<T> b) { return v3t<T>(a.x - b.x, a.y - b.y, a.z - b.z); }
-template <typename T> __host__ __device__ __forceinline__ V3T<T> operator*(T s, V3T<T> a) { return v3t<T>(s * a.x, s * a.y, s * a.z); }
+template <typename T> __host__ __device__ __forceinline__ V3T<T> operator*(typename ident<T>::type s, V3T<T> a) { return v3t<T>(s * a.x, s * a.y, s * a.z); }
 template <typename T> __host__ __device__ __forceinline__ V3T<T> cross(V3T<T> a, V3T<T> b) { return v3t<T>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 template <typename T> __host__ __device__ __forceinline__ T dot(V3T<T> a, V3T<T> b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+// y + s * x, one fused multiply-add per component
+template <typename T> __host__ __device__ __forceinline__ V3T<T> axpy(typename ident<T>::type s, V3T<T> x, V3T<T> y) { return v3t<T>(s * x.x + y.x, s * x.y + y.y, s * x.z + y.z); }
+// a compile-time vector (URDF constant) against a run-time one: the constant stays a scalar float operand
+__device__ __forceinline__ V3 cross_c(V3 a, V3 b) { return cross(a, b); }
+__device__ __forceinline__ V3P cross_c(V3 a, V3P b) { return v3t<P2>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+__device__ __forceinline__ V3P cross_c(V3P a, V3 b) { return v3t<P2>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 __device__ __forceinline__ float norm(V3 a) { return sqrtf(dot(a, a)); }
+__device__ __forceinline__ P2 norm(V3P a) { return vsqrt(dot(a, a)); }
 __host__ __device__ __forceinline__ double norm(D3 a) { return sqrt(dot(a, a)); }
 
 // child -> parent:  E = Rx(ROT*90deg) * Rz(q)
-template <int ROT>
-__device__ __forceinline__ V3 to_parent(V3 v, float c, float s) {
-  float x = c * v.x - s * v.y, y = s * v.x + c * v.y, z = v.z;
-  if (ROT == 1) return v3(x, -z, y);
-  if (ROT == -1) return v3(x, z, -y);
-  return v3(x, y, z);
+template <int ROT, typename T>
+__device__ __forceinline__ V3T<T> to_parent(V3T<T> v, T c, T s) {
+  T x = c * v.x - s * v.y, y = s * v.x + c * v.y, z = v.z;
+  if (ROT == 1) return v3t<T>(x, -z, y);
+  if (ROT == -1) return v3t<T>(x, z, -y);
+  return v3t<T>(x, y, z);
 }
 // parent -> child:  E^T
-template <int ROT>
-__device__ __forceinline__ V3 to_child(V3 v, float c, float s) {
-  V3 u = v;
-  if (ROT == 1) u = v3(v.x, v.z, -v.y);
-  if (ROT == -1) u = v3(v.x, -v.z, v.y);
-  return v3(c * u.x + s * u.y, -s * u.x + c * u.y, u.z);
+template <int ROT, typename T>
+__device__ __forceinline__ V3T<T> to_child(V3T<T> v, T c, T s) {
+  V3T<T> u = v;
+  if (ROT == 1) u = v3t<T>(v.x, v.z, -v.y);
+  if (ROT == -1) u = v3t<T>(v.x, -v.z, v.y);
+  return v3t<T>(c * u.x + s * u.y, c * u.y - s * u.x, u.z);
 }
 
 constexpr float kDt = 1.0f / 500.0f;      // pybullet.py:50
@@ -55,75 +65,84 @@ constexpr int kSolverIters = 50;          // PyBullet numSolverIterations
 constexpr float kResidualThr = 1e-7f;     // PyBullet solverResidualThreshold
 
 // kinematic state of a link frame, expressed in that frame
-struct Kin { V3 w, al, a, v; };
+template <typename T> struct KinT { V3T<T> w, al, a, v; };
 
 // wrench (about the frame origin) of one rigid body riding on a frame with state k:
 // Newton-Euler with qdd = 0 plus btMultiBody's velocity damping  m v (k + k|v|),  I w (k + k|w|).
-__device__ __forceinline__ void body_wrench(const Kin& k, float m, V3 c, float ixx, float iyy, float izz, float ixy, float ixz,
-                                            float iyz, V3& f, V3& n) {
-  V3 wc = cross(k.w, c);
-  V3 vc = k.v + wc;
-  V3 ac = k.a + cross(k.al, c) + cross(k.w, wc);
-  float dl = kDamp + kDamp * norm(vc);
-  V3 F = m * (ac + dl * vc);
-  V3 Iw = v3(ixx * k.w.x + ixy * k.w.y + ixz * k.w.z, ixy * k.w.x + iyy * k.w.y + iyz * k.w.z, ixz * k.w.x + iyz * k.w.y + izz * k.w.z);
-  V3 Ia = v3(ixx * k.al.x + ixy * k.al.y + ixz * k.al.z, ixy * k.al.x + iyy * k.al.y + iyz * k.al.z, ixz * k.al.x + iyz * k.al.y + izz * k.al.z);
-  float da = kDamp + kDamp * norm(k.w);
-  V3 N = Ia + cross(k.w, Iw) + da * Iw;
+// m, c, inertia are URDF constants (scalar float operands for both T).
+template <typename T>
+__device__ __forceinline__ void body_wrench(const KinT<T>& k, float m, V3 c, float ixx, float iyy, float izz, float ixy, float ixz,
+                                            float iyz, V3T<T>& f, V3T<T>& n) {
+  V3T<T> wc = cross_c(k.w, c);
+  V3T<T> vc = k.v + wc;
+  V3T<T> ac = k.a + cross_c(k.al, c) + cross(k.w, wc);
+  T dl = kDamp + kDamp * norm(vc);
+  V3T<T> F = m * axpy<T>(dl, vc, ac);
+  V3T<T> Iw, Ia;
+  if (ixy == 0.f && ixz == 0.f && iyz == 0.f) {  // folded at compile time (arm links have diagonal tensors)
+    Iw = v3t<T>(ixx * k.w.x, iyy * k.w.y, izz * k.w.z);
+    Ia = v3t<T>(ixx * k.al.x, iyy * k.al.y, izz * k.al.z);
+  } else {
+    Iw = v3t<T>(ixx * k.w.x + ixy * k.w.y + ixz * k.w.z, ixy * k.w.x + iyy * k.w.y + iyz * k.w.z, ixz * k.w.x + iyz * k.w.y + izz * k.w.z);
+    Ia = v3t<T>(ixx * k.al.x + ixy * k.al.y + ixz * k.al.z, ixy * k.al.x + iyy * k.al.y + iyz * k.al.z, ixz * k.al.x + iyz * k.al.y + izz * k.al.z);
+  }
+  T da = kDamp + kDamp * norm(k.w);
+  V3T<T> N = axpy<T>(da, Iw, Ia) + cross(k.w, Iw);
   f = f + F;
-  n = n + N + cross(c, F);
+  n = n + N + cross_c(c, F);
 }
 
-template <int I>
-__device__ __forceinline__ Kin kin_step(const Kin& p, float c, float s, float qd) {
+template <int I, typename T>
+__device__ __forceinline__ KinT<T> kin_step(const KinT<T>& p, T c, T s, T qd) {
   using L = pgm::Link<I>;
   const V3 pp = v3(L::px, L::py, L::pz);
-  Kin k;
-  V3 wc = to_child<L::rot>(p.w, c, s);
-  k.w = v3(wc.x, wc.y, wc.z + qd);
-  V3 alc = to_child<L::rot>(p.al, c, s);
-  k.al = v3(alc.x + wc.y * qd, alc.y - wc.x * qd, alc.z);
-  V3 wxp = cross(p.w, pp);
-  k.a = to_child<L::rot>(p.a + cross(p.al, pp) + cross(p.w, wxp), c, s);
+  KinT<T> k;
+  V3T<T> wc = to_child<L::rot>(p.w, c, s);
+  k.w = v3t<T>(wc.x, wc.y, wc.z + qd);
+  V3T<T> alc = to_child<L::rot>(p.al, c, s);
+  k.al = v3t<T>(alc.x + wc.y * qd, alc.y - wc.x * qd, alc.z);
+  V3T<T> wxp = cross_c(p.w, pp);
+  k.a = to_child<L::rot>(p.a + cross_c(p.al, pp) + cross(p.w, wxp), c, s);
   k.v = to_child<L::rot>(p.v + wxp, c, s);
   return k;
 }
 
-template <int I>
-__device__ __forceinline__ void link_wrench(const Kin& k, V3& f, V3& n) {
+template <int I, typename T>
+__device__ __forceinline__ void link_wrench(const KinT<T>& k, V3T<T>& f, V3T<T>& n) {
   using L = pgm::Link<I>;
-  f = v3(0, 0, 0); n = v3(0, 0, 0);
-  body_wrench(k, L::m, v3(L::cx, L::cy, L::cz), L::ixx, L::iyy, L::izz, 0.f, 0.f, 0.f, f, n);
+  f = v3t<T>(0.f, 0.f, 0.f); n = v3t<T>(0.f, 0.f, 0.f);
+  body_wrench<T>(k, L::m, v3(L::cx, L::cy, L::cz), L::ixx, L::iyy, L::izz, 0.f, 0.f, 0.f, f, n);
 }
-template <int K>
-__device__ __forceinline__ void sub_wrench(const Kin& k, V3& f, V3& n) {
+template <int K, typename T>
+__device__ __forceinline__ void sub_wrench(const KinT<T>& k, V3T<T>& f, V3T<T>& n) {
   using S = pgm::Sub<K>;
-  body_wrench(k, S::m, v3(S::cx, S::cy, S::cz), S::ixx, S::iyy, S::izz, S::ixy, S::ixz, S::iyz, f, n);
+  body_wrench<T>(k, S::m, v3(S::cx, S::cy, S::cz), S::ixx, S::iyy, S::izz, S::ixy, S::ixz, S::iyz, f, n);
 }
 
 // child wrench -> parent frame, accumulated
-template <int I>
-__device__ __forceinline__ void wrench_up(V3 fc, V3 nc, float c, float s, V3& f, V3& n) {
+template <int I, typename T>
+__device__ __forceinline__ void wrench_up(V3T<T> fc, V3T<T> nc, T c, T s, V3T<T>& f, V3T<T>& n) {
   using L = pgm::Link<I>;
-  V3 fp = to_parent<L::rot>(fc, c, s);
-  V3 np = to_parent<L::rot>(nc, c, s);
+  V3T<T> fp = to_parent<L::rot>(fc, c, s);
+  V3T<T> np = to_parent<L::rot>(nc, c, s);
   f = f + fp;
-  n = n + np + cross(v3(L::px, L::py, L::pz), fp);
+  n = n + np + cross_c(v3(L::px, L::py, L::pz), fp);
 }
 
 // tau_b[i] = joint torque needed to hold qdd = 0  (== C(q,qd) qd + g(q) + damping)
-__device__ __forceinline__ void rnea_bias(const float* cq, const float* sq, const float* qd, float* tau) {
-  Kin k0;
-  k0.w = v3(0, 0, 0); k0.al = v3(0, 0, 0); k0.v = v3(0, 0, 0);
-  k0.a = v3(0, 0, kGravity);  // gravity as base acceleration
-  V3 f1, n1, f2, n2, f3, n3, f4, n4, f5, n5, f6, n6, f7, n7;
-  Kin k1 = kin_step<1>(k0, cq[0], sq[0], qd[0]); link_wrench<1>(k1, f1, n1);
-  Kin k2 = kin_step<2>(k1, cq[1], sq[1], qd[1]); link_wrench<2>(k2, f2, n2);
-  Kin k3 = kin_step<3>(k2, cq[2], sq[2], qd[2]); link_wrench<3>(k3, f3, n3);
-  Kin k4 = kin_step<4>(k3, cq[3], sq[3], qd[3]); link_wrench<4>(k4, f4, n4);
-  Kin k5 = kin_step<5>(k4, cq[4], sq[4], qd[4]); link_wrench<5>(k5, f5, n5);
-  Kin k6 = kin_step<6>(k5, cq[5], sq[5], qd[5]); link_wrench<6>(k6, f6, n6);
-  Kin k7 = kin_step<7>(k6, cq[6], sq[6], qd[6]); link_wrench<7>(k7, f7, n7);
+template <typename T>
+__device__ __forceinline__ void rnea_bias(const T* cq, const T* sq, const T* qd, T* tau) {
+  KinT<T> k0;
+  k0.w = v3t<T>(0.f, 0.f, 0.f); k0.al = v3t<T>(0.f, 0.f, 0.f); k0.v = v3t<T>(0.f, 0.f, 0.f);
+  k0.a = v3t<T>(0.f, 0.f, kGravity);  // gravity as base acceleration
+  V3T<T> f1, n1, f2, n2, f3, n3, f4, n4, f5, n5, f6, n6, f7, n7;
+  KinT<T> k1 = kin_step<1>(k0, cq[0], sq[0], qd[0]); link_wrench<1>(k1, f1, n1);
+  KinT<T> k2 = kin_step<2>(k1, cq[1], sq[1], qd[1]); link_wrench<2>(k2, f2, n2);
+  KinT<T> k3 = kin_step<3>(k2, cq[2], sq[2], qd[2]); link_wrench<3>(k3, f3, n3);
+  KinT<T> k4 = kin_step<4>(k3, cq[3], sq[3], qd[3]); link_wrench<4>(k4, f4, n4);
+  KinT<T> k5 = kin_step<5>(k4, cq[4], sq[4], qd[4]); link_wrench<5>(k5, f5, n5);
+  KinT<T> k6 = kin_step<6>(k5, cq[5], sq[5], qd[5]); link_wrench<6>(k6, f6, n6);
+  KinT<T> k7 = kin_step<7>(k6, cq[6], sq[6], qd[6]); link_wrench<7>(k7, f7, n7);
   sub_wrench<0>(k7, f7, n7); sub_wrench<1>(k7, f7, n7); sub_wrench<2>(k7, f7, n7);
   tau[6] = n7.z; wrench_up<7>(f7, n7, cq[6], sq[6], f6, n6);
   tau[5] = n6.z; wrench_up<6>(f6, n6, cq[5], sq[5], f5, n5);
@@ -135,8 +154,10 @@ __device__ __forceinline__ void rnea_bias(const float* cq, const float* sq, cons
 }
 
 // ---------------------------------------------------------------------------------------------- CRBA
-// spatial inertia about a frame origin: mass, first moment h = m c, rotational inertia about the origin
-struct SI { float m; V3 h; float xx, yy, zz, xy, xz, yz; };
+// spatial inertia about a frame origin: mass (a sum of URDF constants: always a scalar), first moment h = m c,
+// rotational inertia about the origin
+template <typename T> struct SIT { float m; V3T<T> h; T xx, yy, zz, xy, xz, yz; };
+using SI = SIT<float>;
 
 __device__ __forceinline__ void si_add_body(SI& S, float m, V3 c, float ixx, float iyy, float izz, float ixy, float ixz, float iyz) {
   S.m += m;
@@ -157,41 +178,53 @@ __device__ __forceinline__ void si_add_sub(SI& S) {
   using B = pgm::Sub<K>;
   si_add_body(S, B::m, v3(B::cx, B::cy, B::cz), B::ixx, B::iyy, B::izz, B::ixy, B::ixz, B::iyz);
 }
-// express child composite inertia (frame I) in the parent frame (I-1) and add it to P
-template <int I>
-__device__ __forceinline__ void si_up(const SI& C, float c, float s, SI& P) {
+template <typename T>
+__device__ __forceinline__ SIT<T> si_cast(const SI& S) {
+  SIT<T> R; R.m = S.m; R.h = v3t<T>(S.h.x, S.h.y, S.h.z);
+  R.xx = S.xx; R.yy = S.yy; R.zz = S.zz; R.xy = S.xy; R.xz = S.xz; R.yz = S.yz;
+  return R;
+}
+// composite inertia of frame I-1: its own link (P0, constants) + the child composite C (frame I) re-expressed
+template <int I, typename T>
+__device__ __forceinline__ SIT<T> si_up(const SIT<T>& C, T c, T s, const SI& P0) {
   using L = pgm::Link<I>;
   // rotate about z by q:  T = Rz I Rz^T
-  float xx = c * c * C.xx - 2.f * c * s * C.xy + s * s * C.yy;
-  float yy = s * s * C.xx + 2.f * c * s * C.xy + c * c * C.yy;
-  float xy = c * s * (C.xx - C.yy) + (c * c - s * s) * C.xy;
-  float xz = c * C.xz - s * C.yz;
-  float yz = s * C.xz + c * C.yz;
-  float zz = C.zz;
+  T cc = c * c, ss = s * s, cs = c * s;
+  T cs2 = cs + cs, c2 = cc - ss;
+  T xx = cc * C.xx - cs2 * C.xy + ss * C.yy;
+  T yy = ss * C.xx + cs2 * C.xy + cc * C.yy;
+  T xy = cs * (C.xx - C.yy) + c2 * C.xy;
+  T xz = c * C.xz - s * C.yz;
+  T yz = s * C.xz + c * C.yz;
+  T zz = C.zz;
   // then Rx(+-90): (x,y,z) -> (x,-z,y) / (x,z,-y)
-  float Xx = xx, Yy = yy, Zz = zz, Xy = xy, Xz = xz, Yz = yz;
+  T Xx = xx, Yy = yy, Zz = zz, Xy = xy, Xz = xz, Yz = yz;
   if (L::rot == 1) { Yy = zz; Zz = yy; Xy = -xz; Xz = xy; Yz = -yz; }
   if (L::rot == -1) { Yy = zz; Zz = yy; Xy = xz; Xz = -xy; Yz = -yz; }
-  V3 g = to_parent<L::rot>(C.h, c, s);
-  const V3 p = v3(L::px, L::py, L::pz);
-  float pg2 = 2.f * dot(p, g), pp = dot(p, p);
-  P.m += C.m;
-  P.h = P.h + g + C.m * p;
-  P.xx += Xx - 2.f * g.x * p.x + pg2 - C.m * p.x * p.x + C.m * pp;
-  P.yy += Yy - 2.f * g.y * p.y + pg2 - C.m * p.y * p.y + C.m * pp;
-  P.zz += Zz - 2.f * g.z * p.z + pg2 - C.m * p.z * p.z + C.m * pp;
-  P.xy += Xy - (g.x * p.y + p.x * g.y) - C.m * p.x * p.y;
-  P.xz += Xz - (g.x * p.z + p.x * g.z) - C.m * p.x * p.z;
-  P.yz += Yz - (g.y * p.z + p.y * g.z) - C.m * p.y * p.z;
+  V3T<T> g = to_parent<L::rot>(C.h, c, s);
+  constexpr float px = L::px, py = L::py, pz = L::pz, pp = px * px + py * py + pz * pz;
+  const float m = C.m;  // compile-time after inlining
+  T pg2 = (2.f * px) * g.x + (2.f * py) * g.y + (2.f * pz) * g.z;
+  SIT<T> R;
+  R.m = P0.m + m;
+  R.h = v3t<T>(g.x + (P0.h.x + m * px), g.y + (P0.h.y + m * py), g.z + (P0.h.z + m * pz));
+  R.xx = (Xx - (2.f * px) * g.x) + pg2 + (P0.xx + m * (pp - px * px));
+  R.yy = (Yy - (2.f * py) * g.y) + pg2 + (P0.yy + m * (pp - py * py));
+  R.zz = (Zz - (2.f * pz) * g.z) + pg2 + (P0.zz + m * (pp - pz * pz));
+  R.xy = (Xy - (py * g.x + px * g.y)) + (P0.xy - m * px * py);
+  R.xz = (Xz - (pz * g.x + px * g.z)) + (P0.xz - m * px * pz);
+  R.yz = (Yz - (pz * g.y + py * g.z)) + (P0.yz - m * py * pz);
+  return R;
 }
 // force produced by unit acceleration of a z-axis joint on composite inertia C: n = I[:,z], f = z x h
-__device__ __forceinline__ void si_col(const SI& C, V3& f, V3& n) { f = v3(-C.h.y, C.h.x, 0.f); n = v3(C.xz, C.yz, C.zz); }
-template <int I>
-__device__ __forceinline__ void col_up(V3& f, V3& n, float c, float s) {
+template <typename T>
+__device__ __forceinline__ void si_col(const SIT<T>& C, V3T<T>& f, V3T<T>& n) { f = v3t<T>(-C.h.y, C.h.x, 0.f); n = v3t<T>(C.xz, C.yz, C.zz); }
+template <int I, typename T>
+__device__ __forceinline__ void col_up(V3T<T>& f, V3T<T>& n, T c, T s) {
   using L = pgm::Link<I>;
-  V3 fp = to_parent<L::rot>(f, c, s);
-  V3 np = to_parent<L::rot>(n, c, s);
-  n = np + cross(v3(L::px, L::py, L::pz), fp);
+  V3T<T> fp = to_parent<L::rot>(f, c, s);
+  V3T<T> np = to_parent<L::rot>(n, c, s);
+  n = np + cross_c(v3(L::px, L::py, L::pz), fp);
   f = fp;
 }
 
@@ -199,37 +232,39 @@ __device__ __forceinline__ void col_up(V3& f, V3& n, float c, float s) {
 __host__ __device__ constexpr int sym(int i, int j) { return i >= j ? i * (i + 1) / 2 + j : j * (j + 1) / 2 + i; }
 
 // joint-space mass matrix, 28 packed entries
-__device__ __forceinline__ void crba(const float* cq, const float* sq, float* M) {
-  V3 f7, n7, f6, n6, f5, n5, f4, n4, f3, n3, f2, n2, f1, n1;
-  SI C = si_link<7>();
-  si_add_sub<0>(C); si_add_sub<1>(C); si_add_sub<2>(C);
+template <typename T>
+__device__ __forceinline__ void crba(const T* cq, const T* sq, T* M) {
+  V3T<T> f7, n7, f6, n6, f5, n5, f4, n4, f3, n3, f2, n2, f1, n1;
+  SI C7 = si_link<7>();
+  si_add_sub<0>(C7); si_add_sub<1>(C7); si_add_sub<2>(C7);
+  SIT<T> C = si_cast<T>(C7);
   si_col(C, f7, n7); M[sym(6, 6)] = n7.z;
-  SI P = si_link<6>(); si_up<7>(C, cq[6], sq[6], P); C = P;
+  C = si_up<7>(C, cq[6], sq[6], si_link<6>());
   col_up<7>(f7, n7, cq[6], sq[6]); M[sym(6, 5)] = n7.z;
   si_col(C, f6, n6); M[sym(5, 5)] = n6.z;
-  P = si_link<5>(); si_up<6>(C, cq[5], sq[5], P); C = P;
+  C = si_up<6>(C, cq[5], sq[5], si_link<5>());
   col_up<6>(f7, n7, cq[5], sq[5]); M[sym(6, 4)] = n7.z;
   col_up<6>(f6, n6, cq[5], sq[5]); M[sym(5, 4)] = n6.z;
   si_col(C, f5, n5); M[sym(4, 4)] = n5.z;
-  P = si_link<4>(); si_up<5>(C, cq[4], sq[4], P); C = P;
+  C = si_up<5>(C, cq[4], sq[4], si_link<4>());
   col_up<5>(f7, n7, cq[4], sq[4]); M[sym(6, 3)] = n7.z;
   col_up<5>(f6, n6, cq[4], sq[4]); M[sym(5, 3)] = n6.z;
   col_up<5>(f5, n5, cq[4], sq[4]); M[sym(4, 3)] = n5.z;
   si_col(C, f4, n4); M[sym(3, 3)] = n4.z;
-  P = si_link<3>(); si_up<4>(C, cq[3], sq[3], P); C = P;
+  C = si_up<4>(C, cq[3], sq[3], si_link<3>());
   col_up<4>(f7, n7, cq[3], sq[3]); M[sym(6, 2)] = n7.z;
   col_up<4>(f6, n6, cq[3], sq[3]); M[sym(5, 2)] = n6.z;
   col_up<4>(f5, n5, cq[3], sq[3]); M[sym(4, 2)] = n5.z;
   col_up<4>(f4, n4, cq[3], sq[3]); M[sym(3, 2)] = n4.z;
   si_col(C, f3, n3); M[sym(2, 2)] = n3.z;
-  P = si_link<2>(); si_up<3>(C, cq[2], sq[2], P); C = P;
+  C = si_up<3>(C, cq[2], sq[2], si_link<2>());
   col_up<3>(f7, n7, cq[2], sq[2]); M[sym(6, 1)] = n7.z;
   col_up<3>(f6, n6, cq[2], sq[2]); M[sym(5, 1)] = n6.z;
   col_up<3>(f5, n5, cq[2], sq[2]); M[sym(4, 1)] = n5.z;
   col_up<3>(f4, n4, cq[2], sq[2]); M[sym(3, 1)] = n4.z;
   col_up<3>(f3, n3, cq[2], sq[2]); M[sym(2, 1)] = n3.z;
   si_col(C, f2, n2); M[sym(1, 1)] = n2.z;
-  P = si_link<1>(); si_up<2>(C, cq[1], sq[1], P); C = P;
+  C = si_up<2>(C, cq[1], sq[1], si_link<1>());
   col_up<2>(f7, n7, cq[1], sq[1]); M[sym(6, 0)] = n7.z;
   col_up<2>(f6, n6, cq[1], sq[1]); M[sym(5, 0)] = n6.z;
   col_up<2>(f5, n5, cq[1], sq[1]); M[sym(4, 0)] = n5.z;
@@ -240,18 +275,19 @@ __device__ __forceinline__ void crba(const float* cq, const float* sq, float* M)
 }
 
 // M (packed, SPD) -> M^-1 (packed), in place, via Cholesky
-__device__ __forceinline__ void spd_inverse7(float* A) {
+template <typename T>
+__device__ __forceinline__ void spd_inverse7(T* A) {
   // L L^T = A  (lower, packed)
 #pragma unroll
   for (int j = 0; j < 7; j++) {
-    float d = A[sym(j, j)];
+    T d = A[sym(j, j)];
 #pragma unroll
     for (int k = 0; k < j; k++) d -= A[sym(j, k)] * A[sym(j, k)];
-    float inv = rsqrtf(d);
+    T inv = vrsqrt(d);
     A[sym(j, j)] = inv;  // store 1 / L_jj
 #pragma unroll
     for (int i = j + 1; i < 7; i++) {
-      float v = A[sym(i, j)];
+      T v = A[sym(i, j)];
 #pragma unroll
       for (int k = 0; k < j; k++) v -= A[sym(i, k)] * A[sym(j, k)];
       A[sym(i, j)] = v * inv;
@@ -262,10 +298,10 @@ __device__ __forceinline__ void spd_inverse7(float* A) {
   for (int j = 0; j < 7; j++) {
 #pragma unroll
     for (int i = j + 1; i < 7; i++) {
-      float v = 0.f;
+      // entries A[sym(k, j)] for j < k < i already hold W_kj (computed earlier in this i-loop)
+      T v = -(A[sym(i, j)] * A[sym(j, j)]);
 #pragma unroll
-      for (int k = j; k < i; k++) v -= A[sym(i, k)] * (k == j ? A[sym(j, j)] : A[sym(k, j)]);
-      // note: entries A[sym(k, j)] for j < k < i already hold W_kj (computed earlier in this i-loop)
+      for (int k = j + 1; k < i; k++) v -= A[sym(i, k)] * A[sym(k, j)];
       A[sym(i, j)] = v * A[sym(i, i)];
     }
   }
@@ -274,9 +310,9 @@ __device__ __forceinline__ void spd_inverse7(float* A) {
   for (int i = 0; i < 7; i++) {
 #pragma unroll
     for (int j = 0; j <= i; j++) {
-      float v = 0.f;
+      T v = A[sym(i, i)] * A[sym(i, j)];
 #pragma unroll
-      for (int k = i; k < 7; k++) v += A[sym(k, i)] * A[sym(k, j)];
+      for (int k = i + 1; k < 7; k++) v += A[sym(k, i)] * A[sym(k, j)];
       A[sym(i, j)] = v;
     }
   }
@@ -417,16 +453,23 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
     res = fmaxf(res, fabsf(delta * Mi[sym(d, d)]));                         \
   }
       const float kResAbs = 3.1622777e-4f;  // sqrt(1e-7): compare |residual| instead of residual^2
+      // Consecutive sweeps run in opposite directions, so every sweep after the first would start on the row the
+      // previous one just finished.  Re-solving a row whose residual was zeroed one instruction ago yields delta = 0
+      // in exact arithmetic (clamped or not) and ~1e-8 in fp32 (Bullet, in fp64: ~1e-17); those 49 of 350 row updates
+      // are skipped.  The residual test is unaffected (the skipped row would contribute ~0 to the maximum).
       bool live = true;
+      float carry = 0.f;
+      { float res = 0.f; PG_MOTOR_ROW(6) carry = res; }
       for (int it = 0; it < kSolverIters; it += 2) {
-        if (live) {  // even iteration: backward sweep
-          float res = 0.f;
-          PG_MOTOR_ROW(6) PG_MOTOR_ROW(5) PG_MOTOR_ROW(4) PG_MOTOR_ROW(3) PG_MOTOR_ROW(2) PG_MOTOR_ROW(1) PG_MOTOR_ROW(0)
+        if (live) {  // even iteration: backward sweep (row 6 done above / by the forward sweep before)
+          float res = carry;
+          PG_MOTOR_ROW(5) PG_MOTOR_ROW(4) PG_MOTOR_ROW(3) PG_MOTOR_ROW(2) PG_MOTOR_ROW(1) PG_MOTOR_ROW(0)
           if (res <= kResAbs) live = false;
         }
-        if (live) {  // odd iteration: forward sweep
+        carry = 0.f;
+        if (live) {  // odd iteration: forward sweep (row 0 just solved)
           float res = 0.f;
-          PG_MOTOR_ROW(0) PG_MOTOR_ROW(1) PG_MOTOR_ROW(2) PG_MOTOR_ROW(3) PG_MOTOR_ROW(4) PG_MOTOR_ROW(5) PG_MOTOR_ROW(6)
+          PG_MOTOR_ROW(1) PG_MOTOR_ROW(2) PG_MOTOR_ROW(3) PG_MOTOR_ROW(4) PG_MOTOR_ROW(5) PG_MOTOR_ROW(6)
           if (res <= kResAbs) live = false;
         }
         if (!__any_sync(__activemask(), live)) break;
@@ -449,5 +492,134 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
   }
   if (SYNC && PG_SYNC_D) __syncthreads();
 }
+
+
+#ifdef PG_PAIR_KERNEL
+// ---------------------------------------------------------------------------------------------- two environments / thread
+// The same stepSimulation() for an environment PAIR held in packed registers (pg_packed.cuh).  Lane-wise the
+// arithmetic is the scalar substep's; what differs is control:
+//  * actA / actB: a collided (or padding) half keeps its state -- its lanes still compute (finite values, the state is
+//    a valid frozen one) and the results are dropped by per-half selects;
+//  * the residual early-out of a half snapshots its dv into shared memory (snap) and lets the lanes run on; the
+//    snapshot is restored after the loop, which is exactly "this environment stopped iterating at that sweep";
+//  * a half that needs joint-limit rows / unit impulse limits goes through the scalar cold path afterwards.
+// q, tgt: shared memory, element d at [d * stride] (P2 = float2 per thread); snap: 14 floats at [k * snap_stride].
+__device__ __forceinline__ float half_of(P2 x, int h) { return h ? x.v.y : x.v.x; }
+__device__ __forceinline__ P2 sel2(bool a, bool b, P2 yes, P2 no) { return P2(a ? yes.v.x : no.v.x, b ? yes.v.y : no.v.y); }
+
+template <bool SYNC>
+__device__ __forceinline__ void substep2(bool actA, bool actB, bool velocity, bool unit_imp, P2* q, P2* qd, P2* cq, P2* sq, const P2* tgt,
+                                         int stride, float* snap, int snap_stride) {
+  P2 tau[7], Mi[28];
+  P2 rhs[7], dinv[7], dv[7];
+  const bool any = actA || actB;
+  if (any) rnea_bias(cq, sq, qd, tau);
+  if (SYNC && PG_SYNC_A) __syncthreads();
+  if (any) crba(cq, sq, Mi);
+  if (SYNC && PG_SYNC_B) __syncthreads();
+  bool slowA = unit_imp, slowB = unit_imp;
+  if (any) {
+    spd_inverse7(Mi);
+#pragma unroll
+    for (int i = 0; i < 7; i++) {
+      P2 acc = -(Mi[sym(i, 0)] * tau[0]);
+#pragma unroll
+      for (int j = 1; j < 7; j++) acc -= Mi[sym(i, j)] * tau[j];
+      qd[i] = sel2(actA, actB, vclamp(acc * kDt + qd[i], -kMaxCoordVel, kMaxCoordVel), qd[i]);
+    }
+    const float lo[7] = {pgm::Link<1>::lo, pgm::Link<2>::lo, pgm::Link<3>::lo, pgm::Link<4>::lo, pgm::Link<5>::lo, pgm::Link<6>::lo, pgm::Link<7>::lo};
+    const float hi[7] = {pgm::Link<1>::hi, pgm::Link<2>::hi, pgm::Link<3>::hi, pgm::Link<4>::hi, pgm::Link<5>::hi, pgm::Link<6>::hi, pgm::Link<7>::hi};
+#pragma unroll
+    for (int d = 0; d < 7; d++) {
+      dinv[d] = vinv_guard(Mi[sym(d, d)]);
+      P2 t = tgt[d * stride];
+      P2 qv = q[d * stride];
+      P2 diff = velocity ? (t - qd[d]) : (50.0f * (t - qv) - qd[d]);
+      rhs[d] = diff * dinv[d];
+      dv[d] = 0.f;
+      slowA |= (qv.v.x <= lo[d]) || (qv.v.x >= hi[d]);
+      slowB |= (qv.v.y <= lo[d]) || (qv.v.y >= hi[d]);
+    }
+  }
+  if (SYNC && PG_SYNC_C) __syncthreads();
+  if (any) {
+    bool liveA = actA && !slowA, liveB = actB && !slowB;
+    bool earlyA = false, earlyB = false;
+    if (liveA || liveB) {
+      P2 app[7];
+#pragma unroll
+      for (int d = 0; d < 7; d++) app[d] = 0.f;
+#define PG_MOTOR_ROW2(d)                                                    \
+  {                                                                         \
+    P2 t = fma2(-dv[d], dinv[d], app[d] + rhs[d]);                          \
+    P2 cl = vclamp(t, -motor_imp(d), motor_imp(d));                         \
+    P2 delta = cl - app[d];                                                 \
+    app[d] = cl;                                                            \
+    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] = fma2(Mi[sym(i, d)], delta, dv[i]); \
+    res = vmax(res, vabs((P2)(delta * Mi[sym(d, d)])));                     \
+  }
+#define PG_SWEEP_END2                                                       \
+  if (liveA && res.v.x <= kResAbs) { liveA = false; earlyA = true; _Pragma("unroll") for (int i = 0; i < 7; i++) snap[i * snap_stride] = dv[i].v.x; } \
+  if (liveB && res.v.y <= kResAbs) { liveB = false; earlyB = true; _Pragma("unroll") for (int i = 0; i < 7; i++) snap[(7 + i) * snap_stride] = dv[i].v.y; }
+      const float kResAbs = 3.1622777e-4f;  // sqrt(1e-7): compare |residual| instead of residual^2
+      for (int it = 0; it < kSolverIters; it += 2) {
+        if (liveA || liveB) {  // even iteration: backward sweep
+          P2 res = 0.f;
+          PG_MOTOR_ROW2(6) PG_MOTOR_ROW2(5) PG_MOTOR_ROW2(4) PG_MOTOR_ROW2(3) PG_MOTOR_ROW2(2) PG_MOTOR_ROW2(1) PG_MOTOR_ROW2(0)
+          PG_SWEEP_END2
+        }
+        if (liveA || liveB) {  // odd iteration: forward sweep
+          P2 res = 0.f;
+          PG_MOTOR_ROW2(0) PG_MOTOR_ROW2(1) PG_MOTOR_ROW2(2) PG_MOTOR_ROW2(3) PG_MOTOR_ROW2(4) PG_MOTOR_ROW2(5) PG_MOTOR_ROW2(6)
+          PG_SWEEP_END2
+        }
+        if (!__any_sync(__activemask(), liveA || liveB)) break;
+      }
+#undef PG_MOTOR_ROW2
+#undef PG_SWEEP_END2
+      if (earlyA) {
+#pragma unroll
+        for (int i = 0; i < 7; i++) dv[i].v.x = snap[i * snap_stride];
+      }
+      if (earlyB) {
+#pragma unroll
+        for (int i = 0; i < 7; i++) dv[i].v.y = snap[(7 + i) * snap_stride];
+      }
+    }
+    // cold path, one half at a time
+#pragma unroll 1
+    for (int h = 0; h < 2; h++) {
+      if (h == 0 ? (actA && slowA) : (actB && slowB)) {
+        float mi[7], ql[7], ms[28], qds[7], rs[7], ds[7], dvs[7];
+#pragma unroll
+        for (int k = 0; k < 28; k++) ms[k] = half_of(Mi[k], h);
+#pragma unroll
+        for (int d = 0; d < 7; d++) {
+          mi[d] = unit_imp ? 1.0f : motor_imp(d); ql[d] = half_of(q[d * stride], h);
+          qds[d] = half_of(qd[d], h); rs[d] = half_of(rhs[d], h); ds[d] = half_of(dinv[d], h);
+        }
+        pgs_generic(ms, ql, qds, rs, ds, mi, dvs);
+#pragma unroll
+        for (int d = 0; d < 7; d++) { if (h == 0) dv[d].v.x = dvs[d]; else dv[d].v.y = dvs[d]; }
+      }
+    }
+    // apply, clamp, integrate (inactive halves: velocity kept, dq = 0 keeps q and (cos, sin) bit-identical)
+    const P2 step_dt(actA ? kDt : 0.f, actB ? kDt : 0.f);
+#pragma unroll
+    for (int d = 0; d < 7; d++) {
+      qd[d] = sel2(actA, actB, vclamp(qd[d] + dv[d], -kMaxCoordVel, kMaxCoordVel), qd[d]);
+      P2 dq = qd[d] * step_dt;
+      q[d * stride] = q[d * stride] + dq;
+      P2 d2 = dq * dq;
+      P2 cd = fma2(d2, fma2(d2, 1.0f / 24.0f, -0.5f), 1.0f);
+      P2 sd = dq * fma2(d2, fma2(d2, 1.0f / 120.0f, -1.0f / 6.0f), 1.0f);
+      P2 c0 = cq[d], s0 = sq[d];
+      cq[d] = c0 * cd - s0 * sd;
+      sq[d] = s0 * cd + c0 * sd;
+    }
+  }
+  if (SYNC && PG_SYNC_D) __syncthreads();
+}
+#endif  // PG_PAIR_KERNEL
 
 }  // namespace pg

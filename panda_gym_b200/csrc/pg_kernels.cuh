@@ -361,16 +361,12 @@ __device__ __forceinline__ void ik_dls(V3 base, const float* q0, V3 target, floa
 // RobotTaskEnv.step (core.py:352-368): Panda.set_action (panda.py:120-172) -> sim.step()
 // (pybullet.py:68-71 / reach_ao.py:182-188) -> _get_obs -> is_success / is_truncated / compute_reward,
 // then gymnasium TimeLimit and Monitor bookkeeping.
-__global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ actions) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+// First half of a step for environment e: action limiter, action history, motor targets (written to
+// tgt[d * tstride]), jerk / effort bookkeeping.  q / qd return the state the simulation starts from.
+__device__ __forceinline__ void step_begin(const Params& P, const float* __restrict__ actions, int e, float* q, float* qd, float* tgt,
+                                           int tstride, bool& velocity_mode, bool& unit_imp) {
   const int n = P.n;
-  const bool valid = e < n;  // every thread of the block stays for the barriers of the substep loop
-  __shared__ float s_tgt[7 * kStepBlock], s_q[7 * kStepBlock];  // touched twice per substep: kept out of the register file
-  float* tgt = s_tgt + threadIdx.x;
-  float* qs = s_q + threadIdx.x;
-  float q[7], qd[7], a[7], cq[7], sq[7], q_fk[7];
-  bool velocity_mode = false, unit_imp = false;
-  if (valid) {
+  float a[7];
 #pragma unroll
   for (int d = 0; d < 7; d++) { q[d] = P.q[(size_t)d * n + e]; qd[d] = P.qd[(size_t)d * n + e]; a[d] = 0.f; }
   // --- set_action: limiter
@@ -396,18 +392,18 @@ __global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ 
     float tq[7];
     ik_dls(v3(P.base[0], P.base[1], P.base[2]), q, t, tq);
 #pragma unroll
-    for (int d = 0; d < 7; d++) tgt[d * kStepBlock] = tq[d];
+    for (int d = 0; d < 7; d++) tgt[d * tstride] = tq[d];
   } else {
 #pragma unroll
-    for (int d = 0; d < 7; d++) tgt[d * kStepBlock] = q[d] + __fmul_rn(a[d], 0.05f);  // panda.py:257-261
+    for (int d = 0; d < 7; d++) tgt[d * tstride] = q[d] + __fmul_rn(a[d], 0.05f);  // panda.py:257-261
   }
   if (P.control == 2) { velocity_mode = true;
 #pragma unroll
-    for (int d = 0; d < 7; d++) tgt[d * kStepBlock] = a[d]; }
+    for (int d = 0; d < 7; d++) tgt[d * tstride] = a[d]; }
   if (P.control == 3) {  // teleport (resetJointState), motors stay at their load-time default: v* = 0, impulse 1
     velocity_mode = true; unit_imp = true;
 #pragma unroll
-    for (int d = 0; d < 7; d++) { q[d] = tgt[d * kStepBlock]; qd[d] = 0.f; tgt[d * kStepBlock] = 0.f; }
+    for (int d = 0; d < 7; d++) { q[d] = tgt[d * tstride]; qd[d] = 0.f; tgt[d * tstride] = 0.f; }
   }
   // --- joint velocity / acceleration / jerk bookkeeping (panda.py:167-172), sampled before the sim step
 #pragma unroll
@@ -416,24 +412,15 @@ __global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ 
     float ca = pv - qd[d];
     P.cur_vel[(size_t)d * n + e] = qd[d]; P.cur_acc[(size_t)d * n + e] = ca; P.jerk[(size_t)d * n + e] = fabsf(pa - ca);
   }
-#pragma unroll
-  for (int d = 0; d < 7; d++) { sincosf(q[d], &sq[d], &cq[d]); qs[d * kStepBlock] = q[d]; }
-  }
-  // --- sim.step(): n_substeps x stepSimulation, collision check after each (ReachAO); a collided environment
-  //     stops simulating (reach_ao.py:186-188) but its thread keeps meeting the block barriers
-  bool collided = false, active = valid;
-  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
-  for (int k = 0; k < P.n_substeps; k++) {
-    substep<kStepSync>(active, velocity_mode, unit_imp, qs, qd, cq, sq, tgt, kStepBlock);
-    if (P.task == 1) {
-      bool hit = scene_pass<false, kStepSync>(active, P.scene, P.obs_pos_f, n, e, base, cq, sq, nullptr, nullptr);
-      if (active && hit) { collided = true; active = false; }
-    }
-  }
-  if (!valid) return;
+}
+
+// Second half of a step: state write-back, observation, success / truncation / reward, TimeLimit, Monitor statistics.
+__device__ __forceinline__ void step_end(const Params& P, int e, const float* q, const float* qd, bool collided) {
+  const int n = P.n;
+  float cq[7], sq[7], q_fk[7];
   // joint angles behind PyBullet's cached link transforms = q at the start of the last simulated substep
 #pragma unroll
-  for (int d = 0; d < 7; d++) { q[d] = qs[d * kStepBlock]; q_fk[d] = q[d] - qd[d] * kDt; sincosf(q[d], &sq[d], &cq[d]); }
+  for (int d = 0; d < 7; d++) { q_fk[d] = q[d] - qd[d] * kDt; sincosf(q[d], &sq[d], &cq[d]); }
 #pragma unroll
   for (int d = 0; d < 7; d++) { P.q[(size_t)d * n + e] = q[d]; P.qd[(size_t)d * n + e] = qd[d]; }
   if (P.task == 1) P.collided[e] = collided;
@@ -470,6 +457,110 @@ __global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ 
     atomicAdd(&P.stats[5], (double)len);
   }
 }
+
+// One environment per thread (fallback / A-B reference for k_step2 below).
+__global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ actions) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = P.n;
+  const bool valid = e < n;  // every thread of the block stays for the barriers of the substep loop
+  __shared__ float s_tgt[7 * kStepBlock], s_q[7 * kStepBlock];  // touched twice per substep: kept out of the register file
+  float* tgt = s_tgt + threadIdx.x;
+  float* qs = s_q + threadIdx.x;
+  float q[7], qd[7], cq[7], sq[7];
+  bool velocity_mode = false, unit_imp = false;
+  if (valid) {
+    step_begin(P, actions, e, q, qd, tgt, kStepBlock, velocity_mode, unit_imp);
+#pragma unroll
+    for (int d = 0; d < 7; d++) { sincosf(q[d], &sq[d], &cq[d]); qs[d * kStepBlock] = q[d]; }
+  }
+  // --- sim.step(): n_substeps x stepSimulation, collision check after each (ReachAO); a collided environment
+  //     stops simulating (reach_ao.py:186-188) but its thread keeps meeting the block barriers
+  bool collided = false, active = valid;
+  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
+  for (int k = 0; k < P.n_substeps; k++) {
+    substep<kStepSync>(active, velocity_mode, unit_imp, qs, qd, cq, sq, tgt, kStepBlock);
+    if (P.task == 1) {
+      bool hit = scene_pass<false, kStepSync>(active, P.scene, P.obs_pos_f, n, e, base, cq, sq, nullptr, nullptr);
+      if (active && hit) { collided = true; active = false; }
+    }
+  }
+  if (!valid) return;
+#pragma unroll
+  for (int d = 0; d < 7; d++) q[d] = qs[d * kStepBlock];
+  step_end(P, e, q, qd, collided);
+}
+
+#ifdef PG_PAIR_KERNEL
+// Two environments per thread: thread t of block b owns environments b*448 + t (half A) and b*448 + 224 + t (half B)
+// and runs the dynamics of both on the packed fp32 pipe (pg_packed.cuh, substep2).  The per-step prologue / epilogue
+// and the collision pass are the scalar code, run once per half.
+constexpr int kPairBlock = 224;                  // threads per block (7 warps, up to 255 registers each)
+constexpr int kPairEnvs = 2 * kPairBlock;        // environments per block
+constexpr int kPairSmemBytes = (5 * 7 * kPairBlock * 2 + 14 * kPairBlock) * 4;  // q, tgt, qd, cos, sin (P2) + snapshot
+__global__ void __launch_bounds__(kPairBlock, 1) k_step2(const Params P, const float* __restrict__ actions) {
+  extern __shared__ __align__(16) float s_dyn[];
+  const int n = P.n, t = threadIdx.x;
+  const int e0 = blockIdx.x * kPairEnvs + t;
+  P2* s_q = reinterpret_cast<P2*>(s_dyn) + t;     // element d at [d * kPairBlock]
+  P2* s_tgt = s_q + 7 * kPairBlock;
+  P2* s_qd = s_tgt + 7 * kPairBlock;
+  P2* s_c = s_qd + 7 * kPairBlock;
+  P2* s_s = s_c + 7 * kPairBlock;
+  float* snap = s_dyn + 5 * 7 * kPairBlock * 2 + t;  // element k at [k * kPairBlock]
+  bool velocity_mode = false, unit_imp = false;
+#pragma unroll 1
+  for (int h = 0; h < 2; h++) {
+    const int e = e0 + h * kPairBlock;
+    float q[7], qd[7], c[7], s[7];
+    float* tg = reinterpret_cast<float*>(s_tgt) + h;  // this half of element d at [d * 2 * kPairBlock]
+    if (e < n) {
+      step_begin(P, actions, e, q, qd, tg, 2 * kPairBlock, velocity_mode, unit_imp);
+#pragma unroll
+      for (int d = 0; d < 7; d++) sincosf(q[d], &s[d], &c[d]);
+    } else {
+#pragma unroll
+      for (int d = 0; d < 7; d++) { q[d] = 0.f; qd[d] = 0.f; c[d] = 1.f; s[d] = 0.f; tg[d * 2 * kPairBlock] = 0.f; }
+    }
+#pragma unroll
+    for (int d = 0; d < 7; d++) {
+      (reinterpret_cast<float*>(s_q) + h)[d * 2 * kPairBlock] = q[d];
+      (reinterpret_cast<float*>(s_qd) + h)[d * 2 * kPairBlock] = qd[d];
+      (reinterpret_cast<float*>(s_c) + h)[d * 2 * kPairBlock] = c[d];
+      (reinterpret_cast<float*>(s_s) + h)[d * 2 * kPairBlock] = s[d];
+    }
+  }
+  P2 qd[7], cq[7], sq[7];
+#pragma unroll
+  for (int d = 0; d < 7; d++) { qd[d] = s_qd[d * kPairBlock]; cq[d] = s_c[d * kPairBlock]; sq[d] = s_s[d * kPairBlock]; }
+  bool actA = e0 < n, actB = e0 + kPairBlock < n, collA = false, collB = false;
+  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
+  for (int k = 0; k < P.n_substeps; k++) {
+    substep2<kStepSync>(actA, actB, velocity_mode, unit_imp, s_q, qd, cq, sq, s_tgt, kPairBlock, snap, kPairBlock);
+    if (P.task == 1) {
+#pragma unroll 1
+      for (int h = 0; h < 2; h++) {
+        const bool act = h ? actB : actA;
+        float c[7], s[7];
+#pragma unroll
+        for (int d = 0; d < 7; d++) { c[d] = half_of(cq[d], h); s[d] = half_of(sq[d], h); }
+        bool hit = scene_pass<false, false>(act, P.scene, P.obs_pos_f, n, e0 + h * kPairBlock, base, c, s, nullptr, nullptr);
+        if (act && hit) { if (h) { collB = true; actB = false; } else { collA = true; actA = false; } }
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < 7; d++) s_qd[d * kPairBlock] = qd[d];
+#pragma unroll 1
+  for (int h = 0; h < 2; h++) {
+    const int e = e0 + h * kPairBlock;
+    if (e >= n) continue;
+    float q[7], qv[7];
+#pragma unroll
+    for (int d = 0; d < 7; d++) { q[d] = (reinterpret_cast<float*>(s_q) + h)[d * 2 * kPairBlock]; qv[d] = (reinterpret_cast<float*>(s_qd) + h)[d * 2 * kPairBlock]; }
+    step_end(P, e, q, qv, h ? collB : collA);
+  }
+}
+#endif  // PG_PAIR_KERNEL
 
 // ------------------------------------------------------------------------------------------------ reset
 struct Body { int type; double px, py, pz, sx, sy, sz; };  // sphere (sx = r) or axis-aligned box (half extents)
@@ -727,6 +818,36 @@ __global__ void PG_STEP_BOUNDS k_debug_substeps(int n, float* q_io, float* qd_io
 #pragma unroll
   for (int d = 0; d < 7; d++) { q_io[(size_t)d * n + e] = q[d * kStepBlock]; qd_io[(size_t)d * n + e] = qd[d]; }
 }
+#ifdef PG_PAIR_KERNEL
+__global__ void __launch_bounds__(kPairBlock, 1) k_debug_substeps2(int n, float* q_io, float* qd_io, const float* tgt_in, int nsub, int velocity) {
+  extern __shared__ __align__(16) float s_dyn[];
+  const int t = threadIdx.x, e0 = blockIdx.x * kPairEnvs + t, e1 = e0 + kPairBlock;
+  P2* q = reinterpret_cast<P2*>(s_dyn) + t;
+  P2* tg = q + 7 * kPairBlock;
+  float* snap = s_dyn + 5 * 7 * kPairBlock * 2 + t;
+  const bool vA = e0 < n, vB = e1 < n;
+  P2 qd[7], c[7], s[7];
+#pragma unroll
+  for (int d = 0; d < 7; d++) {
+    q[d * kPairBlock] = P2(vA ? q_io[(size_t)d * n + e0] : 0.f, vB ? q_io[(size_t)d * n + e1] : 0.f);
+    qd[d] = P2(vA ? qd_io[(size_t)d * n + e0] : 0.f, vB ? qd_io[(size_t)d * n + e1] : 0.f);
+    tg[d * kPairBlock] = P2(vA ? tgt_in[(size_t)d * n + e0] : 0.f, vB ? tgt_in[(size_t)d * n + e1] : 0.f);
+  }
+  for (int k = 0; k < nsub; k++) {
+    if ((k % 20) == 0) {
+#pragma unroll
+      for (int d = 0; d < 7; d++) { P2 v = q[d * kPairBlock]; sincosf(v.v.x, &s[d].v.x, &c[d].v.x); sincosf(v.v.y, &s[d].v.y, &c[d].v.y); }
+    }
+    substep2<kStepSync>(vA, vB, velocity != 0, false, q, qd, c, s, tg, kPairBlock, snap, kPairBlock);
+  }
+#pragma unroll
+  for (int d = 0; d < 7; d++) {
+    P2 v = q[d * kPairBlock];
+    if (vA) { q_io[(size_t)d * n + e0] = v.v.x; qd_io[(size_t)d * n + e0] = qd[d].v.x; }
+    if (vB) { q_io[(size_t)d * n + e1] = v.v.y; qd_io[(size_t)d * n + e1] = qd[d].v.y; }
+  }
+}
+#endif
 __global__ void k_debug_minv(int n, const float* q_in, float* out) {
   int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n) return;
