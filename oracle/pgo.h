@@ -74,6 +74,25 @@ double pgo_link_obstacle_distance(const pgo_arm*, int link, const pgo_obstacle*,
 double pgo_gjk_cyl_box(const double c[3], const double a[3], double r, double h,
                        const double b[3], const double e[3], double pa[3], double pb[3]);
 
+/* ---------------------------------------------------------------- Push / PickAndPlace world (pgo_world.c; a18) */
+typedef struct { double pos[3], quat[4] /* xyzw */, lin[3], ang[3]; } pgo_body; /* free rigid box, world-frame velocities */
+typedef struct {
+  double half[3], mass;                       /* the "object" box (push.py:33-39) */
+  double table_pos[3], table_half[3];         /* create_table (pybullet.py:780-815) */
+  double plane_pos[3], plane_half[3];         /* create_plane (pybullet.py:759-778) */
+  double mu_object, mu_static, mu_link, mu_ee; /* lateral friction: Bullet default 0.5; panda.py:69-70 sets link 9 to 1.0 */
+} pgo_world;
+/* kind 0: object (A) on table / plane (B); 1: robot link (A) on object (B); 2: robot link (A) on table top (B).
+ * n = unit normal from B towards A; pa / pb = contact points on A / B; d = signed distance; mu = combined friction */
+typedef struct { int kind, link; double d, n[3], pa[3], pb[3], mu; } pgo_contact;
+void pgo_world_default(pgo_world*);
+/* contact set at the current poses (<= 12 entries: 4 per body pair) */
+int pgo_world_contacts(const pgo_arm*, const pgo_body*, const pgo_world*, pgo_contact* out);
+/* one stepSimulation() of arm + object with contacts; returns the PGS iterations used */
+int pgo_world_substep(pgo_arm*, pgo_body*, const pgo_world*);
+/* getEulerFromQuaternion (pybullet.py:218) */
+void pgo_quat_to_euler(const double quat_xyzw[4], double rpy[3]);
+
 /* ---------------------------------------------------------------- RNG (numpy Generator(PCG64) restated) */
 typedef struct { uint64_t s_hi, s_lo, inc_hi, inc_lo; } pgo_pcg64;
 void pgo_pcg64_seed(pgo_pcg64*, uint64_t seed); /* == np.random.default_rng(seed) / gymnasium seeding.np_random(seed) */
@@ -85,7 +104,7 @@ double pgo_pcg64_uniform(pgo_pcg64*, double lo, double hi); /* Generator.uniform
 typedef struct pgo_env pgo_env; /* opaque */
 
 typedef struct {
-  int task;              /* 0 = Reach (reach.py), 1 = ReachAO (reach_ao.py) */
+  int task;              /* 0 = Reach (reach.py), 1 = ReachAO (reach_ao.py), 2 = Push (push.py), 3 = PickAndPlace (pick_and_place.py) */
   int control;           /* 0 = joints ("js"/"joints": q_tgt = q + 0.05 a), 1 = "ee" (IK), 2 = "jsd" velocity, 3 = "pcc" teleport */
   int reward_type;       /* 0 sparse, 1 dense (Reach) / wang, 2 kumar_her, 3 kumar_optim, 4 kumar (ReachAO) */
   int goal_condition;    /* 0 reach, 1 halt */
@@ -118,6 +137,8 @@ int pgo_env_reset(pgo_env*, uint64_t seed, float* obs, float* achieved, float* d
 void pgo_env_step(pgo_env*, const float* action, float* obs, float* achieved, float* desired, float* reward, int* flags);
 /* direct state access for matched-state parity tests */
 pgo_arm* pgo_env_arm(pgo_env*);
+pgo_body* pgo_env_object(pgo_env*);   /* tasks 2, 3 */
+pgo_world* pgo_env_world(pgo_env*);
 void pgo_env_set_goal(pgo_env*, const double goal[3]);
 void pgo_env_get_goal(const pgo_env*, double goal[3]);
 void pgo_env_set_obstacles(pgo_env*, int n, const pgo_obstacle*);

@@ -8,6 +8,7 @@
 #define _USE_MATH_DEFINES
 #define _GNU_SOURCE
 #include "pgo.h"
+#include "pgo_internal.h"
 #include "panda_model_data.h"
 #include <math.h>
 #include <stdlib.h>
@@ -225,6 +226,26 @@ void pgo_arm_jacobian(const pgo_arm* a0, int link, double* Jt, double* Jr) {
   }
 }
 
+void pgo__arm_point_jacobian(const pgo_arm* a0, int link, const double p[3], double* J) {
+  pgo_arm* a = (pgo_arm*)a0;
+  fk(a);
+  for (int k = 0; k < 3 * a->nd; k++) J[k] = 0;
+  for (int i = link; i >= 0; i = a->L[i].parent) {
+    const pgo_link_t* l = &a->L[i];
+    if (l->jtype == 0) continue;
+    int d = a->dof_of_link[i];
+    double axw[3], r[3], c[3];
+    m3vec(a->Rw[i], l->axis, axw);
+    if (l->jtype == 1) {
+      for (int k = 0; k < 3; k++) r[k] = p[k] - a->ow[i][k];
+      cross(axw, r, c);
+      for (int k = 0; k < 3; k++) J[k * a->nd + d] = c[k];
+    } else {
+      for (int k = 0; k < 3; k++) J[k * a->nd + d] = axw[k];
+    }
+  }
+}
+
 /* ------------------------------------------------------------------ articulated-body algorithm
  * Spatial vectors are (angular; linear) in the link's COM frame (Bullet's btMultiBody convention).  */
 static void build_X(const double* R, const double* rp, double* X) { /* motion transform parent->child */
@@ -382,21 +403,24 @@ void pgo_arm_minv(pgo_arm* a, double* minv) {
 }
 
 /* ------------------------------------------------------------------ one stepSimulation() */
-typedef struct { int dof; double sign, rhs, lo, hi, applied, dinv, resp[PGO_MAXD]; } row_t;
+typedef pgo__row row_t; /* pgo_internal.h */
 
-int pgo_arm_substep(pgo_arm* a) {
+/* 1. forward dynamics with gravity/damping, velocity update (solveExternalForces) */
+void pgo__arm_predict(pgo_arm* a) {
   int nd = a->nd;
   double qdd[PGO_MAXD];
   memcpy(a->q_fk, a->q, sizeof a->q); /* btMultiBodyDynamicsWorld::solveConstraints -> forwardKinematics() */
-  /* 1. forward dynamics with gravity/damping, velocity update (solveExternalForces) */
   aba(a, qdd);
   for (int d = 0; d < nd; d++) {
     a->qd[d] += qdd[d] * a->dt;
     if (a->qd[d] > a->max_coord_vel) a->qd[d] = a->max_coord_vel;
     if (a->qd[d] < -a->max_coord_vel) a->qd[d] = -a->max_coord_vel;
   }
-  /* 2. constraint rows: joint limits were added to the world at URDF import, motors afterwards */
-  row_t rows[3 * PGO_MAXD];
+}
+
+/* 2. constraint rows: joint limits were added to the world at URDF import, motors afterwards */
+int pgo__arm_rows(pgo_arm* a, row_t* rows) {
+  int nd = a->nd;
   int nr = 0;
   const double erp = 0.2; /* solverInfo.m_erp (joint-limit rows) */
   for (int d = 0; d < nd; d++) {
@@ -433,31 +457,56 @@ int pgo_arm_substep(pgo_arm* a) {
     r->rhs = (want - v) * r->dinv;
     r->lo = -a->motor_maximp[d]; r->hi = a->motor_maximp[d]; r->applied = 0;
   }
-  /* 3. projected Gauss-Seidel (btMultiBodyConstraintSolver::solveSingleIteration) */
-  double dv[PGO_MAXD] = {0};
-  int it;
-  for (it = 0; it < a->solver_iters; it++) {
-    double lsq = 0;
-    for (int j = 0; j < nr; j++) {
-      row_t* r = &rows[(it & 1) ? j : nr - 1 - j];
-      double delta = r->rhs - r->sign * dv[r->dof] * r->dinv;
-      double sum = r->applied + delta;
-      if (sum < r->lo) { delta = r->lo - r->applied; r->applied = r->lo; }
-      else if (sum > r->hi) { delta = r->hi - r->applied; r->applied = r->hi; }
-      else r->applied = sum;
-      for (int d = 0; d < nd; d++) dv[d] += r->resp[d] * delta;
-      double res = r->dinv != 0.0 ? delta / r->dinv : 0.0;
-      if (res * res > lsq) lsq = res * res;
-    }
-    if (lsq <= a->residual_thr || it >= a->solver_iters - 1) { it++; break; }
+  return nr;
+}
+
+/* one sweep over the limit + motor rows (btMultiBodyConstraintSolver::solveSingleIteration, non-contact
+ * part): forward on odd iterations, backward on even.  returns the largest squared residual */
+double pgo__arm_sweep(const pgo_arm* a, row_t* rows, int nr, int it, double* dv) {
+  int nd = a->nd;
+  double lsq = 0;
+  for (int j = 0; j < nr; j++) {
+    row_t* r = &rows[(it & 1) ? j : nr - 1 - j];
+    double delta = r->rhs - r->sign * dv[r->dof] * r->dinv;
+    double sum = r->applied + delta;
+    if (sum < r->lo) { delta = r->lo - r->applied; r->applied = r->lo; }
+    else if (sum > r->hi) { delta = r->hi - r->applied; r->applied = r->hi; }
+    else r->applied = sum;
+    for (int d = 0; d < nd; d++) dv[d] += r->resp[d] * delta;
+    double res = r->dinv != 0.0 ? delta / r->dinv : 0.0;
+    if (res * res > lsq) lsq = res * res;
   }
+  return lsq;
+}
+
+/* 4. apply the solver's velocity change, integrate positions (stepPositionsMultiDof) */
+void pgo__arm_finish(pgo_arm* a, const double* dv) {
+  int nd = a->nd;
   for (int d = 0; d < nd; d++) {
     a->qd[d] += dv[d];
     if (a->qd[d] > a->max_coord_vel) a->qd[d] = a->max_coord_vel;
     if (a->qd[d] < -a->max_coord_vel) a->qd[d] = -a->max_coord_vel;
   }
-  /* 4. integrate positions (stepPositionsMultiDof) */
   for (int d = 0; d < nd; d++) a->q[d] += a->qd[d] * a->dt;
+}
+void pgo__arm_response(const pgo_arm* a, const double* tau, double* out) { aba_delta(a, tau, out); }
+int pgo__arm_solver_iters(const pgo_arm* a) { return a->solver_iters; }
+double pgo__arm_residual_thr(const pgo_arm* a) { return a->residual_thr; }
+double pgo__arm_dt(const pgo_arm* a) { return a->dt; }
+const double* pgo__arm_qd(const pgo_arm* a) { return a->qd; }
+
+int pgo_arm_substep(pgo_arm* a) {
+  pgo__arm_predict(a);
+  row_t rows[3 * PGO_MAXD];
+  int nr = pgo__arm_rows(a, rows);
+  /* 3. projected Gauss-Seidel (btMultiBodyConstraintSolver::solveSingleIteration) */
+  double dv[PGO_MAXD] = {0};
+  int it;
+  for (it = 0; it < a->solver_iters; it++) {
+    double lsq = pgo__arm_sweep(a, rows, nr, it, dv);
+    if (lsq <= a->residual_thr || it >= a->solver_iters - 1) { it++; break; }
+  }
+  pgo__arm_finish(a, dv);
   return it;
 }
 

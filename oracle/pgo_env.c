@@ -41,6 +41,9 @@ struct pgo_env {
   int obs_sampler;         /* 0 goal box, 1 wang (70/20/10), 2 experimental (50/50), 3 wang-N (70/30) */
   int randomize_obstacles, allow_overlap, random_num_obs, size_lo, size_hi;
   double table_pos[3], table_half[3];
+  /* Push / PickAndPlace (tasks 2, 3): the free object and its world */
+  pgo_body obj;
+  pgo_world world;
 };
 
 /* ------------------------------------------------------------------ helpers */
@@ -64,6 +67,9 @@ void pgo_env_default_config(pgo_env_config* c, int task) {
   if (task == 0) { /* PandaReach*: Panda(obs_type=("ee",)), base (-0.6,0,0) (panda_tasks.py:81-88) */
     c->obs_js = 0; c->obstacle_obs = 0; c->truncate_on_collision = 0; c->terminate_on_success = 0;
     c->base_pos[0] = -0.6; c->scenario = PGO_SCN_NONE;
+  } else if (task >= 2) { /* PandaPush-v3 / PandaPickAndPlace-v3: ee control, base (-0.6,0,0) (panda_tasks.py:37-72, __init__.py:58-77) */
+    c->obs_js = 0; c->obstacle_obs = 0; c->truncate_on_collision = 0; c->terminate_on_success = 0;
+    c->base_pos[0] = -0.6; c->scenario = PGO_SCN_NONE; c->control = 1;
   } else {         /* PandaReachAO-v3 with TrainConfig() defaults (train_config.py) */
     c->obs_js = 1; c->obstacle_obs = 1; c->truncate_on_collision = 1; c->terminate_on_success = 1;
     c->scenario = PGO_SCN_REACHAO1;
@@ -135,6 +141,8 @@ pgo_env* pgo_env_create(const pgo_env_config* c) {
   e->cfg = *c;
   e->arm = pgo_arm_create(0, c->base_pos);
   setup_scenario(e);
+  pgo_world_default(&e->world);
+  e->obj.quat[3] = 1.0; e->obj.pos[2] = e->world.half[2];
   for (int k = 0; k < PGO_NCL; k++) e->d_link[k] = 0.0; /* reach_ao.py:110 np.zeros */
   for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, 0.0);
   return e;
@@ -148,12 +156,18 @@ void pgo_env_set_obstacles(pgo_env* e, int n, const pgo_obstacle* o) { e->nobs =
 int pgo_env_get_obstacles(const pgo_env* e, pgo_obstacle* o) { memcpy(o, e->obs, e->nobs * sizeof *o); return e->nobs; }
 
 static int task_obs_dim(const pgo_env* e) {
+  if (e->cfg.task >= 2) return 12; /* push.py:49-63 */
   if (e->cfg.task == 0 || e->cfg.obstacle_obs == 0) return 0;
   if (e->nobs == 0) return 27; /* reach_ao.py:904: np.ones(27) whatever the mode */
   switch (e->cfg.obstacle_obs) { case 1: return 36; case 2: return 27; case 3: return 9; case 5: return 81; default: return 1; }
 }
-int pgo_env_obs_dim(const pgo_env* e) { return 6 + (e->cfg.obs_js ? 14 : 0) + task_obs_dim(e); }
-int pgo_env_act_dim(const pgo_env* e) { return e->cfg.control == 1 ? 3 : 7; } /* block_gripper=True */
+static int robot_obs_dim(const pgo_env* e) { return 6 + (e->cfg.obs_js ? 14 : 0) + (e->cfg.task == 3 ? 1 : 0); } /* panda.py:264-288 */
+int pgo_env_obs_dim(const pgo_env* e) { return robot_obs_dim(e) + task_obs_dim(e); }
+/* block_gripper=True except PickAndPlace (panda_tasks.py:49), whose extra finger action moves nothing: the loaded
+ * custom_0 URDF has FIXED finger joints (panda.urdf:467-479) */
+int pgo_env_act_dim(const pgo_env* e) { return (e->cfg.control == 1 ? 3 : 7) + (e->cfg.task == 3 ? 1 : 0); }
+pgo_body* pgo_env_object(pgo_env* e) { return &e->obj; }
+pgo_world* pgo_env_world(pgo_env* e) { return &e->world; }
 
 /* ------------------------------------------------------------------ collision queries */
 int pgo_env_check_collided(pgo_env* e, double* d_link, double* d_table_min) {
@@ -328,12 +342,21 @@ static void robot_obs(pgo_env* e, float* o, float* ag) {
     pgo_arm_get_q(e->arm, q, qd);
     for (int d = 0; d < 7; d++) { o[6 + d] = (float)q[d]; o[13 + d] = (float)qd[d]; }
   }
+  /* fingers opening (panda.py:282-284): getJointState of the fixed joints 9, 10 reports 0 */
+  if (e->cfg.task == 3) o[robot_obs_dim(e) - 1] = 0.0f;
+  if (e->cfg.task >= 2 && ag) for (int k = 0; k < 3; k++) ag[k] = (float)e->obj.pos[k]; /* push.py:65-67 */
 }
 
 static void task_obs(pgo_env* e, float* o) {
   /* reach_ao.py:902-959 */
   int n = task_obs_dim(e);
   if (n == 0) return;
+  if (e->cfg.task >= 2) { /* object position, euler rotation, velocity, angular velocity (push.py:49-63) */
+    double rpy[3];
+    pgo_quat_to_euler(e->obj.quat, rpy);
+    for (int k = 0; k < 3; k++) { o[k] = (float)e->obj.pos[k]; o[3 + k] = (float)rpy[k]; o[6 + k] = (float)e->obj.lin[k]; o[9 + k] = (float)e->obj.ang[k]; }
+    return;
+  }
   if (e->nobs == 0) { for (int k = 0; k < 27; k++) o[k] = 1.0f; return; }
   double dmin[PGO_NCL], u[PGO_NCL][3], all = 1e300;
   for (int i = 0; i < PGO_NCL; i++) {
@@ -366,7 +389,7 @@ static void task_obs(pgo_env* e, float* o) {
 
 void pgo_env_get_obs(pgo_env* e, float* obs, float* ag, float* dg) {
   robot_obs(e, obs, ag);
-  task_obs(e, obs + 6 + (e->cfg.obs_js ? 14 : 0));
+  task_obs(e, obs + robot_obs_dim(e));
   if (dg) for (int k = 0; k < 3; k++) dg[k] = (float)e->goal[k];
 }
 
@@ -391,6 +414,20 @@ int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, i
   e->steps = 0;
   if (e->cfg.task == 0) {
     for (int k = 0; k < 3; k++) e->goal[k] = pgo_pcg64_uniform(&e->rng, e->goal_lo[k], e->goal_hi[k]); /* reach.py:75-78 */
+  } else if (e->cfg.task >= 2) {
+    /* Push.reset (push.py:69-87) / PickAndPlace.reset (pick_and_place.py:65-85): goal then object, xy range 0.3;
+     * PickAndPlace lifts the goal by U(0, 0.2) and flattens it again with probability 0.3 */
+    const double half = e->world.half[2], hi_z = e->cfg.task == 3 ? 0.2 : 0.0;
+    double noise[3];
+    noise[0] = pgo_pcg64_uniform(&e->rng, -0.15, 0.15); noise[1] = pgo_pcg64_uniform(&e->rng, -0.15, 0.15);
+    noise[2] = pgo_pcg64_uniform(&e->rng, 0.0, hi_z);
+    if (e->cfg.task == 3 && pgo_pcg64_double(&e->rng) < 0.3) noise[2] = 0.0;
+    e->goal[0] = 0.0 + noise[0]; e->goal[1] = 0.0 + noise[1]; e->goal[2] = half + noise[2];
+    noise[0] = pgo_pcg64_uniform(&e->rng, -0.15, 0.15); noise[1] = pgo_pcg64_uniform(&e->rng, -0.15, 0.15);
+    noise[2] = pgo_pcg64_uniform(&e->rng, 0.0, 0.0);
+    memset(&e->obj, 0, sizeof e->obj);                   /* set_base_pose: identity orientation, velocities zeroed */
+    e->obj.pos[0] = 0.0 + noise[0]; e->obj.pos[1] = 0.0 + noise[1]; e->obj.pos[2] = half + noise[2];
+    e->obj.quat[3] = 1.0;
   } else {
     e->goal_reached = 0; e->is_collided = 0;
     status |= set_coll_free_goal(e, 0, 0.1);           /* fixed_target None */
@@ -462,7 +499,7 @@ static float reward_one(pgo_env* e, const float* ag, const float* dg) {
   const pgo_env_config* c = &e->cfg;
   float d = f32_distance(ag, dg);
   float thr = (float)c->ee_error_threshold;
-  if (c->task == 0) return c->reward_type == 0 ? -(float)(d > thr) : -d; /* reach.py:84-89 */
+  if (c->task != 1) return c->reward_type == 0 ? -(float)(d > thr) : -d; /* reach.py:84-89, push.py:93-98, pick_and_place.py:91-96 */
   double v[3]; pgo_arm_link_state(e->arm, EE_LINK, 0, 0, v, 0);
   double speed = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
   double effort = norm7(e->cur_acc), jerk = norm7(e->jerk);
@@ -501,6 +538,7 @@ void pgo_env_compute_reward(pgo_env* e, const float* ag, const float* dg, int n,
 void pgo_env_step(pgo_env* e, const float* action, float* obs, float* ag, float* dg, float* reward, int* flags) {
   set_action(e, action);
   for (int k = 0; k < e->cfg.n_substeps; k++) {
+    if (e->cfg.task >= 2) pgo_world_substep(e->arm, &e->obj, &e->world); else
     pgo_arm_substep(e->arm);
     if (e->cfg.task == 1) { /* step_check_collision (reach_ao.py:182-188) */
       e->is_collided = pgo_env_check_collided(e, 0, 0);
@@ -537,7 +575,7 @@ int pgo_test_integers_shuffle(uint64_t seed, int skip, int lo, int hi, int n, in
 int pgo_bench_rollout(const pgo_env_config* cfg, uint64_t seed, int steps, double* checksum) {
   pgo_env* e = pgo_env_create(cfg);
   pgo_pcg64 ar; pgo_pcg64_seed(&ar, seed ^ 0xabcdef);
-  float obs[64], ag[3], dg[3], r, a[8];
+  float obs[128], ag[3], dg[3], r, a[8];
   int flags[4], succ, episodes = 0;
   double cs = 0;
   pgo_env_reset(e, seed, obs, ag, dg, &succ);

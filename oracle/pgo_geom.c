@@ -14,6 +14,7 @@
  *   - deep penetration (cores overlap) reports -(sum of margins): only the sign is consumed by the path.
  */
 #include "pgo.h"
+#include "pgo_internal.h"
 #include "panda_model_data.h"
 #include <math.h>
 #include <string.h>
@@ -254,4 +255,41 @@ double pgo_link_obstacle_distance(const pgo_arm* a, int link, const pgo_obstacle
     if (d < best) { best = d; for (int k = 0; k < 3; k++) { if (pa) pa[k] = ta[k]; if (pb) pb[k] = tb[k]; } }
   }
   return best;
+}
+
+/* ------------------------------------------------------------------ primitive vs oriented box (contact pass of
+ * the Push / PickAndPlace world, pgo_world.c): evaluated in the box frame with the routines above */
+int pgo__prim_link(const pgo_arm* a, int prim) { const pgo_prim_t* P; pgo__arm_prims(a, &P); return P[prim].link; }
+double pgo__prim_obb(const pgo_arm* a, int prim, const double bpos[3], const double bR[9], const double half[3],
+                     double pa[3], double pb[3], double n[3]) {
+  const pgo_prim_t* P; pgo__arm_prims(a, &P);
+  pgo__arm_fk((pgo_arm*)a);
+  double c[3], ax[3], cl[3], al[3], la[3], lb[3];
+  prim_world(a, &P[prim], c, ax);
+  for (int i = 0; i < 3; i++) { /* world -> box frame: R^T (x - bpos) */
+    cl[i] = 0; al[i] = 0;
+    for (int k = 0; k < 3; k++) { cl[i] += bR[3 * k + i] * (c[k] - bpos[k]); al[i] += bR[3 * k + i] * ax[k]; }
+  }
+  pgo_obstacle ob; ob.type = 1;
+  for (int k = 0; k < 3; k++) { ob.pos[k] = 0.0; ob.size[k] = half[k]; }
+  double d = prim_obstacle(cl, al, &P[prim], &ob, la, lb);
+  double v[3] = {lb[0] - la[0], lb[1] - la[1], lb[2] - la[2]};
+  double L = sqrt(dot3(v, v));
+  double nl[3];
+  if (L > 1e-9) { double s = d >= 0 ? 1.0 / L : -1.0 / L; for (int k = 0; k < 3; k++) nl[k] = v[k] * s; }
+  else { /* deep overlap (cores intersect): push along the line of centres */
+    double cn = sqrt(dot3(cl, cl));
+    for (int k = 0; k < 3; k++) nl[k] = cn > 1e-12 ? -cl[k] / cn : (k == 2 ? -1.0 : 0.0);
+  }
+  for (int i = 0; i < 3; i++) {
+    pa[i] = bpos[i]; pb[i] = bpos[i]; n[i] = 0;
+    for (int k = 0; k < 3; k++) { pa[i] += bR[3 * i + k] * la[k]; pb[i] += bR[3 * i + k] * lb[k]; n[i] += bR[3 * i + k] * nl[k]; }
+  }
+  return d;
+}
+void pgo__prim_world(const pgo_arm* a, int prim, double c[3], double ax[3], double* r, double* h, int* type) {
+  const pgo_prim_t* P; pgo__arm_prims(a, &P);
+  pgo__arm_fk((pgo_arm*)a);
+  prim_world(a, &P[prim], c, ax);
+  *r = P[prim].radius; *h = P[prim].half_len; *type = P[prim].type;
 }

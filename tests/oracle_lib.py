@@ -30,6 +30,21 @@ class Obstacle(ctypes.Structure):
     _fields_ = [("type", c_int), ("pos", c_double * 3), ("size", c_double * 3)]
 
 
+class Body(ctypes.Structure):
+    _fields_ = [("pos", c_double * 3), ("quat", c_double * 4), ("lin", c_double * 3), ("ang", c_double * 3)]
+
+
+class World(ctypes.Structure):
+    _fields_ = [("half", c_double * 3), ("mass", c_double), ("table_pos", c_double * 3), ("table_half", c_double * 3),
+                ("plane_pos", c_double * 3), ("plane_half", c_double * 3),
+                ("mu_object", c_double), ("mu_static", c_double), ("mu_link", c_double), ("mu_ee", c_double)]
+
+
+class Contact(ctypes.Structure):
+    _fields_ = [("kind", c_int), ("link", c_int), ("d", c_double), ("n", c_double * 3), ("pa", c_double * 3),
+                ("pb", c_double * 3), ("mu", c_double)]
+
+
 class Pcg64(ctypes.Structure):
     _fields_ = [("s_hi", c_u64), ("s_lo", c_u64), ("inc_hi", c_u64), ("inc_lo", c_u64)]
 
@@ -101,6 +116,12 @@ def lib():
     sig("pgo_env_compute_reward", None, P, P, P, c_int, P)
     sig("pgo_env_is_collided", c_int, P)
     sig("pgo_bench_rollout", c_int, P, c_u64, c_int, P)
+    sig("pgo_env_object", ctypes.POINTER(Body), P)
+    sig("pgo_env_world", ctypes.POINTER(World), P)
+    sig("pgo_world_default", None, P)
+    sig("pgo_world_contacts", c_int, P, P, P, P)
+    sig("pgo_world_substep", c_int, P, P, P)
+    sig("pgo_quat_to_euler", None, P, P)
     sig("pgo_test_distance", None, P, P, c_int, P)
     sig("pgo_test_integers_shuffle", c_int, c_u64, c_int, c_int, c_int, c_int, P)
     _lib = L
@@ -258,6 +279,27 @@ class Env:
         d = np.zeros(9); t = c_double(0)
         c = self.L.pgo_env_check_collided(self.h, dp(d), ctypes.byref(t))
         return bool(c), d, t.value
+
+    # ---- Push / PickAndPlace (tasks 2, 3): the free object
+    def object_state(self):
+        b = self.L.pgo_env_object(self.h).contents
+        return np.array(b.pos[:]), np.array(b.quat[:]), np.array(b.lin[:]), np.array(b.ang[:])
+
+    def set_object_state(self, pos, quat=(0, 0, 0, 1), lin=(0, 0, 0), ang=(0, 0, 0)):
+        b = self.L.pgo_env_object(self.h).contents
+        for k in range(3):
+            b.pos[k] = float(pos[k]); b.lin[k] = float(lin[k]); b.ang[k] = float(ang[k])
+        for k in range(4):
+            b.quat[k] = float(quat[k])
+
+    def world_substep(self):
+        return self.L.pgo_world_substep(self.L.pgo_env_arm(self.h), self.L.pgo_env_object(self.h), self.L.pgo_env_world(self.h))
+
+    def contacts(self):
+        arr = (Contact * 12)()
+        n = self.L.pgo_world_contacts(self.L.pgo_env_arm(self.h), self.L.pgo_env_object(self.h), self.L.pgo_env_world(self.h), arr)
+        return [dict(kind=c.kind, link=c.link, d=c.d, n=np.array(c.n[:]), pa=np.array(c.pa[:]), pb=np.array(c.pb[:]), mu=c.mu)
+                for c in arr[:n]]
 
     def compute_reward(self, ag, dg):
         ag = np.ascontiguousarray(ag, dtype=np.float32).reshape(-1, 3); dg = np.ascontiguousarray(dg, dtype=np.float32).reshape(-1, 3)

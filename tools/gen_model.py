@@ -304,7 +304,7 @@ def emit_cuda(links, order, path):
     o.append("constexpr float kEErot_c = %s, kEErot_s = %s;  // link11 axes = Rz(angle) * link7 axes: cos, sin" % (ff(R[0][0]), ff(R[1][0])))
     # COM of link index 0 (sample_obstacle_wang uses get_link_position(0))
     # collision primitives: 9 collision links, link8 / ee expressed in the link7 frame
-    coll = [0, 1, 2, 3, 4, 5, 6, 7, 9]
+    coll = [0, 1, 2, 3, 4, 5, 6, 7, 9, 8]  # slot 9 = panda_hand: not a ReachAO collision link, used by the contact pass of Push / PickAndPlace
     k = 0
     o.append("// collision primitives: slot = index into the 9 ReachAO collision links (link1..link8, panda_ee);")
     o.append("// frame = moving link whose frame the numbers are in (1..7); type 0 sphere, 1 cylinder")
