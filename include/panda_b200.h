@@ -21,7 +21,10 @@ typedef struct pg_env_s* pg_handle;
 
 enum pg_status { PG_OK = 0, PG_ERR_ARG = -1, PG_ERR_CUDA = -2, PG_ERR_STATE = -3, PG_ERR_UNSUPPORTED = -4 };
 
-enum pg_task { PG_TASK_REACH = 0, PG_TASK_REACH_AO = 1 };                       /* envs/tasks/reach.py, reach_ao.py */
+/* envs/tasks/reach.py, reach_ao.py, push.py, pick_and_place.py.  Push / PickAndPlace add one free rigid box with
+ * frictional contacts (object-table, robot-object, robot-table); PickAndPlace is simulated as the reference loads it:
+ * franka_panda_custom_0 has FIXED finger joints, so the 4th action entry moves nothing and the finger width reads 0. */
+enum pg_task { PG_TASK_REACH = 0, PG_TASK_REACH_AO = 1, PG_TASK_PUSH = 2, PG_TASK_PICK_AND_PLACE = 3 };
 enum pg_control { PG_CTRL_JOINTS = 0, PG_CTRL_EE = 1, PG_CTRL_JSD = 2, PG_CTRL_PCC = 3 }; /* panda.py:141-165 */
 enum pg_reward { PG_REW_SPARSE = 0, PG_REW_DENSE_OR_WANG = 1, PG_REW_KUMAR_HER = 2, PG_REW_KUMAR_OPTIM = 3, PG_REW_KUMAR = 4 };
 enum pg_obstacle_obs { PG_OOBS_NONE = 0, PG_OOBS_VECTORS_CLOSEST_PER_LINK = 1, PG_OOBS_VECTORS = 2,
@@ -138,6 +141,7 @@ enum pg_view_id {
   PG_V_STATS,             /* f64 [8] episodes, successes, collisions, timeouts, sum_return, sum_length, reset_failures, - */
   PG_V_STEP_COUNT,        /* i32 [n] */
   PG_V_D_LINK,            /* f32 [9][n] distances_closest_obstacles (reach_ao.py:897) */
+  PG_V_OBJECT,            /* f32 [13][n] object position, quaternion xyzw, linear / angular velocity (get_base_* of pybullet.py:182-247) */
   PG_V_COUNT
 };
 typedef struct { void* ptr; int dtype; /* 0 f32, 1 u8, 2 i32, 3 f64, 4 u64 */ int ndim; int64_t shape[3]; } pg_view;
@@ -153,6 +157,8 @@ int64_t pg_launch_count(pg_handle h);
 int pg_set_joint_state(pg_handle h, const float* q_dev, const float* qd_dev, void* stream);
 int pg_set_goal(pg_handle h, const double* goal_dev /* [3][n] */, void* stream);
 int pg_set_obstacles(pg_handle h, const double* pos_dev /* [n_obstacles][3][n] */, void* stream);
+/* set_base_pose + resetBaseVelocity of the "object" body (pybullet.py:350-361): f32 [13][n] position, quaternion xyzw, linear, angular velocity */
+int pg_set_object_state(pg_handle h, const float* obj_dev, void* stream);
 /* recompute observation / flags at the current state without stepping (RobotTaskEnv._get_obs) */
 int pg_observe(pg_handle h, void* stream);
 /* n_sub raw stepSimulation() calls with POSITION_CONTROL targets / max forces, no task logic:

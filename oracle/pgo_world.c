@@ -119,26 +119,77 @@ int pgo_world_contacts(const pgo_arm* a, const pgo_body* b, const pgo_world* w, 
     int link = pgo__prim_link(a, k);
     double mu_l = link == EE_LINK_IDX ? w->mu_ee : w->mu_link;
     c.link = link;
+    double cc[3], ax[3], r, h; int type;
+    pgo__prim_world(a, k, cc, ax, &r, &h, &type);
     c.kind = 1; c.mu = mu_l * w->mu_object;
     c.d = pgo__prim_obb(a, k, b->pos, R, w->half, c.pa, c.pb, dir);
     for (int i = 0; i < 3; i++) c.n[i] = -dir[i];
-    if (c.d < BREAKING) keep_closest(cr, &nr, &c);
-    /* table top: lowest point of the primitive */
-    double cc[3], ax[3], r, h; int type;
-    pgo__prim_world(a, k, cc, ax, &r, &h, &type);
-    if (!over_rect(cc, w->table_pos, w->table_half)) continue;
+    int done = 0;
+    if (type == 1 && c.d < BREAKING + 0.05) {
+      /* cylinder against a box FACE: the closest point of a generator parallel to the face is not unique (it would
+       * be picked by rounding noise), so the contact is spread like a manifold: both ends of the generator facing
+       * the box, clipped to the face, each with its own distance */
+      double dl[3], cl[3], al[3];
+      for (int i = 0; i < 3; i++) {
+        dl[i] = R[i] * dir[0] + R[3 + i] * dir[1] + R[6 + i] * dir[2];
+        al[i] = R[i] * ax[0] + R[3 + i] * ax[1] + R[6 + i] * ax[2];
+        cl[i] = R[i] * (cc[0] - b->pos[0]) + R[3 + i] * (cc[1] - b->pos[1]) + R[6 + i] * (cc[2] - b->pos[2]);
+      }
+      int kf = fabs(dl[0]) > fabs(dl[1]) ? (fabs(dl[0]) > fabs(dl[2]) ? 0 : 2) : (fabs(dl[1]) > fabs(dl[2]) ? 1 : 2);
+      if (fabs(dl[kf]) > 0.999) {
+        double sg = dl[kf] > 0 ? 1.0 : -1.0, u[3] = {0, 0, 0}, rr = r + 0.001;
+        u[kf] = sg;
+        double ua = u[0] * al[0] + u[1] * al[1] + u[2] * al[2], L;
+        for (int i = 0; i < 3; i++) u[i] -= ua * al[i];
+        L = sqrt(dot3(u, u));
+        if (L > 1e-6) {
+          double g0[3], t0 = -h, t1 = h;
+          for (int i = 0; i < 3; i++) g0[i] = cl[i] + rr * u[i] / L;
+          for (int j = 0; j < 3; j++) {
+            if (j == kf) continue;
+            /* |g0_j + t al_j| <= half_j */
+            if (fabs(al[j]) < 1e-9) { if (fabs(g0[j]) > w->half[j]) t1 = t0 - 1.0; continue; }
+            double ta = (-w->half[j] - g0[j]) / al[j], tb = (w->half[j] - g0[j]) / al[j];
+            if (ta > tb) { double t = ta; ta = tb; tb = t; }
+            if (ta > t0) t0 = ta;
+            if (tb < t1) t1 = tb;
+          }
+          if (t1 >= t0) {
+            done = 1;
+            for (int end = 0; end < 2; end++) {
+              if (end == 1 && t1 - t0 < 1e-6) break;
+              double t = end == 0 ? t0 : t1, gl[3], nl[3] = {0, 0, 0};
+              for (int i = 0; i < 3; i++) gl[i] = g0[i] + t * al[i];
+              nl[kf] = -sg;
+              c.d = -sg * gl[kf] - w->half[kf];
+              for (int i = 0; i < 3; i++) {
+                c.pa[i] = b->pos[i] + R[3 * i] * gl[0] + R[3 * i + 1] * gl[1] + R[3 * i + 2] * gl[2];
+                c.n[i] = R[3 * i] * nl[0] + R[3 * i + 1] * nl[1] + R[3 * i + 2] * nl[2];
+              }
+              for (int i = 0; i < 3; i++) c.pb[i] = c.pa[i] - c.d * c.n[i];
+              if (c.d < BREAKING) keep_closest(cr, &nr, &c);
+            }
+          }
+        }
+      }
+    }
+    if (!done && c.d < BREAKING) keep_closest(cr, &nr, &c);
+    /* table top: lowest point(s) of the primitive; a cylinder contributes both ends of its lowest generator */
     c.kind = 2; c.mu = mu_l * w->mu_static;
     c.n[0] = 0; c.n[1] = 0; c.n[2] = 1;
-    if (type == 0) { c.pa[0] = cc[0]; c.pa[1] = cc[1]; c.pa[2] = cc[2] - r; }
-    else {
-      r += 0.001; /* hull margin of a URDF cylinder */
-      double t = fabs(ax[2]) < 1e-6 ? 0.0 : (ax[2] > 0 ? -h : h);
-      double u[3] = {-ax[2] * ax[0], -ax[2] * ax[1], 1.0 - ax[2] * ax[2]}, L = sqrt(dot3(u, u));
-      for (int i = 0; i < 3; i++) c.pa[i] = cc[i] + t * ax[i] - (L > 1e-9 ? r * u[i] / L : 0.0);
+    for (int end = 0; end < 2; end++) {
+      if (type == 0) { if (end) break; c.pa[0] = cc[0]; c.pa[1] = cc[1]; c.pa[2] = cc[2] - r; }
+      else {
+        double rr = r + 0.001; /* hull margin of a URDF cylinder */
+        double t = end == 0 ? -h : h;
+        double u[3] = {-ax[2] * ax[0], -ax[2] * ax[1], 1.0 - ax[2] * ax[2]}, L = sqrt(dot3(u, u));
+        for (int i = 0; i < 3; i++) c.pa[i] = cc[i] + t * ax[i] - (L > 1e-6 ? rr * u[i] / L : 0.0);
+      }
+      if (!over_rect(c.pa, w->table_pos, w->table_half)) continue;
+      c.d = c.pa[2] - top;
+      c.pb[0] = c.pa[0]; c.pb[1] = c.pa[1]; c.pb[2] = top;
+      if (c.d < BREAKING) keep_closest(cs, &ns, &c);
     }
-    c.d = c.pa[2] - top;
-    c.pb[0] = c.pa[0]; c.pb[1] = c.pa[1]; c.pb[2] = top;
-    if (c.d < BREAKING) keep_closest(cs, &ns, &c);
   }
   int n = 0;
   for (int i = 0; i < nt; i++) out[n++] = ct[i];

@@ -54,7 +54,7 @@ class HerBatch(ctypes.Structure):
 
 VIEW_IDS = {name: i for i, name in enumerate([
     "observation", "achieved_goal", "desired_goal", "reward", "done", "flags", "terminal_observation",
-    "terminal_achieved", "ep_return", "ep_length", "q", "qd", "goal", "obstacle_pos", "stats", "step_count", "d_link"])}
+    "terminal_achieved", "ep_return", "ep_length", "q", "qd", "goal", "obstacle_pos", "stats", "step_count", "d_link", "object"])}
 
 # every symbol include/panda_b200.h declares: (name, restype, argtypes)
 P = c_void_p
@@ -82,6 +82,7 @@ SYMBOLS = [
     ("pg_set_joint_state", c_int, [P, P, P, P]),
     ("pg_set_goal", c_int, [P, P, P]),
     ("pg_set_obstacles", c_int, [P, P, P]),
+    ("pg_set_object_state", c_int, [P, P, P]),
     ("pg_observe", c_int, [P, P]),
     ("pg_debug_substeps", c_int, [c_int, c_int, P, P, P, P, c_int, c_int, P]),
     ("pg_debug_minv", c_int, [c_int, c_int, P, P, P]),

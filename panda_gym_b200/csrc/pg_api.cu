@@ -84,8 +84,9 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
     if (s->n_obstacles == 0) t = 27;
     else t = P.obstacle_obs == 1 ? 36 : (P.obstacle_obs == 2 ? 27 : (P.obstacle_obs == 3 ? 9 : (P.obstacle_obs == 5 ? 81 : 1)));
   }
+  if (P.task >= 2) t = 12;  // push.py:49-63
   P.task_obs_dim = t;
-  P.obs_dim = 6 + (P.obs_js ? 14 : 0) + t;
+  P.obs_dim = 6 + (P.obs_js ? 14 : 0) + (P.task == PG_TASK_PICK_AND_PLACE ? 1 : 0) + t;  // + fingers width (panda.py:282-284)
 }
 
 void set_goal_box(pg_stage* s, double xl, double xh, double yl, double yh, double zl, double zh) {
@@ -160,6 +161,11 @@ int pg_default_config(pg_config* c, int task, const char* scenario) {
     c->obs_js = 0; c->obstacle_obs = PG_OOBS_NONE; c->base_position[0] = -0.6;
     return pg_stage_from_scenario(&c->stage, "reach_classic");
   }
+  if (task == PG_TASK_PUSH || task == PG_TASK_PICK_AND_PLACE) {
+    // PandaPush-v3 / PandaPickAndPlace-v3 (panda_tasks.py:37-72, __init__.py:58-77): ee control, obs_type ("ee",), base (-0.6, 0, 0)
+    c->control = PG_CTRL_EE; c->obs_js = 0; c->obstacle_obs = PG_OOBS_NONE; c->base_position[0] = -0.6;
+    return pg_stage_from_scenario(&c->stage, "reach_classic");
+  }
   if (task != PG_TASK_REACH_AO) return fail(PG_ERR_ARG, "unknown task");
   c->obs_js = 1; c->obstacle_obs = PG_OOBS_VECTORS_CLOSEST_PER_LINK; c->truncate_on_collision = 1; c->terminate_on_success = 1;
   return pg_stage_from_scenario(&c->stage, scenario ? scenario : "reachao1");
@@ -181,11 +187,14 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   const int n = cfg->n_envs;
   P.n = n; P.task = cfg->task; P.control = cfg->control; P.reward_type = cfg->reward_type; P.goal_condition = cfg->goal_condition;
   P.action_limiter = cfg->action_limiter; P.obs_js = cfg->obs_js; P.obstacle_obs = cfg->obstacle_obs;
-  P.act_dim = cfg->control == PG_CTRL_EE ? 3 : 7;  // block_gripper = True for Reach / ReachAO
+  if (cfg->task < 0 || cfg->task > PG_TASK_PICK_AND_PLACE) { delete h; return fail(PG_ERR_ARG, "unknown task"); }
+  // block_gripper = True except PickAndPlace (panda_tasks.py:49): its extra finger action drives nothing, the loaded
+  // URDF has fixed finger joints
+  P.act_dim = (cfg->control == PG_CTRL_EE ? 3 : 7) + (cfg->task == PG_TASK_PICK_AND_PLACE ? 1 : 0);
   P.n_substeps = cfg->n_substeps; P.truncate_on_collision = cfg->truncate_on_collision; P.terminate_on_success = cfg->terminate_on_success;
   P.auto_reset = cfg->auto_reset; P.collision_reward = (float)cfg->collision_reward; P.safety_distance = cfg->safety_distance;
   for (int k = 0; k < 3; k++) { P.base[k] = (float)cfg->base_position[k]; P.based[k] = cfg->base_position[k]; }
-  if (cfg->task == PG_TASK_REACH) {  // table 1.1 x 0.7 x 0.4 at x = -0.3 (reach.py:33); never queried
+  if (cfg->task != PG_TASK_REACH_AO) {  // table 1.1 x 0.7 x 0.4 at x = -0.3 (reach.py:33, push.py:31); Reach never queries it
     P.table_pos[0] = -0.3; P.table_half[0] = 0.55; P.table_half[1] = 0.35;
   } else {                           // table 2.0 x 1.3 x 0.4 (reach_ao.py:272)
     P.table_pos[0] = 0.0; P.table_half[0] = 1.0; P.table_half[1] = 0.65;
@@ -195,6 +204,13 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   P.scene.has_table = cfg->task == PG_TASK_REACH_AO;
   P.scene.table_margin = (float)tm;
   for (int k = 0; k < 3; k++) { P.scene.table_pos[k] = (float)P.table_pos[k]; P.scene.table_core[k] = (float)(P.table_half[k] - tm); }
+  {  // Push / PickAndPlace world (push.py:29-47, pybullet.py:759-815)
+    pg::WorldParams& W = P.world;
+    W.half[0] = W.half[1] = W.half[2] = 0.02f; W.mass = 1.0f; P.obj_half_z = 0.04 / 2;
+    for (int k = 0; k < 3; k++) { W.table_pos[k] = (float)P.table_pos[k]; W.table_half[k] = (float)P.table_half[k]; }
+    W.plane_top = -0.4f;
+    W.mu_object = 0.5f; W.mu_static = 0.5f; W.mu_link = 0.5f; W.mu_ee = 1.0f;  // Bullet default lateral friction; panda.py:69-70
+  }
   fill_stage(h, &cfg->stage);
   // observation width is fixed at creation (gym spaces); allocate for the widest layout
   const int max_obs = 6 + 14 + 81;
@@ -204,11 +220,11 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   A(P.recent, 7 * n, true) A(P.prev, 7 * n, true) A(P.cur_vel, 7 * n, true) A(P.cur_acc, 7 * n, true) A(P.jerk, 7 * n, true)
   A(P.d_link, 9 * n, true) A(P.past_vec, 54 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
   A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
-  A(P.rng, 4 * n, true) A(P.episode, n, true)
+  A(P.rng, 4 * n, true) A(P.episode, n, true) A(P.obj, 13 * n, true)
   A(P.obs, (size_t)max_obs * n, true) A(P.achieved, 3 * n, true) A(P.desired, 3 * n, true) A(P.reward, n, true)
   A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true) A(P.done, n, true) A(P.flags, n, true)
   A(P.stats, 8, false) A(P.reset_list, n, false) A(P.reset_count, 1, false)
-  A(h->d_actions, 7 * n, false)
+  A(h->d_actions, 8 * n, false)
 #undef A
   // obstacles start where create_obstacle_* puts them: (0.1, 0, 0.1) (reach_ao.py:819, 841)
   {
@@ -307,6 +323,8 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
     pg::k_step2<<<(h->P.n + pg::kPairEnvs - 1) / pg::kPairEnvs, pg::kPairBlock, pg::kPairSmemBytes, (cudaStream_t)stream>>>(h->P, actions_dev);
   } else
 #endif
+  if (h->P.task >= 2) pg::k_step_obj<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
+  else
   pg::k_step<<<(h->P.n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
   h->launches++;
   if (h->P.auto_reset) {
@@ -431,6 +449,7 @@ int pg_get_view(pg_handle h, int id, pg_view* v) {
     case PG_V_STATS: set(P.stats, 3, 1, 8, 0, 0); break;
     case PG_V_STEP_COUNT: set(P.steps, 2, 1, n, 0, 0); break;
     case PG_V_D_LINK: set(P.d_link, 0, 2, 9, n, 0); break;
+    case PG_V_OBJECT: set(P.obj, 0, 2, 13, n, 0); break;
     default: return fail(PG_ERR_ARG, "unknown view id");
   }
   return PG_OK;
@@ -453,6 +472,12 @@ int pg_set_goal(pg_handle h, const double* goal_dev, void* stream) {
   if (!h || !goal_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
   PG_CUDA(cudaMemcpyAsync(h->P.goal, goal_dev, (size_t)3 * h->P.n * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return PG_OK;
+}
+int pg_set_object_state(pg_handle h, const float* obj_dev, void* stream) {
+  if (!h || !obj_dev) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  PG_CUDA(cudaMemcpyAsync(h->P.obj, obj_dev, (size_t)13 * h->P.n * sizeof(float), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return PG_OK;
 }
 int pg_set_obstacles(pg_handle h, const double* pos_dev, void* stream) {

@@ -87,6 +87,7 @@ __device__ __forceinline__ void prim_contacts(const Frame& F, const WorldParams&
     if (sphere_box<float>(cl, bound, o, core, m).d < kBreaking) {  // bounding-sphere reject
       Contact ct; ct.kind = 1; ct.mu = mu_l * W.mu_object;
       V3 dl, pal;
+      bool done = false;
       if (Pm::type == 0) {
         Closest k = sphere_box<float>(cl, Pm::r, o, core, m);
         ct.d = k.d; dl = k.dir; pal = cl + Pm::r * dl;
@@ -108,8 +109,49 @@ __device__ __forceinline__ void prim_contacts(const Frame& F, const WorldParams&
         ct.d = d - kHullMargin - m;
         if (L > 1e-9f) { dl = (1.0f / L) * v; pal = qa + kHullMargin * dl; }
         else { float cn = norm(cl); dl = cn > 1e-12f ? (-1.0f / cn) * cl : v3(0.f, 0.f, -1.f); pal = qa; }  // deep overlap: line of centres
+        // cylinder against a box FACE: the closest point of a generator parallel to the face is not unique (rounding
+        // noise would pick it), so the contact is spread like a manifold: both ends of the generator facing the box,
+        // clipped to the face, each with its own distance
+        if (ct.d < kBreaking) {
+          const float dls[3] = {dl.x, dl.y, dl.z}, als[3] = {al.x, al.y, al.z}, cls[3] = {cl.x, cl.y, cl.z};
+          const int kf = fabsf(dls[0]) > fabsf(dls[1]) ? (fabsf(dls[0]) > fabsf(dls[2]) ? 0 : 2) : (fabsf(dls[1]) > fabsf(dls[2]) ? 1 : 2);
+          if (fabsf(dls[kf]) > 0.999f) {
+            const float sg = dls[kf] > 0.f ? 1.f : -1.f, rr = Pm::r + kHullMargin;
+            float u[3] = {0.f, 0.f, 0.f};
+            u[kf] = sg;
+            const float ua = u[0] * als[0] + u[1] * als[1] + u[2] * als[2];
+            for (int i = 0; i < 3; i++) u[i] -= ua * als[i];
+            const float Lu = sqrtf(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+            if (Lu > 1e-6f) {
+              float g0[3], t0 = -Pm::h, t1 = Pm::h;
+              for (int i = 0; i < 3; i++) g0[i] = cls[i] + rr * u[i] / Lu;
+              for (int j = 0; j < 3; j++) {
+                if (j == kf) continue;
+                if (fabsf(als[j]) < 1e-9f) { if (fabsf(g0[j]) > W.half[j]) t1 = t0 - 1.f; continue; }
+                float ta = (-W.half[j] - g0[j]) / als[j], tb = (W.half[j] - g0[j]) / als[j];
+                if (ta > tb) { float t = ta; ta = tb; tb = t; }
+                t0 = fmaxf(t0, ta); t1 = fminf(t1, tb);
+              }
+              if (t1 >= t0) {
+                done = true;
+                for (int end = 0; end < 2; end++) {
+                  if (end == 1 && t1 - t0 < 1e-6f) break;
+                  const float t = end == 0 ? t0 : t1;
+                  float gl[3], nl[3] = {0.f, 0.f, 0.f};
+                  for (int i = 0; i < 3; i++) gl[i] = g0[i] + t * als[i];
+                  nl[kf] = -sg;
+                  ct.d = -sg * gl[kf] - W.half[kf];
+                  ct.pa = bx + rot_apply(R, v3(gl[0], gl[1], gl[2]));
+                  ct.n = rot_apply(R, v3(nl[0], nl[1], nl[2]));
+                  ct.pb = ct.pa - ct.d * ct.n;
+                  if (ct.d < kBreaking) keep_closest(cr, nr, ct);
+                }
+              }
+            }
+          }
+        }
       }
-      if (ct.d < kBreaking) {
+      if (!done && ct.d < kBreaking) {
         V3 dw = rot_apply(R, dl);
         ct.n = v3(-dw.x, -dw.y, -dw.z);
         ct.pa = bx + rot_apply(R, pal);
@@ -118,22 +160,26 @@ __device__ __forceinline__ void prim_contacts(const Frame& F, const WorldParams&
       }
     }
   }
-  // --- vs the table top: lowest point of the primitive over the table rectangle
-  if (over_rect(c, W.table_pos, W.table_half)) {
+  // --- vs the table top: lowest point(s) of the primitive; a cylinder contributes both ends of its lowest generator
+  {
     const float top = W.table_pos[2] + W.table_half[2];
     Contact ct; ct.kind = 2; ct.mu = mu_l * W.mu_static; ct.n = v3(0.f, 0.f, 1.f);
-    if (Pm::type == 0) ct.pa = v3(c.x, c.y, c.z - Pm::r);
-    else {
-      const float r = Pm::r + kHullMargin;
-      float t = fabsf(a.z) < 1e-6f ? 0.f : (a.z > 0.f ? -Pm::h : Pm::h);
-      V3 u = v3(-a.z * a.x, -a.z * a.y, 1.f - a.z * a.z);
-      float L = norm(u);
-      ct.pa = c + t * a;
-      if (L > 1e-9f) ct.pa = ct.pa - (r / L) * u;
+#pragma unroll
+    for (int end = 0; end < (Pm::type == 0 ? 1 : 2); end++) {
+      if (Pm::type == 0) ct.pa = v3(c.x, c.y, c.z - Pm::r);
+      else {
+        const float r = Pm::r + kHullMargin;
+        const float t = end == 0 ? -Pm::h : Pm::h;
+        V3 u = v3(-a.z * a.x, -a.z * a.y, 1.f - a.z * a.z);
+        float L = norm(u);
+        ct.pa = c + t * a;
+        if (L > 1e-6f) ct.pa = ct.pa - (r / L) * u;
+      }
+      if (!over_rect(ct.pa, W.table_pos, W.table_half)) continue;
+      ct.d = ct.pa.z - top;
+      ct.pb = v3(ct.pa.x, ct.pa.y, top);
+      if (ct.d < kBreaking) keep_closest(cs, ns, ct);
     }
-    ct.d = ct.pa.z - top;
-    ct.pb = v3(ct.pa.x, ct.pa.y, top);
-    if (ct.d < kBreaking) keep_closest(cs, ns, ct);
   }
 }
 

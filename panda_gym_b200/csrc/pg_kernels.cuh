@@ -4,6 +4,7 @@
 #pragma once
 #include <stdint.h>
 #include "pg_scene.cuh"
+#include "pg_contact.cuh"
 #include "pg_neutral.h"
 
 namespace pg {
@@ -51,6 +52,8 @@ struct Params {
   double table_pos[3], table_half[3];
   StageDev st;
   SceneParams scene;
+  WorldParams world;             // Push / PickAndPlace (tasks 2, 3)
+  double obj_half_z;             // object_size / 2 in fp64 for the reset arithmetic (push.py:22, :73)
   uint64_t base_seed;
   // SoA state
   float *q, *qd;                 // [7][n]
@@ -60,6 +63,7 @@ struct Params {
   float *recent, *prev;          // [7][n] action history (panda.py:138-139)
   float *cur_vel, *cur_acc, *jerk; // [7][n] (panda.py:167-172)
   float* d_link;                 // [9][n]
+  float* obj;                    // [13][n] object position, quaternion xyzw, linear / angular velocity (tasks 2, 3)
   float* past_vec;               // [2][27][n] previous two vector observations ("vectors+past", reach_ao.py:918-922)
   uint8_t *have_recent, *have_prev, *collided, *goal_reached, *need_reset;
   int *steps, *ep_len, *last_len;
@@ -198,6 +202,27 @@ __device__ __forceinline__ void observe(const Params& P, int e, const float* q, 
     off = 20;
   }
   ag_out[0] = ee.x; ag_out[1] = ee.y; ag_out[2] = ee.z;
+  if (P.task >= 2) {
+    // fingers opening (panda.py:282-284): the loaded URDF has fixed finger joints, getJointState reports 0
+    if (P.task == 3) o[off++] = 0.f;
+    // Push.get_obs (push.py:49-63): object position, euler rotation (getEulerFromQuaternion), velocity, angular velocity
+    float b[13];
+#pragma unroll
+    for (int k = 0; k < 13; k++) b[k] = P.obj[(size_t)k * n + e];
+    float x = b[3], y = b[4], z = b[5], w = b[6], roll, pitch, yaw;
+    float sarg = -2.f * (x * z - w * y);
+    if (sarg <= -0.99999f) { roll = 0.f; pitch = -1.57079632679f; yaw = 2.f * atan2f(x, -y); }
+    else if (sarg >= 0.99999f) { roll = 0.f; pitch = 1.57079632679f; yaw = 2.f * atan2f(-x, y); }
+    else {
+      roll = atan2f(2.f * (y * z + w * x), w * w - x * x - y * y + z * z);
+      pitch = asinf(sarg);
+      yaw = atan2f(2.f * (x * y + w * z), w * w + x * x - y * y - z * z);
+    }
+    o[off] = b[0]; o[off + 1] = b[1]; o[off + 2] = b[2]; o[off + 3] = roll; o[off + 4] = pitch; o[off + 5] = yaw;
+#pragma unroll
+    for (int k = 0; k < 6; k++) o[off + 6 + k] = b[7 + k];
+    ag_out[0] = b[0]; ag_out[1] = b[1]; ag_out[2] = b[2];  // push.py:65-67
+  }
   if (P.task == 1 && P.obstacle_obs != 0) {
     if (P.scene.nobs == 0) {  // reach_ao.py:904
       for (int k = 0; k < 27; k++) o[off + k] = 1.0f;
@@ -233,7 +258,7 @@ __device__ __forceinline__ void observe(const Params& P, int e, const float* q, 
   }
   float* a = P.achieved + (size_t)e * 3;
   float* g = P.desired + (size_t)e * 3;
-  a[0] = ee.x; a[1] = ee.y; a[2] = ee.z;
+  a[0] = ag_out[0]; a[1] = ag_out[1]; a[2] = ag_out[2];
   g[0] = (float)P.goal[e]; g[1] = (float)P.goal[(size_t)n + e]; g[2] = (float)P.goal[(size_t)2 * n + e];
 }
 
@@ -258,7 +283,7 @@ __device__ __forceinline__ float reward_fn(const Params& P, int src, const float
   const int n = P.n;
   float d = f32_distance(ag, dg);
   float thr = P.st.ee_thr;
-  if (P.task == 0) return P.reward_type == 0 ? -(float)(d > thr) : -d;
+  if (P.task != 1) return P.reward_type == 0 ? -(float)(d > thr) : -d;  // reach.py:84-89, push.py:93-98, pick_and_place.py:91-96
   float coll = (float)P.collided[src];
   float r;
   if (P.reward_type == 0) {
@@ -375,6 +400,7 @@ __device__ __forceinline__ void step_begin(const Params& P, const float* __restr
   if (P.action_limiter == 1) {
     bool any = false; float mx = 0.f;
     for (int k = 0; k < 7; k++) if (k < na) { any |= (a[k] < -1.f || a[k] > 1.f); mx = fmaxf(mx, fabsf(a[k])); }
+    if (na > 7) { float a7 = actions[(size_t)e * na + 7]; any |= (a7 < -1.f || a7 > 1.f); mx = fmaxf(mx, fabsf(a7)); }  // PickAndPlace joints: finger entry
     if (any) for (int k = 0; k < 7; k++) a[k] = a[k] / mx;
   } else {
 #pragma unroll
@@ -387,7 +413,7 @@ __device__ __forceinline__ void step_begin(const Params& P, const float* __restr
   // --- targets
   if (P.control == 1) {
     // ee_displacement_to_target_arm_angles (panda.py:226-246): uses the CACHED end-effector position (last observation)
-    const float* lo = P.achieved + (size_t)e * 3;
+    const float* lo = P.obs + (size_t)e * P.obs_dim;  // observation[0:3] = get_ee_position()
     V3 t = v3(lo[0] + __fmul_rn(a[0], 0.05f), lo[1] + __fmul_rn(a[1], 0.05f), fmaxf(0.f, lo[2] + __fmul_rn(a[2], 0.05f)));
     float tq[7];
     ik_dls(v3(P.base[0], P.base[1], P.base[2]), q, t, tq);
@@ -488,6 +514,39 @@ __global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ 
 #pragma unroll
   for (int d = 0; d < 7; d++) q[d] = qs[d * kStepBlock];
   step_end(P, e, q, qd, collided);
+}
+
+// Push / PickAndPlace (tasks 2, 3): the same step with the object world (pg_contact.cuh) in place of the arm-only
+// substep.  One environment per thread; rows and contacts live in local memory.
+__device__ __forceinline__ ObjState load_obj(const Params& P, int e) {
+  const size_t n = P.n;
+  ObjState B;
+  B.x = v3(P.obj[e], P.obj[n + e], P.obj[2 * n + e]);
+  B.qx = P.obj[3 * n + e]; B.qy = P.obj[4 * n + e]; B.qz = P.obj[5 * n + e]; B.qw = P.obj[6 * n + e];
+  B.v = v3(P.obj[7 * n + e], P.obj[8 * n + e], P.obj[9 * n + e]);
+  B.w = v3(P.obj[10 * n + e], P.obj[11 * n + e], P.obj[12 * n + e]);
+  return B;
+}
+__device__ __forceinline__ void store_obj(const Params& P, int e, const ObjState& B) {
+  const size_t n = P.n;
+  P.obj[e] = B.x.x; P.obj[n + e] = B.x.y; P.obj[2 * n + e] = B.x.z;
+  P.obj[3 * n + e] = B.qx; P.obj[4 * n + e] = B.qy; P.obj[5 * n + e] = B.qz; P.obj[6 * n + e] = B.qw;
+  P.obj[7 * n + e] = B.v.x; P.obj[8 * n + e] = B.v.y; P.obj[9 * n + e] = B.v.z;
+  P.obj[10 * n + e] = B.w.x; P.obj[11 * n + e] = B.w.y; P.obj[12 * n + e] = B.w.z;
+}
+__global__ void __launch_bounds__(kBlock) k_step_obj(const Params P, const float* __restrict__ actions) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= P.n) return;
+  float q[7], qd[7], cq[7], sq[7], tgt[7];
+  bool velocity_mode = false, unit_imp = false;
+  step_begin(P, actions, e, q, qd, tgt, 1, velocity_mode, unit_imp);
+#pragma unroll
+  for (int d = 0; d < 7; d++) sincosf(q[d], &sq[d], &cq[d]);
+  ObjState B = load_obj(P, e);
+  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
+  for (int k = 0; k < P.n_substeps; k++) world_substep(velocity_mode, unit_imp, base, P.world, q, qd, cq, sq, tgt, B);
+  store_obj(P, e, B);
+  step_end(P, e, q, qd, false);
 }
 
 #ifdef PG_PAIR_KERNEL
@@ -690,6 +749,19 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
   const StageDev& st = P.st;
   if (P.task == 0) {
     for (int k = 0; k < 3; k++) goal[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]);
+  } else if (P.task >= 2) {
+    // Push.reset (push.py:69-87) / PickAndPlace.reset (pick_and_place.py:65-85): goal, then object; xy range 0.3;
+    // PickAndPlace lifts the goal by U(0, 0.2) and flattens it again with probability 0.3
+    const double half = P.obj_half_z;
+    double nx = pcg_uniform(g, -0.15, 0.15), ny = pcg_uniform(g, -0.15, 0.15), nz = pcg_uniform(g, 0.0, P.task == 3 ? 0.2 : 0.0);
+    if (P.task == 3 && pcg_double(g) < 0.3) nz = 0.0;
+    goal[0] = 0.0 + nx; goal[1] = 0.0 + ny; goal[2] = half + nz;
+    nx = pcg_uniform(g, -0.15, 0.15); ny = pcg_uniform(g, -0.15, 0.15); nz = pcg_uniform(g, 0.0, 0.0);
+    ObjState B;
+    B.x = v3((float)(0.0 + nx), (float)(0.0 + ny), (float)(half + nz));
+    B.qx = B.qy = B.qz = 0.f; B.qw = 1.f; B.v = v3(0, 0, 0); B.w = v3(0, 0, 0);  // set_base_pose: identity orientation, velocities zeroed
+    store_obj(P, e, B);
+    P.have_recent[e] = 0; P.have_prev[e] = 0;
   } else {
     P.goal_reached[e] = 0; P.collided[e] = 0;
     Body table; table.type = 1; table.px = P.table_pos[0]; table.py = P.table_pos[1]; table.pz = P.table_pos[2];

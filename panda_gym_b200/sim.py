@@ -55,7 +55,8 @@ def make_config(task, n_envs, scenario=None, config=None, control_type=None, rew
         cfg.collision_reward = float(c.collision_reward)
         cfg.safety_distance = float(c.safety_distance)
     else:
-        cfg.control = CONTROL[control_type or "js"]
+        # PandaReach* / PandaPush* / PandaPickAndPlace* ids pass control_type "ee" or "joints" (panda_gym/__init__.py:23-77)
+        cfg.control = CONTROL[control_type or ("js" if task == 0 else "ee")]
         cfg.reward_type = REWARD_CLASSIC[reward_type or "sparse"]
     if base_position is not None:
         for k in range(3):
@@ -194,6 +195,12 @@ class PandaBatch:
     def set_goal(self, goal):
         g = goal.to(self.device, torch.float64).contiguous()
         _lib.check(self.lib.pg_set_goal(self.h, ctypes.c_void_p(g.data_ptr()), self._stream()))
+
+    def set_object_state(self, obj):
+        """[13][n]: position, quaternion xyzw, linear velocity, angular velocity of the Push / PickAndPlace object."""
+        o = obj.to(self.device, torch.float32).contiguous()
+        assert o.numel() == 13 * self.n
+        _lib.check(self.lib.pg_set_object_state(self.h, ctypes.c_void_p(o.data_ptr()), self._stream()))
 
     def set_obstacles(self, pos):
         p = pos.to(self.device, torch.float64).contiguous()
