@@ -323,7 +323,7 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
     pg::k_step2<<<(h->P.n + pg::kPairEnvs - 1) / pg::kPairEnvs, pg::kPairBlock, pg::kPairSmemBytes, (cudaStream_t)stream>>>(h->P, actions_dev);
   } else
 #endif
-  if (h->P.task >= 2) pg::k_step_obj<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
+  if (h->P.task >= 2) pg::k_step_obj<<<(h->P.n + pg::kObjBlock - 1) / pg::kObjBlock, pg::kObjBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
   else
   pg::k_step<<<(h->P.n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
   h->launches++;

@@ -275,6 +275,7 @@ __device__ __noinline__ void setup_row(Row& r, const ArmKin& K, const float* Mi,
   }
 }
 
+// returns the impulse change; the row's residual (what Bullet's early-out tests) is delta / dinv
 __device__ __forceinline__ float solve_row(Row& r, float lo, float hi, float inv_mass, float* dva, V3& dvl, V3& dvw) {
   float jv = 0.f;
   if (r.arm) {
@@ -292,8 +293,9 @@ __device__ __forceinline__ float solve_row(Row& r, float lo, float hi, float inv
     for (int d = 0; d < 7; d++) dva[d] = fmaf(r.ra[d], delta, dva[d]);
   }
   if (r.body) { dvl = axpy<float>(delta * inv_mass, r.jl, dvl); dvw = axpy<float>(delta, r.rw, dvw); }
-  return r.dinv != 0.f ? delta / r.dinv : 0.f;
+  return delta;
 }
+__device__ __forceinline__ float row_residual(const Row& r, float delta) { return r.dinv != 0.f ? fabsf(delta / r.dinv) : 0.f; }
 
 // ------------------------------------------------------------------------------------------------ one stepSimulation()
 // q, qd, cq, sq, tgt as in substep() (pg_dynamics.cuh) with stride 1; B = the object.  Returns the PGS iterations used.
@@ -376,6 +378,8 @@ __device__ __noinline__ int world_substep(bool velocity, bool unit_imp, V3 base,
     res = fmaxf(res, fabsf(delta * Mi[sym(d, d)]));                         \
   }
   V3 dvl = v3(0, 0, 0), dvw = v3(0, 0, 0);
+  bool obj_island = true, obj_live = true;
+  for (int i = 0; i < nc; i++) obj_island &= ct[i].kind != 1;
   const float inv_mass = 1.0f / W.mass;
   int it = 0;
   for (; it < kSolverIters; it++) {
@@ -387,11 +391,29 @@ __device__ __noinline__ int world_substep(bool velocity, bool unit_imp, V3 base,
       PG_WM_ROW(6) PG_WM_ROW(5) PG_WM_ROW(4) PG_WM_ROW(3) PG_WM_ROW(2) PG_WM_ROW(1) PG_WM_ROW(0)
       PG_WL_ROW(6) PG_WL_ROW(5) PG_WL_ROW(4) PG_WL_ROW(3) PG_WL_ROW(2) PG_WL_ROW(1) PG_WL_ROW(0)
     }
-    for (int i = 0; i < nc; i++) res = fmaxf(res, fabsf(solve_row(nrow[i], 0.f, 1e10f, inv_mass, dv, dvl, dvw)));
-    for (int i = 0; i < 2 * nc; i++) {
-      float tot = nrow[i >> 1].applied;
-      if (tot > 0.f) { float lim = ct[i >> 1].mu * tot; res = fmaxf(res, fabsf(solve_row(frow[i], -lim, lim, inv_mass, dv, dvl, dvw))); }
+    // Rows of the object-table pair form an independent island while nothing else touches the object.  Once every one
+    // of them moves by less than an ulp of its impulse the island sits at its fixed point -- further sweeps would
+    // reproduce the same values -- and it is skipped for the rest of the solve (the arm usually needs all 50 sweeps,
+    // the resting object 3-5).
+    const bool skip_obj = obj_island && !obj_live;
+    float act = 0.f;
+    for (int i = 0; i < nc; i++) {
+      if (skip_obj && ct[i].kind == 0) continue;
+      float delta = solve_row(nrow[i], 0.f, 1e10f, inv_mass, dv, dvl, dvw);
+      res = fmaxf(res, row_residual(nrow[i], delta));
+      if (ct[i].kind == 0) act = fmaxf(act, fabsf(delta) - 2.4e-7f * fabsf(nrow[i].applied));
     }
+    for (int i = 0; i < 2 * nc; i++) {
+      if (skip_obj && ct[i >> 1].kind == 0) continue;
+      float tot = nrow[i >> 1].applied;
+      if (tot > 0.f) {
+        float lim = ct[i >> 1].mu * tot;
+        float delta = solve_row(frow[i], -lim, lim, inv_mass, dv, dvl, dvw);
+        res = fmaxf(res, row_residual(frow[i], delta));
+        if (ct[i >> 1].kind == 0) act = fmaxf(act, fabsf(delta) - 2.4e-7f * lim);
+      }
+    }
+    if (obj_island && obj_live && act <= 0.f) obj_live = false;
     if (res <= 3.1622777e-4f) { it++; break; }  // sqrt(1e-7)
   }
 #undef PG_WM_ROW

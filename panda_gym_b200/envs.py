@@ -27,8 +27,10 @@ def register_envs(max_ep_steps):
         for control_type in ("ee", "joints"):
             rs = "Dense" if reward_type == "dense" else ""
             cs = "Joints" if control_type == "joints" else ""
-            _REGISTERED["PandaReach%s%s-v3" % (cs, rs)] = dict(
-                cls="reach", max_episode_steps=max_ep_steps, kwargs=dict(reward_type=reward_type, control_type=control_type))
+            kw = dict(reward_type=reward_type, control_type=control_type)
+            _REGISTERED["PandaReach%s%s-v3" % (cs, rs)] = dict(cls="reach", max_episode_steps=max_ep_steps, kwargs=dict(kw))
+            _REGISTERED["PandaPush%s%s-v3" % (cs, rs)] = dict(cls="push", max_episode_steps=max_ep_steps, kwargs=dict(kw))
+            _REGISTERED["PandaPickAndPlace%s%s-v3" % (cs, rs)] = dict(cls="pnp", max_episode_steps=max_ep_steps, kwargs=dict(kw))
     register_reach_ao(max_ep_steps)
 
 
@@ -38,7 +40,7 @@ def make(env_id, **kwargs):
     spec = _REGISTERED[env_id]
     kw = dict(spec["kwargs"])
     kw.update(kwargs)
-    cls = PandaReachAOEnv if spec["cls"] == "ao" else PandaReachEnv
+    cls = {"ao": PandaReachAOEnv, "reach": PandaReachEnv, "push": PandaPushEnv, "pnp": PandaPickAndPlaceEnv}[spec["cls"]]
     return cls(max_episode_steps=spec["max_episode_steps"], **kw)
 
 
@@ -154,3 +156,31 @@ class PandaReachEnv(RobotTaskEnv):
             for k, (lo, hi) in enumerate(((-goal_range / 2, goal_range / 2), (-goal_range / 2, goal_range / 2), (0.0, goal_range))):
                 cfg.stage.goal_lo[k], cfg.stage.goal_hi[k] = lo, hi
         self._setup(cfg, device, False, max_episode_steps)
+
+
+class PandaPushEnv(RobotTaskEnv):
+    """reference panda_tasks.py:55-69 + envs/tasks/push.py (block_gripper=True, cube 4 cm, mass 1)."""
+
+    _TASK = 2
+
+    def __init__(self, render=False, reward_type="sparse", control_type="js", max_episode_steps=50, device=0):
+        cfg = sim.make_config(self._TASK, 1, control_type=control_type, reward_type=reward_type, max_episode_steps=max_episode_steps,
+                              auto_reset=False)
+        self._setup(cfg, device, False, max_episode_steps)
+        # sim.get_base_* of the "object" body (pybullet.py:182-247), what Push.get_obs reads
+        self.sim.get_base_position = lambda body="object": self.batch.view("object")[0:3, 0].cpu().numpy().astype(np.float64)
+        self.sim.get_base_orientation = lambda body="object": self.batch.view("object")[3:7, 0].cpu().numpy().astype(np.float64)
+        self.sim.get_base_velocity = lambda body="object": self.batch.view("object")[7:10, 0].cpu().numpy().astype(np.float64)
+        self.sim.get_base_angular_velocity = lambda body="object": self.batch.view("object")[10:13, 0].cpu().numpy().astype(np.float64)
+
+
+class PandaPickAndPlaceEnv(PandaPushEnv):
+    """reference panda_tasks.py:37-52 + envs/tasks/pick_and_place.py.  Simulated as the reference loads it: the
+    franka_panda_custom_0 URDF has FIXED finger joints, so the 4th action entry moves nothing, the finger width in the
+    observation is 0 and lifted goals are out of reach (documented in DESIGN.md)."""
+
+    _TASK = 3
+
+    def __init__(self, render=False, reward_type="sparse", control_type="ee", max_episode_steps=50, device=0):
+        super().__init__(render=render, reward_type=reward_type, control_type=control_type, max_episode_steps=max_episode_steps,
+                         device=device)

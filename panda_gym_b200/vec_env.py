@@ -21,6 +21,8 @@ ENV_IDS = {}
 for _rew, _rs in (("sparse", ""), ("dense", "Dense")):
     for _ct, _cs in (("ee", ""), ("joints", "Joints")):
         ENV_IDS["PandaReach%s%s-v3" % (_cs, _rs)] = dict(task=0, reward_type=_rew, control_type=_ct)
+        ENV_IDS["PandaPush%s%s-v3" % (_cs, _rs)] = dict(task=2, reward_type=_rew, control_type=_ct)
+        ENV_IDS["PandaPickAndPlace%s%s-v3" % (_cs, _rs)] = dict(task=3, reward_type=_rew, control_type=_ct)
 ENV_IDS["PandaReachAO-v3"] = dict(task=1)
 
 
