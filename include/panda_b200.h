@@ -152,6 +152,11 @@ int pg_num_envs(pg_handle h);
 /* number of kernels this library launched on behalf of the handle so far */
 int64_t pg_launch_count(pg_handle h);
 
+/* Panda.get_manipulability (panda.py:314-317; called by ReachAO.compute_reward, reach_ao.py:1311): Yoshikawa index
+ * sqrt(det(Jv Jv^T)) of the translational Jacobian at roboticstoolbox's Panda end-effector link (panda_link8).
+ * q_dev NULL: the handle's current joint angles, out_dev f32 [num_envs]; else q_dev f32 [7][n] -> out_dev f32 [n]. */
+int pg_manipulability(pg_handle h, const float* q_dev, int64_t n, float* out_dev, void* stream);
+
 /* ---- matched-state entry points used by the parity tests (pybullet getters/setters of pybullet.py) ---- */
 /* resetJointState for every env (pybullet.py:427-435): q_dev f32 [7][n]; velocities zeroed unless qd_dev given */
 int pg_set_joint_state(pg_handle h, const float* q_dev, const float* qd_dev, void* stream);

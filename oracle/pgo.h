@@ -55,6 +55,8 @@ void pgo_arm_ik(const pgo_arm*, int link, const double pos[3], const double* qua
 void pgo_arm_set_ik(pgo_arm*, double joint_damping, int max_iters, double residual_thr);
 /* translational Jacobian (3 x ndof) of a link COM, world frame */
 void pgo_arm_jacobian(const pgo_arm*, int link, double* Jt, double* Jr);
+/* Panda.get_manipulability (panda.py:314-317): Yoshikawa index of the translational Jacobian at the flange (panda_link8) */
+double pgo_arm_manipulability(const pgo_arm*);
 
 /* ---------------------------------------------------------------- closest distances (getClosestPoints) */
 typedef struct {

@@ -246,6 +246,29 @@ void pgo__arm_point_jacobian(const pgo_arm* a0, int link, const double p[3], dou
   }
 }
 
+/* Panda.get_manipulability (panda.py:314-317): rtb.models.Panda().manipulability(q, axes="trans") = Yoshikawa index
+ * sqrt(det(Jv Jv^T)), Jv = 3 x 7 translational Jacobian of roboticstoolbox's URDF Panda at its end-effector link
+ * panda_link8 (the flange: link7 frame + (0, 0, 0.107); the toolbox declares panda_hand and below as the gripper, so
+ * ee_links = [panda_link8], no tool transform).  The toolbox model is franka_description's chain, whose joint origins
+ * equal the loaded URDF's (checked in tests against Franka's published DH table); the index does not depend on the
+ * base offset.  PARITY UNPINNED: roboticstoolbox is not installable here and the reference holds no vector for it. */
+double pgo_arm_manipulability(const pgo_arm* a0) {
+  pgo_arm* a = (pgo_arm*)a0;
+  fk(a);
+  const int flange = 7; /* panda_link8 in both model tables */
+  double J[3 * PGO_MAXD], A[3][3];
+  pgo__arm_point_jacobian(a0, flange, a->ow[flange], J);
+  for (int r = 0; r < 3; r++)
+    for (int c = 0; c < 3; c++) {
+      double v = 0;
+      for (int d = 0; d < 7; d++) v += J[r * a->nd + d] * J[c * a->nd + d];
+      A[r][c] = v;
+    }
+  double det = A[0][0] * (A[1][1] * A[2][2] - A[1][2] * A[2][1]) - A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+               A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+  return det > 0 ? sqrt(det) : 0.0;
+}
+
 /* ------------------------------------------------------------------ articulated-body algorithm
  * Spatial vectors are (angular; linear) in the link's COM frame (Bullet's btMultiBody convention).  */
 static void build_X(const double* R, const double* rp, double* X) { /* motion transform parent->child */

@@ -496,6 +496,17 @@ int pg_observe(pg_handle h, void* stream) {
   return PG_OK;
 }
 
+int pg_manipulability(pg_handle h, const float* q_dev, int64_t n, float* out_dev, void* stream) {
+  if (!h || !out_dev) return fail(PG_ERR_ARG, "NULL handle or output");
+  if (q_dev && n <= 0) return fail(PG_ERR_ARG, "n must be positive when q_dev is given");
+  PG_CUDA(cudaSetDevice(h->device));
+  const int m = q_dev ? (int)n : h->P.n;
+  pg::k_manipulability<<<(m + 127) / 128, 128, 0, (cudaStream_t)stream>>>(m, q_dev ? q_dev : h->P.q, out_dev);
+  h->launches++;
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
 int pg_debug_substeps(int device, int n, float* q, float* qd, const float* tgt, const float* f, int n_sub, int velocity_mode, void* stream) {
   if (!q || !qd || !tgt || !f || n <= 0) return fail(PG_ERR_ARG, "bad argument");
   static const float kForces[7] = {87.f, 87.f, 87.f, 87.f, 12.f, 120.f, 120.f};  // panda.py:63, compiled into the kernels

@@ -935,6 +935,35 @@ __global__ void k_debug_minv(int n, const float* q_in, float* out) {
 #pragma unroll
   for (int k = 0; k < 28; k++) out[(size_t)k * n + e] = M[k];
 }
+// Panda.get_manipulability (panda.py:314-317): roboticstoolbox Panda().manipulability(q, axes="trans") = Yoshikawa index
+// sqrt(det(Jv Jv^T)) of the 3 x 7 translational Jacobian at the toolbox model's end-effector link panda_link8 (flange =
+// link7 frame + (0, 0, 0.107)).  compute_reward refreshes it every step (reach_ao.py:1311, :1381); it feeds no reward.
+// q f32 [7][n] -> out f32 [n].  Same formula as oracle pgo_arm_manipulability.
+__global__ void k_manipulability(int n, const float* __restrict__ q_in, float* __restrict__ out) {
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  float c[7], s[7];
+#pragma unroll
+  for (int d = 0; d < 7; d++) sincosf(q_in[(size_t)d * n + e], &s[d], &c[d]);
+  ArmKin K;
+  arm_kin(v3(0.f, 0.f, 0.f), c, s, K);
+  const V3 p = frame_point(K.F7, 0.f, 0.f, 0.107f);
+  // det(Jv Jv^T) by Cauchy-Binet = sum over the 35 column triples of det(J_S)^2: no cancellation between the terms, so the
+  // index keeps its relative accuracy in fp32 near singular poses (the 3 x 3 Gram determinant does not)
+  V3 J[7];
+#pragma unroll
+  for (int d = 0; d < 7; d++) J[d] = cross(K.ax[d], p - K.org[d]);
+  float det = 0.f;
+#pragma unroll
+  for (int i = 0; i < 5; i++)
+#pragma unroll
+    for (int j = i + 1; j < 6; j++) {
+      V3 cij = cross(J[i], J[j]);
+#pragma unroll
+      for (int k = j + 1; k < 7; k++) { float m = dot(cij, J[k]); det = fmaf(m, m, det); }
+    }
+  out[e] = det > 0.f ? sqrtf(det) : 0.f;
+}
 __global__ void k_debug_ik(int n, const float* q_in, const float* tgt, float bx, float by, float bz, float* out) {
   int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n) return;

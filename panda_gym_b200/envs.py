@@ -72,6 +72,7 @@ class RobotTaskEnv:
         self.robot = _Namespace()
         self.robot.get_joint_angles = lambda: self.batch.view("q")[:, 0].cpu().numpy().astype(np.float64)
         self.robot.get_joint_velocities = lambda: self.batch.view("qd")[:, 0].cpu().numpy().astype(np.float64)
+        self.robot.get_manipulability = lambda: float(self.batch.manipulability()[0])  # panda.py:314-317
         self.sim = _Namespace()
         self.sim.dt = (1.0 / 500) * self.batch.cfg.n_substeps  # PyBullet.dt (pybullet.py:63-66)
 

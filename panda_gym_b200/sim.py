@@ -169,6 +169,17 @@ class PandaBatch:
     def observe(self):
         _lib.check(self.lib.pg_observe(self.h, self._stream()))
 
+    def manipulability(self, q=None):
+        """Panda.get_manipulability (panda.py:314-317) for every environment (q None) or for q f32 [7][m] on the device."""
+        if q is None:
+            out = torch.empty(self.n, dtype=torch.float32, device=self.device)
+            _lib.check(self.lib.pg_manipulability(self.h, None, 0, ctypes.c_void_p(out.data_ptr()), self._stream()))
+        else:
+            assert q.is_cuda and q.dtype == torch.float32 and q.dim() == 2 and q.shape[0] == 7 and q.is_contiguous()
+            out = torch.empty(q.shape[1], dtype=torch.float32, device=q.device)
+            _lib.check(self.lib.pg_manipulability(self.h, ctypes.c_void_p(q.data_ptr()), q.shape[1], ctypes.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
     def save_state(self):
         sid = ctypes.c_int(-1)
         _lib.check(self.lib.pg_save_state(self.h, ctypes.byref(sid), self._stream()))

@@ -190,6 +190,9 @@ class PandaVecEnv:
         idx = self._indices(indices)
         if method_name == "compute_reward":
             return [self.compute_reward(args[0], args[1], args[2] if len(args) > 2 else None, env_index=i) for i in idx]
+        if method_name == "get_manipulability":  # robot.get_manipulability (panda.py:314-317)
+            m = self.batch.manipulability().cpu().numpy()
+            return [float(m[i]) for i in idx]
         raise _lib.PandaB200Error("env_method(%r) is not part of the supported hot path" % method_name)
 
     def _indices(self, indices):

@@ -91,6 +91,7 @@ def lib():
     sig("pgo_arm_ik", None, P, c_int, P, P, P)
     sig("pgo_arm_set_ik", None, P, c_double, c_int, c_double)
     sig("pgo_arm_jacobian", None, P, c_int, P, P)
+    sig("pgo_arm_manipulability", c_double, P)
     sig("pgo_box_margin", c_double, P)
     sig("pgo_prim_obstacle_distance", c_double, P, c_int, P, P, P)
     sig("pgo_link_obstacle_distance", c_double, P, c_int, P, P, P)
@@ -191,6 +192,9 @@ class Arm:
         Jt = np.zeros((3, self.nd)); Jr = np.zeros((3, self.nd))
         self.L.pgo_arm_jacobian(self.h, link, dp(Jt), dp(Jr))
         return Jt, Jr
+
+    def manipulability(self):
+        return float(self.L.pgo_arm_manipulability(self.h))
 
     def link_obstacle_distance(self, link, obstacle):
         pa = np.zeros(3); pb = np.zeros(3)

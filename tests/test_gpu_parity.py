@@ -505,3 +505,28 @@ def test_full_size_properties(sim):
     assert st[0] == total_done and st[0] == st[1] + st[2] + st[3]
     assert st[6] == 0  # no rejection loop hit its cap
     b.close()
+
+
+# ------------------------------------------------------------------------------------------ a15: manipulability
+def test_manipulability_matches_oracle(sim, oracle):
+    """Panda.get_manipulability (panda.py:314-317): Yoshikawa index at the flange, kernel vs oracle, rel 1e-4."""
+    rng = np.random.default_rng(15)
+    n = 513
+    Q = rng.uniform(Q_LO, Q_HI, (n, 7)).astype(np.float32)
+    Q[0] = [0.0, 0.41, 0.0, -1.85, 0.0, 2.26, 0.79]  # Panda.neutral_joint_values (panda.py:56)
+    cfg = sim.make_config(1, n, scenario="reachao3", max_episode_steps=100, auto_reset=False)
+    b = sim.PandaBatch(cfg, device=0)
+    b.seed(3)
+    b.reset()
+    got_free = b.manipulability(soa(Q)).cpu().numpy()
+    b.set_joint_state(soa(Q))
+    got_state = b.manipulability().cpu().numpy()
+    arm = oracle.Arm(model=0, base=(-0.6, 0.0, 0.0))
+    want = np.zeros(n)
+    for e in range(n):
+        arm.set_q(Q[e].astype(np.float64), np.zeros(7))
+        want[e] = arm.manipulability()
+    err = np.abs(got_free - want)
+    assert (err < 2e-6 + 1e-4 * want).all(), (err.max(), want[err.argmax()])
+    assert np.array_equal(got_state, got_free)
+    assert abs(got_free[0] - 0.160705) < 1e-5

@@ -94,3 +94,34 @@ def test_minv_symmetric_positive(oracle):
         M = arm.minv()
         assert np.allclose(M, M.T, atol=1e-9)
         assert np.all(np.linalg.eigvalsh(M) > 0)
+
+
+def test_manipulability_matches_franka_dh_table():
+    """a15: the oracle's Yoshikawa index (panda.py:314-317) against an independent statement of the kinematics --
+    Franka's published modified-DH table (what roboticstoolbox's DH Panda uses) with a numerical Jacobian."""
+    import oracle_lib as O
+
+    def fk(q):
+        aa = [0, 0, 0, 0.0825, -0.0825, 0, 0.088, 0]
+        dd = [0.333, 0, 0.316, 0, 0.384, 0, 0, 0.107]
+        al = [0, -np.pi / 2, np.pi / 2, np.pi / 2, -np.pi / 2, np.pi / 2, np.pi / 2, 0]
+        T = np.eye(4)
+        for i in range(8):
+            th = q[i] if i < 7 else 0.0
+            ca, sa, ct, st = np.cos(al[i]), np.sin(al[i]), np.cos(th), np.sin(th)
+            T = T @ np.array([[ct, -st, 0, aa[i]], [st * ca, ct * ca, -sa, -dd[i] * sa], [st * sa, ct * sa, ca, dd[i] * ca], [0, 0, 0, 1]])
+        return T[:3, 3]
+
+    def manip(q):
+        J = np.zeros((3, 7))
+        for i in range(7):
+            e = np.zeros(7); e[i] = 1e-6
+            J[:, i] = (fk(q + e) - fk(q - e)) / 2e-6
+        return np.sqrt(max(np.linalg.det(J @ J.T), 0.0))
+
+    arm = O.Arm(model=0, base=(-0.6, 0.0, 0.0))
+    rng = np.random.default_rng(4)
+    qs = [np.zeros(7), np.array([0.0, 0.41, 0.0, -1.85, 0.0, 2.26, 0.79])] + [rng.uniform(-2.5, 2.5, 7) for _ in range(50)]
+    for q in qs:
+        arm.set_q(q, np.zeros(7))
+        assert abs(arm.manipulability() - manip(q)) < 1e-7
