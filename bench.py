@@ -69,6 +69,11 @@ def summarize_clocks(samples):
             "reasons": sorted(reasons)}
 
 
+def workload_name(scenario, n):
+    return ("BASELINE configs[1]: PandaReachAO-v3 collision-avoidance reach, scenario %s, %d envs/GPU, joints control, "
+            "sparse reward + collision penalty -100, TimeLimit 100, 20 substeps, auto-reset" % (scenario, n))
+
+
 def cpu_reference_line(args, scenario):
     import oracle_lib as O
     O.build()
@@ -91,8 +96,9 @@ def cpu_reference_line(args, scenario):
         "impl": "reference", "metric": "env-steps/sec (whole box)", "value": value, "unit": "env-steps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_all / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "PandaReachAO-v3 %s, joints control, sparse, collision penalty, TimeLimit 100" % scenario,
-                   "note": "CPU restatement of the reference path (PyBullet itself is not installable here)"},
+        "config": {"workload": workload_name(scenario, args.envs_per_gpu), "envs_per_gpu": args.envs_per_gpu, "scenario": scenario,
+                   "note": "reference arm: CPU restatement of the reference path (PyBullet itself is not installable here), "
+                           "a bounded sample of the workload per timed step"},
         "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -217,15 +223,21 @@ def main():
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
     hbm_achieved = BYTES_PER_ENV_STEP * N / (ms_per_step * 1e-3) / 1e9
     stats = env.episode_stats()
+    traffic = None  # dram__bytes_read + dram__bytes_write of one k_step launch, from the committed ncu --set full capture
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_k_step_traffic.json")) as f:
+            tj = json.load(f)
+        if args.scenario == "reachao3" and N == 65536:
+            traffic = tj["traffic_bytes_per_launch"]
+    except Exception:
+        pass
 
     if rank == 0:
         line = {
             "metric": "env-steps/sec (whole box)", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": "BASELINE configs[1]: PandaReachAO-v3 collision-avoidance reach, scenario %s, %d envs/GPU, "
-                                   "joints control, sparse reward + collision penalty -100, TimeLimit 100, 20 substeps, auto-reset"
-                                   % (args.scenario, N),
+            "config": {"workload": workload_name(args.scenario, N),
                        "envs_per_gpu": N, "scenario": args.scenario, "sharding": "envs partitioned contiguously, no data-path collective",
                        "l2": "flushed between timed steps (256 MiB write); per-step CUDA-event timing on the launch stream",
                        "actions": "U(-1,1), counter-based, pre-generated in HBM"},
@@ -234,7 +246,7 @@ def main():
             "gpu_launches": launches,
             "clocks": summarize_clocks(samples),
             "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
-                         "frac": achieved_tflops / fp32_peak if fp32_peak else None, "traffic": None, "kernel": "k_step",
+                         "frac": achieved_tflops / fp32_peak if fp32_peak else None, "traffic": traffic, "kernel": "k_step",
                          "flops_per_env_step": flops,
                          "peak_source": "FP32 FMA micro-benchmark measured in this run (pg_debug_fma_peak); MEASURED_PEAKS.json has no FP32 figure",
                          "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
