@@ -31,3 +31,29 @@ def allreduce_stats(stats, group=None):
     out["mean_return"] = out["sum_return"] / ep
     out["mean_length"] = out["sum_length"] / ep
     return out
+
+
+def allgather_samples(samples, group=None):
+    """Replay all-gather: every rank contributes the minibatch it sampled from its own replay shard
+    (``HerReplayBuffer.sample``: the shard holds the transitions of the rank's environments) and receives the
+    concatenation over ranks, rank-major -- what a single learner that trains on all shards consumes
+    (SURVEY 8e).  The nine fields of a sample are packed into one ``[B, W]`` row block so the exchange is ONE
+    ``all_gather_into_tensor`` (NCCL over NVLink on GPUs; gloo in the CPU tests), then split back into views of the
+    gathered block.  Every rank must pass the same batch size.  Without an initialised process group it returns
+    the input unchanged."""
+    from .her import DictReplayBufferSamples
+    if not (dist.is_available() and dist.is_initialized()):
+        return samples
+    world = dist.get_world_size(group)
+    o, no = samples.observations, samples.next_observations
+    keys = ("observation", "achieved_goal", "desired_goal")
+    fields = [o[k] for k in keys] + [samples.actions] + [no[k] for k in keys] + [samples.dones, samples.rewards]
+    B = fields[0].shape[0]
+    widths = [int(f.numel() // B) for f in fields]
+    packed = torch.cat([f.reshape(B, w).to(torch.float32) for f, w in zip(fields, widths)], dim=1).contiguous()
+    out = torch.empty((world * B, packed.shape[1]), dtype=packed.dtype, device=packed.device)
+    dist.all_gather_into_tensor(out, packed, group=group)
+    parts = torch.split(out, widths, dim=1)
+    obs = {k: parts[i] for i, k in enumerate(keys)}
+    nobs = {k: parts[4 + i] for i, k in enumerate(keys)}
+    return DictReplayBufferSamples(obs, parts[3], nobs, parts[7], parts[8])

@@ -36,3 +36,36 @@ def test_two_rank_sharding_and_stats_allreduce():
     assert r0 == r1                                                         # every rank sees the global statistics
     assert r0["episodes"] == 21.0 and r0["successes"] == 6.0 and r0["collisions"] == 10.0
     assert abs(r0["success_rate"] - 6.0 / 21.0) < 1e-12 and abs(r0["mean_return"] + 150.0 / 21.0) < 1e-12
+
+
+def _gather_worker(rank, world, port, out):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from panda_gym_b200.her import DictReplayBufferSamples
+    from panda_gym_b200.sharding import allgather_samples
+    B, od, ad = 5, 56, 7
+    g = torch.Generator().manual_seed(100 + rank)
+    mk = lambda w: torch.rand((B, w), generator=g) + 10.0 * rank
+    local = DictReplayBufferSamples({"observation": mk(od), "achieved_goal": mk(3), "desired_goal": mk(3)}, mk(ad),
+                                    {"observation": mk(od), "achieved_goal": mk(3), "desired_goal": mk(3)}, mk(1), mk(1))
+    full = allgather_samples(local)
+    ok = full.observations["observation"].shape == (world * B, od) and full.actions.shape == (world * B, ad)
+    sl = slice(rank * B, (rank + 1) * B)   # my own block sits at my rank's offset, bit-identical
+    ok &= torch.equal(full.observations["observation"][sl], local.observations["observation"])
+    ok &= torch.equal(full.next_observations["desired_goal"][sl], local.next_observations["desired_goal"])
+    ok &= torch.equal(full.actions[sl], local.actions) and torch.equal(full.rewards[sl], local.rewards) and torch.equal(full.dones[sl], local.dones)
+    other = 1 - rank                        # the other rank's block carries its rank offset
+    ok &= bool((full.rewards[other * B:(other + 1) * B] >= 10.0 * other).all() and (full.rewards[other * B:(other + 1) * B] < 10.0 * other + 1).all())
+    out[rank] = (bool(ok), float(full.actions.sum()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_replay_allgather():
+    world = 2
+    mgr = mp.Manager(); out = mgr.dict()
+    port = 29870 + os.getpid() % 100
+    mp.spawn(_gather_worker, args=(world, port, out), nprocs=world, join=True)
+    assert out[0][0] and out[1][0]
+    assert out[0][1] == out[1][1]           # both ranks hold the same gathered batch
