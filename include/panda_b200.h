@@ -30,6 +30,10 @@ enum pg_reward { PG_REW_SPARSE = 0, PG_REW_DENSE_OR_WANG = 1, PG_REW_KUMAR_HER =
 enum pg_obstacle_obs { PG_OOBS_NONE = 0, PG_OOBS_VECTORS_CLOSEST_PER_LINK = 1, PG_OOBS_VECTORS = 2,
                        PG_OOBS_CLOSEST_PER_LINK = 3, PG_OOBS_CLOSEST = 4, PG_OOBS_VECTORS_PAST = 5 };      /* reach_ao.py:908-932 */
 enum pg_goal_sampler { PG_GOAL_BOX = 0, PG_GOAL_SHELL = 1 };                     /* reach_ao.py:1183-1211 */
+/* ReachAO.robot_pose_randomizer of the scenario (reach_ao.py:62-63, 521-604, 669, 711); it replaces Panda.reset when
+ * TrainConfig.randomize_robot_pose is set (reach_ao.py:132-133).  Only set_random_robot_base (:1238-1241, scenario
+ * wangexp-N) is built; the others call roboticstoolbox's ik_lm_chan (panda.py:220-224), which is not restated. */
+enum pg_pose_randomizer { PG_POSE_RTB_IK = 0, PG_POSE_RANDOM_BASE = 1 };
 enum pg_obstacle_sampler { PG_OSMP_GOAL_BOX = 0, PG_OSMP_WANG = 1, PG_OSMP_EXPERIMENTAL = 2, PG_OSMP_WANG_N = 3 }; /* :610-644, 650-660 */
 
 #define PG_MAX_OBSTACLES 8
@@ -52,6 +56,7 @@ typedef struct {
   int max_episode_steps;            /* gymnasium TimeLimit (panda_gym/__init__.py:15-20) */
   double ee_error_threshold;        /* reach_ao.py:71 / reach.py:15 */
   double speed_threshold;           /* reach_ao.py:72 */
+  int pose_randomizer;              /* pg_pose_randomizer; used only with pg_config.randomize_robot_pose */
 } pg_stage;
 
 /* Environment configuration.  Replaces the constructor arguments of PandaReachAOEnv / PandaReachEnv
@@ -72,6 +77,8 @@ typedef struct {
   double safety_distance;    /* train_config.py:39 */
   double base_position[3];   /* panda_tasks.py:82 / :148 */
   int auto_reset;            /* 1: done environments are reset inside pg_step (SB3 VecEnv semantics) */
+  int randomize_robot_pose;  /* train_config.py:26: Panda.reset <- the scenario's robot_pose_randomizer, then
+                                set_coll_free_robot (reach_ao.py:991-992, 1035-1060) */
   pg_stage stage;
 } pg_config;
 

@@ -123,6 +123,7 @@ typedef struct {
   int scenario;          /* ReachAO: see PGO_SCN_* */
   int n_obstacles;       /* wang-N / wangexp-N */
   double base_pos[3];
+  int randomize_robot_pose; /* train_config.py:26; restated only for set_random_robot_base (scenario wangexp-N, reach_ao.py:711) */
 } pgo_env_config;
 
 enum { PGO_SCN_NONE = 0, PGO_SCN_REACH1, PGO_SCN_REACH2, PGO_SCN_REACH3, PGO_SCN_REACHAO1, PGO_SCN_REACHAO2,

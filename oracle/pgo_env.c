@@ -40,6 +40,7 @@ struct pgo_env {
   double goal_rmin, goal_rmax; int goal_upper, goal_front, goal_34;
   int obs_sampler;         /* 0 goal box, 1 wang (70/20/10), 2 experimental (50/50), 3 wang-N (70/30) */
   int randomize_obstacles, allow_overlap, random_num_obs, size_lo, size_hi;
+  double neutral0; /* Panda.neutral_joint_values[0], mutated by set_random_robot_base */
   double table_pos[3], table_half[3];
   /* Push / PickAndPlace (tasks 2, 3): the free object and its world */
   pgo_body obj;
@@ -407,10 +408,34 @@ static int is_success(pgo_env* e, const float* ag, const float* dg) {
   return d < thr;
 }
 
+/* set_random_robot_base (reach_ao.py:1238-1241): neutral_joint_values[0] <- U(joint_lim_min[0], joint_lim_max[0])
+ * (panda.py:77-79), then set_joint_neutral.  It stands in for Panda.reset when randomize_robot_pose is set (:132-133). */
+static void random_robot_base(pgo_env* e) {
+  e->neutral0 = pgo_pcg64_uniform(&e->rng, -2.7437, 2.7437);
+  for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, d == 0 ? e->neutral0 : NEUTRAL[d]);
+}
+/* set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the robot pose while the robot is within 0.05 */
+static int set_coll_free_robot(pgo_env* e) {
+  int status = 0;
+  for (int j = 0; j < e->nobs; j++) {
+    int i = 0;
+    while (0.05 >= robot_body_distance(e, &e->obs[j])) {
+      if (i > 9999) { /* set_joint_neutral with the mutated neutral_joint_values[0] = the pose it already has */
+        status = 4; break;
+      }
+      i++;
+      random_robot_base(e);
+    }
+  }
+  return status;
+}
+
 int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, int* success) {
   int status = 0;
+  const int rbase = e->cfg.task == 1 && e->cfg.randomize_robot_pose && e->cfg.scenario == PGO_SCN_WANGEXP;
   pgo_pcg64_seed(&e->rng, seed);                       /* core.py:302 */
-  for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, NEUTRAL[d]); /* panda.py:290-298 */
+  if (rbase) random_robot_base(e);                     /* robot.reset = robot_pose_randomizer (reach_ao.py:132-133) */
+  else for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, NEUTRAL[d]); /* panda.py:290-298 */
   e->steps = 0;
   if (e->cfg.task == 0) {
     for (int k = 0; k < 3; k++) e->goal[k] = pgo_pcg64_uniform(&e->rng, e->goal_lo[k], e->goal_hi[k]); /* reach.py:75-78 */
@@ -433,6 +458,7 @@ int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, i
     status |= set_coll_free_goal(e, 0, 0.1);           /* fixed_target None */
     if (e->randomize_obstacles) status |= set_coll_free_obs(e, 0.03);
     else status |= set_coll_free_goal(e, 1, 0.03);
+    if (rbase) status |= set_coll_free_robot(e);       /* reach_ao.py:991-992 */
     e->dummy[0] = 0; e->dummy[1] = 0; e->dummy[2] = -5.0;
     if (e->random_num_obs) {                           /* reach_ao.py:1062-1082 */
       u32buf b = {0, 0};

@@ -24,6 +24,7 @@ class Stage(ctypes.Structure):
         ("obstacle_sampler", c_int), ("randomize_obstacle_position", c_int), ("allow_overlapping_obstacles", c_int),
         ("random_num_obs", c_int), ("sample_size_lo", c_int), ("sample_size_hi", c_int),
         ("max_episode_steps", c_int), ("ee_error_threshold", c_double), ("speed_threshold", c_double),
+        ("pose_randomizer", c_int),
     ]
 
 
@@ -34,7 +35,7 @@ class Config(ctypes.Structure):
         ("action_limiter", c_int), ("obs_js", c_int), ("obstacle_obs", c_int), ("n_substeps", c_int),
         ("truncate_on_collision", c_int), ("terminate_on_success", c_int),
         ("collision_reward", c_double), ("safety_distance", c_double), ("base_position", c_double * 3),
-        ("auto_reset", c_int), ("stage", Stage),
+        ("auto_reset", c_int), ("randomize_robot_pose", c_int), ("stage", Stage),
     ]
 
 

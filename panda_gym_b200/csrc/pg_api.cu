@@ -76,6 +76,7 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   d.obs_sampler = s->obstacle_sampler; d.randomize_obstacles = s->randomize_obstacle_position;
   d.allow_overlap = s->allow_overlapping_obstacles; d.random_num_obs = s->random_num_obs;
   d.size_lo = s->sample_size_lo; d.size_hi = s->sample_size_hi;
+  d.random_base = (h->cfg.randomize_robot_pose && s->pose_randomizer == PG_POSE_RANDOM_BASE) ? 1 : 0;
   d.max_episode_steps = s->max_episode_steps;
   d.ee_thr = (float)s->ee_error_threshold; d.speed_thr = (float)s->speed_threshold;
   // observation width (reach_ao.py:902-932: np.ones(27) when the scenario has no obstacles)
@@ -87,6 +88,17 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   if (P.task >= 2) t = 12;  // push.py:49-63
   P.task_obs_dim = t;
   P.obs_dim = 6 + (P.obs_js ? 14 : 0) + (P.task == PG_TASK_PICK_AND_PLACE ? 1 : 0) + t;  // + fingers width (panda.py:282-284)
+}
+
+// randomize_robot_pose (train_config.py:26): which scenario randomizers exist on the device
+int check_pose_randomizer(const pg_config* cfg, const pg_stage* s) {
+  if (!cfg->randomize_robot_pose || cfg->task != PG_TASK_REACH_AO) return PG_OK;
+  if (s->pose_randomizer != PG_POSE_RANDOM_BASE)
+    return fail(PG_ERR_UNSUPPORTED, "randomize_robot_pose: this scenario's robot_pose_randomizer calls roboticstoolbox ik_lm_chan "
+                                    "(panda.py:220-224), which is not built; only set_random_robot_base (wangexp-N) is");
+  for (int j = 0; j < s->n_obstacles; j++)
+    if (s->obstacle_type[j] != 0) return fail(PG_ERR_UNSUPPORTED, "randomize_robot_pose with cuboid obstacles is not built");
+  return PG_OK;
 }
 
 void set_goal_box(pg_stage* s, double xl, double xh, double yl, double yh, double zl, double zh) {
@@ -146,6 +158,7 @@ int pg_stage_from_scenario(pg_stage* s, const char* scenario) {
     if (count < 0 || count > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "wangexp-N: N out of range");
     set_goal_shell(s, 0.5, 0.8, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG;
     for (int i = 0; i < count; i++) add_sphere(s, 0.05);
+    s->pose_randomizer = PG_POSE_RANDOM_BASE;  // :711
   } else {
     return fail(PG_ERR_ARG, std::string("Scenario ") + scenario + " not found!");  // reach_ao.py:262-264
   }
@@ -175,6 +188,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   if (!cfg || !out) return fail(PG_ERR_ARG, "NULL argument");
   if (cfg->n_envs <= 0) return fail(PG_ERR_ARG, "n_envs must be positive");
   if (cfg->stage.n_obstacles < 0 || cfg->stage.n_obstacles > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "n_obstacles out of range");
+  if (int rc = check_pose_randomizer(cfg, &cfg->stage)) return rc;
   int ndev = 0;
   cudaError_t ce = cudaGetDeviceCount(&ndev);
   if (ce != cudaSuccess || ndev == 0) return fail(PG_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
@@ -252,6 +266,7 @@ int pg_destroy(pg_handle h) {
 int pg_set_stage(pg_handle h, const pg_stage* s) {
   if (!h || !s) return fail(PG_ERR_ARG, "NULL argument");
   if (s->n_obstacles < 0 || s->n_obstacles > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "n_obstacles out of range");
+  if (int rc = check_pose_randomizer(&h->cfg, s)) return rc;
   h->cfg.stage = *s;
   fill_stage(h, s);
   return PG_OK;

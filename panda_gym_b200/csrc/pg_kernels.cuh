@@ -38,6 +38,7 @@ struct StageDev {  // device copy of pg_stage (scenario parameter block)
   int nobs, obs_type[kMaxObst];
   double obs_size[kMaxObst][3];
   int obs_sampler, randomize_obstacles, allow_overlap, random_num_obs, size_lo, size_hi;
+  int random_base;   // randomize_robot_pose with set_random_robot_base (reach_ao.py:1238-1241)
   int max_episode_steps;
   float ee_thr, speed_thr;
 };
@@ -633,11 +634,15 @@ __device__ inline double box_margin_d(double sx, double sy, double sz) { double 
 // min distance robot (all 36 primitives at the neutral pose, base offset) vs body: body-level getClosestPoints
 // cutoff: pairs whose analytic lower bound exceeds it are skipped (the caller only compares the result to it)
 // WARP: the 32 lanes of a warp work on the same environment and split the primitives (then min-reduce)
+// (c0, s0) = cos / sin of joint 1 relative to the neutral pose (set_random_robot_base): joint 1 turns about the base's
+// vertical axis and the base link's primitives are symmetric about it, so the turned robot against a SPHERE body equals
+// the neutral robot against the body turned back by the same angle
 template <bool WARP>
-__device__ __noinline__ double robot_body_distance(const Params& P, const Body& b, double cutoff) {
+__device__ __noinline__ double robot_body_distance(const Params& P, const Body& b, double cutoff, double c0 = 1.0, double s0 = 0.0) {
   double best = 1e300;
   const int k0 = WARP ? (threadIdx.x & 31) : 0, kstep = WARP ? 32 : 1;
-  D3 o = v3t<double>(b.px - P.based[0], b.py - P.based[1], b.pz - P.based[2]);
+  const double ox = b.px - P.based[0], oy = b.py - P.based[1];
+  D3 o = v3t<double>(c0 * ox + s0 * oy, -s0 * ox + c0 * oy, b.pz - P.based[2]);
   double m = b.type == 1 ? box_margin_d(b.sx, b.sy, b.sz) : 0.0;
   D3 core = v3t<double>(b.sx - m, b.sy - m, b.sz - m);
   for (int k = k0; k < pgm::kNumNeutralPrim; k += kstep) {
@@ -693,16 +698,15 @@ __device__ inline void sample_goal(const StageDev& st, Pcg& g, double* out) {
   if (st.goal_sampler == 0) for (int k = 0; k < 3; k++) out[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]);
   else sample_hollow(g, st.goal_rmin, st.goal_rmax, st.goal_upper, st.goal_front, st.goal_34, out);
 }
-__device__ inline void sample_obstacle(const Params& P, Pcg& g, const double* goal, double* out) {
+__device__ inline void sample_obstacle(const Params& P, Pcg& g, const double* goal, const double* ee, double* out) {
   const StageDev& st = P.st;
   double s[3], c[3];
-  double ee[3] = {pgm::kNeutralEE[0] + P.based[0], pgm::kNeutralEE[1] + P.based[1], pgm::kNeutralEE[2] + P.based[2]};
   if (st.obs_sampler == 0) { for (int k = 0; k < 3; k++) out[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]); return; }
   double r = pcg_double(g);
   if (st.obs_sampler == 1) {
     if (r > 0.3) { sample_hollow(g, 0.1, 0.5, 0, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = goal[k]; }
     else if (r > 0.1) { sample_hollow(g, 0.1, 0.4, 0, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = ee[k]; }
-    else { sample_hollow(g, 0.3, 0.6, 1, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = pgm::kNeutralLink0[k] + P.based[k]; }
+    else { sample_hollow(g, 0.3, 0.6, 1, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = ee[3 + k]; }  // get_link_position(0) = COM of panda_link1
   } else if (st.obs_sampler == 2) {
     sample_hollow(g, 0.1, 0.5, 0, 0, 0, s);
     for (int k = 0; k < 3; k++) c[k] = r > 0.5 ? goal[k] : ee[k];
@@ -744,13 +748,26 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
   P.episode[e] = ep + 1;
   uint64_t seed = seeds ? seeds[e] : episode_seed(P.base_seed, first_env + (uint64_t)e, ep);
   Pcg g; pcg_seed(g, seed);
-  float q[7], qd[7], cq[7], sq[7];
-#pragma unroll
-  for (int d = 0; d < 7; d++) { q[d] = (float)pgm::kNeutralQ[d]; qd[d] = 0.f; P.q[(size_t)d * n + e] = q[d]; P.qd[(size_t)d * n + e] = 0.f; sincosf(q[d], &sq[d], &cq[d]); }
-  P.steps[e] = 0; P.ep_ret[e] = 0.f; P.ep_len[e] = 0;
-  double goal[3];
-  int status = 0;
   const StageDev& st = P.st;
+  // Panda.reset (panda.py:290-298) -- or, with randomize_robot_pose, the scenario's randomizer in its place
+  // (reach_ao.py:132-133): set_random_robot_base draws joint 1 from its limits (panda.py:77-79) and keeps the rest neutral
+  const bool rbase = P.task == 1 && st.random_base;
+  double q0 = pgm::kNeutralQ[0], c0 = 1.0, s0 = 0.0;
+  if (rbase) { q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - pgm::kNeutralQ[0]); s0 = sin(q0 - pgm::kNeutralQ[0]); }
+  float q[7], qd[7], cq[7], sq[7];
+  P.steps[e] = 0; P.ep_ret[e] = 0.f; P.ep_len[e] = 0;
+  double goal[3], ee[6];  // ee[0..2] = get_ee_position(), ee[3..5] = get_link_position(0), both at the reset pose
+  int status = 0;
+#define PG_EE_AT_POSE()                                                                                   \
+  do {                                                                                                    \
+    ee[0] = c0 * pgm::kNeutralEE[0] - s0 * pgm::kNeutralEE[1] + P.based[0];                               \
+    ee[1] = s0 * pgm::kNeutralEE[0] + c0 * pgm::kNeutralEE[1] + P.based[1];                               \
+    ee[2] = pgm::kNeutralEE[2] + P.based[2];                                                              \
+    ee[3] = c0 * pgm::kNeutralLink0[0] - s0 * pgm::kNeutralLink0[1] + P.based[0];                         \
+    ee[4] = s0 * pgm::kNeutralLink0[0] + c0 * pgm::kNeutralLink0[1] + P.based[1];                         \
+    ee[5] = pgm::kNeutralLink0[2] + P.based[2];                                                           \
+  } while (0)
+  PG_EE_AT_POSE();
   if (P.task == 0) {
     for (int k = 0; k < 3; k++) goal[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]);
   } else if (P.task >= 2) {
@@ -778,13 +795,13 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
       int i = 0;
       for (;;) {
         sample_goal(st, g, goal);
-        if (i > 9999) { for (int k = 0; k < 3; k++) goal[k] = pgm::kNeutralEE[k] + P.based[k]; status = 1; break; }
+        if (i > 9999) { for (int k = 0; k < 3; k++) goal[k] = ee[k]; status = 1; break; }
         i++;
         probe.px = goal[0]; probe.py = goal[1]; probe.pz = goal[2];
         bool coll = false;
         if (pass == 1) for (int j = 0; j < st.nobs; j++) coll |= body_body_collision(probe, obstacle_body(P, j, e), margin);
         coll |= body_body_collision(probe, table, margin);
-        if (!coll) coll |= (margin >= robot_body_distance<WARP>(P, probe, margin));
+        if (!coll) coll |= (margin >= robot_body_distance<WARP>(P, probe, margin, c0, s0));
         if (!coll) break;
       }
     }
@@ -796,7 +813,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
           if (i > 9999) { status = 2; break; }
           i++;
           double pos[3];
-          sample_obstacle(P, g, goal, pos);
+          sample_obstacle(P, g, goal, ee, pos);
           for (int k = 0; k < 3; k++) P.obs_pos[(size_t)(j * 3 + k) * n + e] = pos[k];
           Body ob = obstacle_body(P, j, e);
           bool coll = body_body_collision(table, ob, margin);
@@ -806,8 +823,19 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
             probe.px = probe.py = probe.pz = 0.0;  // the probe sphere is moved to the origin and left there
             coll |= !body_body_collision(probe, ob, 1.0);
           }
-          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance<WARP>(P, ob, margin + P.safety_distance));
+          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance<WARP>(P, ob, margin + P.safety_distance, c0, s0));
           if (!coll) break;
+        }
+      }
+    }
+    if (rbase) {  // set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the pose while the robot is within 0.05
+      for (int j = 0; j < st.nobs; j++) {
+        Body ob = obstacle_body(P, j, e);
+        int i = 0;
+        while (0.05 >= robot_body_distance<WARP>(P, ob, 0.05, c0, s0)) {
+          if (i > 9999) { status |= 4; break; }  // set_joint_neutral: neutral_joint_values[0] already holds the last draw
+          i++;
+          q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - pgm::kNeutralQ[0]); s0 = sin(q0 - pgm::kNeutralQ[0]);
         }
       }
     }
@@ -824,6 +852,13 @@ __global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t*
     }
     P.have_recent[e] = 0; P.have_prev[e] = 0;
     for (int k = 0; k < st.nobs * 3; k++) P.obs_pos_f[(size_t)k * n + e] = (float)P.obs_pos[(size_t)k * n + e];
+  }
+#undef PG_EE_AT_POSE
+#pragma unroll
+  for (int d = 0; d < 7; d++) {
+    q[d] = (float)(d == 0 ? q0 : pgm::kNeutralQ[d]); qd[d] = 0.f;
+    P.q[(size_t)d * n + e] = q[d]; P.qd[(size_t)d * n + e] = 0.f;
+    sincosf(q[d], &sq[d], &cq[d]);
   }
   for (int k = 0; k < 3; k++) P.goal[(size_t)k * n + e] = goal[k];
   P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;

@@ -22,7 +22,7 @@ class EnvConfig(ctypes.Structure):
         ("truncate_on_collision", c_int), ("terminate_on_success", c_int),
         ("collision_reward", c_double), ("ee_error_threshold", c_double), ("speed_threshold", c_double),
         ("safety_distance", c_double), ("max_episode_steps", c_int), ("scenario", c_int), ("n_obstacles", c_int),
-        ("base_pos", c_double * 3),
+        ("base_pos", c_double * 3), ("randomize_robot_pose", c_int),
     ]
 
 

@@ -513,7 +513,7 @@ def test_manipulability_matches_oracle(sim, oracle):
     rng = np.random.default_rng(15)
     n = 513
     Q = rng.uniform(Q_LO, Q_HI, (n, 7)).astype(np.float32)
-    Q[0] = [0.0, 0.41, 0.0, -1.85, 0.0, 2.26, 0.79]  # Panda.neutral_joint_values (panda.py:56)
+    Q[0] = [0.0, 0.41, 0.0, -1.85, 0.0, 2.26, 0.79]  # upstream panda-gym neutral pose (a well-conditioned configuration)
     cfg = sim.make_config(1, n, scenario="reachao3", max_episode_steps=100, auto_reset=False)
     b = sim.PandaBatch(cfg, device=0)
     b.seed(3)
@@ -530,3 +530,61 @@ def test_manipulability_matches_oracle(sim, oracle):
     assert (err < 2e-6 + 1e-4 * want).all(), (err.max(), want[err.argmax()])
     assert np.array_equal(got_state, got_free)
     assert abs(got_free[0] - 0.160705) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------ N2: randomised start pose
+def test_random_robot_base_reset_matches_oracle(sim, oracle):
+    """randomize_robot_pose with set_random_robot_base (wangexp-N; reach_ao.py:1238-1241, :1035-1060): joint 1, goal and
+    obstacle layout of seeded resets equal the oracle's (same numpy PCG64 stream), then a rollout stays in tolerance."""
+    from panda_gym_b200.config import TrainConfig
+    n = 96
+    tc = TrainConfig()
+    tc.randomize_robot_pose = True
+    cfg = sim.make_config(1, n, scenario="wangexp-3", config=tc, max_episode_steps=100, auto_reset=False)
+    b = sim.PandaBatch(cfg)
+    b.seed(900)
+    b.reset()
+    torch.cuda.synchronize()
+    goal = b.view("goal").cpu().numpy()
+    opos = b.view("obstacle_pos").cpu().numpy()
+    obs = b.view("observation").cpu().numpy()
+    q = b.view("q").cpu().numpy()
+    envs, redrawn = [], 0
+    for i in range(n):
+        e = oracle.Env(task=1, scenario="wangexp-3", randomize_robot_pose=1, max_episode_steps=100)
+        o, info = e.reset(900 + i)
+        envs.append(e)
+        qo = e.arm.q()[0]
+        redrawn += int(qo[0] != np.random.default_rng(900 + i).uniform(-2.7437, 2.7437))
+        assert np.float32(qo[0]) == q[0, i], "joint 1 differs from the numpy-PCG64 stream"
+        assert np.allclose(q[1:, i], qo[1:7].astype(np.float32))
+        assert np.allclose(e.goal(), goal[:, i], rtol=0, atol=1e-13)
+        for j, (_, p, _) in enumerate(e.obstacles()):
+            assert np.allclose(p, opos[j, :, i], atol=1e-12)
+        assert np.abs(o["observation"][:29] - obs[i, :29]).max() < 2e-5
+        assert np.abs(o["observation"][29:] - obs[i, 29:]).max() < 5e-4
+    assert redrawn > 0, "no seed exercised set_coll_free_robot's re-draw; widen the seed range"
+    rng = np.random.default_rng(5)
+    for _ in range(5):
+        A = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
+        b.step(torch.from_numpy(A).cuda())
+        og = b.view("observation").cpu().numpy()
+        fg = b.view("flags").cpu().numpy()
+        for i, e in enumerate(envs):
+            if e is None:
+                continue
+            o, r, f = e.step(A[i])
+            assert (fg[i] & 15) == flags_of(f)
+            assert np.abs(o["observation"][:20] - og[i, :20]).max() < 1e-3
+            if f["terminated"] or f["truncated"]:
+                envs[i] = None
+    b.close()
+
+
+def test_randomize_robot_pose_needs_a_built_randomizer(sim):
+    from panda_gym_b200.config import TrainConfig
+    from panda_gym_b200._lib import PandaB200Error
+    tc = TrainConfig()
+    tc.randomize_robot_pose = True
+    with pytest.raises(PandaB200Error, match="ik_lm_chan"):
+        sim.PandaBatch(sim.make_config(1, 4, scenario="reachao3", config=tc))

@@ -69,6 +69,8 @@ def test_make_config_maps_trainconfig(lib):
     assert cfg.collision_reward == -50 and cfg.stage.max_episode_steps == 75 and cfg.stage.speed_threshold == 0.01
     with pytest.raises(lib.PandaB200Error):
         sim.make_config(1, 1, scenario="reachao1", config=TrainConfig(randomize_robot_pose=True))
+    cfg = sim.make_config(1, 1, scenario="wangexp-3", config=TrainConfig(randomize_robot_pose=True))  # set_random_robot_base
+    assert cfg.randomize_robot_pose == 1 and cfg.stage.pose_randomizer == 1 and cfg.stage.n_obstacles == 3
     with pytest.raises(lib.PandaB200Error):
         sim.make_config(1, 1, scenario="no_such_scenario")
 

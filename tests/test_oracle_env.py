@@ -95,3 +95,30 @@ def test_ee_control_uses_ik(oracle):
     for _ in range(10):
         o, r, f = e.step(np.array([0, 0, 1.0], np.float32))
     assert o["achieved_goal"][2] > z0 + 0.1
+
+
+def test_random_robot_base_reset(oracle):
+    """N2 (reach_ao.py:1238-1241, :1035-1060): with randomize_robot_pose the wangexp scenario draws joint 1 first from
+    the env's numpy stream, keeps the other joints neutral and ends collision-free with 0.05 margin to every obstacle."""
+    import numpy as np
+    e = oracle.Env(task=1, scenario="wangexp-3", randomize_robot_pose=1, max_episode_steps=100)
+    moved = 0
+    for seed in range(40):
+        o, info = e.reset(seed)
+        q = e.arm.q()[0]
+        first = np.random.default_rng(seed).uniform(-2.7437, 2.7437)
+        assert np.allclose(q[1:7], [-0.3, 0.0, -2.2, 0.0, 2.0, np.pi / 4])
+        assert -2.7437 <= q[0] <= 2.7437
+        moved += int(q[0] != first)         # set_coll_free_robot re-drew the pose
+        if q[0] == first:
+            assert info["status"] == 0
+        for _, p, size in e.obstacles():    # no obstacle within 0.05 of the robot
+            for link in range(0, 12):
+                d, _, _ = e.arm.link_obstacle_distance(link, oracle.make_obstacle(0, p, size))
+                assert d > 0.05 - 1e-12
+        # the observation reports the turned pose: q0 sits right after ee position / velocity (panda.py:264-288)
+        assert abs(o["observation"][6] - np.float32(q[0])) < 1e-6
+    assert moved < 40  # most seeds keep their first draw
+    plain = oracle.Env(task=1, scenario="wangexp-3", max_episode_steps=100)
+    plain.reset(3)
+    assert plain.arm.q()[0][0] == 0.0      # flag off: Panda.reset to the neutral pose

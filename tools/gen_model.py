@@ -370,7 +370,7 @@ def emit_neutral(links, root, order, path):
         ",\n".join(rows),
         "};",
         "static __device__ __constant__ double kNeutralEE[3] = {%r, %r, %r};     // COM of link 11 (get_ee_position)" % tuple(ee),
-        "static __device__ __constant__ double kNeutralLink0[3] = {%r, %r, %r};  // COM of link 0 (get_link_position(0))" % tuple(l0),
+        "static __device__ __constant__ double kNeutralLink0[3] = {%r, %r, %r};  // COM of pybullet link 0 = panda_link1 (get_link_position(0)); turns with joint 1" % tuple(l0),
         "static __device__ __constant__ double kNeutralQ[7] = {%s};" % ", ".join(repr(x) for x in neutral),
         "}  // namespace pgm",
     ]
