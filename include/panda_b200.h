@@ -159,6 +159,21 @@ int pg_num_envs(pg_handle h);
 /* number of kernels this library launched on behalf of the handle so far */
 int64_t pg_launch_count(pg_handle h);
 
+/* Evaluation metrics of evaluation/evaluate.py:perform_benchmark (:131-300) accumulated on the device for every
+ * environment (the caller immediately above the step path).  pg_set_eval_metrics(h, 1) zeroes the
+ * accumulators and makes every pg_step launch one extra small kernel after the step kernel (before the auto-reset);
+ * enable = 0 stops it.  pg_get_eval_metrics copies 12 doubles to the host:
+ *   [0] successful episodes            [1] sum of their lengths
+ *   [2] sum over them of (sum of ||joint acceleration|| per step / length)      -> mean_effort          (:269, :291)
+ *   [3] sum over them of (sum of manipulability per step / length)              -> mean_manipulability  (:270, :292)
+ *   [4] sum of ||joint jerk|| over all their steps                              -> mean_norm_jerk       (:268, :293)
+ *   [5] sum of ||ee velocity|| over all their steps                             -> mean_ee_speed        (:271, :294)
+ *   [6] finished episodes   [7] sum of their lengths   [8] collisions (is_truncated and not is_success)
+ *   [9] sum of episode rewards   [10] timeouts   [11] reserved
+ * Episode classification follows :264-279: is_success first, then is_truncated, else timeout. */
+int pg_set_eval_metrics(pg_handle h, int enable, void* stream);
+int pg_get_eval_metrics(pg_handle h, double* out12_host, void* stream);
+
 /* Panda.get_manipulability (panda.py:314-317; called by ReachAO.compute_reward, reach_ao.py:1311): Yoshikawa index
  * sqrt(det(Jv Jv^T)) of the translational Jacobian at roboticstoolbox's Panda end-effector link (panda_link8).
  * q_dev NULL: the handle's current joint angles, out_dev f32 [num_envs]; else q_dev f32 [7][n] -> out_dev f32 [n]. */

@@ -148,6 +148,8 @@ void pgo_env_set_obstacles(pgo_env*, int n, const pgo_obstacle*);
 int pgo_env_get_obstacles(const pgo_env*, pgo_obstacle*);
 /* ReachAO.check_collided (reach_ao.py:896-900): fills d_link[9]; returns collided flag */
 int pgo_env_check_collided(pgo_env*, double* d_link, double* d_table_min);
+/* per-step readings of evaluation/evaluate.py:perform_benchmark (:252-259): effort, jerk norm, manipulability, ee speed */
+void pgo_env_step_metrics(pgo_env*, double out[4]);
 /* observation pieces at the current state */
 void pgo_env_get_obs(pgo_env*, float* obs, float* achieved, float* desired);
 /* compute_reward(achieved, desired) vectorised over n rows, the HER relabel entry (core.py:282) */

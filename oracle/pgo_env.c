@@ -521,6 +521,16 @@ static void set_action(pgo_env* e, const float* action) {
 
 static double norm7(const double* v) { double s = 0; for (int d = 0; d < 7; d++) s += v[d] * v[d]; return sqrt(s); }
 
+/* what evaluation/evaluate.py:perform_benchmark reads after every env.step (:252-259): task.get_norm_effort()
+ * (reach_ao.py:1299-1302), task.get_norm_jerk() (:1304-1305), task.manipulability (:1311, :1381 -> panda.py:314-317 at the
+ * current joint angles) and ||robot.get_ee_velocity()|| */
+void pgo_env_step_metrics(pgo_env* e, double out[4]) {
+  double v[3]; pgo_arm_link_state(e->arm, EE_LINK, 0, 0, v, 0);
+  out[0] = norm7(e->cur_acc); out[1] = norm7(e->jerk);
+  out[2] = pgo_arm_manipulability(e->arm);
+  out[3] = sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+}
+
 static float reward_one(pgo_env* e, const float* ag, const float* dg) {
   const pgo_env_config* c = &e->cfg;
   float d = f32_distance(ag, dg);

@@ -38,6 +38,7 @@ struct pg_env_s {
   uint64_t first_env;
   int64_t launches;
   float* d_actions;                 // staging for the host-buffer step
+  int eval_metrics;                 // pg_set_eval_metrics: launch k_eval_metrics after every step
   int grid() const { return (P.n + pg::kBlock - 1) / pg::kBlock; }
 };
 
@@ -195,7 +196,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   if (device < 0 || device >= ndev) return fail(PG_ERR_ARG, "bad device index");
   PG_CUDA(cudaSetDevice(device));
   pg_env_s* h = new pg_env_s();
-  h->cfg = *cfg; h->device = device; h->launches = 0; h->first_env = 0; h->d_actions = nullptr;
+  h->cfg = *cfg; h->device = device; h->launches = 0; h->first_env = 0; h->d_actions = nullptr; h->eval_metrics = 0;
   pg::Params& P = h->P;
   memset(&P, 0, sizeof P);
   const int n = cfg->n_envs;
@@ -238,6 +239,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   A(P.obs, (size_t)max_obs * n, true) A(P.achieved, 3 * n, true) A(P.desired, 3 * n, true) A(P.reward, n, true)
   A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true) A(P.done, n, true) A(P.flags, n, true)
   A(P.stats, 8, false) A(P.reset_list, n, false) A(P.reset_count, 1, false)
+  A(P.ev_acc, 4 * n, true) A(P.ev_len, n, true) A(P.ev_ret, n, true) A(P.ev, 12, false)
   A(h->d_actions, 8 * n, false)
 #undef A
   // obstacles start where create_obstacle_* puts them: (0.1, 0, 0.1) (reach_ao.py:819, 841)
@@ -342,6 +344,10 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   else
   pg::k_step<<<(h->P.n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
   h->launches++;
+  if (h->eval_metrics) {  // perform_benchmark's bookkeeping, on the post-step state and before the auto-reset
+    pg::k_eval_metrics<<<(h->P.n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(h->P);
+    h->launches++;
+  }
   if (h->P.auto_reset) {
     pg::k_reset<true><<<148 * 8, pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, nullptr, nullptr, h->first_env);  // 4736 warps, grid-stride over the list
     h->launches++;
@@ -508,6 +514,26 @@ int pg_observe(pg_handle h, void* stream) {
   pg::k_observe<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P);
   h->launches++;
   PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_set_eval_metrics(pg_handle h, int enable, void* stream) {
+  if (!h) return fail(PG_ERR_ARG, "NULL handle");
+  PG_CUDA(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t n = h->P.n;
+  PG_CUDA(cudaMemsetAsync(h->P.ev, 0, 12 * sizeof(double), s));
+  PG_CUDA(cudaMemsetAsync(h->P.ev_acc, 0, 4 * n * sizeof(float), s));
+  PG_CUDA(cudaMemsetAsync(h->P.ev_len, 0, n * sizeof(int), s));
+  PG_CUDA(cudaMemsetAsync(h->P.ev_ret, 0, n * sizeof(float), s));
+  h->eval_metrics = enable ? 1 : 0;
+  return PG_OK;
+}
+int pg_get_eval_metrics(pg_handle h, double* out12_host, void* stream) {
+  if (!h || !out12_host) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  PG_CUDA(cudaMemcpyAsync(out12_host, h->P.ev, 12 * sizeof(double), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  PG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
   return PG_OK;
 }
 

@@ -76,6 +76,11 @@ struct Params {
   uint8_t *done, *flags;
   double* stats;                 // [8]
   int *reset_list, *reset_count;   // compacted indices of environments that finished in the last step
+  // evaluation metrics of perform_benchmark (evaluation/evaluate.py:131-300), filled by k_eval_metrics when enabled
+  float* ev_acc;                 // [4][n] running sums of the current episode: effort, manipulability, jerk norm, ee speed
+  int* ev_len;                   // [n] steps of the current episode
+  float* ev_ret;                 // [n] return of the current episode
+  double* ev;                    // [12] see pg_get_eval_metrics
 };
 
 // panda.py:63 joint_forces
@@ -970,6 +975,65 @@ __global__ void k_debug_minv(int n, const float* q_in, float* out) {
 #pragma unroll
   for (int k = 0; k < 28; k++) out[(size_t)k * n + e] = M[k];
 }
+// Yoshikawa index at the flange for joint cosines / sines (see k_manipulability)
+__device__ __forceinline__ float manipulability_cs(const float* c, const float* s) {
+  ArmKin K;
+  arm_kin(v3(0.f, 0.f, 0.f), c, s, K);
+  const V3 p = frame_point(K.F7, 0.f, 0.f, 0.107f);
+  V3 J[7];
+#pragma unroll
+  for (int d = 0; d < 7; d++) J[d] = cross(K.ax[d], p - K.org[d]);
+  float det = 0.f;
+#pragma unroll
+  for (int i = 0; i < 5; i++)
+#pragma unroll
+    for (int j = i + 1; j < 6; j++) {
+      V3 cij = cross(J[i], J[j]);
+#pragma unroll
+      for (int k = j + 1; k < 7; k++) { float m = dot(cij, J[k]); det = fmaf(m, m, det); }
+    }
+  return det > 0.f ? sqrtf(det) : 0.f;
+}
+
+// The per-step bookkeeping of evaluation/evaluate.py:perform_benchmark (:236-262) and its episode-end accounting
+// (:264-283), for every environment, on the state k_step left behind and BEFORE the auto-reset overwrites it:
+//   per step     total_effort += ||current_joint_acceleration||   (reach_ao.py:1299-1302)
+//                jerk.append(||current_joint_jerk||)              (:1304-1305)
+//                total_manipulability += task.manipulability      (:1311, :1381 -> panda.py:314-317 at the new q)
+//                ee_speed.append(||get_ee_velocity()||)           (observation[3:6])
+//   episode end  is_success -> success bucket (length, effort / length, manipulability / length, all jerk and speed
+//                samples); else is_truncated -> collision; else timeout; reward and length always
+__global__ void __launch_bounds__(128) k_eval_metrics(const Params P) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x, n = P.n;
+  if (e >= n) return;
+  float c[7], s[7], a2 = 0.f, j2 = 0.f;
+#pragma unroll
+  for (int d = 0; d < 7; d++) {
+    sincosf(P.q[(size_t)d * n + e], &s[d], &c[d]);
+    float a = P.cur_acc[(size_t)d * n + e], j = P.jerk[(size_t)d * n + e];
+    a2 = fmaf(a, a, a2); j2 = fmaf(j, j, j2);
+  }
+  const float* o = P.obs + (size_t)e * P.obs_dim;
+  const float speed = sqrtf(o[3] * o[3] + o[4] * o[4] + o[5] * o[5]);
+  float effort = P.ev_acc[e] + sqrtf(a2), manip = P.ev_acc[(size_t)n + e] + manipulability_cs(c, s);
+  float jerk = P.ev_acc[(size_t)2 * n + e] + sqrtf(j2), sp = P.ev_acc[(size_t)3 * n + e] + speed;
+  int len = P.ev_len[e] + 1;
+  float ret = P.ev_ret[e] + P.reward[e];
+  if (P.done[e]) {
+    const uint8_t f = P.flags[e];
+    atomicAdd(&P.ev[6], 1.0); atomicAdd(&P.ev[7], (double)len); atomicAdd(&P.ev[9], (double)ret);
+    if (f & 1) {
+      atomicAdd(&P.ev[0], 1.0); atomicAdd(&P.ev[1], (double)len);
+      atomicAdd(&P.ev[2], (double)effort / len); atomicAdd(&P.ev[3], (double)manip / len);
+      atomicAdd(&P.ev[4], (double)jerk); atomicAdd(&P.ev[5], (double)sp);
+    } else if (f & 4) atomicAdd(&P.ev[8], 1.0);
+    else atomicAdd(&P.ev[10], 1.0);
+    effort = manip = jerk = sp = ret = 0.f; len = 0;
+  }
+  P.ev_acc[e] = effort; P.ev_acc[(size_t)n + e] = manip; P.ev_acc[(size_t)2 * n + e] = jerk; P.ev_acc[(size_t)3 * n + e] = sp;
+  P.ev_len[e] = len; P.ev_ret[e] = ret;
+}
+
 // Panda.get_manipulability (panda.py:314-317): roboticstoolbox Panda().manipulability(q, axes="trans") = Yoshikawa index
 // sqrt(det(Jv Jv^T)) of the 3 x 7 translational Jacobian at the toolbox model's end-effector link panda_link8 (flange =
 // link7 frame + (0, 0, 0.107)).  compute_reward refreshes it every step (reach_ao.py:1311, :1381); it feeds no reward.

@@ -57,3 +57,22 @@ def allgather_samples(samples, group=None):
     obs = {k: parts[i] for i, k in enumerate(keys)}
     nobs = {k: parts[4 + i] for i, k in enumerate(keys)}
     return DictReplayBufferSamples(obs, parts[3], nobs, parts[7], parts[8])
+
+
+def benchmark_results(raw, n_substeps=20, group=None):
+    """The ``results`` dict of evaluation/evaluate.py:perform_benchmark (:286-300) from the 12 accumulators of
+    ``pg_get_eval_metrics`` (summed over ranks first when a process group is up).  Same keys, same rounding."""
+    import numpy as np
+    v = torch.as_tensor(np.asarray(raw, dtype=np.float64)).clone()
+    if dist.is_available() and dist.is_initialized():
+        if dist.get_backend(group) == "nccl":
+            v = v.cuda()
+        dist.all_reduce(v, op=dist.ReduceOp.SUM, group=group)
+    ns, ls, eff, man, jerk, spd, ne, le, ncol, ret, nto = [float(x) for x in v.cpu().tolist()[:11]]
+    div = lambda a, b: float("nan") if b == 0 else a / b   # np.mean of an empty list is nan in the reference too
+    r4 = lambda x: float(np.round(x, 4))
+    return {"mean_reward": r4(div(ret, ne)), "success_rate": r4(div(ns, ne)), "collision_rate": r4(div(ncol, ne)),
+            "timeout_rate": r4(div(nto, ne)), "num_episodes": r4(ne), "mean_ep_length": r4(div(le, ne)),
+            "mean_ep_length_success": r4(div(ls, ns)), "mean_num_sim_steps": r4(div(le * n_substeps, ne)),
+            "mean_num_sim_steps_success": r4(div(ls * n_substeps, ns)), "mean_effort": r4(div(eff, ns)),
+            "mean_manipulability": r4(div(man, ns)), "mean_norm_jerk": r4(div(jerk, ls)), "mean_ee_speed": r4(div(spd, ls))}

@@ -172,6 +172,15 @@ class PandaBatch:
     def observe(self):
         _lib.check(self.lib.pg_observe(self.h, self._stream()))
 
+    def set_eval_metrics(self, enable=True):
+        """Start (and zero) / stop the on-device accumulation of perform_benchmark's metrics (evaluate.py:131-300)."""
+        _lib.check(self.lib.pg_set_eval_metrics(self.h, 1 if enable else 0, self._stream()))
+
+    def eval_metrics_raw(self):
+        out = np.zeros(12, np.float64)
+        _lib.check(self.lib.pg_get_eval_metrics(self.h, out.ctypes.data_as(ctypes.c_void_p), self._stream()))
+        return out
+
     def manipulability(self, q=None):
         """Panda.get_manipulability (panda.py:314-317) for every environment (q None) or for q f32 [7][m] on the device."""
         if q is None:

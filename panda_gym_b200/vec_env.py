@@ -172,6 +172,15 @@ class PandaVecEnv:
         self.step_async(actions)
         return self.step_wait()
 
+    def start_benchmark(self):
+        """Begin accumulating perform_benchmark's metrics (evaluation/evaluate.py:131-300) on the device."""
+        self.batch.set_eval_metrics(True)
+
+    def benchmark_results(self, group=None):
+        """perform_benchmark's ``results`` dict over every episode finished since ``start_benchmark`` (all ranks)."""
+        from .sharding import benchmark_results
+        return benchmark_results(self.batch.eval_metrics_raw(), n_substeps=self.batch.cfg.n_substeps, group=group)
+
     def close(self):
         self.batch.close()
 

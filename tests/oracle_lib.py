@@ -113,6 +113,7 @@ def lib():
     sig("pgo_env_set_obstacles", None, P, c_int, P)
     sig("pgo_env_get_obstacles", c_int, P, P)
     sig("pgo_env_check_collided", c_int, P, P, P)
+    sig("pgo_env_step_metrics", None, P, P)
     sig("pgo_env_get_obs", None, P, P, P, P)
     sig("pgo_env_compute_reward", None, P, P, P, c_int, P)
     sig("pgo_env_is_collided", c_int, P)
@@ -278,6 +279,11 @@ class Env:
     def set_obstacles(self, obs_list):
         arr = (Obstacle * max(1, len(obs_list)))(*obs_list)
         self.L.pgo_env_set_obstacles(self.h, len(obs_list), arr)
+
+    def step_metrics(self):
+        out = np.zeros(4)
+        self.L.pgo_env_step_metrics(self.h, dp(out))
+        return out
 
     def check_collided(self):
         d = np.zeros(9); t = c_double(0)

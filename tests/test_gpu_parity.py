@@ -588,3 +588,67 @@ def test_randomize_robot_pose_needs_a_built_randomizer(sim):
     tc.randomize_robot_pose = True
     with pytest.raises(PandaB200Error, match="ik_lm_chan"):
         sim.PandaBatch(sim.make_config(1, 4, scenario="reachao3", config=tc))
+
+# ------------------------------------------------------------------------------------------ N3: evaluation metrics
+def test_benchmark_metrics_match_perform_benchmark_on_the_oracle(sim, oracle):
+    """evaluation/evaluate.py:perform_benchmark (:131-300) replayed on oracle envs -- many episodes per env, each reset with
+    an explicit seed like the reference's reset(seed=seed) -- against the device accumulators (pg_get_eval_metrics) turned
+    into the same ``results`` dict: counts exact, means within 1e-3 relative."""
+    from panda_gym_b200.sharding import benchmark_results
+    n, T, steps = 48, 15, 40
+    cfg = sim.make_config(1, n, scenario="reachao1", max_episode_steps=T, ee_error_threshold=0.2, auto_reset=False)
+    b = sim.PandaBatch(cfg)
+    next_seed = np.arange(500, 500 + n)
+    b.reset(seeds=torch.tensor(next_seed, dtype=torch.int64, device=dev()))
+    b.set_eval_metrics(True)
+    refs = [oracle.Env(task=1, scenario="reachao1", max_episode_steps=T, ee_error_threshold=0.2) for _ in range(n)]
+    for i, e in enumerate(refs):
+        e.reset(int(next_seed[i]))
+    rng = np.random.default_rng(3)
+    ep = [dict(r=0.0, eff=0.0, man=0.0, jerk=[], speed=[], n=0) for _ in range(n)]
+    done_events, ep_rewards, ep_lengths, len_succ, efforts, manips, jerks, speeds = [], [], [], [], [], [], [], []
+    for t in range(steps):
+        A = rng.uniform(-1, 1, (n, 7)).astype(np.float32)
+        A[1::3, 1] = 1.0; A[1::3, 3] = -1.0   # a third of the arms folds down onto the table: collisions
+        b.step(torch.from_numpy(A).cuda())
+        fg = b.view("flags").cpu().numpy()
+        dn = b.view("done").cpu().numpy()
+        mask = np.zeros(n, np.uint8)
+        for i, e in enumerate(refs):
+            o, r, f = e.step(A[i])
+            m = e.step_metrics()
+            s = ep[i]
+            s["r"] += r; s["eff"] += m[0]; s["jerk"].append(m[1]); s["man"] += m[2]; s["speed"].append(m[3]); s["n"] += 1
+            done = f["terminated"] or f["truncated"] or f["time_limit"]
+            assert bool(dn[i]) == done and (fg[i] & 15) == flags_of(f)
+            if done:  # evaluate.py:264-283
+                if f["is_success"]:
+                    done_events.append(1); len_succ.append(s["n"]); jerks.append(s["jerk"]); efforts.append(s["eff"] / s["n"])
+                    manips.append(s["man"] / s["n"]); speeds.append(s["speed"])
+                elif f["truncated"]:
+                    done_events.append(-1)
+                else:
+                    done_events.append(0)
+                ep_rewards.append(s["r"]); ep_lengths.append(s["n"])
+                ep[i] = dict(r=0.0, eff=0.0, man=0.0, jerk=[], speed=[], n=0)
+                next_seed[i] += n
+                e.reset(int(next_seed[i]))
+                mask[i] = 1
+        if mask.any():
+            b.reset(mask=torch.from_numpy(mask).cuda(), seeds=torch.tensor(next_seed, dtype=torch.int64, device=dev()))
+    got = benchmark_results(b.eval_metrics_raw(), n_substeps=20)
+    assert done_events.count(1) >= 5 and done_events.count(-1) >= 5 and done_events.count(0) >= 5, "test needs all three outcomes"
+    flat = lambda ll: np.array([x for l in ll for x in l])
+    want = {"mean_reward": np.mean(ep_rewards), "success_rate": done_events.count(1) / len(done_events),
+            "collision_rate": done_events.count(-1) / len(done_events), "timeout_rate": done_events.count(0) / len(done_events),
+            "num_episodes": len(done_events), "mean_ep_length": np.mean(ep_lengths), "mean_ep_length_success": np.mean(len_succ),
+            "mean_num_sim_steps": np.mean([i * 20 for i in ep_lengths]), "mean_num_sim_steps_success": np.mean([i * 20 for i in len_succ]),
+            "mean_effort": np.mean(efforts), "mean_manipulability": np.mean(manips), "mean_norm_jerk": np.mean(flat(jerks)),
+            "mean_ee_speed": np.mean(flat(speeds))}
+    assert set(got) == set(want)
+    for k in ("success_rate", "collision_rate", "timeout_rate", "num_episodes", "mean_ep_length", "mean_ep_length_success",
+              "mean_num_sim_steps", "mean_num_sim_steps_success", "mean_reward"):
+        assert got[k] == float(np.round(want[k], 4)), (k, got[k], want[k])
+    for k in ("mean_effort", "mean_manipulability", "mean_norm_jerk", "mean_ee_speed"):
+        assert abs(got[k] - want[k]) < 1e-3 * abs(want[k]) + 1e-4, (k, got[k], want[k])
+    b.close()

@@ -123,3 +123,17 @@ def test_product_does_not_import_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert "oracle_lib" not in src and "liboracle" not in src, f
                 assert not re.search(r'#include\s+"[^"]*pgo', src) and not re.search(r"\bpgo_\w+\s*\(", src), f
+
+
+def test_benchmark_results_from_accumulators():
+    """sharding.benchmark_results: perform_benchmark's results dict (evaluation/evaluate.py:286-300) from the 12 device sums."""
+    from panda_gym_b200.sharding import benchmark_results
+    #      succ  len_s  eff   man  jerk  speed  eps  len   coll  ret    timeouts
+    raw = [4.0, 40.0, 2.0, 0.4, 8.0, 12.0, 10.0, 130.0, 5.0, -420.0, 1.0, 0.0]
+    r = benchmark_results(raw, n_substeps=20)
+    assert r["success_rate"] == 0.4 and r["collision_rate"] == 0.5 and r["timeout_rate"] == 0.1 and r["num_episodes"] == 10.0
+    assert r["mean_reward"] == -42.0 and r["mean_ep_length"] == 13.0 and r["mean_ep_length_success"] == 10.0
+    assert r["mean_num_sim_steps"] == 260.0 and r["mean_num_sim_steps_success"] == 200.0
+    assert r["mean_effort"] == 0.5 and r["mean_manipulability"] == 0.1 and r["mean_norm_jerk"] == 0.2 and r["mean_ee_speed"] == 0.3
+    empty = benchmark_results([0.0] * 12)
+    assert empty["num_episodes"] == 0.0 and empty["mean_effort"] != empty["mean_effort"]  # nan, like np.mean([])
