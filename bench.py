@@ -115,6 +115,10 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=65536)
     ap.add_argument("--ref-steps-per-env", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--curriculum", action="store_true",
+                    help="BASELINE configs[2]: cycle the stage block reachao1 -> reachao2 -> reachao3 -> wangexp-3 every "
+                         "--stage-every vector steps inside the timed region (pg_set_stage; use --steps >= 4 x --stage-every)")
+    ap.add_argument("--stage-every", type=int, default=50)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -140,6 +144,8 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    if args.curriculum:
+        args.scenario = "reachao1"  # first stage of the cycle
     N = args.envs_per_gpu
     W = max(3, args.warmup)
     K = args.steps
@@ -167,9 +173,14 @@ def main():
         dist.barrier()
     torch.cuda.synchronize()
     t_wall0 = time.perf_counter()
+    stages = ["reachao1", "reachao2", "reachao3", "wangexp-3"]
+    stage_switches = 0
     for k in range(K):
         flush.fill_(k & 0xFF)  # L2 flush, outside the per-step event pair
         ev[k][0].record()
+        if args.curriculum and k > 0 and k % args.stage_every == 0:  # inside the timed region: the switch is part of the cost
+            env.set_stage(stages[(k // args.stage_every) % len(stages)], max_episode_steps=100)
+            stage_switches += 1
         b.step(actions[W + k])
         if world > 1 and (k % 10) == 9:  # episode statistics all-reduce: the one collective of the path
             s = stats_buf.clone()
@@ -237,10 +248,14 @@ def main():
             "metric": "env-steps/sec (whole box)", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": workload_name(args.scenario, N),
+            "config": {"workload": (workload_name(args.scenario, N) if not args.curriculum else
+                                    workload_name("reachao1 -> reachao2 -> reachao3 -> wangexp-3 (curriculum)", N).replace("configs[1]", "configs[2]")),
                        "envs_per_gpu": N, "scenario": args.scenario, "sharding": "envs partitioned contiguously, no data-path collective",
                        "l2": "flushed between timed steps (256 MiB write); per-step CUDA-event timing on the launch stream",
-                       "actions": "U(-1,1), counter-based, pre-generated in HBM"},
+                       "actions": "U(-1,1), counter-based, pre-generated in HBM",
+                       "curriculum": ({"stages": stages, "every": args.stage_every, "switches": stage_switches,
+                                       "note": "BASELINE configs[2]: stage parameter block swapped inside the timed region"}
+                                      if args.curriculum else None)},
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "PandaVecEnv.step(numpy actions) -> numpy obs/reward/done (pg_step_host, pinned buffers)", "steps": Ke},
             "gpu_launches": launches,

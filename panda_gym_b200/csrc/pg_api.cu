@@ -656,9 +656,8 @@ int pg_her_create(int device, int64_t buffer_size, int n_envs, int obs_dim, int 
   auto A = [&](void** p, size_t bytes) -> int {
     PG_CUDA(cudaMalloc(p, bytes)); PG_CUDA(cudaMemset(*p, 0, bytes)); h->bufs.push_back(*p); return PG_OK; };
 #define HA(ptr, count, type) { int rc = A((void**)&ptr, (size_t)(count) * sizeof(type)); if (rc != PG_OK) { pg_her_destroy(h); return rc; } }
-  HA(H.obs, cap * obs_dim, float) HA(H.next_obs, cap * obs_dim, float) HA(H.ag, cap * 3, float) HA(H.dg, cap * 3, float)
-  HA(H.next_ag, cap * 3, float) HA(H.next_dg, cap * 3, float) HA(H.action, cap * act_dim, float) HA(H.reward, cap, float)
-  HA(H.done, cap, float) HA(H.timeout, cap, float) HA(H.ep_start, cap, int) HA(H.ep_length, cap, int)
+  H.rec_w = (pg::her_used(obs_dim, act_dim) + 15) / 16 * 16;  // whole 64 B lines per record
+  HA(H.rec, cap * H.rec_w, float) HA(H.ep_start, cap, int) HA(H.ep_length, cap, int)
   HA(H.cur_ep_start, n_envs, int) HA(H.cursor, 2, int) HA(H.valid, cap, int) HA(H.n_valid, 1, int)
   HA(H.block_counts, (cap + pg::kHerBlock - 1) / pg::kHerBlock + 1, int) HA(H.mt, 625, uint32_t)
   HA(H.s_row, max_batch, int) HA(H.s_env, max_batch, int) HA(H.s_t, max_batch, int) HA(H.status, 1, int)

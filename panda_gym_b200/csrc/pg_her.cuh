@@ -15,9 +15,14 @@ namespace pg {
 struct HerParams {
   int rows, n_envs, obs_dim, act_dim;
   float her_ratio;
-  // storage [rows][n_envs][...]
-  float *obs, *next_obs, *ag, *dg, *next_ag, *next_dg, *action, *reward, *done, *timeout;
-  int *ep_start, *ep_length;  // [rows][n_envs]
+  // storage: ONE record per transition, [rows][n_envs][rec_w] f32, rec_w = used width rounded up to 16 floats (64 B):
+  //   observation od | next observation od | achieved 3 | desired 3 | next achieved 3 | next desired 3 | action ad |
+  //   reward | done | timeout | ep_start (int bits) | pad
+  // A sampled transition is one contiguous, 64 B-aligned read (576 B at obs 56 / act 7) instead of ten scattered
+  // fields of ten arrays (each a separate 32 B sector: measured 2x read amplification).
+  float* rec;
+  int rec_w;
+  int *ep_start, *ep_length;  // [rows][n_envs] (bookkeeping + valid-index compaction; ep_start is mirrored into the record)
   int* cur_ep_start;          // [n_envs]
   int* cursor;                // [0] pos, [1] full
   // sampling scratch
@@ -31,6 +36,13 @@ struct HerParams {
   int* status;                // [0] != 0 when sample() could not run (no valid transition)
 };
 
+// record field offsets (floats)
+__host__ __device__ __forceinline__ int her_used(int od, int ad) { return 2 * od + 12 + ad + 4; }
+__device__ __forceinline__ int her_off_ag(const HerParams& H) { return 2 * H.obs_dim; }
+__device__ __forceinline__ int her_off_act(const HerParams& H) { return 2 * H.obs_dim + 12; }
+__device__ __forceinline__ int her_off_rew(const HerParams& H) { return 2 * H.obs_dim + 12 + H.act_dim; }
+__device__ __forceinline__ int her_off_eps(const HerParams& H) { return 2 * H.obs_dim + 12 + H.act_dim + 3; }
+
 // ------------------------------------------------------------------------------------------ add
 // DictReplayBuffer.add + HerReplayBuffer episode bookkeeping; one thread per environment
 __global__ void k_her_add_book(HerParams H, const uint8_t* __restrict__ done) {
@@ -41,6 +53,7 @@ __global__ void k_her_add_book(HerParams H, const uint8_t* __restrict__ done) {
   int st = H.ep_start[(size_t)pos * ne + e], len = H.ep_length[(size_t)pos * ne + e];
   if (len > 0) for (int i = pos; i < st + len; i++) H.ep_length[(size_t)(i % rows) * ne + e] = 0;
   H.ep_start[(size_t)pos * ne + e] = H.cur_ep_start[e];
+  H.rec[((size_t)pos * ne + e) * H.rec_w + her_off_eps(H)] = __int_as_float(H.cur_ep_start[e]);
   if (done[e]) {  // _compute_episode_length, evaluated with the cursor already advanced
     int start = H.cur_ep_start[e], end = (pos + 1) % rows;
     if (end < start) end += rows;
@@ -53,21 +66,23 @@ __global__ void k_her_add_data(HerParams H, const float* __restrict__ obs, const
                                const float* __restrict__ act, const float* __restrict__ rew, const uint8_t* __restrict__ done,
                                const uint8_t* __restrict__ timeout) {
   const int pos = H.cursor[0], ne = H.n_envs, od = H.obs_dim, ad = H.act_dim;
-  const int per = 2 * od + 12 + ad + 3;
+  const int per = 2 * od + 12 + ad + 3;  // everything but ep_start (k_her_add_book writes that slot)
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)ne * per) return;
   int e = (int)(i / per), k = (int)(i % per);
-  size_t base = (size_t)pos * ne + e;
-  if (k < od) H.obs[base * od + k] = obs[(size_t)e * od + k];
-  else if ((k -= od) < od) H.next_obs[base * od + k] = nobs[(size_t)e * od + k];
-  else if ((k -= od) < 3) H.ag[base * 3 + k] = ag[(size_t)e * 3 + k];
-  else if ((k -= 3) < 3) H.dg[base * 3 + k] = dg[(size_t)e * 3 + k];
-  else if ((k -= 3) < 3) H.next_ag[base * 3 + k] = nag[(size_t)e * 3 + k];
-  else if ((k -= 3) < 3) H.next_dg[base * 3 + k] = ndg[(size_t)e * 3 + k];
-  else if ((k -= 3) < ad) H.action[base * ad + k] = act[(size_t)e * ad + k];
-  else if ((k -= ad) == 0) H.reward[base] = rew[e];
-  else if (k == 1) H.done[base] = done[e] ? 1.f : 0.f;
-  else H.timeout[base] = timeout ? (timeout[e] ? 1.f : 0.f) : 0.f;
+  float* dst = H.rec + ((size_t)pos * ne + e) * H.rec_w + k;  // consecutive threads -> consecutive floats of the record
+  float v;
+  if (k < od) v = obs[(size_t)e * od + k];
+  else if ((k -= od) < od) v = nobs[(size_t)e * od + k];
+  else if ((k -= od) < 3) v = ag[(size_t)e * 3 + k];
+  else if ((k -= 3) < 3) v = dg[(size_t)e * 3 + k];
+  else if ((k -= 3) < 3) v = nag[(size_t)e * 3 + k];
+  else if ((k -= 3) < 3) v = ndg[(size_t)e * 3 + k];
+  else if ((k -= 3) < ad) v = act[(size_t)e * ad + k];
+  else if ((k -= ad) == 0) v = rew[e];
+  else if (k == 1) v = done[e] ? 1.f : 0.f;
+  else v = timeout ? (timeout[e] ? 1.f : 0.f) : 0.f;
+  *dst = v;
 }
 __global__ void k_her_advance(HerParams H) {
   int pos = H.cursor[0] + 1;
@@ -251,30 +266,35 @@ __global__ void k_her_gather(HerParams H, Params P, HerBatch O, int B, int nb_vi
   const int k = warp;                       // SB3 sample order: first nb_virtual are virtual
   const bool is_virtual = k < nb_virtual;
   const int out = is_virtual ? (B - nb_virtual) + k : k - nb_virtual;
-  const int ne = H.n_envs, od = H.obs_dim, ad = H.act_dim, rows = H.rows;
+  const int ne = H.n_envs, od = H.obs_dim, ad = H.act_dim, rows = H.rows, w = H.rec_w;
   const int row = H.s_row[k], env = H.s_env[k];
-  const size_t src = (size_t)row * ne + env;
-  for (int i = lane; i < od; i += 32) { O.obs[(size_t)out * od + i] = H.obs[src * od + i]; O.next_obs[(size_t)out * od + i] = H.next_obs[src * od + i]; }
-  for (int i = lane; i < ad; i += 32) O.action[(size_t)out * ad + i] = H.action[src * ad + i];
+  const float* __restrict__ rec = H.rec + ((size_t)row * ne + env) * w;
+  const int o_ag = her_off_ag(H), o_act = her_off_act(H), o_rew = her_off_rew(H);
+  // field-wise copy out of the contiguous record (warp-uniform loops: no divergence; the whole record is 9 x 64 B lines)
+  for (int i = lane; i < od; i += 32) {
+    const float a = rec[i], b = rec[od + i];
+    O.obs[(size_t)out * od + i] = a; O.next_obs[(size_t)out * od + i] = b;
+  }
+  for (int i = lane; i < ad; i += 32) O.action[(size_t)out * ad + i] = rec[o_act + i];
+  // new goal: the achieved goal of a later transition of the same episode (virtual) or the stored desired goal
   float g[3], nag[3];
   if (is_virtual) {
-    int st = H.ep_start[src];
-    int trow = (H.s_t[k] + st) % rows;
-    for (int i = 0; i < 3; i++) g[i] = H.next_ag[((size_t)trow * ne + env) * 3 + i];
-  } else {
-    for (int i = 0; i < 3; i++) g[i] = H.dg[src * 3 + i];
-  }
-  for (int i = 0; i < 3; i++) nag[i] = H.next_ag[src * 3 + i];
+    const int st = __float_as_int(rec[o_rew + 3]);
+    const int trow = (H.s_t[k] + st) % rows;
+    const float* fut = H.rec + ((size_t)trow * ne + env) * w + o_ag + 6;  // its next achieved goal
+    g[0] = fut[0]; g[1] = fut[1]; g[2] = fut[2];
+  } else { g[0] = rec[o_ag + 3]; g[1] = rec[o_ag + 4]; g[2] = rec[o_ag + 5]; }
+  nag[0] = rec[o_ag + 6]; nag[1] = rec[o_ag + 7]; nag[2] = rec[o_ag + 8];
   if (lane < 3) {
-    O.ag[(size_t)out * 3 + lane] = H.ag[src * 3 + lane];
+    O.ag[(size_t)out * 3 + lane] = rec[o_ag + lane];
     O.next_ag[(size_t)out * 3 + lane] = nag[lane];
     O.dg[(size_t)out * 3 + lane] = g[lane];
-    O.next_dg[(size_t)out * 3 + lane] = is_virtual ? g[lane] : H.next_dg[src * 3 + lane];
+    O.next_dg[(size_t)out * 3 + lane] = is_virtual ? g[lane] : rec[o_ag + 9 + lane];
   }
   if (lane == 0) {
     // virtual reward = env.compute_reward(next_achieved_goal, new_goal) of environment `reward_env` (SB3: indices=[0])
-    O.reward[out] = is_virtual ? reward_fn(P, reward_env, nag, g) : H.reward[src];
-    O.done[out] = H.done[src] * (1.f - H.timeout[src]);
+    O.reward[out] = is_virtual ? reward_fn(P, reward_env, nag, g) : rec[o_rew];
+    O.done[out] = rec[o_rew + 1] * (1.f - rec[o_rew + 2]);  // dones * (1 - timeouts)
   }
 }
 

@@ -737,7 +737,7 @@ __device__ inline Body obstacle_body(const Params& P, int j, int e) {
 // code on the same PCG64 state, the 36-primitive robot distance query is split across the lanes.  Grid-stride
 // over the list.
 template <bool WARP>
-__global__ void __launch_bounds__(kBlock) k_reset(const Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
+__global__ void __launch_bounds__(kBlock) k_reset(const __grid_constant__ Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
                                                   uint64_t first_env) {
   const int n = P.n;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
