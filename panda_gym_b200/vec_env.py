@@ -111,6 +111,9 @@ class PandaVecEnv:
             npv["done_bool"] = npv["done"].view(np.bool_)
             self._ring.append((h, out, npv))
         self._ring_pos = 0
+        v = self.batch.view
+        self._term_src = tuple(v(name) for name in ("terminal_observation", "terminal_achieved", "ep_return", "ep_length"))
+        self._term_ring = [tuple(torch.empty_like(x) for x in self._term_src) for _ in range(self.n_host_buffers)]
         self._h_actions = pinned((n, ad), torch.float32)
         self._np_actions = self._h_actions.numpy()
         self.observation_space = spaces.Dict(dict(
@@ -154,15 +157,16 @@ class PandaVecEnv:
         else:
             rewards, dones, flags = npv["reward"], npv["done_bool"], npv["flags"]
         b = self.batch
-        # terminal data lives in device buffers that the NEXT step overwrites: snapshot the finished rows now (device
-        # gather, no host copy) and move them to the host only if somebody asks
-        didx = torch.nonzero(b.view("done"), as_tuple=False).flatten()
-        snap = (b.view("terminal_observation").index_select(0, didx), b.view("terminal_achieved").index_select(0, didx),
-                b.view("ep_return").index_select(0, didx), b.view("ep_length").index_select(0, didx))
+        # terminal data lives in device buffers that a later step overwrites: keep a device-side copy of them in a
+        # 3-deep ring (four asynchronous device-to-device copies, ~15 MB at 65 536 envs = a few microseconds of HBM time, no
+        # host synchronisation) and gather / move the finished rows to the host only if somebody asks
+        snap = self._term_ring[self._ring_pos]
+        for dst, src in zip(snap, self._term_src):
+            dst.copy_(src, non_blocking=True)
 
         def fetch(idx, snap=snap):
-            assert len(idx) == snap[0].shape[0]
-            return tuple(x.cpu().numpy() for x in snap)
+            sel = torch.as_tensor(np.asarray(idx, dtype=np.int64), device=snap[0].device)
+            return tuple(x.index_select(0, sel).cpu().numpy() for x in snap)
 
         infos = LazyInfos(prev_desired if self.copy_outputs else prev_desired.copy(), flags, dones, fetch, time.time() - self._t0)
         self._last_desired = obs["desired_goal"]
