@@ -29,8 +29,20 @@ import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints exactly one JSON line
+# Rank 0 must print exactly ONE JSON line on stdout.  Native libraries write there too (NCCL's "NCCL version ..." banner at
+# communicator creation, at any NCCL_DEBUG level >= VERSION), so file descriptor 1 points at stderr for the whole run and is
+# switched back only for the final line.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    sys.stdout.flush()
+    os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
+    os.dup2(2, 1)
+
+
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
@@ -126,7 +138,7 @@ def main():
 
     if args.impl == "reference":
         if rank == 0:
-            print(json.dumps(cpu_reference_line(args, args.scenario)), flush=True)
+            emit(cpu_reference_line(args, args.scenario))
         return 0
 
     import numpy as np
@@ -282,7 +294,7 @@ def main():
             rate, dt, _ = O.cpu_rollout(per_env, cores, scenario=args.scenario, max_episode_steps=100, seed=2)
             line["cpu_baseline"] = {"value": rate, "unit": "env-steps/s", "cores": cores, "kind": "port",
                                     "sample": "%d envs (one per host thread) x %d env-steps of the same workload, %.1f s" % (cores, per_env, dt)}
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
