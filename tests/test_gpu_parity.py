@@ -652,3 +652,50 @@ def test_benchmark_metrics_match_perform_benchmark_on_the_oracle(sim, oracle):
     for k in ("mean_effort", "mean_manipulability", "mean_norm_jerk", "mean_ee_speed"):
         assert abs(got[k] - want[k]) < 1e-3 * abs(want[k]) + 1e-4, (k, got[k], want[k])
     b.close()
+
+
+# ------------------------------------------------------------------------------------------ committed fixture
+def test_cuda_path_against_committed_rollouts(sim):
+    """The CUDA path against tests/golden/oracle_rollouts.json (frozen oracle rollouts, tools/gen_oracle_golden.py) -- no
+    oracle build involved: seeded resets, then the recorded actions; flags and rewards exact, observations in tolerance."""
+    import json
+    import os
+    from panda_gym_b200.config import TrainConfig
+    data = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_rollouts.json")))
+    steps_checked = 0
+    for c in data["cases"]:
+        kw, task, recs = c["kw"], c["task"], c["rollouts"]
+        n = len(recs)
+        tc = TrainConfig()
+        tc.randomize_robot_pose = bool(kw.get("randomize_robot_pose", 0))
+        control = {0: "joints", 1: "ee"}.get(kw.get("control")) if task == 0 else None
+        cfg = sim.make_config(task, n, scenario=kw.get("scenario"), config=tc if task == 1 else None, control_type=control,
+                              max_episode_steps=kw["max_episode_steps"], auto_reset=False)
+        b = sim.PandaBatch(cfg)
+        b.reset(seeds=torch.tensor([r["seed"] for r in recs], dtype=torch.int64, device=dev()))
+        og = b.view("observation").cpu().numpy()
+        contact = task >= 2   # Push: contact dynamics amplify fp32 rounding (DESIGN section 9)
+        for i, r in enumerate(recs):
+            assert np.abs(np.asarray(r["reset_obs"]) - og[i]).max() < 5e-4, c["name"]
+            assert np.abs(np.asarray(r["goal"]) - b.view("desired_goal").cpu().numpy()[i]).max() < 1e-6
+        T = max(len(r["actions"]) for r in recs)
+        for t in range(T):
+            A = np.zeros((n, b.act_dim), np.float32)
+            for i, r in enumerate(recs):
+                if t < len(r["actions"]):
+                    A[i] = r["actions"][t]
+            b.step(torch.from_numpy(A).to(dev()))
+            og = b.view("observation").cpu().numpy(); rg = b.view("reward").cpu().numpy(); fg = b.view("flags").cpu().numpy()
+            for i, r in enumerate(recs):
+                if t >= len(r["actions"]):
+                    continue
+                f = r["flags"][t]
+                want_flags = f[0] | (f[1] << 1) | (f[2] << 2) | ((1 if (f[3] and not f[1]) else 0) << 3)
+                assert (fg[i] & 15) == want_flags, (c["name"], r["seed"], t)
+                assert rg[i] == np.float32(r["rewards"][t]), (c["name"], r["seed"], t)
+                k = 20 if len(r["obs"][t]) >= 20 else 6
+                tol = 2e-3 if contact else 1e-3
+                assert np.abs(np.asarray(r["obs"][t][:k]) - og[i, :k]).max() < tol, (c["name"], r["seed"], t)
+                steps_checked += 1
+        b.close()
+    assert steps_checked > 200

@@ -89,3 +89,26 @@ def test_hollow_sphere_sampler_matches_numpy_restatement(oracle):
             r = np.linalg.norm(e.goal()); assert 0.5 - 1e-9 <= r <= 0.85 + 1e-9 and e.goal()[2] >= 0
         assert first.shape == (3,)
     assert hits > 10
+
+
+def test_oracle_reproduces_committed_rollouts(oracle):
+    """Drift guard: tests/golden/oracle_rollouts.json (tools/gen_oracle_golden.py) froze seeded oracle rollouts; a changed
+    oracle would silently change what GPU 'parity' means."""
+    import json
+    import os
+    import numpy as np
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "oracle_rollouts.json")
+    data = json.load(open(path))
+    n = 0
+    for c in data["cases"]:
+        for rec in c["rollouts"]:
+            e = oracle.Env(task=c["task"], **c["kw"])
+            o, _ = e.reset(rec["seed"])
+            assert np.allclose(o["observation"], rec["reset_obs"], rtol=0, atol=1e-6), c["name"]
+            assert np.allclose(o["desired_goal"], rec["goal"], rtol=0, atol=1e-7)
+            for a, r, f, ob in zip(rec["actions"], rec["rewards"], rec["flags"], rec["obs"]):
+                o, rr, ff = e.step(np.asarray(a, np.float32))
+                assert rr == r and [int(ff["is_success"]), int(ff["terminated"]), int(ff["truncated"]), int(ff["time_limit"])] == f
+                assert np.allclose(o["observation"], ob, rtol=0, atol=1e-6), c["name"]
+                n += 1
+    assert n > 200
