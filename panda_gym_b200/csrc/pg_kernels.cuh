@@ -654,6 +654,14 @@ __device__ __noinline__ double robot_body_distance(const Params& P, const Body& 
     const pgm::NeutralPrim& np = pgm::kNeutralPrims[k];
     D3 c = v3t<double>(np.c[0], np.c[1], np.c[2]);
     double d;
+    if (b.type == 0) {
+      // sphere body: the caller only compares the result with `cutoff`, so a primitive whose bounding sphere (radius r for a
+      // sphere, r + h + hull margin >= the true bound for a cylinder) stays farther than that is skipped on SQUARED distances --
+      // no fp64 sqrt / divide on the common path (they were 35 % of this kernel's stall samples)
+      const double dx = c.x - o.x, dy = c.y - o.y, dz = c.z - o.z;
+      const double reach = cutoff + b.sx + np.r + (np.type == 0 ? 0.0 : np.h + (double)kHullMargin);
+      if (dx * dx + dy * dy + dz * dz > reach * reach) continue;
+    }
     if (np.type == 0) d = b.type == 0 ? sphere_sphere<double>(c, np.r, o, b.sx).d : sphere_box<double>(c, np.r, o, core, m).d;
     else {
       D3 a = v3t<double>(np.a[0], np.a[1], np.a[2]);
