@@ -635,6 +635,7 @@ struct pg_her_s {
   pg::HerBatch out;      // library-owned output batch (max_batch rows)
   int64_t launches;
   uint64_t fast_counter;
+  bool valid_stale;      // the compacted valid-index list must be rebuilt (something was added since the last sample)
 };
 
 extern "C" {
@@ -645,7 +646,7 @@ int pg_her_create(int device, int64_t buffer_size, int n_envs, int obs_dim, int 
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(PG_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
   PG_CUDA(cudaSetDevice(device));
   pg_her_s* h = new pg_her_s();
-  h->device = device; h->launches = 0; h->fast_counter = 0; h->max_batch = max_batch;
+  h->device = device; h->launches = 0; h->fast_counter = 0; h->max_batch = max_batch; h->valid_stale = true;
   pg::HerParams& H = h->H;
   memset(&H, 0, sizeof H);
   H.rows = (int)(buffer_size / n_envs > 0 ? buffer_size / n_envs : 1);  // SB3: buffer_size // n_envs
@@ -705,6 +706,7 @@ int pg_her_add(pg_her_handle h, const float* obs, const float* ag, const float* 
   int64_t tot = (int64_t)H.n_envs * (2 * H.obs_dim + 12 + H.act_dim + 3);
   pg::k_her_add_data<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(H, obs, ag, dg, next_obs, next_ag, next_dg, action, reward, done, timeout);
   pg::k_her_advance<<<1, 1, 0, s>>>(H);
+  h->valid_stale = true;
   h->launches += 3;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -718,13 +720,18 @@ int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, 
   const pg::HerParams& H = h->H;
   const int total = (int)h->capacity, nb = (total + pg::kHerBlock - 1) / pg::kHerBlock;
   const int B = (int)batch, nbv = (int)(H.her_ratio * (float)B);  // int(her_ratio * batch_size)
-  pg::k_her_count<<<nb, pg::kHerBlock, 0, s>>>(H, total);
-  pg::k_her_scan_blocks<<<1, 1024, 0, s>>>(H, nb);
-  pg::k_her_scatter<<<nb, pg::kHerBlock, 0, s>>>(H, total);
+  if (h->valid_stale) {  // valid = flatnonzero(ep_length > 0): unchanged until the next add(), so several gradient steps per
+                         // environment step (SB3 gradient_steps > 1) pay the 1 M-entry compaction once
+    pg::k_her_count<<<nb, pg::kHerBlock, 0, s>>>(H, total);
+    pg::k_her_scan_blocks<<<1, 1024, 0, s>>>(H, nb);
+    pg::k_her_scatter<<<nb, pg::kHerBlock, 0, s>>>(H, total);
+    h->launches += 3;
+    h->valid_stale = false;
+  }
   if (exact_rng) pg::k_her_indices_exact<<<1, 256, 0, s>>>(H, B, nbv);
   else pg::k_her_indices_fast<<<(B + 255) / 256, 256, 0, s>>>(H, B, nbv, fast_seed, h->fast_counter++);
   pg::k_her_gather<<<(unsigned)(((int64_t)B * 32 + 255) / 256), 256, 0, s>>>(H, env->P, h->out, B, nbv, reward_env);
-  h->launches += 5;
+  h->launches += 2;
   PG_CUDA(cudaGetLastError());
   out->observation = h->out.obs; out->achieved_goal = h->out.ag; out->desired_goal = h->out.dg;
   out->next_observation = h->out.next_obs; out->next_achieved_goal = h->out.next_ag; out->next_desired_goal = h->out.next_dg;
