@@ -205,12 +205,6 @@ int pg_debug_fma_peak(int device, int blocks, int iters, double* tflops_out);
 /* launch shape of the step kernel: out[6] = registers/thread, maxThreadsPerBlock, static smem bytes, local bytes,
  * block size, resident blocks per SM */
 int pg_debug_step_kernel_attrs(int device, int* out);
-/* Which step kernel pg_step launches (process-wide): 1 = one environment per thread (default), 2 = two environments
- * per thread on the packed fp32 pipe (FFMA2) -- an A/B experiment that is only present in builds with
- * -DPG_PAIR_KERNEL (else PG_ERR_UNSUPPORTED).  Same results to fp32 rounding. */
-int pg_set_step_kernel(int which);
-int pg_get_step_kernel(void);
-
 /* ---------------------------------------------------------------------------------------------------------
  * On-device Hindsight-Experience-Replay buffer.  Replaces stable_baselines3 HerReplayBuffer (SB3 >= 2.0) as the
  * reference uses it (classes/train_config.py:2,15; default kwargs n_sampled_goal = 4, strategy "future"):

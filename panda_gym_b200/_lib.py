@@ -93,8 +93,6 @@ SYMBOLS = [
     ("pg_debug_ik", c_int, [c_int, c_int, P, P, P, P, P]),
     ("pg_debug_fma_peak", c_int, [c_int, c_int, c_int, P]),
     ("pg_debug_step_kernel_attrs", c_int, [c_int, P]),
-    ("pg_set_step_kernel", c_int, [c_int]),
-    ("pg_get_step_kernel", c_int, []),
     ("pg_her_create", c_int, [c_int, c_i64, c_int, c_int, c_int, c_int, c_i64, P]),
     ("pg_her_destroy", c_int, [P]),
     ("pg_her_add", c_int, [P] * 12),

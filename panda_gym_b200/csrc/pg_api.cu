@@ -13,6 +13,7 @@
 #include "../../include/panda_b200.h"
 #include "pg_kernels.cuh"
 #include "pg_her.cuh"
+#include "pg_launch.h"
 
 namespace {
 
@@ -39,7 +40,7 @@ struct pg_env_s {
   int64_t launches;
   float* d_actions;                 // staging for the host-buffer step
   int eval_metrics;                 // pg_set_eval_metrics: launch k_eval_metrics after every step
-  int grid() const { return (P.n + pg::kBlock - 1) / pg::kBlock; }
+  int sm_count;                     // cudaDevAttrMultiProcessorCount (grid of the auto-reset kernel)
 };
 
 namespace {
@@ -195,7 +196,10 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   if (ce != cudaSuccess || ndev == 0) return fail(PG_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
   if (device < 0 || device >= ndev) return fail(PG_ERR_ARG, "bad device index");
   PG_CUDA(cudaSetDevice(device));
+  int sms = 148;
+  PG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   pg_env_s* h = new pg_env_s();
+  h->sm_count = sms;
   h->cfg = *cfg; h->device = device; h->launches = 0; h->first_env = 0; h->d_actions = nullptr; h->eval_metrics = 0;
   pg::Params& P = h->P;
   memset(&P, 0, sizeof P);
@@ -249,7 +253,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
       for (int e = 0; e < n; e++) { init[(size_t)(j * 3 + 0) * n + e] = 0.1; init[(size_t)(j * 3 + 1) * n + e] = 0.0; init[(size_t)(j * 3 + 2) * n + e] = 0.1; }
     cudaError_t e2 = cudaMemcpy(P.obs_pos, init.data(), init.size() * sizeof(double), cudaMemcpyHostToDevice);
     if (e2 != cudaSuccess) { pg_destroy(h); return fail(PG_ERR_CUDA, cudaGetErrorString(e2)); }
-    pg::k_mirror_obstacles<<<(unsigned)(((size_t)pg::kMaxObst * 3 * n + 255) / 256), 256>>>(P);
+    pg::launch_mirror_obstacles(P, 0);
   }
   P.base_seed = 0;
   *out = h;
@@ -282,49 +286,10 @@ int pg_seed(pg_handle h, uint64_t base_seed, uint64_t first_env_index) {
   return PG_OK;
 }
 
-// Which step kernel runs: 1 = one environment per thread (default), 2 = two environments per thread on the packed
-// fp32 pipe -- an experiment kept for A/B measurements, compiled only with -DPG_PAIR_KERNEL (measured slower on B200:
-// FFMA2 holds the fma pipe for two cycles, so it only saves issue slots, and 7 warps/SM hide less latency than 14;
-// profiles/r01_k_step_summary.md section F).  PANDA_B200_STEP_KERNEL / pg_set_step_kernel() select it.
-static int g_step_kernel = 0;
-static int step_kernel() {
-  if (g_step_kernel == 0) {
-    const char* e = getenv("PANDA_B200_STEP_KERNEL");
-#ifdef PG_PAIR_KERNEL
-    g_step_kernel = (e && e[0] == '2') ? 2 : 1;
-#else
-    (void)e;
-    g_step_kernel = 1;
-#endif
-  }
-  return g_step_kernel;
-}
-#ifdef PG_PAIR_KERNEL
-static cudaError_t pair_kernel_smem() {  // opt in to > 48 KB dynamic shared memory, once per device
-  static bool done[64] = {};
-  int dev = 0;
-  cudaError_t r = cudaGetDevice(&dev);
-  if (r != cudaSuccess || dev < 0 || dev >= 64 || done[dev]) return r;
-  r = cudaFuncSetAttribute(pg::k_step2, cudaFuncAttributeMaxDynamicSharedMemorySize, pg::kPairSmemBytes);
-  if (r == cudaSuccess) r = cudaFuncSetAttribute(pg::k_debug_substeps2, cudaFuncAttributeMaxDynamicSharedMemorySize, pg::kPairSmemBytes);
-  if (r == cudaSuccess) done[dev] = true;
-  return r;
-}
-#endif
-int pg_set_step_kernel(int which) {
-  if (which != 1 && which != 2) return fail(PG_ERR_ARG, "step kernel must be 1 or 2");
-#ifndef PG_PAIR_KERNEL
-  if (which == 2) return fail(PG_ERR_UNSUPPORTED, "the packed two-environment kernel is not compiled in (-DPG_PAIR_KERNEL)");
-#endif
-  g_step_kernel = which;
-  return PG_OK;
-}
-int pg_get_step_kernel(void) { return step_kernel(); }
-
 int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, void* stream) {
   if (!h) return fail(PG_ERR_ARG, "NULL handle");
   PG_CUDA(cudaSetDevice(h->device));
-  pg::k_reset<false><<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, mask_dev, seeds_dev, h->first_env);
+  pg::launch_reset_all(h->P, mask_dev, seeds_dev, h->first_env, (cudaStream_t)stream);
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -334,22 +299,15 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   if (!h || !actions_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
   if (h->P.auto_reset) PG_CUDA(cudaMemsetAsync(h->P.reset_count, 0, sizeof(int), (cudaStream_t)stream));
-#ifdef PG_PAIR_KERNEL
-  if (step_kernel() == 2) {
-    PG_CUDA(pair_kernel_smem());
-    pg::k_step2<<<(h->P.n + pg::kPairEnvs - 1) / pg::kPairEnvs, pg::kPairBlock, pg::kPairSmemBytes, (cudaStream_t)stream>>>(h->P, actions_dev);
-  } else
-#endif
-  if (h->P.task >= 2) pg::k_step_obj<<<(h->P.n + pg::kObjBlock - 1) / pg::kObjBlock, pg::kObjBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
-  else
-  pg::k_step<<<(h->P.n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(h->P, actions_dev);
+  if (h->P.task >= 2) pg::launch_step_obj(h->P, actions_dev, (cudaStream_t)stream);
+  else pg::launch_step(h->P, actions_dev, (cudaStream_t)stream);
   h->launches++;
   if (h->eval_metrics) {  // perform_benchmark's bookkeeping, on the post-step state and before the auto-reset
-    pg::k_eval_metrics<<<(h->P.n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(h->P);
+    pg::launch_eval_metrics(h->P, (cudaStream_t)stream);
     h->launches++;
   }
   if (h->P.auto_reset) {
-    pg::k_reset<true><<<148 * 8, pg::kBlock, 0, (cudaStream_t)stream>>>(h->P, nullptr, nullptr, h->first_env);  // 4736 warps, grid-stride over the list
+    pg::launch_reset_list(h->P, h->first_env, h->sm_count, (cudaStream_t)stream);
     h->launches++;
   }
   PG_CUDA(cudaGetLastError());
@@ -394,7 +352,7 @@ int pg_compute_reward(pg_handle h, const float* ag, const float* dg, float* out,
   if (env_index < 0 || env_index >= h->P.n) return fail(PG_ERR_ARG, "env_index out of range");
   if (n <= 0) return PG_OK;
   PG_CUDA(cudaSetDevice(h->device));
-  pg::k_reward<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h->P, ag, dg, out, n, env_index);
+  pg::launch_reward(h->P, ag, dg, out, n, env_index, (cudaStream_t)stream);
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -404,7 +362,7 @@ int pg_random_actions(pg_handle h, uint64_t seed, uint64_t counter, float* actio
   if (!h || !actions_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
   int64_t m = (int64_t)h->P.n * h->P.act_dim;
-  pg::k_random_actions<<<(unsigned)((m + 255) / 256), 256, 0, (cudaStream_t)stream>>>(actions_dev, m, seed, counter);
+  pg::launch_random_actions(actions_dev, m, seed, counter, (cudaStream_t)stream);
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -505,13 +463,13 @@ int pg_set_obstacles(pg_handle h, const double* pos_dev, void* stream) {
   if (!h || !pos_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
   PG_CUDA(cudaMemcpyAsync(h->P.obs_pos, pos_dev, (size_t)h->P.st.nobs * 3 * h->P.n * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
-  pg::k_mirror_obstacles<<<(unsigned)(((size_t)pg::kMaxObst * 3 * h->P.n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(h->P);
+  pg::launch_mirror_obstacles(h->P, (cudaStream_t)stream);
   return PG_OK;
 }
 int pg_observe(pg_handle h, void* stream) {
   if (!h) return fail(PG_ERR_ARG, "NULL handle");
   PG_CUDA(cudaSetDevice(h->device));
-  pg::k_observe<<<h->grid(), pg::kBlock, 0, (cudaStream_t)stream>>>(h->P);
+  pg::launch_observe(h->P, (cudaStream_t)stream);
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -542,7 +500,7 @@ int pg_manipulability(pg_handle h, const float* q_dev, int64_t n, float* out_dev
   if (q_dev && n <= 0) return fail(PG_ERR_ARG, "n must be positive when q_dev is given");
   PG_CUDA(cudaSetDevice(h->device));
   const int m = q_dev ? (int)n : h->P.n;
-  pg::k_manipulability<<<(m + 127) / 128, 128, 0, (cudaStream_t)stream>>>(m, q_dev ? q_dev : h->P.q, out_dev);
+  pg::launch_manipulability(m, q_dev ? q_dev : h->P.q, out_dev, (cudaStream_t)stream);
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -553,27 +511,21 @@ int pg_debug_substeps(int device, int n, float* q, float* qd, const float* tgt, 
   static const float kForces[7] = {87.f, 87.f, 87.f, 87.f, 12.f, 120.f, 120.f};  // panda.py:63, compiled into the kernels
   for (int d = 0; d < 7; d++) if (f[d] != kForces[d]) return fail(PG_ERR_UNSUPPORTED, "max_force must equal Panda.joint_forces (panda.py:63)");
   PG_CUDA(cudaSetDevice(device));
-#ifdef PG_PAIR_KERNEL
-  if (step_kernel() == 2) {
-    PG_CUDA(pair_kernel_smem());
-    pg::k_debug_substeps2<<<(n + pg::kPairEnvs - 1) / pg::kPairEnvs, pg::kPairBlock, pg::kPairSmemBytes, (cudaStream_t)stream>>>(n, q, qd, tgt, n_sub, velocity_mode);
-  } else
-#endif
-  pg::k_debug_substeps<<<(n + pg::kStepBlock - 1) / pg::kStepBlock, pg::kStepBlock, 0, (cudaStream_t)stream>>>(n, q, qd, tgt, f[0], f[1], f[2], f[3], f[4], f[5], f[6], n_sub, velocity_mode);
+  pg::launch_debug_substeps(n, q, qd, tgt, f, n_sub, velocity_mode, (cudaStream_t)stream);
   PG_CUDA(cudaGetLastError());
   return PG_OK;
 }
 int pg_debug_minv(int device, int n, const float* q, float* out, void* stream) {
   if (!q || !out || n <= 0) return fail(PG_ERR_ARG, "bad argument");
   PG_CUDA(cudaSetDevice(device));
-  pg::k_debug_minv<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, q, out);
+  pg::launch_debug_minv(n, q, out, (cudaStream_t)stream);
   PG_CUDA(cudaGetLastError());
   return PG_OK;
 }
 int pg_debug_ik(int device, int n, const float* q, const float* tgt, const float* base, float* out, void* stream) {
   if (!q || !tgt || !out || !base || n <= 0) return fail(PG_ERR_ARG, "bad argument");
   PG_CUDA(cudaSetDevice(device));
-  pg::k_debug_ik<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(n, q, tgt, base[0], base[1], base[2], out);
+  pg::launch_debug_ik(n, q, tgt, base[0], base[1], base[2], out, (cudaStream_t)stream);
   PG_CUDA(cudaGetLastError());
   return PG_OK;
 }
@@ -581,23 +533,7 @@ int pg_debug_ik(int device, int n, const float* q, const float* tgt, const float
 int pg_debug_step_kernel_attrs(int device, int* out /* [6]: regs, maxThreadsPerBlock, static smem, local bytes, block, blocks/SM */) {
   if (!out) return fail(PG_ERR_ARG, "bad argument");
   PG_CUDA(cudaSetDevice(device));
-  cudaFuncAttributes a;
-  int occ = 0;
-#ifdef PG_PAIR_KERNEL
-  if (step_kernel() == 2) {
-    PG_CUDA(pair_kernel_smem());
-    PG_CUDA(cudaFuncGetAttributes(&a, pg::k_step2));
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pg::k_step2, pg::kPairBlock, pg::kPairSmemBytes);
-    out[2] = (int)a.sharedSizeBytes + pg::kPairSmemBytes; out[4] = pg::kPairBlock;
-  } else
-#endif
-  {
-    PG_CUDA(cudaFuncGetAttributes(&a, pg::k_step));
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pg::k_step, pg::kStepBlock, 0);
-    out[2] = (int)a.sharedSizeBytes; out[4] = pg::kStepBlock;
-  }
-  out[0] = a.numRegs; out[1] = a.maxThreadsPerBlock; out[3] = (int)a.localSizeBytes;
-  out[5] = occ;
+  PG_CUDA(pg::step_kernel_attrs(out));
   return PG_OK;
 }
 
@@ -608,11 +544,11 @@ int pg_debug_fma_peak(int device, int blocks, int iters, double* tflops_out) {
   PG_CUDA(cudaMalloc(&d, 4));
   cudaEvent_t e0, e1;
   PG_CUDA(cudaEventCreate(&e0)); PG_CUDA(cudaEventCreate(&e1));
-  pg::k_fma_peak<<<blocks, 256>>>(d, iters, 0.999f, 0.001f);  // warm-up
+  pg::launch_fma_peak(blocks, d, iters, 0);  // warm-up
   float best = 1e30f;
   for (int r = 0; r < 5; r++) {
     PG_CUDA(cudaEventRecord(e0));
-    pg::k_fma_peak<<<blocks, 256>>>(d, iters, 0.999f, 0.001f);
+    pg::launch_fma_peak(blocks, d, iters, 0);
     PG_CUDA(cudaEventRecord(e1));
     PG_CUDA(cudaEventSynchronize(e1));
     float ms = 0; PG_CUDA(cudaEventElapsedTime(&ms, e0, e1));
@@ -702,10 +638,7 @@ int pg_her_add(pg_her_handle h, const float* obs, const float* ag, const float* 
   PG_CUDA(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   const pg::HerParams& H = h->H;
-  pg::k_her_add_book<<<(H.n_envs + 127) / 128, 128, 0, s>>>(H, done);
-  int64_t tot = (int64_t)H.n_envs * (2 * H.obs_dim + 12 + H.act_dim + 3);
-  pg::k_her_add_data<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(H, obs, ag, dg, next_obs, next_ag, next_dg, action, reward, done, timeout);
-  pg::k_her_advance<<<1, 1, 0, s>>>(H);
+  pg::launch_her_add(H, obs, ag, dg, next_obs, next_ag, next_dg, action, reward, done, timeout, s);
   h->valid_stale = true;
   h->launches += 3;
   PG_CUDA(cudaGetLastError());
@@ -718,19 +651,16 @@ int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, 
   PG_CUDA(cudaSetDevice(h->device));
   cudaStream_t s = (cudaStream_t)stream;
   const pg::HerParams& H = h->H;
-  const int total = (int)h->capacity, nb = (total + pg::kHerBlock - 1) / pg::kHerBlock;
+  const int total = (int)h->capacity;
   const int B = (int)batch, nbv = (int)(H.her_ratio * (float)B);  // int(her_ratio * batch_size)
   if (h->valid_stale) {  // valid = flatnonzero(ep_length > 0): unchanged until the next add(), so several gradient steps per
                          // environment step (SB3 gradient_steps > 1) pay the 1 M-entry compaction once
-    pg::k_her_count<<<nb, pg::kHerBlock, 0, s>>>(H, total);
-    pg::k_her_scan_blocks<<<1, 1024, 0, s>>>(H, nb);
-    pg::k_her_scatter<<<nb, pg::kHerBlock, 0, s>>>(H, total);
+    pg::launch_her_compact(H, total, s);
     h->launches += 3;
     h->valid_stale = false;
   }
-  if (exact_rng) pg::k_her_indices_exact<<<1, 256, 0, s>>>(H, B, nbv);
-  else pg::k_her_indices_fast<<<(B + 255) / 256, 256, 0, s>>>(H, B, nbv, fast_seed, h->fast_counter++);
-  pg::k_her_gather<<<(unsigned)(((int64_t)B * 32 + 255) / 256), 256, 0, s>>>(H, env->P, h->out, B, nbv, reward_env);
+  pg::launch_her_indices(H, B, nbv, exact_rng != 0, fast_seed, h->fast_counter++, s);
+  pg::launch_her_gather(H, env->P, h->out, B, nbv, reward_env, s);
   h->launches += 2;
   PG_CUDA(cudaGetLastError());
   out->observation = h->out.obs; out->achieved_goal = h->out.ag; out->desired_goal = h->out.dg;

@@ -184,7 +184,7 @@ __device__ __forceinline__ void prim_contacts(const Frame& F, const WorldParams&
 }
 
 // contact set at the current poses; returns the count (<= 12), order: object-table, robot-object, robot-table
-__device__ __noinline__ int world_contacts(const WorldParams& W, const Frame& F7, const ObjState& B, Contact* out) {
+static __device__ __noinline__ int world_contacts(const WorldParams& W, const Frame& F7, const ObjState& B, Contact* out) {
   Contact ct[kPairContacts], cr[kPairContacts], cs[kPairContacts];
   int nt = 0, nr = 0, ns = 0;
   Rot R = quat_rot(B.qx, B.qy, B.qz, B.qw);
@@ -238,7 +238,7 @@ __device__ __forceinline__ V3 inv_inertia_apply(const Rot& R, V3 iinv, V3 x) {  
 }
 
 // one row of contact c along direction t (normal or friction axis); velocities are the predicted ones
-__device__ __noinline__ void setup_row(Row& r, const ArmKin& K, const float* Mi, const float* qd, const ObjState& B, const WorldParams& W,
+static __device__ __noinline__ void setup_row(Row& r, const ArmKin& K, const float* Mi, const float* qd, const ObjState& B, const WorldParams& W,
                                        const Rot& R, V3 iinv, const Contact& c, V3 t, bool friction) {
   float denom = 0.f, rel = 0.f;
   r.arm = c.kind != 0; r.body = c.kind != 2; r.applied = 0.f;
@@ -299,7 +299,7 @@ __device__ __forceinline__ float row_residual(const Row& r, float delta) { retur
 
 // ------------------------------------------------------------------------------------------------ one stepSimulation()
 // q, qd, cq, sq, tgt as in substep() (pg_dynamics.cuh) with stride 1; B = the object.  Returns the PGS iterations used.
-__device__ __noinline__ int world_substep(bool velocity, bool unit_imp, V3 base, const WorldParams& W, float* q, float* qd, float* cq,
+static __device__ __noinline__ int world_substep(bool velocity, bool unit_imp, V3 base, const WorldParams& W, float* q, float* qd, float* cq,
                                           float* sq, const float* tgt, ObjState& B) {
   // collision detection sees the poses at the start of the step
   ArmKin K;

@@ -12,14 +12,13 @@
 // joint origin is Rx(0 / +-90 deg), which the templates below fold into sign flips.
 #pragma once
 #include "pg_model.cuh"
-#include "pg_packed.cuh"
+#include <cuda_runtime.h>
 
 namespace pg {
 
 template <typename T> struct V3T { T x, y, z; };
 using V3 = V3T<float>;
 using D3 = V3T<double>;
-using V3P = V3T<P2>;
 template <typename T> struct ident { using type = T; };
 template <typename T> __host__ __device__ __forceinline__ V3T<T> v3t(T x, T y, T z) { V3T<T> r; r.x = x; r.y = y; r.z = z; return r; }
 __host__ __device__ __forceinline__ V3 v3(float x, float y, float z) { return v3t<float>(x, y, z); }
@@ -32,10 +31,7 @@ template <typename T> __host__ __device__ __forceinline__ T dot(V3T<T> a, V3T<T>
 template <typename T> __host__ __device__ __forceinline__ V3T<T> axpy(typename ident<T>::type s, V3T<T> x, V3T<T> y) { return v3t<T>(s * x.x + y.x, s * x.y + y.y, s * x.z + y.z); }
 // a compile-time vector (URDF constant) against a run-time one: the constant stays a scalar float operand
 __device__ __forceinline__ V3 cross_c(V3 a, V3 b) { return cross(a, b); }
-__device__ __forceinline__ V3P cross_c(V3 a, V3P b) { return v3t<P2>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
-__device__ __forceinline__ V3P cross_c(V3P a, V3 b) { return v3t<P2>(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 __device__ __forceinline__ float norm(V3 a) { return sqrtf(dot(a, a)); }
-__device__ __forceinline__ P2 norm(V3P a) { return vsqrt(dot(a, a)); }
 __host__ __device__ __forceinline__ double norm(D3 a) { return sqrt(dot(a, a)); }
 
 // child -> parent:  E = Rx(ROT*90deg) * Rz(q)
@@ -283,7 +279,7 @@ __device__ __forceinline__ void spd_inverse7(T* A) {
     T d = A[sym(j, j)];
 #pragma unroll
     for (int k = 0; k < j; k++) d -= A[sym(j, k)] * A[sym(j, k)];
-    T inv = vrsqrt(d);
+    T inv = rsqrtf(d);
     A[sym(j, j)] = inv;  // store 1 / L_jj
 #pragma unroll
     for (int i = j + 1; i < 7; i++) {
@@ -322,7 +318,7 @@ __device__ __forceinline__ void spd_inverse7(T* A) {
 // limits.  Bullet order: rows = [limits (dof order), motors (dof order)]; even iterations sweep backward, odd
 // forward; stop when max |residual| <= sqrt(1e-7).  Not inlined (its register working set is larger than the hot
 // loop's); inputs arrive through local memory and are re-loaded into registers, the sweeps are fully unrolled.
-__device__ __noinline__ void pgs_generic(const float* Mi_in, const float* q, const float* qd, const float* rhs_in, const float* dinv_in,
+static __device__ __noinline__ void pgs_generic(const float* Mi_in, const float* q, const float* qd, const float* rhs_in, const float* dinv_in,
                                          const float* max_imp_in, float* dv_out) {
   const float lo[7] = {pgm::Link<1>::lo, pgm::Link<2>::lo, pgm::Link<3>::lo, pgm::Link<4>::lo, pgm::Link<5>::lo, pgm::Link<6>::lo, pgm::Link<7>::lo};
   const float hi[7] = {pgm::Link<1>::hi, pgm::Link<2>::hi, pgm::Link<3>::hi, pgm::Link<4>::hi, pgm::Link<5>::hi, pgm::Link<6>::hi, pgm::Link<7>::hi};
@@ -493,133 +489,5 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
   if (SYNC && PG_SYNC_D) __syncthreads();
 }
 
-
-#ifdef PG_PAIR_KERNEL
-// ---------------------------------------------------------------------------------------------- two environments / thread
-// The same stepSimulation() for an environment PAIR held in packed registers (pg_packed.cuh).  Lane-wise the
-// arithmetic is the scalar substep's; what differs is control:
-//  * actA / actB: a collided (or padding) half keeps its state -- its lanes still compute (finite values, the state is
-//    a valid frozen one) and the results are dropped by per-half selects;
-//  * the residual early-out of a half snapshots its dv into shared memory (snap) and lets the lanes run on; the
-//    snapshot is restored after the loop, which is exactly "this environment stopped iterating at that sweep";
-//  * a half that needs joint-limit rows / unit impulse limits goes through the scalar cold path afterwards.
-// q, tgt: shared memory, element d at [d * stride] (P2 = float2 per thread); snap: 14 floats at [k * snap_stride].
-__device__ __forceinline__ float half_of(P2 x, int h) { return h ? x.v.y : x.v.x; }
-__device__ __forceinline__ P2 sel2(bool a, bool b, P2 yes, P2 no) { return P2(a ? yes.v.x : no.v.x, b ? yes.v.y : no.v.y); }
-
-template <bool SYNC>
-__device__ __forceinline__ void substep2(bool actA, bool actB, bool velocity, bool unit_imp, P2* q, P2* qd, P2* cq, P2* sq, const P2* tgt,
-                                         int stride, float* snap, int snap_stride) {
-  P2 tau[7], Mi[28];
-  P2 rhs[7], dinv[7], dv[7];
-  const bool any = actA || actB;
-  if (any) rnea_bias(cq, sq, qd, tau);
-  if (SYNC && PG_SYNC_A) __syncthreads();
-  if (any) crba(cq, sq, Mi);
-  if (SYNC && PG_SYNC_B) __syncthreads();
-  bool slowA = unit_imp, slowB = unit_imp;
-  if (any) {
-    spd_inverse7(Mi);
-#pragma unroll
-    for (int i = 0; i < 7; i++) {
-      P2 acc = -(Mi[sym(i, 0)] * tau[0]);
-#pragma unroll
-      for (int j = 1; j < 7; j++) acc -= Mi[sym(i, j)] * tau[j];
-      qd[i] = sel2(actA, actB, vclamp(acc * kDt + qd[i], -kMaxCoordVel, kMaxCoordVel), qd[i]);
-    }
-    const float lo[7] = {pgm::Link<1>::lo, pgm::Link<2>::lo, pgm::Link<3>::lo, pgm::Link<4>::lo, pgm::Link<5>::lo, pgm::Link<6>::lo, pgm::Link<7>::lo};
-    const float hi[7] = {pgm::Link<1>::hi, pgm::Link<2>::hi, pgm::Link<3>::hi, pgm::Link<4>::hi, pgm::Link<5>::hi, pgm::Link<6>::hi, pgm::Link<7>::hi};
-#pragma unroll
-    for (int d = 0; d < 7; d++) {
-      dinv[d] = vinv_guard(Mi[sym(d, d)]);
-      P2 t = tgt[d * stride];
-      P2 qv = q[d * stride];
-      P2 diff = velocity ? (t - qd[d]) : (50.0f * (t - qv) - qd[d]);
-      rhs[d] = diff * dinv[d];
-      dv[d] = 0.f;
-      slowA |= (qv.v.x <= lo[d]) || (qv.v.x >= hi[d]);
-      slowB |= (qv.v.y <= lo[d]) || (qv.v.y >= hi[d]);
-    }
-  }
-  if (SYNC && PG_SYNC_C) __syncthreads();
-  if (any) {
-    bool liveA = actA && !slowA, liveB = actB && !slowB;
-    bool earlyA = false, earlyB = false;
-    if (liveA || liveB) {
-      P2 app[7];
-#pragma unroll
-      for (int d = 0; d < 7; d++) app[d] = 0.f;
-#define PG_MOTOR_ROW2(d)                                                    \
-  {                                                                         \
-    P2 t = fma2(-dv[d], dinv[d], app[d] + rhs[d]);                          \
-    P2 cl = vclamp(t, -motor_imp(d), motor_imp(d));                         \
-    P2 delta = cl - app[d];                                                 \
-    app[d] = cl;                                                            \
-    _Pragma("unroll") for (int i = 0; i < 7; i++) dv[i] = fma2(Mi[sym(i, d)], delta, dv[i]); \
-    res = vmax(res, vabs((P2)(delta * Mi[sym(d, d)])));                     \
-  }
-#define PG_SWEEP_END2                                                       \
-  if (liveA && res.v.x <= kResAbs) { liveA = false; earlyA = true; _Pragma("unroll") for (int i = 0; i < 7; i++) snap[i * snap_stride] = dv[i].v.x; } \
-  if (liveB && res.v.y <= kResAbs) { liveB = false; earlyB = true; _Pragma("unroll") for (int i = 0; i < 7; i++) snap[(7 + i) * snap_stride] = dv[i].v.y; }
-      const float kResAbs = 3.1622777e-4f;  // sqrt(1e-7): compare |residual| instead of residual^2
-      for (int it = 0; it < kSolverIters; it += 2) {
-        if (liveA || liveB) {  // even iteration: backward sweep
-          P2 res = 0.f;
-          PG_MOTOR_ROW2(6) PG_MOTOR_ROW2(5) PG_MOTOR_ROW2(4) PG_MOTOR_ROW2(3) PG_MOTOR_ROW2(2) PG_MOTOR_ROW2(1) PG_MOTOR_ROW2(0)
-          PG_SWEEP_END2
-        }
-        if (liveA || liveB) {  // odd iteration: forward sweep
-          P2 res = 0.f;
-          PG_MOTOR_ROW2(0) PG_MOTOR_ROW2(1) PG_MOTOR_ROW2(2) PG_MOTOR_ROW2(3) PG_MOTOR_ROW2(4) PG_MOTOR_ROW2(5) PG_MOTOR_ROW2(6)
-          PG_SWEEP_END2
-        }
-        if (!__any_sync(__activemask(), liveA || liveB)) break;
-      }
-#undef PG_MOTOR_ROW2
-#undef PG_SWEEP_END2
-      if (earlyA) {
-#pragma unroll
-        for (int i = 0; i < 7; i++) dv[i].v.x = snap[i * snap_stride];
-      }
-      if (earlyB) {
-#pragma unroll
-        for (int i = 0; i < 7; i++) dv[i].v.y = snap[(7 + i) * snap_stride];
-      }
-    }
-    // cold path, one half at a time
-#pragma unroll 1
-    for (int h = 0; h < 2; h++) {
-      if (h == 0 ? (actA && slowA) : (actB && slowB)) {
-        float mi[7], ql[7], ms[28], qds[7], rs[7], ds[7], dvs[7];
-#pragma unroll
-        for (int k = 0; k < 28; k++) ms[k] = half_of(Mi[k], h);
-#pragma unroll
-        for (int d = 0; d < 7; d++) {
-          mi[d] = unit_imp ? 1.0f : motor_imp(d); ql[d] = half_of(q[d * stride], h);
-          qds[d] = half_of(qd[d], h); rs[d] = half_of(rhs[d], h); ds[d] = half_of(dinv[d], h);
-        }
-        pgs_generic(ms, ql, qds, rs, ds, mi, dvs);
-#pragma unroll
-        for (int d = 0; d < 7; d++) { if (h == 0) dv[d].v.x = dvs[d]; else dv[d].v.y = dvs[d]; }
-      }
-    }
-    // apply, clamp, integrate (inactive halves: velocity kept, dq = 0 keeps q and (cos, sin) bit-identical)
-    const P2 step_dt(actA ? kDt : 0.f, actB ? kDt : 0.f);
-#pragma unroll
-    for (int d = 0; d < 7; d++) {
-      qd[d] = sel2(actA, actB, vclamp(qd[d] + dv[d], -kMaxCoordVel, kMaxCoordVel), qd[d]);
-      P2 dq = qd[d] * step_dt;
-      q[d * stride] = q[d * stride] + dq;
-      P2 d2 = dq * dq;
-      P2 cd = fma2(d2, fma2(d2, 1.0f / 24.0f, -0.5f), 1.0f);
-      P2 sd = dq * fma2(d2, fma2(d2, 1.0f / 120.0f, -1.0f / 6.0f), 1.0f);
-      P2 c0 = cq[d], s0 = sq[d];
-      cq[d] = c0 * cd - s0 * sd;
-      sq[d] = s0 * cd + c0 * sd;
-    }
-  }
-  if (SYNC && PG_SYNC_D) __syncthreads();
-}
-#endif  // PG_PAIR_KERNEL
 
 }  // namespace pg

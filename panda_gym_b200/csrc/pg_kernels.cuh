@@ -5,7 +5,6 @@
 #include <stdint.h>
 #include "pg_scene.cuh"
 #include "pg_contact.cuh"
-#include "pg_neutral.h"
 
 namespace pg {
 
@@ -490,38 +489,6 @@ __device__ __forceinline__ void step_end(const Params& P, int e, const float* q,
   }
 }
 
-// One environment per thread (fallback / A-B reference for k_step2 below).
-__global__ void PG_STEP_BOUNDS k_step(const Params P, const float* __restrict__ actions) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  const int n = P.n;
-  const bool valid = e < n;  // every thread of the block stays for the barriers of the substep loop
-  __shared__ float s_tgt[7 * kStepBlock], s_q[7 * kStepBlock];  // touched twice per substep: kept out of the register file
-  float* tgt = s_tgt + threadIdx.x;
-  float* qs = s_q + threadIdx.x;
-  float q[7], qd[7], cq[7], sq[7];
-  bool velocity_mode = false, unit_imp = false;
-  if (valid) {
-    step_begin(P, actions, e, q, qd, tgt, kStepBlock, velocity_mode, unit_imp);
-#pragma unroll
-    for (int d = 0; d < 7; d++) { sincosf(q[d], &sq[d], &cq[d]); qs[d * kStepBlock] = q[d]; }
-  }
-  // --- sim.step(): n_substeps x stepSimulation, collision check after each (ReachAO); a collided environment
-  //     stops simulating (reach_ao.py:186-188) but its thread keeps meeting the block barriers
-  bool collided = false, active = valid;
-  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
-  for (int k = 0; k < P.n_substeps; k++) {
-    substep<kStepSync>(active, velocity_mode, unit_imp, qs, qd, cq, sq, tgt, kStepBlock);
-    if (P.task == 1) {
-      bool hit = scene_pass<false, kStepSync>(active, P.scene, P.obs_pos_f, n, e, base, cq, sq, nullptr, nullptr);
-      if (active && hit) { collided = true; active = false; }
-    }
-  }
-  if (!valid) return;
-#pragma unroll
-  for (int d = 0; d < 7; d++) q[d] = qs[d * kStepBlock];
-  step_end(P, e, q, qd, collided);
-}
-
 // Push / PickAndPlace (tasks 2, 3): the same step with the object world (pg_contact.cuh) in place of the arm-only
 // substep.  One environment per thread; rows and contacts live in local memory.
 __device__ __forceinline__ ObjState load_obj(const Params& P, int e) {
@@ -540,449 +507,7 @@ __device__ __forceinline__ void store_obj(const Params& P, int e, const ObjState
   P.obj[7 * n + e] = B.v.x; P.obj[8 * n + e] = B.v.y; P.obj[9 * n + e] = B.v.z;
   P.obj[10 * n + e] = B.w.x; P.obj[11 * n + e] = B.w.y; P.obj[12 * n + e] = B.w.z;
 }
-// Launch shape: BASELINE configs[3] runs 16 384 environments per GPU = 512 warps for 592 warp schedulers, so the kernel is
-// latency-bound whatever the block size; 32-thread blocks at least spread the warps over all 148 SMs (128-thread blocks
-// left 20 SMs idle) and give each warp a whole L1 for its solver rows.
-constexpr int kObjBlock = 32;
-__global__ void __launch_bounds__(kObjBlock) k_step_obj(const Params P, const float* __restrict__ actions) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= P.n) return;
-  float q[7], qd[7], cq[7], sq[7], tgt[7];
-  bool velocity_mode = false, unit_imp = false;
-  step_begin(P, actions, e, q, qd, tgt, 1, velocity_mode, unit_imp);
-#pragma unroll
-  for (int d = 0; d < 7; d++) sincosf(q[d], &sq[d], &cq[d]);
-  ObjState B = load_obj(P, e);
-  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
-  for (int k = 0; k < P.n_substeps; k++) world_substep(velocity_mode, unit_imp, base, P.world, q, qd, cq, sq, tgt, B);
-  store_obj(P, e, B);
-  step_end(P, e, q, qd, false);
-}
 
-#ifdef PG_PAIR_KERNEL
-// Two environments per thread: thread t of block b owns environments b*448 + t (half A) and b*448 + 224 + t (half B)
-// and runs the dynamics of both on the packed fp32 pipe (pg_packed.cuh, substep2).  The per-step prologue / epilogue
-// and the collision pass are the scalar code, run once per half.
-constexpr int kPairBlock = 224;                  // threads per block (7 warps, up to 255 registers each)
-constexpr int kPairEnvs = 2 * kPairBlock;        // environments per block
-constexpr int kPairSmemBytes = (5 * 7 * kPairBlock * 2 + 14 * kPairBlock) * 4;  // q, tgt, qd, cos, sin (P2) + snapshot
-__global__ void __launch_bounds__(kPairBlock, 1) k_step2(const Params P, const float* __restrict__ actions) {
-  extern __shared__ __align__(16) float s_dyn[];
-  const int n = P.n, t = threadIdx.x;
-  const int e0 = blockIdx.x * kPairEnvs + t;
-  P2* s_q = reinterpret_cast<P2*>(s_dyn) + t;     // element d at [d * kPairBlock]
-  P2* s_tgt = s_q + 7 * kPairBlock;
-  P2* s_qd = s_tgt + 7 * kPairBlock;
-  P2* s_c = s_qd + 7 * kPairBlock;
-  P2* s_s = s_c + 7 * kPairBlock;
-  float* snap = s_dyn + 5 * 7 * kPairBlock * 2 + t;  // element k at [k * kPairBlock]
-  bool velocity_mode = false, unit_imp = false;
-#pragma unroll 1
-  for (int h = 0; h < 2; h++) {
-    const int e = e0 + h * kPairBlock;
-    float q[7], qd[7], c[7], s[7];
-    float* tg = reinterpret_cast<float*>(s_tgt) + h;  // this half of element d at [d * 2 * kPairBlock]
-    if (e < n) {
-      step_begin(P, actions, e, q, qd, tg, 2 * kPairBlock, velocity_mode, unit_imp);
-#pragma unroll
-      for (int d = 0; d < 7; d++) sincosf(q[d], &s[d], &c[d]);
-    } else {
-#pragma unroll
-      for (int d = 0; d < 7; d++) { q[d] = 0.f; qd[d] = 0.f; c[d] = 1.f; s[d] = 0.f; tg[d * 2 * kPairBlock] = 0.f; }
-    }
-#pragma unroll
-    for (int d = 0; d < 7; d++) {
-      (reinterpret_cast<float*>(s_q) + h)[d * 2 * kPairBlock] = q[d];
-      (reinterpret_cast<float*>(s_qd) + h)[d * 2 * kPairBlock] = qd[d];
-      (reinterpret_cast<float*>(s_c) + h)[d * 2 * kPairBlock] = c[d];
-      (reinterpret_cast<float*>(s_s) + h)[d * 2 * kPairBlock] = s[d];
-    }
-  }
-  P2 qd[7], cq[7], sq[7];
-#pragma unroll
-  for (int d = 0; d < 7; d++) { qd[d] = s_qd[d * kPairBlock]; cq[d] = s_c[d * kPairBlock]; sq[d] = s_s[d * kPairBlock]; }
-  bool actA = e0 < n, actB = e0 + kPairBlock < n, collA = false, collB = false;
-  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
-  for (int k = 0; k < P.n_substeps; k++) {
-    substep2<kStepSync>(actA, actB, velocity_mode, unit_imp, s_q, qd, cq, sq, s_tgt, kPairBlock, snap, kPairBlock);
-    if (P.task == 1) {
-#pragma unroll 1
-      for (int h = 0; h < 2; h++) {
-        const bool act = h ? actB : actA;
-        float c[7], s[7];
-#pragma unroll
-        for (int d = 0; d < 7; d++) { c[d] = half_of(cq[d], h); s[d] = half_of(sq[d], h); }
-        bool hit = scene_pass<false, false>(act, P.scene, P.obs_pos_f, n, e0 + h * kPairBlock, base, c, s, nullptr, nullptr);
-        if (act && hit) { if (h) { collB = true; actB = false; } else { collA = true; actA = false; } }
-      }
-    }
-  }
-#pragma unroll
-  for (int d = 0; d < 7; d++) s_qd[d * kPairBlock] = qd[d];
-#pragma unroll 1
-  for (int h = 0; h < 2; h++) {
-    const int e = e0 + h * kPairBlock;
-    if (e >= n) continue;
-    float q[7], qv[7];
-#pragma unroll
-    for (int d = 0; d < 7; d++) { q[d] = (reinterpret_cast<float*>(s_q) + h)[d * 2 * kPairBlock]; qv[d] = (reinterpret_cast<float*>(s_qd) + h)[d * 2 * kPairBlock]; }
-    step_end(P, e, q, qv, h ? collB : collA);
-  }
-}
-#endif  // PG_PAIR_KERNEL
-
-// ------------------------------------------------------------------------------------------------ reset
-struct Body { int type; double px, py, pz, sx, sy, sz; };  // sphere (sx = r) or axis-aligned box (half extents)
-
-__device__ inline double box_margin_d(double sx, double sy, double sz) { double m = fmin(sx, fmin(sy, sz)); return fmin(0.04, 0.1 * m); }
-
-// min distance robot (all 36 primitives at the neutral pose, base offset) vs body: body-level getClosestPoints
-// cutoff: pairs whose analytic lower bound exceeds it are skipped (the caller only compares the result to it)
-// WARP: the 32 lanes of a warp work on the same environment and split the primitives (then min-reduce)
-// (c0, s0) = cos / sin of joint 1 relative to the neutral pose (set_random_robot_base): joint 1 turns about the base's
-// vertical axis and the base link's primitives are symmetric about it, so the turned robot against a SPHERE body equals
-// the neutral robot against the body turned back by the same angle
-template <bool WARP>
-__device__ __noinline__ double robot_body_distance(const Params& P, const Body& b, double cutoff, double c0 = 1.0, double s0 = 0.0) {
-  double best = 1e300;
-  const int k0 = WARP ? (threadIdx.x & 31) : 0, kstep = WARP ? 32 : 1;
-  const double ox = b.px - P.based[0], oy = b.py - P.based[1];
-  D3 o = v3t<double>(c0 * ox + s0 * oy, -s0 * ox + c0 * oy, b.pz - P.based[2]);
-  double m = b.type == 1 ? box_margin_d(b.sx, b.sy, b.sz) : 0.0;
-  D3 core = v3t<double>(b.sx - m, b.sy - m, b.sz - m);
-  for (int k = k0; k < pgm::kNumNeutralPrim; k += kstep) {
-    const pgm::NeutralPrim& np = pgm::kNeutralPrims[k];
-    D3 c = v3t<double>(np.c[0], np.c[1], np.c[2]);
-    double d;
-    if (b.type == 0) {
-      // sphere body: the caller only compares the result with `cutoff`, so a primitive whose bounding sphere (radius r for a
-      // sphere, r + h + hull margin >= the true bound for a cylinder) stays farther than that is skipped on SQUARED distances --
-      // no fp64 sqrt / divide on the common path (they were 35 % of this kernel's stall samples)
-      const double dx = c.x - o.x, dy = c.y - o.y, dz = c.z - o.z;
-      const double reach = cutoff + b.sx + np.r + (np.type == 0 ? 0.0 : np.h + (double)kHullMargin);
-      if (dx * dx + dy * dy + dz * dz > reach * reach) continue;
-    }
-    if (np.type == 0) d = b.type == 0 ? sphere_sphere<double>(c, np.r, o, b.sx).d : sphere_box<double>(c, np.r, o, core, m).d;
-    else {
-      D3 a = v3t<double>(np.a[0], np.a[1], np.a[2]);
-      if (b.type == 0) d = cyl_sphere<double>(c, a, np.r, np.h, o, b.sx).d;
-      else {
-        // analytic lower bound: cover the cylinder with ns spheres along its axis
-        int ns = np.h <= np.r ? 1 : (np.h <= 2 * np.r ? 2 : (np.h <= 3 * np.r ? 3 : 4));
-        double seg = np.h / ns, cover = sqrt(np.r * np.r + seg * seg) + (double)kHullMargin, lb = 1e300;
-        for (int i = 0; i < ns; i++) lb = fmin(lb, sphere_box<double>(c + (-np.h + (2 * i + 1) * seg) * a, cover, o, core, m).d);
-        if (lb > cutoff || lb >= best) continue;
-        d = cyl_box<double>(c, a, np.r, np.h, o, core, m).d;
-      }
-    }
-    best = fmin(best, d);
-  }
-  if (WARP) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
-  }
-  return best;
-}
-// check_collision(bodyA, bodyB, margin) for the sphere / box bodies of the scene (reach_ao.py:1169-1181)
-__device__ inline bool body_body_collision(const Body& a, const Body& b, double margin) {
-  if (a.type == 0 && b.type == 0) {
-    double dx = a.px - b.px, dy = a.py - b.py, dz = a.pz - b.pz;
-    return margin >= sqrt(dx * dx + dy * dy + dz * dz) - a.sx - b.sx;
-  }
-  if (a.type == 1 && b.type == 1)  // Bullet's SAT box-box detector reports nothing for separated boxes
-    return fabs(a.px - b.px) <= a.sx + b.sx && fabs(a.py - b.py) <= a.sy + b.sy && fabs(a.pz - b.pz) <= a.sz + b.sz;
-  const Body& s = a.type == 0 ? a : b;
-  const Body& x = a.type == 0 ? b : a;
-  double m = box_margin_d(x.sx, x.sy, x.sz);
-  double d = sphere_box<double>(v3t<double>(s.px, s.py, s.pz), s.sx, v3t<double>(x.px, x.py, x.pz), v3t<double>(x.sx - m, x.sy - m, x.sz - m), m).d;
-  return margin >= d;
-}
-
-__device__ inline void sample_hollow(Pcg& g, double rmin, double rmax, int upper, int front, int q34, double* out) {
-  const double PI = 3.141592653589793;
-  double phi = pcg_uniform(g, 0.0, 2 * PI);
-  double theta = upper ? pcg_uniform(g, 0.0, 0.5 * PI) : pcg_uniform(g, 0.0, PI);
-  if (front) phi = pcg_uniform(g, -0.5 * PI, 0.5 * PI);
-  if (q34) phi = pcg_uniform(g, -0.75 * PI, 0.75 * PI);
-  double r = cbrt(pcg_uniform(g, rmin * rmin * rmin, rmax * rmax * rmax));
-  out[0] = r * sin(theta) * cos(phi); out[1] = r * sin(theta) * sin(phi); out[2] = r * cos(theta);
-}
-__device__ inline void sample_goal(const StageDev& st, Pcg& g, double* out) {
-  if (st.goal_sampler == 0) for (int k = 0; k < 3; k++) out[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]);
-  else sample_hollow(g, st.goal_rmin, st.goal_rmax, st.goal_upper, st.goal_front, st.goal_34, out);
-}
-__device__ inline void sample_obstacle(const Params& P, Pcg& g, const double* goal, const double* ee, double* out) {
-  const StageDev& st = P.st;
-  double s[3], c[3];
-  if (st.obs_sampler == 0) { for (int k = 0; k < 3; k++) out[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]); return; }
-  double r = pcg_double(g);
-  if (st.obs_sampler == 1) {
-    if (r > 0.3) { sample_hollow(g, 0.1, 0.5, 0, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = goal[k]; }
-    else if (r > 0.1) { sample_hollow(g, 0.1, 0.4, 0, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = ee[k]; }
-    else { sample_hollow(g, 0.3, 0.6, 1, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = ee[3 + k]; }  // get_link_position(0) = COM of panda_link1
-  } else if (st.obs_sampler == 2) {
-    sample_hollow(g, 0.1, 0.5, 0, 0, 0, s);
-    for (int k = 0; k < 3; k++) c[k] = r > 0.5 ? goal[k] : ee[k];
-  } else {
-    if (r > 0.3) { sample_hollow(g, 0.2, 0.6, 0, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = goal[k]; }
-    else { sample_hollow(g, 0.2, 0.4, 0, 0, 0, s); for (int k = 0; k < 3; k++) c[k] = ee[k]; }
-  }
-  for (int k = 0; k < 3; k++) out[k] = s[k] + c[k];
-}
-
-__device__ inline Body obstacle_body(const Params& P, int j, int e) {
-  Body b; b.type = P.st.obs_type[j];
-  b.px = P.obs_pos[(size_t)(j * 3 + 0) * P.n + e]; b.py = P.obs_pos[(size_t)(j * 3 + 1) * P.n + e]; b.pz = P.obs_pos[(size_t)(j * 3 + 2) * P.n + e];
-  b.sx = P.st.obs_size[j][0]; b.sy = P.st.obs_size[j][1]; b.sz = P.st.obs_size[j][2];
-  return b;
-}
-
-// RobotTaskEnv.reset (core.py:298-308) = Panda.reset (panda.py:290-298) + Reach.reset (reach.py:63-78) /
-// ReachAO.reset (reach_ao.py:965-1033) with its rejection-sampling helpers (:1101-1181)
-//
-// WARP = false: one thread per environment (full / masked resets).  WARP = true: auto-reset of the few environments
-// k_step appended to the compact list, one WARP per environment: every lane runs the same (cheap, serial) sampling
-// code on the same PCG64 state, the 36-primitive robot distance query is split across the lanes.  Grid-stride
-// over the list.
-template <bool WARP>
-__global__ void __launch_bounds__(kBlock) k_reset(const __grid_constant__ Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
-                                                  uint64_t first_env) {
-  const int n = P.n;
-  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int count = WARP ? *P.reset_count : n;
-  const int stride = WARP ? (gridDim.x * blockDim.x) >> 5 : gridDim.x * blockDim.x;
-  const bool leader = WARP ? (threadIdx.x & 31) == 0 : true;
-  for (int item = WARP ? tid >> 5 : tid; item < count; item += stride) {
-  int e = item;
-  if (WARP) e = P.reset_list[item];
-  else if (mask && !mask[e]) continue;
-  P.need_reset[e] = 0;
-  uint32_t ep = P.episode[e];
-  P.episode[e] = ep + 1;
-  uint64_t seed = seeds ? seeds[e] : episode_seed(P.base_seed, first_env + (uint64_t)e, ep);
-  Pcg g; pcg_seed(g, seed);
-  const StageDev& st = P.st;
-  // Panda.reset (panda.py:290-298) -- or, with randomize_robot_pose, the scenario's randomizer in its place
-  // (reach_ao.py:132-133): set_random_robot_base draws joint 1 from its limits (panda.py:77-79) and keeps the rest neutral
-  const bool rbase = P.task == 1 && st.random_base;
-  double q0 = pgm::kNeutralQ[0], c0 = 1.0, s0 = 0.0;
-  if (rbase) { q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - pgm::kNeutralQ[0]); s0 = sin(q0 - pgm::kNeutralQ[0]); }
-  float q[7], qd[7], cq[7], sq[7];
-  P.steps[e] = 0; P.ep_ret[e] = 0.f; P.ep_len[e] = 0;
-  double goal[3], ee[6];  // ee[0..2] = get_ee_position(), ee[3..5] = get_link_position(0), both at the reset pose
-  int status = 0;
-#define PG_EE_AT_POSE()                                                                                   \
-  do {                                                                                                    \
-    ee[0] = c0 * pgm::kNeutralEE[0] - s0 * pgm::kNeutralEE[1] + P.based[0];                               \
-    ee[1] = s0 * pgm::kNeutralEE[0] + c0 * pgm::kNeutralEE[1] + P.based[1];                               \
-    ee[2] = pgm::kNeutralEE[2] + P.based[2];                                                              \
-    ee[3] = c0 * pgm::kNeutralLink0[0] - s0 * pgm::kNeutralLink0[1] + P.based[0];                         \
-    ee[4] = s0 * pgm::kNeutralLink0[0] + c0 * pgm::kNeutralLink0[1] + P.based[1];                         \
-    ee[5] = pgm::kNeutralLink0[2] + P.based[2];                                                           \
-  } while (0)
-  PG_EE_AT_POSE();
-  if (P.task == 0) {
-    for (int k = 0; k < 3; k++) goal[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]);
-  } else if (P.task >= 2) {
-    // Push.reset (push.py:69-87) / PickAndPlace.reset (pick_and_place.py:65-85): goal, then object; xy range 0.3;
-    // PickAndPlace lifts the goal by U(0, 0.2) and flattens it again with probability 0.3
-    const double half = P.obj_half_z;
-    double nx = pcg_uniform(g, -0.15, 0.15), ny = pcg_uniform(g, -0.15, 0.15), nz = pcg_uniform(g, 0.0, P.task == 3 ? 0.2 : 0.0);
-    if (P.task == 3 && pcg_double(g) < 0.3) nz = 0.0;
-    goal[0] = 0.0 + nx; goal[1] = 0.0 + ny; goal[2] = half + nz;
-    nx = pcg_uniform(g, -0.15, 0.15); ny = pcg_uniform(g, -0.15, 0.15); nz = pcg_uniform(g, 0.0, 0.0);
-    ObjState B;
-    B.x = v3((float)(0.0 + nx), (float)(0.0 + ny), (float)(half + nz));
-    B.qx = B.qy = B.qz = 0.f; B.qw = 1.f; B.v = v3(0, 0, 0); B.w = v3(0, 0, 0);  // set_base_pose: identity orientation, velocities zeroed
-    store_obj(P, e, B);
-    P.have_recent[e] = 0; P.have_prev[e] = 0;
-  } else {
-    P.goal_reached[e] = 0; P.collided[e] = 0;
-    Body table; table.type = 1; table.px = P.table_pos[0]; table.py = P.table_pos[1]; table.pz = P.table_pos[2];
-    table.sx = P.table_half[0]; table.sy = P.table_half[1]; table.sz = P.table_half[2];
-    Body probe; probe.type = 0; probe.sx = 0.05; probe.sy = probe.sz = 0;
-    // set_coll_free_goal: pass 0 = (["table","robot"], 0.1); pass 1 (only without obstacle randomisation) = all bodies, 0.03
-    const int passes = st.randomize_obstacles ? 1 : 2;
-    for (int pass = 0; pass < passes; pass++) {
-      const double margin = pass == 0 ? 0.1 : 0.03;
-      int i = 0;
-      for (;;) {
-        sample_goal(st, g, goal);
-        if (i > 9999) { for (int k = 0; k < 3; k++) goal[k] = ee[k]; status = 1; break; }
-        i++;
-        probe.px = goal[0]; probe.py = goal[1]; probe.pz = goal[2];
-        bool coll = false;
-        if (pass == 1) for (int j = 0; j < st.nobs; j++) coll |= body_body_collision(probe, obstacle_body(P, j, e), margin);
-        coll |= body_body_collision(probe, table, margin);
-        if (!coll) coll |= (margin >= robot_body_distance<WARP>(P, probe, margin, c0, s0));
-        if (!coll) break;
-      }
-    }
-    if (st.randomize_obstacles) {  // set_coll_free_obs(0.03)
-      const double margin = 0.03;
-      for (int j = 0; j < st.nobs && status < 2; j++) {
-        int i = 0;
-        for (;;) {
-          if (i > 9999) { status = 2; break; }
-          i++;
-          double pos[3];
-          sample_obstacle(P, g, goal, ee, pos);
-          for (int k = 0; k < 3; k++) P.obs_pos[(size_t)(j * 3 + k) * n + e] = pos[k];
-          Body ob = obstacle_body(P, j, e);
-          bool coll = body_body_collision(table, ob, margin);
-          coll |= body_body_collision(probe, ob, margin);
-          if (!st.allow_overlap) {
-            for (int k = 0; k < st.nobs; k++) if (k != j) coll |= body_body_collision(obstacle_body(P, k, e), ob, 0.0);
-            probe.px = probe.py = probe.pz = 0.0;  // the probe sphere is moved to the origin and left there
-            coll |= !body_body_collision(probe, ob, 1.0);
-          }
-          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance<WARP>(P, ob, margin + P.safety_distance, c0, s0));
-          if (!coll) break;
-        }
-      }
-    }
-    if (rbase) {  // set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the pose while the robot is within 0.05
-      for (int j = 0; j < st.nobs; j++) {
-        Body ob = obstacle_body(P, j, e);
-        int i = 0;
-        while (0.05 >= robot_body_distance<WARP>(P, ob, 0.05, c0, s0)) {
-          if (i > 9999) { status |= 4; break; }  // set_joint_neutral: neutral_joint_values[0] already holds the last draw
-          i++;
-          q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - pgm::kNeutralQ[0]); s0 = sin(q0 - pgm::kNeutralQ[0]);
-        }
-      }
-    }
-    if (st.random_num_obs) {  // set_random_num_obs (reach_ao.py:1062-1082)
-      int nb = st.nobs;
-      uint32_t span = (uint32_t)(st.size_hi - 1 - st.size_lo);
-      int k = st.size_lo + (span == 0 ? 0 : (int)pcg_lemire32(g, span));
-      int to_move = abs(k - nb), order[kMaxObst];
-      for (int i = 0; i < nb; i++) order[i] = i;
-      for (int i = nb - 1; i >= 1; i--) { int j = (int)pcg_interval32(g, (uint32_t)i); int t = order[i]; order[i] = order[j]; order[j] = t; }
-      for (int i = 0; i < nb && to_move > 0; i++, to_move--) {
-        P.obs_pos[(size_t)(order[i] * 3 + 0) * n + e] = 99.9; P.obs_pos[(size_t)(order[i] * 3 + 1) * n + e] = 99.9; P.obs_pos[(size_t)(order[i] * 3 + 2) * n + e] = -99.9;
-      }
-    }
-    P.have_recent[e] = 0; P.have_prev[e] = 0;
-    for (int k = 0; k < st.nobs * 3; k++) P.obs_pos_f[(size_t)k * n + e] = (float)P.obs_pos[(size_t)k * n + e];
-  }
-#undef PG_EE_AT_POSE
-#pragma unroll
-  for (int d = 0; d < 7; d++) {
-    q[d] = (float)(d == 0 ? q0 : pgm::kNeutralQ[d]); qd[d] = 0.f;
-    P.q[(size_t)d * n + e] = q[d]; P.qd[(size_t)d * n + e] = 0.f;
-    sincosf(q[d], &sq[d], &cq[d]);
-  }
-  for (int k = 0; k < 3; k++) P.goal[(size_t)k * n + e] = goal[k];
-  P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;
-  if (status && leader) atomicAdd(&P.stats[6], 1.0);
-  float ag[3], dg[3];
-  observe(P, e, q, qd, q, cq, sq, ag, true);
-  dg[0] = (float)goal[0]; dg[1] = (float)goal[1]; dg[2] = (float)goal[2];
-  bool succ = is_success(P, e, ag, dg);
-  if (!WARP) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
-  }
-}
-
-// refresh observation / goals at the current state (no stepping)
-__global__ void __launch_bounds__(kBlock) k_observe(const Params P) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= P.n) return;
-  float q[7], qd[7], cq[7], sq[7], ag[3];
-#pragma unroll
-  for (int d = 0; d < 7; d++) { q[d] = P.q[(size_t)d * P.n + e]; qd[d] = P.qd[(size_t)d * P.n + e]; sincosf(q[d], &sq[d], &cq[d]); }
-  observe(P, e, q, qd, q, cq, sq, ag, true);
-  if (P.task == 1) {
-    bool hit = scene_pass<false, false>(true, P.scene, P.obs_pos_f, P.n, e, v3(P.base[0], P.base[1], P.base[2]), cq, sq, nullptr, nullptr);
-    P.flags[e] = (uint8_t)((P.flags[e] & ~4) | (hit ? 4 : 0));
-  }
-}
-
-__global__ void k_mirror_obstacles(const Params P) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < (int64_t)kMaxObst * 3 * P.n) P.obs_pos_f[i] = (float)P.obs_pos[i];
-}
-
-__global__ void k_reward(const Params P, const float* __restrict__ ag, const float* __restrict__ dg, float* __restrict__ out, int64_t m, int src) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= m) return;
-  float a[3] = {ag[3 * i], ag[3 * i + 1], ag[3 * i + 2]}, g[3] = {dg[3 * i], dg[3 * i + 1], dg[3 * i + 2]};
-  out[i] = reward_fn(P, src, a, g);
-}
-
-__global__ void k_random_actions(float* __restrict__ out, int64_t m, uint64_t seed, uint64_t counter) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= m) return;
-  uint64_t h = splitmix64(seed ^ splitmix64(counter * 0x100000001B3ULL + (uint64_t)i));
-  out[i] = (float)((double)(h >> 11) * (2.0 / 9007199254740992.0) - 1.0);
-}
-
-// ------------------------------------------------------------------------------------------------ debug / parity kernels
-__global__ void PG_STEP_BOUNDS k_debug_substeps(int n, float* q_io, float* qd_io, const float* tgt_in, float f0, float f1, float f2,
-                                                           float f3, float f4, float f5, float f6, int nsub, int velocity) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool valid = e < n;
-  __shared__ float s_tgt[7 * kStepBlock], s_q[7 * kStepBlock];
-  float* t = s_tgt + threadIdx.x;
-  float* q = s_q + threadIdx.x;  // element d at q[d * kStepBlock]
-  float qd[7], c[7], s[7];
-  if (valid) {
-#pragma unroll
-    for (int d = 0; d < 7; d++) { q[d * kStepBlock] = q_io[(size_t)d * n + e]; qd[d] = qd_io[(size_t)d * n + e]; t[d * kStepBlock] = tgt_in[(size_t)d * n + e]; sincosf(q[d * kStepBlock], &s[d], &c[d]); }
-  }
-  for (int k = 0; k < nsub; k++) {
-    // parity kernel: re-evaluate cos/sin exactly every 20 substeps like the env step does
-    if (valid && k > 0 && (k % 20) == 0) {
-#pragma unroll
-      for (int d = 0; d < 7; d++) sincosf(q[d * kStepBlock], &s[d], &c[d]);
-    }
-    substep<kStepSync>(valid, velocity != 0, false, q, qd, c, s, t, kStepBlock);
-  }
-  if (!valid) return;
-#pragma unroll
-  for (int d = 0; d < 7; d++) { q_io[(size_t)d * n + e] = q[d * kStepBlock]; qd_io[(size_t)d * n + e] = qd[d]; }
-}
-#ifdef PG_PAIR_KERNEL
-__global__ void __launch_bounds__(kPairBlock, 1) k_debug_substeps2(int n, float* q_io, float* qd_io, const float* tgt_in, int nsub, int velocity) {
-  extern __shared__ __align__(16) float s_dyn[];
-  const int t = threadIdx.x, e0 = blockIdx.x * kPairEnvs + t, e1 = e0 + kPairBlock;
-  P2* q = reinterpret_cast<P2*>(s_dyn) + t;
-  P2* tg = q + 7 * kPairBlock;
-  float* snap = s_dyn + 5 * 7 * kPairBlock * 2 + t;
-  const bool vA = e0 < n, vB = e1 < n;
-  P2 qd[7], c[7], s[7];
-#pragma unroll
-  for (int d = 0; d < 7; d++) {
-    q[d * kPairBlock] = P2(vA ? q_io[(size_t)d * n + e0] : 0.f, vB ? q_io[(size_t)d * n + e1] : 0.f);
-    qd[d] = P2(vA ? qd_io[(size_t)d * n + e0] : 0.f, vB ? qd_io[(size_t)d * n + e1] : 0.f);
-    tg[d * kPairBlock] = P2(vA ? tgt_in[(size_t)d * n + e0] : 0.f, vB ? tgt_in[(size_t)d * n + e1] : 0.f);
-  }
-  for (int k = 0; k < nsub; k++) {
-    if ((k % 20) == 0) {
-#pragma unroll
-      for (int d = 0; d < 7; d++) { P2 v = q[d * kPairBlock]; sincosf(v.v.x, &s[d].v.x, &c[d].v.x); sincosf(v.v.y, &s[d].v.y, &c[d].v.y); }
-    }
-    substep2<kStepSync>(vA, vB, velocity != 0, false, q, qd, c, s, tg, kPairBlock, snap, kPairBlock);
-  }
-#pragma unroll
-  for (int d = 0; d < 7; d++) {
-    P2 v = q[d * kPairBlock];
-    if (vA) { q_io[(size_t)d * n + e0] = v.v.x; qd_io[(size_t)d * n + e0] = qd[d].v.x; }
-    if (vB) { q_io[(size_t)d * n + e1] = v.v.y; qd_io[(size_t)d * n + e1] = qd[d].v.y; }
-  }
-}
-#endif
-__global__ void k_debug_minv(int n, const float* q_in, float* out) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n) return;
-  float c[7], s[7], M[28];
-#pragma unroll
-  for (int d = 0; d < 7; d++) sincosf(q_in[(size_t)d * n + e], &s[d], &c[d]);
-  crba(c, s, M);
-  spd_inverse7(M);
-#pragma unroll
-  for (int k = 0; k < 28; k++) out[(size_t)k * n + e] = M[k];
-}
 // Yoshikawa index at the flange for joint cosines / sines (see k_manipulability)
 __device__ __forceinline__ float manipulability_cs(const float* c, const float* s) {
   ArmKin K;
@@ -1001,95 +526,6 @@ __device__ __forceinline__ float manipulability_cs(const float* c, const float* 
       for (int k = j + 1; k < 7; k++) { float m = dot(cij, J[k]); det = fmaf(m, m, det); }
     }
   return det > 0.f ? sqrtf(det) : 0.f;
-}
-
-// The per-step bookkeeping of evaluation/evaluate.py:perform_benchmark (:236-262) and its episode-end accounting
-// (:264-283), for every environment, on the state k_step left behind and BEFORE the auto-reset overwrites it:
-//   per step     total_effort += ||current_joint_acceleration||   (reach_ao.py:1299-1302)
-//                jerk.append(||current_joint_jerk||)              (:1304-1305)
-//                total_manipulability += task.manipulability      (:1311, :1381 -> panda.py:314-317 at the new q)
-//                ee_speed.append(||get_ee_velocity()||)           (observation[3:6])
-//   episode end  is_success -> success bucket (length, effort / length, manipulability / length, all jerk and speed
-//                samples); else is_truncated -> collision; else timeout; reward and length always
-__global__ void __launch_bounds__(128) k_eval_metrics(const Params P) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x, n = P.n;
-  if (e >= n) return;
-  float c[7], s[7], a2 = 0.f, j2 = 0.f;
-#pragma unroll
-  for (int d = 0; d < 7; d++) {
-    sincosf(P.q[(size_t)d * n + e], &s[d], &c[d]);
-    float a = P.cur_acc[(size_t)d * n + e], j = P.jerk[(size_t)d * n + e];
-    a2 = fmaf(a, a, a2); j2 = fmaf(j, j, j2);
-  }
-  const float* o = P.obs + (size_t)e * P.obs_dim;
-  const float speed = sqrtf(o[3] * o[3] + o[4] * o[4] + o[5] * o[5]);
-  float effort = P.ev_acc[e] + sqrtf(a2), manip = P.ev_acc[(size_t)n + e] + manipulability_cs(c, s);
-  float jerk = P.ev_acc[(size_t)2 * n + e] + sqrtf(j2), sp = P.ev_acc[(size_t)3 * n + e] + speed;
-  int len = P.ev_len[e] + 1;
-  float ret = P.ev_ret[e] + P.reward[e];
-  if (P.done[e]) {
-    const uint8_t f = P.flags[e];
-    atomicAdd(&P.ev[6], 1.0); atomicAdd(&P.ev[7], (double)len); atomicAdd(&P.ev[9], (double)ret);
-    if (f & 1) {
-      atomicAdd(&P.ev[0], 1.0); atomicAdd(&P.ev[1], (double)len);
-      atomicAdd(&P.ev[2], (double)effort / len); atomicAdd(&P.ev[3], (double)manip / len);
-      atomicAdd(&P.ev[4], (double)jerk); atomicAdd(&P.ev[5], (double)sp);
-    } else if (f & 4) atomicAdd(&P.ev[8], 1.0);
-    else atomicAdd(&P.ev[10], 1.0);
-    effort = manip = jerk = sp = ret = 0.f; len = 0;
-  }
-  P.ev_acc[e] = effort; P.ev_acc[(size_t)n + e] = manip; P.ev_acc[(size_t)2 * n + e] = jerk; P.ev_acc[(size_t)3 * n + e] = sp;
-  P.ev_len[e] = len; P.ev_ret[e] = ret;
-}
-
-// Panda.get_manipulability (panda.py:314-317): roboticstoolbox Panda().manipulability(q, axes="trans") = Yoshikawa index
-// sqrt(det(Jv Jv^T)) of the 3 x 7 translational Jacobian at the toolbox model's end-effector link panda_link8 (flange =
-// link7 frame + (0, 0, 0.107)).  compute_reward refreshes it every step (reach_ao.py:1311, :1381); it feeds no reward.
-// q f32 [7][n] -> out f32 [n].  Same formula as oracle pgo_arm_manipulability.
-__global__ void k_manipulability(int n, const float* __restrict__ q_in, float* __restrict__ out) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n) return;
-  float c[7], s[7];
-#pragma unroll
-  for (int d = 0; d < 7; d++) sincosf(q_in[(size_t)d * n + e], &s[d], &c[d]);
-  ArmKin K;
-  arm_kin(v3(0.f, 0.f, 0.f), c, s, K);
-  const V3 p = frame_point(K.F7, 0.f, 0.f, 0.107f);
-  // det(Jv Jv^T) by Cauchy-Binet = sum over the 35 column triples of det(J_S)^2: no cancellation between the terms, so the
-  // index keeps its relative accuracy in fp32 near singular poses (the 3 x 3 Gram determinant does not)
-  V3 J[7];
-#pragma unroll
-  for (int d = 0; d < 7; d++) J[d] = cross(K.ax[d], p - K.org[d]);
-  float det = 0.f;
-#pragma unroll
-  for (int i = 0; i < 5; i++)
-#pragma unroll
-    for (int j = i + 1; j < 6; j++) {
-      V3 cij = cross(J[i], J[j]);
-#pragma unroll
-      for (int k = j + 1; k < 7; k++) { float m = dot(cij, J[k]); det = fmaf(m, m, det); }
-    }
-  out[e] = det > 0.f ? sqrtf(det) : 0.f;
-}
-__global__ void k_debug_ik(int n, const float* q_in, const float* tgt, float bx, float by, float bz, float* out) {
-  int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n) return;
-  float q[7], o[7];
-#pragma unroll
-  for (int d = 0; d < 7; d++) q[d] = q_in[(size_t)d * n + e];
-  ik_dls(v3(bx, by, bz), q, v3(tgt[e], tgt[(size_t)n + e], tgt[(size_t)2 * n + e]), o);
-#pragma unroll
-  for (int d = 0; d < 7; d++) out[(size_t)d * n + e] = o[d];
-}
-
-__global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a, float b) {
-  float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
-  for (int i = 0; i < iters; i++) {
-    x0 = fmaf(x0, a, b); x1 = fmaf(x1, a, b); x2 = fmaf(x2, a, b); x3 = fmaf(x3, a, b);
-    x4 = fmaf(x4, a, b); x5 = fmaf(x5, a, b); x6 = fmaf(x6, a, b); x7 = fmaf(x7, a, b);
-  }
-  float s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
-  if (s == 123.456f) out[0] = s;
 }
 
 }  // namespace pg
