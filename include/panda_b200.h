@@ -91,7 +91,9 @@ int pg_stage_from_scenario(pg_stage* stage, const char* scenario);
 
 int pg_create(const pg_config* cfg, int device, pg_handle* out);
 int pg_destroy(pg_handle h);                                   /* RobotTaskEnv.close (core.py:370-371) */
-int pg_set_stage(pg_handle h, const pg_stage* stage);          /* setup_training.py:233-252 */
+/* Curriculum stage switch (setup_training.py:233-252 rebuilds the SubprocVecEnv for the next stage): swaps the scenario
+ * block AND resets every environment on `stream` -- all episodes start fresh in the new scene, like the rebuilt VecEnv. */
+int pg_set_stage(pg_handle h, const pg_stage* stage, void* stream);
 /* VecEnv.seed(seed): environment i draws its first reset from numpy-compatible PCG64(seed + first_env_index + i) */
 int pg_seed(pg_handle h, uint64_t base_seed, uint64_t first_env_index);
 
@@ -115,6 +117,13 @@ typedef struct {
 } pg_host_out;
 int pg_step_host(pg_handle h, const float* actions_host, const pg_host_out* out, void* stream);
 int pg_reset_host(pg_handle h, const pg_host_out* out, void* stream);
+/* current results -> host buffers without stepping (synchronises the stream) */
+int pg_copy_out(pg_handle h, const pg_host_out* out, void* stream);
+/* The six results live in one device slab.  A caller that carves its six host buffers out of ONE (page-locked) block at
+ * these byte offsets -- offsets6[] in pg_host_out field order: observation, achieved_goal, desired_goal, reward, done,
+ * flags -- gets them with a single device-to-host copy of total_bytes per step instead of six.  The observation offset
+ * and total_bytes depend on the current observation width (re-query after pg_set_stage changes it). */
+int pg_host_layout(pg_handle h, int64_t* offsets6, int64_t* total_bytes);
 
 /* Task.compute_reward(achieved_goal, desired_goal, info) vectorised over n rows (core.py:282; the HER relabel
  * entry).  Like the reference (reach_ao.py:1319,1336,1377) collision / jerk / effort terms read the LIVE state
@@ -221,6 +230,8 @@ typedef struct {
   float *next_observation, *next_achieved_goal, *next_desired_goal;
   float *action, *reward, *done;                                     /* [batch][act_dim], [batch], [batch] */
   int64_t batch, n_virtual;
+  int64_t row_stride;  /* floats between consecutive rows of EVERY field: the batch is one [batch][row_stride] block (64 B
+                          multiples) and the fields are column ranges of it -- what sharding.allgather_samples exchanges */
 } pg_her_batch;  /* device pointers owned by the buffer, valid until the next pg_her_sample */
 int pg_her_create(int device, int64_t buffer_size, int n_envs, int obs_dim, int act_dim, int n_sampled_goal, int64_t max_batch, pg_her_handle* out);
 int pg_her_destroy(pg_her_handle h);

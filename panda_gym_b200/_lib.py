@@ -50,7 +50,7 @@ class HostOut(ctypes.Structure):
 
 class HerBatch(ctypes.Structure):
     _fields_ = [(k, c_void_p) for k in ("observation", "achieved_goal", "desired_goal", "next_observation", "next_achieved_goal",
-                                        "next_desired_goal", "action", "reward", "done")] + [("batch", c_i64), ("n_virtual", c_i64)]
+                                        "next_desired_goal", "action", "reward", "done")] + [("batch", c_i64), ("n_virtual", c_i64), ("row_stride", c_i64)]
 
 
 VIEW_IDS = {name: i for i, name in enumerate([
@@ -64,12 +64,14 @@ SYMBOLS = [
     ("pg_stage_from_scenario", c_int, [P, ctypes.c_char_p]),
     ("pg_create", c_int, [P, c_int, P]),
     ("pg_destroy", c_int, [P]),
-    ("pg_set_stage", c_int, [P, P]),
+    ("pg_set_stage", c_int, [P, P, P]),
     ("pg_seed", c_int, [P, c_u64, c_u64]),
     ("pg_reset", c_int, [P, P, P, P]),
     ("pg_step", c_int, [P, P, P]),
     ("pg_step_host", c_int, [P, P, P, P]),
     ("pg_reset_host", c_int, [P, P, P]),
+    ("pg_copy_out", c_int, [P, P, P]),
+    ("pg_host_layout", c_int, [P, P, P]),
     ("pg_compute_reward", c_int, [P, P, P, P, c_i64, c_int, P]),
     ("pg_random_actions", c_int, [P, c_u64, c_u64, P, P]),
     ("pg_save_state", c_int, [P, P, P]),

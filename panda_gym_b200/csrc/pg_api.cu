@@ -41,6 +41,8 @@ struct pg_env_s {
   float* d_actions;                 // staging for the host-buffer step
   int eval_metrics;                 // pg_set_eval_metrics: launch k_eval_metrics after every step
   int sm_count;                     // cudaDevAttrMultiProcessorCount (grid of the auto-reset kernel)
+  uint8_t* out_slab;                // per-step results, one allocation (see pg_create)
+  size_t slab_obs_off;
 };
 
 namespace {
@@ -240,8 +242,17 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   A(P.d_link, 9 * n, true) A(P.past_vec, 54 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
   A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
   A(P.rng, 4 * n, true) A(P.episode, n, true) A(P.obj, 13 * n, true)
-  A(P.obs, (size_t)max_obs * n, true) A(P.achieved, 3 * n, true) A(P.desired, 3 * n, true) A(P.reward, n, true)
-  A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true) A(P.done, n, true) A(P.flags, n, true)
+  {  // the six per-step results live in ONE slab so that the host-buffer step moves them with a single device-to-host copy:
+     // [achieved 3n f32 | desired 3n f32 | reward n f32 | done n u8 | flags n u8 | pad to 256 B | observation n x obs_dim f32]
+     // (the observation comes last: its width depends on the stage, the copy stops after n x obs_dim)
+    h->slab_obs_off = ((size_t)30 * n + 255) / 256 * 256;
+    const size_t bytes = h->slab_obs_off + (size_t)max_obs * n * sizeof(float);
+    A(h->out_slab, bytes, true)
+    P.achieved = (float*)h->out_slab; P.desired = P.achieved + 3 * (size_t)n; P.reward = P.desired + 3 * (size_t)n;
+    P.done = h->out_slab + (size_t)28 * n; P.flags = h->out_slab + (size_t)29 * n;
+    P.obs = (float*)(h->out_slab + h->slab_obs_off);
+  }
+  A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true)
   A(P.stats, 8, false) A(P.reset_list, n, false) A(P.reset_count, 1, false)
   A(P.ev_acc, 4 * n, true) A(P.ev_len, n, true) A(P.ev_ret, n, true) A(P.ev, 12, false)
   A(h->d_actions, 8 * n, false)
@@ -269,13 +280,16 @@ int pg_destroy(pg_handle h) {
   return PG_OK;
 }
 
-int pg_set_stage(pg_handle h, const pg_stage* s) {
+int pg_set_stage(pg_handle h, const pg_stage* s, void* stream) {
   if (!h || !s) return fail(PG_ERR_ARG, "NULL argument");
   if (s->n_obstacles < 0 || s->n_obstacles > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "n_obstacles out of range");
   if (int rc = check_pose_randomizer(&h->cfg, s)) return rc;
   h->cfg.stage = *s;
   fill_stage(h, s);
-  return PG_OK;
+  // The reference rebuilds the whole VecEnv for a new stage (setup_training.py:233-252), so every environment starts a
+  // fresh episode in the new scene.  Same here: running episodes would otherwise meet newly enabled obstacle slots at
+  // stale positions, goals of the old sampler and (when the observation width changes) a cached EE at the old stride.
+  return pg_reset(h, nullptr, nullptr, stream);
 }
 
 int pg_seed(pg_handle h, uint64_t base_seed, uint64_t first_env_index) {
@@ -317,6 +331,14 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
 static int copy_out(pg_handle h, const pg_host_out* o, cudaStream_t s) {
   const pg::Params& P = h->P;
   const size_t n = P.n;
+  // host buffers laid out like the device slab (pg_host_layout): ONE copy instead of six
+  uint8_t* base = (uint8_t*)o->achieved_goal;
+  if (base && (uint8_t*)o->desired_goal == base + 12 * n && (uint8_t*)o->reward == base + 24 * n && o->done == base + 28 * n &&
+      o->flags == base + 29 * n && (uint8_t*)o->observation == base + h->slab_obs_off) {
+    PG_CUDA(cudaMemcpyAsync(base, h->out_slab, h->slab_obs_off + n * P.obs_dim * sizeof(float), cudaMemcpyDeviceToHost, s));
+    PG_CUDA(cudaStreamSynchronize(s));
+    return PG_OK;
+  }
   if (o->observation) PG_CUDA(cudaMemcpyAsync(o->observation, P.obs, n * P.obs_dim * sizeof(float), cudaMemcpyDeviceToHost, s));
   if (o->achieved_goal) PG_CUDA(cudaMemcpyAsync(o->achieved_goal, P.achieved, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
   if (o->desired_goal) PG_CUDA(cudaMemcpyAsync(o->desired_goal, P.desired, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
@@ -325,6 +347,20 @@ static int copy_out(pg_handle h, const pg_host_out* o, cudaStream_t s) {
   if (o->flags) PG_CUDA(cudaMemcpyAsync(o->flags, P.flags, n, cudaMemcpyDeviceToHost, s));
   PG_CUDA(cudaStreamSynchronize(s));
   return PG_OK;
+}
+
+int pg_host_layout(pg_handle h, int64_t* offsets6, int64_t* total_bytes) {
+  if (!h || !offsets6 || !total_bytes) return fail(PG_ERR_ARG, "NULL argument");
+  const int64_t n = h->P.n;
+  offsets6[0] = (int64_t)h->slab_obs_off; offsets6[1] = 0; offsets6[2] = 12 * n; offsets6[3] = 24 * n; offsets6[4] = 28 * n; offsets6[5] = 29 * n;
+  *total_bytes = (int64_t)h->slab_obs_off + n * h->P.obs_dim * (int64_t)sizeof(float);
+  return PG_OK;
+}
+
+int pg_copy_out(pg_handle h, const pg_host_out* out, void* stream) {
+  if (!h || !out) return fail(PG_ERR_ARG, "NULL argument");
+  PG_CUDA(cudaSetDevice(h->device));
+  return copy_out(h, out, (cudaStream_t)stream);
 }
 
 int pg_step_host(pg_handle h, const float* actions_host, const pg_host_out* out, void* stream) {
@@ -571,6 +607,8 @@ struct pg_her_s {
   pg::HerBatch out;      // library-owned output batch (max_batch rows)
   int64_t launches;
   uint64_t fast_counter;
+  int sm_count;
+  double her_ratio;      // SB3 her_ratio in double: nb_virtual = int(her_ratio * batch_size) must round like Python does
   bool valid_stale;      // the compacted valid-index list must be rebuilt (something was added since the last sample)
 };
 
@@ -581,13 +619,17 @@ int pg_her_create(int device, int64_t buffer_size, int n_envs, int obs_dim, int 
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) return fail(PG_ERR_CUDA, "no CUDA device: this library has no CPU fallback");
   PG_CUDA(cudaSetDevice(device));
+  int her_sms = 148;
+  PG_CUDA(cudaDeviceGetAttribute(&her_sms, cudaDevAttrMultiProcessorCount, device));
+  if ((pg::her_used(obs_dim, act_dim) + 15) / 16 * 16 > 256) return fail(PG_ERR_ARG, "record wider than 256 floats (obs_dim too large)");
   pg_her_s* h = new pg_her_s();
+  h->sm_count = her_sms;
   h->device = device; h->launches = 0; h->fast_counter = 0; h->max_batch = max_batch; h->valid_stale = true;
   pg::HerParams& H = h->H;
   memset(&H, 0, sizeof H);
   H.rows = (int)(buffer_size / n_envs > 0 ? buffer_size / n_envs : 1);  // SB3: buffer_size // n_envs
   H.n_envs = n_envs; H.obs_dim = obs_dim; H.act_dim = act_dim;
-  H.her_ratio = 1.0f - 1.0f / (float)(n_sampled_goal + 1);
+  h->her_ratio = 1.0 - (1.0 / (double)(n_sampled_goal + 1));  // SB3: 1 - (1.0 / (n_sampled_goal + 1)), a Python float
   h->capacity = (int64_t)H.rows * n_envs;
   const size_t cap = (size_t)h->capacity;
   auto A = [&](void** p, size_t bytes) -> int {
@@ -598,9 +640,8 @@ int pg_her_create(int device, int64_t buffer_size, int n_envs, int obs_dim, int 
   HA(H.cur_ep_start, n_envs, int) HA(H.cursor, 2, int) HA(H.valid, cap, int) HA(H.n_valid, 1, int)
   HA(H.block_counts, (cap + pg::kHerBlock - 1) / pg::kHerBlock + 1, int) HA(H.mt, 625, uint32_t)
   HA(H.s_row, max_batch, int) HA(H.s_env, max_batch, int) HA(H.s_t, max_batch, int) HA(H.status, 1, int)
-  HA(h->out.obs, max_batch * obs_dim, float) HA(h->out.next_obs, max_batch * obs_dim, float) HA(h->out.ag, max_batch * 3, float)
-  HA(h->out.dg, max_batch * 3, float) HA(h->out.next_ag, max_batch * 3, float) HA(h->out.next_dg, max_batch * 3, float)
-  HA(h->out.action, max_batch * act_dim, float) HA(h->out.reward, max_batch, float) HA(h->out.done, max_batch, float)
+  HA(H.s_trow, max_batch, int)
+  HA(h->out.packed, (size_t)max_batch * H.rec_w, float)
 #undef HA
   // default stream state = np.random.seed(0)-like is NOT assumed: callers load a state with pg_her_set_mt_state
   *out = h;
@@ -652,7 +693,7 @@ int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, 
   cudaStream_t s = (cudaStream_t)stream;
   const pg::HerParams& H = h->H;
   const int total = (int)h->capacity;
-  const int B = (int)batch, nbv = (int)(H.her_ratio * (float)B);  // int(her_ratio * batch_size)
+  const int B = (int)batch, nbv = (int)(h->her_ratio * (double)B);  // int(her_ratio * batch_size), double like SB3
   if (h->valid_stale) {  // valid = flatnonzero(ep_length > 0): unchanged until the next add(), so several gradient steps per
                          // environment step (SB3 gradient_steps > 1) pay the 1 M-entry compaction once
     pg::launch_her_compact(H, total, s);
@@ -660,13 +701,17 @@ int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, 
     h->valid_stale = false;
   }
   pg::launch_her_indices(H, B, nbv, exact_rng != 0, fast_seed, h->fast_counter++, s);
-  pg::launch_her_gather(H, env->P, h->out, B, nbv, reward_env, s);
+  pg::launch_her_gather(H, env->P, h->out, B, nbv, reward_env, h->sm_count, s);
   h->launches += 2;
   PG_CUDA(cudaGetLastError());
-  out->observation = h->out.obs; out->achieved_goal = h->out.ag; out->desired_goal = h->out.dg;
-  out->next_observation = h->out.next_obs; out->next_achieved_goal = h->out.next_ag; out->next_desired_goal = h->out.next_dg;
-  out->action = h->out.action; out->reward = h->out.reward; out->done = h->out.done;
-  out->batch = batch; out->n_virtual = nbv;
+  // the batch is ONE [batch][row_stride] block in the record's field order; the nine fields are column ranges of it
+  float* pk = h->out.packed;
+  const int od = H.obs_dim;
+  out->observation = pk; out->next_observation = pk + od;
+  out->achieved_goal = pk + 2 * od; out->desired_goal = pk + 2 * od + 3;
+  out->next_achieved_goal = pk + 2 * od + 6; out->next_desired_goal = pk + 2 * od + 9;
+  out->action = pk + 2 * od + 12; out->reward = pk + 2 * od + 12 + H.act_dim; out->done = out->reward + 1;
+  out->batch = batch; out->n_virtual = nbv; out->row_stride = H.rec_w;
   return PG_OK;
 }
 

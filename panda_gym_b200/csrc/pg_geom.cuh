@@ -114,6 +114,74 @@ template <typename T> __host__ __device__ __forceinline__ ClosestT<T> cyl_sphere
   ClosestT<T> k; k.d = d - T(kHullMargin) - R; k.dir = n; return k;
 }
 
+// ------------------------------------------------------------------------------------ segment vs axis-aligned box, exact
+// Closest points between the segment c + t a (|t| <= h, a unit) and the box |x_k| <= e_k centred at the origin.
+// f(t) = dist^2(c + t a, box) is convex, C1 and piecewise quadratic, so g = f'/2 = a . (p - clamp(p)) is monotone and
+// piecewise LINEAR with breakpoints where a coordinate of p(t) crosses +-e_k.  Shrink a bracket [tl, tr] (g(tl) <= 0 < g(tr))
+// over the six breakpoints; no breakpoint is left inside it, so the root is one linear interpolation away.  No iteration,
+// no tolerance: this is what lets the collision pass decide cylinder-box pairs without GJK (see cyl_box_bound).
+template <typename T> struct SegBoxT { T s, t; V3T<T> pa, pb; };  // distance, parameter, point on the segment, point on the box
+template <typename T> __host__ __device__ __forceinline__ V3T<T> box_clamp(V3T<T> p, V3T<T> e) {
+  return v3t<T>(tmin<T>(tmax<T>(p.x, -e.x), e.x), tmin<T>(tmax<T>(p.y, -e.y), e.y), tmin<T>(tmax<T>(p.z, -e.z), e.z));
+}
+template <typename T> __host__ __device__ __forceinline__ T segbox_slope(V3T<T> c, V3T<T> a, V3T<T> e, T t) {
+  V3T<T> p = c + t * a;
+  return dot(a, p - box_clamp(p, e));
+}
+template <typename T> __host__ __device__ __forceinline__ SegBoxT<T> seg_box(V3T<T> c, V3T<T> a, T h, V3T<T> e) {
+  T tl = -h, tr = h, gl = segbox_slope(c, a, e, tl), gr = segbox_slope(c, a, e, tr), t;
+  if (gl >= T(0)) t = tl;
+  else if (gr <= T(0)) t = tr;
+  else {
+    const T ck[3] = {c.x, c.y, c.z}, ak[3] = {a.x, a.y, a.z}, ek[3] = {e.x, e.y, e.z};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      if (tabs<T>(ak[k]) > T(1e-12)) {
+        const T inv = T(1) / ak[k];
+#pragma unroll
+        for (int sg = 0; sg < 2; sg++) {
+          const T tb = ((sg ? ek[k] : -ek[k]) - ck[k]) * inv;
+          if (tb > tl && tb < tr) {
+            const T gb = segbox_slope(c, a, e, tb);
+            if (gb <= T(0)) { tl = tb; gl = gb; } else { tr = tb; gr = gb; }
+          }
+        }
+      }
+    }
+    const T den = gr - gl;
+    t = den > T(0) ? tl - gl * (tr - tl) / den : tl;
+  }
+  SegBoxT<T> r;
+  r.t = t; r.pa = c + t * a; r.pb = box_clamp(r.pa, e);
+  r.s = tnorm(r.pa - r.pb);
+  return r;
+}
+
+// Solid cylinder (centre c relative to the box centre, unit axis a, radius r, half length h) vs box core e: what can be said
+// without iterating.  Every cylinder point is within r of its axis segment, so with s = dist(segment, box), u = unit(box
+// point - segment point) and the plane through the box point normal to u separating the two bodies:
+//     dist(cylinder, box) >= s - r sin(theta),  sin(theta) = sqrt(1 - (u.a)^2)                      (lb)
+// with EQUALITY when u is perpendicular to the axis (the closest feature is the lateral surface: always the case when the
+// segment's closest point is interior): `exact`.  Otherwise the closest feature is an end cap / rim; the distance from the
+// box point to the solid cylinder bounds the pair from above (ub).  The link colliders are capsules (cylinder + two
+// spheres of the same radius at its ends), so a slanted end contact reaches the sphere first and the band lb < thr <= ub
+// is a sliver: only there does the caller fall back to GJK.
+template <typename T> struct CylBoxBoundT { T lb, s; V3T<T> u, pb; bool exact; };
+template <typename T> __host__ __device__ __forceinline__ CylBoxBoundT<T> cyl_box_bound(V3T<T> c, V3T<T> a, T r, T h, V3T<T> e) {
+  SegBoxT<T> sb = seg_box<T>(c, a, h, e);
+  CylBoxBoundT<T> k;
+  k.s = sb.s; k.pb = sb.pb;
+  if (sb.s > T(1e-9)) {
+    k.u = (T(1) / sb.s) * (sb.pb - sb.pa);
+    const T ua = dot(k.u, a);
+    k.exact = tabs<T>(ua) < (sizeof(T) == 8 ? T(1e-9) : T(1e-4));  // r (1 - sin) = r ua^2 / 2: far below the arithmetic's resolution
+    k.lb = tmax<T>(sb.s - r * tsqrt(tmax<T>(T(1) - ua * ua, T(0))), T(0));
+  } else {  // the axis itself touches the core: cores overlap
+    k.u = v3t<T>(T(0), T(0), T(0)); k.exact = true; k.lb = T(0);
+  }
+  return k;
+}
+
 // ------------------------------------------------------------------------------------ GJK: cylinder core vs box core
 template <typename T> struct GjkIn { V3T<T> c, a, b, e; T r, h; };
 template <typename T> __host__ __device__ __forceinline__ void gjk_support(const GjkIn<T>& g, V3T<T> d, V3T<T>& sa, V3T<T>& sb) {

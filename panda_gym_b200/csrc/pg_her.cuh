@@ -14,7 +14,6 @@ namespace pg {
 
 struct HerParams {
   int rows, n_envs, obs_dim, act_dim;
-  float her_ratio;
   // storage: ONE record per transition, [rows][n_envs][rec_w] f32, rec_w = used width rounded up to 16 floats (64 B):
   //   observation od | next observation od | achieved 3 | desired 3 | next achieved 3 | next desired 3 | action ad |
   //   reward | done | timeout | ep_start (int bits) | pad
@@ -33,6 +32,7 @@ struct HerParams {
   uint32_t* raw;              // raw tempered words for one sample() call
   int raw_cap;
   int *s_row, *s_env, *s_t;   // last sampled indices (in SB3's order: virtual first, then real)
+  int* s_trow;                // storage row of the future transition of each virtual sample ((t + ep_start) % rows)
   int* status;                // [0] != 0 when sample() could not run (no valid transition)
 };
 
@@ -45,8 +45,8 @@ __device__ __forceinline__ int her_off_act(const HerParams& H) { return 2 * H.ob
 __device__ __forceinline__ int her_off_rew(const HerParams& H) { return 2 * H.obs_dim + 12 + H.act_dim; }
 __device__ __forceinline__ int her_off_eps(const HerParams& H) { return 2 * H.obs_dim + 12 + H.act_dim + 3; }
 
-struct HerBatch {  // output, row-major, order = torch.cat((real, virtual)) like SB3
-  float *obs, *ag, *dg, *next_obs, *next_ag, *next_dg, *action, *reward, *done;
+struct HerBatch {  // output: [batch][rec_w] rows in the record's field order, order = torch.cat((real, virtual)) like SB3
+  float* packed;
 };
 
 }  // namespace pg

@@ -35,6 +35,6 @@ void launch_her_add(const HerParams& H, const float* obs, const float* ag, const
                     const float* ndg, const float* act, const float* rew, const uint8_t* done, const uint8_t* timeout, cudaStream_t s);
 void launch_her_compact(const HerParams& H, int total, cudaStream_t s);
 void launch_her_indices(const HerParams& H, int B, int nbv, bool exact, uint64_t seed, uint64_t counter, cudaStream_t s);
-void launch_her_gather(const HerParams& H, const Params& P, const HerBatch& O, int B, int nbv, int reward_env, cudaStream_t s);
+void launch_her_gather(const HerParams& H, const Params& P, const HerBatch& O, int B, int nbv, int reward_env, int sm_count, cudaStream_t s);
 
 }  // namespace pg

@@ -41,11 +41,11 @@ __device__ __noinline__ double robot_body_distance(const Params& P, const Body& 
       D3 a = v3t<double>(np.a[0], np.a[1], np.a[2]);
       if (b.type == 0) d = cyl_sphere<double>(c, a, np.r, np.h, o, b.sx).d;
       else {
-        // analytic lower bound: cover the cylinder with ns spheres along its axis
-        int ns = np.h <= np.r ? 1 : (np.h <= 2 * np.r ? 2 : (np.h <= 3 * np.r ? 3 : 4));
-        double seg = np.h / ns, cover = sqrt(np.r * np.r + seg * seg) + (double)kHullMargin, lb = 1e300;
-        for (int i = 0; i < ns; i++) lb = fmin(lb, sphere_box<double>(c + (-np.h + (2 * i + 1) * seg) * a, cover, o, core, m).d);
+        // closed form unless the closest feature is a slanted end cap (cyl_box_bound), GJK only there
+        CylBoxBoundT<double> bd = cyl_box_bound<double>(c - o, a, np.r, np.h, core);
+        const double lb = bd.lb - (double)kHullMargin - m;
         if (lb > cutoff || lb >= best) continue;
+        if (bd.exact) { best = lb; continue; }
         d = cyl_box<double>(c, a, np.r, np.h, o, core, m).d;
       }
     }

@@ -52,20 +52,14 @@ __device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obs
     V3 a = frame_dir(F, Pm::ax, Pm::ay, Pm::az);
     if (ob.type == 0) k = cyl_sphere<float>(c, a, Pm::r, Pm::h, o, ob.sx);
     else {
-      // cylinder-box needs GJK: first bound it from below (analytically) with a cover of the cylinder by NS
-      // spheres along its axis, radius sqrt(r^2 + (h/NS)^2); a pair that cannot beat the running minimum of this
-      // link is skipped
+      // cylinder-box: closed form whenever the closest feature of the cylinder is its lateral surface (cyl_box_bound);
+      // a pair whose lower bound cannot beat the running minimum of this link is skipped; only a slanted end-cap
+      // contact that could still win goes to GJK (deferred to the warp-convergent queue when there is one)
       V3 core = v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin);
-      constexpr int NS = Pm::h <= Pm::r ? 1 : (Pm::h <= 2.f * Pm::r ? 2 : (Pm::h <= 3.f * Pm::r ? 3 : 4));
-      constexpr float seg = Pm::h / NS;
-      const float cover = sqrtf(Pm::r * Pm::r + seg * seg) + kHullMargin;
-      float lb = 3.0e38f;
-#pragma unroll
-      for (int i = 0; i < NS; i++) {
-        float t = -Pm::h + (2 * i + 1) * seg;
-        lb = fminf(lb, sphere_box<float>(c + t * a, cover, o, core, ob.margin).d);
-      }
+      CylBoxBoundT<float> bd = cyl_box_bound<float>(c - o, a, Pm::r, Pm::h, core);
+      const float lb = bd.lb - kHullMargin - ob.margin;
       if (lb >= best) return;
+      if (bd.exact) { best = lb; bdir = bd.lb > 0.f ? bd.u : v3(0.f, 0.f, 0.f); return; }
       if (Q && Q->n < CylBoxQueue::kCap) {
         CylBoxCand& cd = Q->q[Q->n++];
         cd.c = c; cd.a = a; cd.r = Pm::r; cd.h = Pm::h; cd.lb = lb; cd.j = j; cd.slot = Pm::slot;
@@ -89,9 +83,22 @@ __device__ __forceinline__ bool prim_hits_obstacle(const Frame& F, V3 o, const O
     float rr = Pm::r + ob.margin;
     return dot(v, v) <= rr * rr;  // centre inside the core gives v = 0: a hit
   }
-  float best = 1e-6f; V3 dir;
-  prim_vs_obstacle<K>(F, o, ob, best, dir);
-  return best <= 0.f;
+  V3 a = frame_dir(F, Pm::ax, Pm::ay, Pm::az);
+  if (ob.type == 0) { float best = 1e-6f; V3 dir; prim_vs_obstacle<K>(F, o, ob, best, dir); return best <= 0.f; }
+  // cylinder vs box, sign only: decided in closed form except in the sliver between the two bounds (see cyl_box_bound)
+  V3 core = v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), rel = c - o;
+  const float thr = kHullMargin + ob.margin;
+  {  // bounding sphere of the cylinder against the core
+    V3 v = rel - box_clamp<float>(rel, core);
+    const float reach = Pm::r + Pm::h + thr;
+    if (dot(v, v) > reach * reach) return false;
+  }
+  CylBoxBoundT<float> bd = cyl_box_bound<float>(rel, a, Pm::r, Pm::h, core);
+  if (bd.lb > thr) return false;
+  if (bd.exact) return true;
+  V3 on;
+  if (point_cylinder<float>(bd.pb, rel, a, Pm::r, Pm::h, on) <= thr) return true;  // the box's closest point already reaches the cylinder
+  return cyl_box<float>(c, a, Pm::r, Pm::h, o, core, ob.margin).d <= 0.f;
 }
 
 template <int K>
@@ -113,7 +120,8 @@ template <int K0, int N> struct PrimLoop {
     return fminf(PrimLoop<K0, N - 1>::table(F, S), prim_vs_table<K0 + N - 1>(F, S));
   }
   static __device__ __forceinline__ bool hits(const Frame& F, V3 o, const Obst& ob) {
-    return PrimLoop<K0, N - 1>::hits(F, o, ob) | prim_hits_obstacle<K0 + N - 1>(F, o, ob);
+    // last primitive first: the spheres of a link come after its cylinder, and once a sphere hits the cylinder is not needed
+    return prim_hits_obstacle<K0 + N - 1>(F, o, ob) || PrimLoop<K0, N - 1>::hits(F, o, ob);
   }
 };
 template <int K0> struct PrimLoop<K0, 0> {

@@ -116,6 +116,7 @@ __device__ void mt_twist(uint32_t* mt) {
   __syncthreads();
 }
 
+constexpr int kHerChunk = 1024;  // phase-B elements staged in shared memory at a time
 // Index sampling, numpy-exact.  ONE block of 256 threads (blockDim >= 128 so each twist phase fits 3 values/thread).
 //   phase A: np.random.choice(valid, B) == randint(0, n_valid, B): masked rejection on 32-bit draws, all elements
 //            share one mask -> accept flags + ordered compaction, chunk by chunk;
@@ -125,7 +126,9 @@ __device__ void mt_twist(uint32_t* mt) {
 __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, int nb_virtual) {
   __shared__ uint32_t mt[625];
   __shared__ int s_scan[256];
-  __shared__ int s_count, s_stop, s_pos;
+  __shared__ int s_count, s_stop, s_pos, s_tw_ok;
+  __shared__ uint32_t s_rng[kHerChunk], s_tw[624];  // per-element range -> accepted draw; tempered words of the state
+  __shared__ int s_cur[kHerChunk], s_st[kHerChunk];
   const int t = threadIdx.x;
   for (int k = t; k < 625; k += blockDim.x) mt[k] = H.mt[k];
   __syncthreads();
@@ -162,34 +165,59 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
       if (s_count >= B) break;
     }
   }
-  // ---- phase B (future strategy): t = randint(cur, ep_len) per virtual sample, sequential consumption
+  // ---- phase B (future strategy): t = randint(cur, ep_len) per virtual sample.  numpy draws element by element with a
+  // PER-ELEMENT mask and an element whose range is 0 consumes nothing: a sequential automaton over the raw stream.  Only
+  // that automaton is serial: the per-element ranges (dependent global-memory gathers) and the tempering of the 624
+  // state words are done by the whole block, chunk by chunk; thread 0 walks shared memory only (a few ns per element).
+  // The state is regenerated lazily, when a draw is needed and none is left, exactly like numpy.
   __syncthreads();
-  int done_el = 0;
-  while (done_el < nb_virtual) {
-    if (s_pos >= 624) { __syncthreads(); mt_twist(mt); if (t == 0) s_pos = 0; __syncthreads(); }
-    if (t == 0) {
-      int pos = s_pos, k = done_el;
-      while (k < nb_virtual) {
-        int row = H.s_row[k], env = H.s_env[k];
-        int st = H.ep_start[(size_t)row * ne + env], len = H.ep_length[(size_t)row * ne + env];
-        int cur = ((row - st) % rows + rows) % rows;
-        uint32_t r = (uint32_t)(len - 1 - cur);  // high - 1 - low
-        uint32_t v = 0;
-        if (r != 0) {
-          uint32_t m = r; m |= m >> 1; m |= m >> 2; m |= m >> 4; m |= m >> 8; m |= m >> 16;
-          bool got = false;
-          while (pos < 624) { v = mt_temper(mt[pos++]) & m; if (v <= r) { got = true; break; } }
-          if (!got) break;  // state exhausted mid-element: twist and retry this element
-        }
-        H.s_t[k] = cur + (int)v;
-        k++;
-      }
-      s_pos = pos; s_count = k;
+  if (t == 0) s_tw_ok = 0;
+  for (int c0 = 0; c0 < nb_virtual; c0 += kHerChunk) {
+    const int cn = nb_virtual - c0 < kHerChunk ? nb_virtual - c0 : kHerChunk;
+    __syncthreads();
+    for (int k = t; k < cn; k += blockDim.x) {
+      const int row = H.s_row[c0 + k], env = H.s_env[c0 + k];
+      const int st = H.ep_start[(size_t)row * ne + env], len = H.ep_length[(size_t)row * ne + env];
+      const int cur = ((row - st) % rows + rows) % rows;
+      s_rng[k] = (uint32_t)(len - 1 - cur);  // high - 1 - low
+      s_cur[k] = cur; s_st[k] = st;
     }
+    if (t == 0) s_count = 0;
     __syncthreads();
-    done_el = s_count;
-    __syncthreads();
+    while (s_count < cn) {
+      if (!s_tw_ok) {
+        __syncthreads();
+        for (int k = t; k < 624; k += blockDim.x) s_tw[k] = mt_temper(mt[k]);
+        if (t == 0) s_tw_ok = 1;
+        __syncthreads();
+      }
+      if (t == 0) {
+        int pos = s_pos, k = s_count;
+        bool need = false;
+        while (k < cn) {
+          const uint32_t r = s_rng[k];
+          uint32_t v = 0;
+          if (r != 0) {
+            uint32_t m = r; m |= m >> 1; m |= m >> 2; m |= m >> 4; m |= m >> 8; m |= m >> 16;
+            bool got = false;
+            while (pos < 624) { v = s_tw[pos++] & m; if (v <= r) { got = true; break; } }
+            if (!got) { need = true; break; }  // state exhausted mid-element: regenerate and retry this element
+          }
+          s_rng[k] = v;  // the slot now holds the accepted draw
+          k++;
+        }
+        s_pos = pos; s_count = k; s_stop = need ? 1 : 0;
+      }
+      __syncthreads();
+      if (s_stop) { mt_twist(mt); if (t == 0) { s_pos = 0; s_tw_ok = 0; } __syncthreads(); }
+    }
+    for (int k = t; k < cn; k += blockDim.x) {
+      const int tt = s_cur[k] + (int)s_rng[k];
+      H.s_t[c0 + k] = tt;
+      H.s_trow[c0 + k] = (tt + s_st[k]) % rows;
+    }
   }
+  __syncthreads();
   if (t == 0) mt[624] = (uint32_t)s_pos;
   __syncthreads();
   for (int k = t; k < 625; k += blockDim.x) H.mt[k] = mt[k];
@@ -211,50 +239,81 @@ __global__ void k_her_indices_fast(HerParams H, int B, int nb_virtual, uint64_t 
     int st = H.ep_start[(size_t)row * ne + env], len = H.ep_length[(size_t)row * ne + env];
     int cur = ((row - st) % rows + rows) % rows;
     uint64_t h2 = splitmix64(h);
-    H.s_t[k] = cur + (int)(((h2 >> 32) * (uint64_t)(len - cur)) >> 32);
+    const int tt = cur + (int)(((h2 >> 32) * (uint64_t)(len - cur)) >> 32);
+    H.s_t[k] = tt;
+    H.s_trow[k] = (tt + st) % rows;
   }
 }
 
 // ------------------------------------------------------------------------------------------ gather + relabel
-// one warp per sampled transition
-__global__ void k_her_gather(HerParams H, Params P, HerBatch O, int B, int nb_virtual, int reward_env) {
-  int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= B) return;
-  const int k = warp;                       // SB3 sample order: first nb_virtual are virtual
-  const bool is_virtual = k < nb_virtual;
-  const int out = is_virtual ? (B - nb_virtual) + k : k - nb_virtual;
-  const int ne = H.n_envs, od = H.obs_dim, ad = H.act_dim, rows = H.rows, w = H.rec_w;
-  const int row = H.s_row[k], env = H.s_env[k];
-  const float* __restrict__ rec = H.rec + ((size_t)row * ne + env) * w;
-  const int o_ag = her_off_ag(H), o_act = her_off_act(H), o_rew = her_off_rew(H);
-  // field-wise copy out of the contiguous record (warp-uniform loops: no divergence; the whole record is 9 x 64 B lines)
-  for (int i = lane; i < od; i += 32) {
-    const float a = rec[i], b = rec[od + i];
-    O.obs[(size_t)out * od + i] = a; O.next_obs[(size_t)out * od + i] = b;
-  }
-  for (int i = lane; i < ad; i += 32) O.action[(size_t)out * ad + i] = rec[o_act + i];
-  // new goal: the achieved goal of a later transition of the same episode (virtual) or the stored desired goal
-  float g[3], nag[3];
-  if (is_virtual) {
-    const int st = __float_as_int(rec[o_rew + 3]);
-    const int trow = (H.s_t[k] + st) % rows;
-    const float* fut = H.rec + ((size_t)trow * ne + env) * w + o_ag + 6;  // its next achieved goal
-    g[0] = fut[0]; g[1] = fut[1]; g[2] = fut[2];
-  } else { g[0] = rec[o_ag + 3]; g[1] = rec[o_ag + 4]; g[2] = rec[o_ag + 5]; }
-  nag[0] = rec[o_ag + 6]; nag[1] = rec[o_ag + 7]; nag[2] = rec[o_ag + 8];
-  if (lane < 3) {
-    O.ag[(size_t)out * 3 + lane] = rec[o_ag + lane];
-    O.next_ag[(size_t)out * 3 + lane] = nag[lane];
-    O.dg[(size_t)out * 3 + lane] = g[lane];
-    O.next_dg[(size_t)out * 3 + lane] = is_virtual ? g[lane] : rec[o_ag + 9 + lane];
-  }
-  if (lane == 0) {
-    // virtual reward = env.compute_reward(next_achieved_goal, new_goal) of environment `reward_env` (SB3: indices=[0])
-    O.reward[out] = is_virtual ? reward_fn(P, reward_env, nag, g) : rec[o_rew];
-    O.done[out] = rec[o_rew + 1] * (1.f - rec[o_rew + 2]);  // dones * (1 - timeouts)
+// Gather + relabel.  The output row of a sample is the stored record itself (same field order, whole 64 B lines) with
+// four fields patched: desired / next desired goal <- future achieved goal (virtual samples), reward <- recomputed,
+// done <- done * (1 - timeout).  One warp moves kGatherPer records per trip as 16-byte vectors: all loads of the trip
+// (records + future goals, located by the index kernels so nothing here depends on a loaded value) are issued before
+// the first store, the records are patched in shared memory by spare lanes and leave as full-line float4 stores.
+// HBM-bound: 1.15 KB read + written per sample (576 B record, a 32 B sector of the future record, 576 B out).
+constexpr int kGatherWarps = 8, kGatherPer = 4;
+__global__ void __launch_bounds__(kGatherWarps * 32) k_her_gather(HerParams H, Params P, HerBatch O, int B, int nb_virtual, int reward_env) {
+  extern __shared__ float4 s_rec[];  // [warp][kGatherPer][rec_w / 4]
+  if (H.status[0] != 0) return;      // nothing valid to sample from: leave the batch alone (the host raises)
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int ne = H.n_envs, w = H.rec_w, w4 = w >> 2;
+  const int o_ag = her_off_ag(H), o_rew = her_off_rew(H);
+  float4* mine = s_rec + (size_t)wib * kGatherPer * w4;
+  const int stride = gridDim.x * kGatherWarps * kGatherPer;
+  for (int base = (blockIdx.x * kGatherWarps + wib) * kGatherPer; base < B; base += stride) {
+    float4 v0[kGatherPer], v1[kGatherPer];
+    float fut[kGatherPer];
+#pragma unroll
+    for (int j = 0; j < kGatherPer; j++) {
+      const int k = base + j;  // SB3 sample order: the first nb_virtual are virtual
+      v0[j] = make_float4(0.f, 0.f, 0.f, 0.f); v1[j] = v0[j]; fut[j] = 0.f;
+      if (k < B) {
+        const int row = H.s_row[k], env = H.s_env[k];
+        const float4* __restrict__ rec = reinterpret_cast<const float4*>(H.rec + ((size_t)row * ne + env) * w);
+        if (lane < w4) v0[j] = __ldg(rec + lane);
+        if (lane + 32 < w4) v1[j] = __ldg(rec + lane + 32);
+        if (k < nb_virtual && lane < 3)  // next achieved goal of the future transition of the same episode
+          fut[j] = __ldg(H.rec + ((size_t)H.s_trow[k] * ne + env) * w + o_ag + 6 + lane);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kGatherPer; j++) {
+      if (lane < w4) mine[j * w4 + lane] = v0[j];
+      if (lane + 32 < w4) mine[j * w4 + lane + 32] = v1[j];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < kGatherPer; j++) {
+      if (base + j < nb_virtual && lane < 3) {
+        float* r = reinterpret_cast<float*>(mine + j * w4);
+        r[o_ag + 3 + lane] = fut[j]; r[o_ag + 9 + lane] = fut[j];
+      }
+    }
+    __syncwarp();
+    if (lane < kGatherPer && base + lane < B) {
+      float* r = reinterpret_cast<float*>(mine + lane * w4);
+      if (base + lane < nb_virtual) {
+        // virtual reward = env.compute_reward(next_achieved_goal, new_goal) of environment `reward_env` (SB3: indices=[0])
+        const float nag[3] = {r[o_ag + 6], r[o_ag + 7], r[o_ag + 8]}, g[3] = {r[o_ag + 3], r[o_ag + 4], r[o_ag + 5]};
+        r[o_rew] = reward_fn(P, reward_env, nag, g);
+      }
+      r[o_rew + 1] = r[o_rew + 1] * (1.f - r[o_rew + 2]);  // dones * (1 - timeouts)
+    }
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < kGatherPer; j++) {
+      const int k = base + j;
+      if (k < B) {
+        const int out = k < nb_virtual ? (B - nb_virtual) + k : k - nb_virtual;  // torch.cat((real, virtual))
+        float4* dst = reinterpret_cast<float4*>(O.packed + (size_t)out * w);
+        if (lane < w4) dst[lane] = mine[j * w4 + lane];
+        if (lane + 32 < w4) dst[lane + 32] = mine[j * w4 + lane + 32];
+      }
+    }
+    __syncwarp();
   }
 }
-
 
 // ------------------------------------------------------------------------------------------ launchers
 void launch_her_add(const HerParams& H, const float* obs, const float* ag, const float* dg, const float* nobs, const float* nag,
@@ -274,8 +333,12 @@ void launch_her_indices(const HerParams& H, int B, int nbv, bool exact, uint64_t
   if (exact) k_her_indices_exact<<<1, 256, 0, s>>>(H, B, nbv);
   else k_her_indices_fast<<<(B + 255) / 256, 256, 0, s>>>(H, B, nbv, seed, counter);
 }
-void launch_her_gather(const HerParams& H, const Params& P, const HerBatch& O, int B, int nbv, int reward_env, cudaStream_t s) {
-  k_her_gather<<<(unsigned)(((int64_t)B * 32 + 255) / 256), 256, 0, s>>>(H, P, O, B, nbv, reward_env);
+void launch_her_gather(const HerParams& H, const Params& P, const HerBatch& O, int B, int nbv, int reward_env, int sm_count, cudaStream_t s) {
+  const int per_block = kGatherWarps * kGatherPer;
+  int blocks = (B + per_block - 1) / per_block, cap = sm_count * 8;  // persistent: 8 blocks (64 warps) per SM
+  if (blocks > cap) blocks = cap;
+  const size_t smem = (size_t)per_block * H.rec_w * sizeof(float);  // 18 KB at 576 B records; rec_w <= 256 floats checked at create
+  k_her_gather<<<blocks, kGatherWarps * 32, smem, s>>>(H, P, O, B, nbv, reward_env);
 }
 
 }  // namespace pg

@@ -103,9 +103,7 @@ class RobotTaskEnv:
         is_success = bool(flags & 1)
         terminated = bool(flags & 2)
         truncated = bool(flags & 4) or bool(flags & 8)  # task truncation (collision) or TimeLimit
-        info = {"is_success": is_success, "is_truncated": bool(flags & 4)}
-        if flags & 8:
-            info["TimeLimit.truncated"] = True
+        info = {"is_success": is_success, "is_truncated": bool(flags & 4)}  # core.py:365; gymnasium's TimeLimit adds no key
         return self._obs(), reward, terminated, truncated, info
 
     def compute_reward(self, achieved_goal, desired_goal, info=None):

@@ -72,7 +72,10 @@ class HerReplayBuffer:
         dev = self.batch.device
         f = torch.float32
         if timeouts is None and infos is not None:
-            timeouts = np.array([bool(infos[i].get("TimeLimit.truncated", False)) for i in range(self.n_envs)])
+            if hasattr(infos, "time_limit_truncated"):  # LazyInfos: the vectorised form of the per-env lookup below
+                timeouts = infos.time_limit_truncated
+            else:
+                timeouts = np.array([bool(infos[i].get("TimeLimit.truncated", False)) for i in range(self.n_envs)])
         t = [self._dev(obs["observation"], dev, f), self._dev(obs["achieved_goal"], dev, f), self._dev(obs["desired_goal"], dev, f),
              self._dev(next_obs["observation"], dev, f), self._dev(next_obs["achieved_goal"], dev, f),
              self._dev(next_obs["desired_goal"], dev, f), self._dev(action, dev, f), self._dev(reward, dev, f),
@@ -81,10 +84,18 @@ class HerReplayBuffer:
         ptrs = [ctypes.c_void_p(x.data_ptr()) for x in t] + [ctypes.c_void_p(to.data_ptr()) if to is not None else None]
         _lib.check(self.lib.pg_her_add(self.h, *ptrs, self._stream()))
 
-    def _view(self, ptr, shape):
+    def _view(self, ptr, shape, row_stride):
         from .sim import _CudaArray
         with torch.cuda.device(self.batch.device):
-            return torch.as_tensor(_CudaArray(ptr, shape, 0, self), device=self.batch.device)
+            return torch.as_tensor(_CudaArray(ptr, shape, 0, self, strides=(4 * row_stride, 4)), device=self.batch.device)
+
+    def _raise_if_empty(self):
+        status = ctypes.c_int()
+        _lib.check(self.lib.pg_her_last_indices(self.h, 1, None, None, None, None, ctypes.byref(status)))
+        if status.value:
+            raise RuntimeError("Unable to sample before the end of the first episode. We recommend choosing a value for "
+                               "learning_starts that is greater than the maximum number of timesteps in the environment.")
+        self._seen_valid = True
 
     def sample(self, batch_size, env=None):
         B = int(batch_size)
@@ -95,22 +106,32 @@ class HerReplayBuffer:
             key = np.ascontiguousarray(st[1], dtype=np.uint32)
             _lib.check(self.lib.pg_her_set_mt_state(self.h, key.ctypes.data_as(ctypes.c_void_p), int(st[2])))
         _lib.check(self.lib.pg_her_sample(self.h, self.batch.h, B, 1 if exact else 0, self.device_seed, 0, ctypes.byref(out), self._stream()))
+        # SB3 raises when no episode has finished yet.  The gather kernel leaves the batch untouched in that case; the
+        # status word is read back (a 4-byte copy + sync) on every numpy-mode call, and in device mode until the first
+        # successful sample (an on-device buffer that has held a finished episode practically never empties again).
+        if exact or not getattr(self, "_seen_valid", False):
+            self._raise_if_empty()
         if exact:  # ... and take it back, advanced exactly as np.random.choice + np.random.randint would have
-            status = ctypes.c_int()
-            _lib.check(self.lib.pg_her_last_indices(self.h, B, None, None, None, None, ctypes.byref(status)))
-            if status.value:
-                raise RuntimeError("Unable to sample before the end of the first episode. We recommend choosing a value for "
-                                   "learning_starts that is greater than the maximum number of timesteps in the environment.")
             key = np.zeros(624, np.uint32); pos = ctypes.c_int()
             _lib.check(self.lib.pg_her_get_mt_state(self.h, key.ctypes.data_as(ctypes.c_void_p), ctypes.byref(pos)))
-            np.random.set_state(("MT19937", key, pos.value, 0, 0.0))
+            np.random.set_state(("MT19937", key, pos.value, st[3], st[4]))  # has_gauss / cached_gaussian pass through untouched
+        self.last_n_virtual = int(out.n_virtual)
         od, ad = self.obs_dim, self.act_dim
-        v = self._view
+        rs = int(out.row_stride)
+        self._last_packed = (out.observation, B, rs)
+        v = lambda ptr, shape: self._view(ptr, shape, rs)
         observations = {"observation": v(out.observation, (B, od)), "achieved_goal": v(out.achieved_goal, (B, 3)),
                         "desired_goal": v(out.desired_goal, (B, 3))}
         next_observations = {"observation": v(out.next_observation, (B, od)), "achieved_goal": v(out.next_achieved_goal, (B, 3)),
                              "desired_goal": v(out.next_desired_goal, (B, 3))}
         return DictReplayBufferSamples(observations, v(out.action, (B, ad)), next_observations, v(out.done, (B, 1)), v(out.reward, (B, 1)))
+
+    def last_packed(self):
+        """The last sampled batch as ONE ``[B, row_stride]`` device block (record field order: observation | next observation
+        | achieved | desired | next achieved | next desired | action | reward | done | ...): what
+        ``sharding.allgather_samples`` exchanges with a single collective."""
+        ptr, B, rs = self._last_packed
+        return self._view(ptr, (B, rs), rs)
 
     def last_indices(self, batch_size):
         B = int(batch_size)

@@ -18,6 +18,30 @@ def first_reset_seeds(base_seed, rank, envs_per_rank):
     return [base_seed + g for g in range(lo, hi)]
 
 
+def bind_to_local_numa(device_index):
+    """Pin the calling process to the CPUs NVML reports as local to CUDA device ``device_index`` (one process per GPU).
+    Page-locked host buffers allocated afterwards come from that NUMA node, so the per-step result copy of every rank
+    stays on its own socket / PCIe root instead of all ranks sharing the launcher's node.  Returns a small report dict
+    (or the reason nothing was done); never raises."""
+    import os
+    try:
+        import pynvml
+        props = torch.cuda.get_device_properties(device_index)
+        pynvml.nvmlInit()
+        bus = "%08x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w in range(words) for b in range(64) if (int(mask[w]) >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return {"bound": False, "why": "no overlap between the GPU's local CPUs and this process's allowed set"}
+        os.sched_setaffinity(0, allowed)
+        return {"bound": True, "pci": bus, "cpus": "%d-%d (%d)" % (allowed[0], allowed[-1], len(allowed))}
+    except Exception as ex:  # NVML missing, container without topology, ...
+        return {"bound": False, "why": repr(ex)[:200]}
+
+
 def allreduce_stats(stats, group=None):
     """Sum the 8-entry statistics vector over all ranks (in place on a clone); returns a dict."""
     s = stats.detach().clone().to(torch.float64)
@@ -31,6 +55,23 @@ def allreduce_stats(stats, group=None):
     out["mean_return"] = out["sum_return"] / ep
     out["mean_length"] = out["sum_length"] / ep
     return out
+
+
+def allgather_packed(packed, obs_dim, act_dim, group=None):
+    """Replay all-gather of a batch that already IS one ``[B, W]`` block -- ``HerReplayBuffer.last_packed()``, rows in the
+    stored record's field order -- with ONE ``all_gather_into_tensor`` and no packing pass; the nine fields come back as
+    column ranges of the gathered ``[world * B, W]`` block (rank-major)."""
+    from .her import DictReplayBufferSamples
+    out = packed
+    if dist.is_available() and dist.is_initialized():
+        world = dist.get_world_size(group)
+        out = torch.empty((world * packed.shape[0], packed.shape[1]), dtype=packed.dtype, device=packed.device)
+        dist.all_gather_into_tensor(out, packed.contiguous(), group=group)
+    od, ad = int(obs_dim), int(act_dim)
+    c = 2 * od
+    obs = {"observation": out[:, :od], "achieved_goal": out[:, c:c + 3], "desired_goal": out[:, c + 3:c + 6]}
+    nobs = {"observation": out[:, od:c], "achieved_goal": out[:, c + 6:c + 9], "desired_goal": out[:, c + 9:c + 12]}
+    return DictReplayBufferSamples(obs, out[:, c + 12:c + 12 + ad], nobs, out[:, c + 13 + ad:c + 14 + ad], out[:, c + 12 + ad:c + 13 + ad])
 
 
 def allgather_samples(samples, group=None):

@@ -19,9 +19,9 @@ _TYPESTR = {0: "<f4", 1: "|u1", 2: "<i4", 3: "<f8", 4: "<i8"}
 class _CudaArray:
     """Minimal __cuda_array_interface__ carrier so torch can view a library-owned buffer without copying."""
 
-    def __init__(self, ptr, shape, dtype_code, owner):
+    def __init__(self, ptr, shape, dtype_code, owner, strides=None):
         self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": _TYPESTR[dtype_code], "data": (ptr, False),
-                                         "version": 2, "strides": None}
+                                         "version": 2, "strides": None if strides is None else tuple(strides)}
         self._owner = owner
 
 
@@ -132,7 +132,8 @@ class PandaBatch:
         _lib.check(self.lib.pg_seed(self.h, int(seed), int(first_env_index)))
 
     def set_stage(self, stage):
-        _lib.check(self.lib.pg_set_stage(self.h, ctypes.byref(stage)))
+        """Swap the scenario block; every environment is reset into the new scene (pg_set_stage)."""
+        _lib.check(self.lib.pg_set_stage(self.h, ctypes.byref(stage), self._stream()))
         self._views = {}
 
     def reset(self, mask=None, seeds=None):
@@ -154,6 +155,17 @@ class PandaBatch:
 
     def reset_host(self, out):
         _lib.check(self.lib.pg_reset_host(self.h, ctypes.byref(out), self._stream()))
+
+    def copy_out(self, out):
+        _lib.check(self.lib.pg_copy_out(self.h, ctypes.byref(out), self._stream()))
+
+    def host_layout(self):
+        """Byte offsets (observation, achieved_goal, desired_goal, reward, done, flags) and total size of the one-block
+        host layout that pg_step_host fills with a single device-to-host copy."""
+        off = (ctypes.c_int64 * 6)()
+        tot = ctypes.c_int64()
+        _lib.check(self.lib.pg_host_layout(self.h, off, ctypes.byref(tot)))
+        return [int(x) for x in off], int(tot.value)
 
     def random_actions(self, seed, counter, out=None):
         if out is None:

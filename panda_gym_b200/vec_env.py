@@ -27,9 +27,18 @@ ENV_IDS["PandaReachAO-v3"] = dict(task=1)
 
 
 class LazyInfos:
-    """``infos`` list built on demand: SB3 indexes it per env; building 65 536 dicts per step eagerly would cost
-    more than the simulation.  Behaves like a read-only sequence of dicts.  Terminal observations / episode
-    statistics of the finished environments are fetched from the device once, on first use, and only their rows."""
+    """``infos`` of one vector step.  SB3 indexes it per env (``infos[i]``); building 65 536 dicts per step eagerly would
+    cost more than the simulation, so the per-env dict is built on ``__getitem__`` only and everything a Monitor /
+    replay buffer needs is ALSO available vectorised:
+
+      ``is_success``, ``is_truncated``, ``time_limit_truncated``  bool arrays [n]
+      ``finished``                 indices of the environments whose episode ended in this step
+      ``episode_returns`` / ``episode_lengths``  Monitor's ``r`` / ``l`` of those episodes (fetched once, on first use)
+      ``terminal_observations()``  dict of the finished rows' last observations
+
+    ``TimeLimit.truncated`` follows SB3's SubprocVecEnv worker on gymnasium >= 0.26: ``truncated and not terminated``
+    where gymnasium's ``truncated`` is the task's ``is_truncated()`` (collision, core.py:364) OR the TimeLimit wrapper.
+    So a collision-truncated ReachAO episode reports True and the learner bootstraps through it."""
 
     def __init__(self, desired, flags, done, fetch_terminal, t):
         self._desired, self._flags, self._done = desired, flags, done
@@ -39,22 +48,53 @@ class LazyInfos:
     def __len__(self):
         return len(self._flags)
 
+    # ---- vectorised accessors
+    @property
+    def is_success(self):
+        return (self._flags & 1) != 0
+
+    @property
+    def is_truncated(self):
+        return (self._flags & 4) != 0
+
+    @property
+    def time_limit_truncated(self):
+        f = self._flags
+        return ((f & 12) != 0) & ((f & 2) == 0)
+
+    @property
+    def finished(self):
+        return np.flatnonzero(self._done)
+
     def _terminal(self):
         if self._term is None:
             idx = np.flatnonzero(self._done)
             obs, ag, r, l = self._fetch(idx)
-            self._term = ({int(e): k for k, e in enumerate(idx)}, obs, ag, r, l)
+            self._term = ({int(e): k for k, e in enumerate(idx)}, obs, ag, r, l, idx)
         return self._term
 
+    @property
+    def episode_returns(self):
+        return self._terminal()[3]
+
+    @property
+    def episode_lengths(self):
+        return self._terminal()[4]
+
+    def terminal_observations(self):
+        _, obs, ag, _, _, idx = self._terminal()
+        return {"observation": obs, "achieved_goal": ag, "desired_goal": np.asarray(self._desired)[idx]}
+
+    # ---- SB3's per-env view
     def __getitem__(self, i):
         if isinstance(i, slice):
             return [self[j] for j in range(*i.indices(len(self)))]
         if i < 0:
             i += len(self)
         f = int(self._flags[i])
-        info = {"is_success": bool(f & 1), "is_truncated": bool(f & 4), "TimeLimit.truncated": bool(f & 8)}
+        info = {"is_success": bool(f & 1), "is_truncated": bool(f & 4), "TimeLimit.truncated": bool(f & 12) and not bool(f & 2)}
         if self._done[i]:
-            pos, obs, ag, r, l = self._terminal()
+            pos, obs, ag, r, l, _ = self._terminal()
             k = pos[int(i)]
             info["terminal_observation"] = {"observation": obs[k].copy(), "achieved_goal": ag[k].copy(),
                                             "desired_goal": np.array(self._desired[i], copy=True)}
@@ -101,13 +141,21 @@ class PandaVecEnv:
             return torch.empty(shape, dtype=dtype).pin_memory()
 
         self._ring = []
+        off, total = self.batch.host_layout()
         for _ in range(self.n_host_buffers):
-            h = dict(observation=pinned((n, od), torch.float32), achieved_goal=pinned((n, 3), torch.float32),
-                     desired_goal=pinned((n, 3), torch.float32), reward=pinned((n,), torch.float32),
-                     done=pinned((n,), torch.uint8), flags=pinned((n,), torch.uint8))
+            # one page-locked block per ring slot, laid out like the device slab: a step is ONE device-to-host copy
+            blk = pinned((total,), torch.uint8)
+
+            def carve(o, shape, dtype, blk=blk):
+                nbytes = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+                return blk[o:o + nbytes].view(dtype).view(shape)
+
+            h = dict(observation=carve(off[0], (n, od), torch.float32), achieved_goal=carve(off[1], (n, 3), torch.float32),
+                     desired_goal=carve(off[2], (n, 3), torch.float32), reward=carve(off[3], (n,), torch.float32),
+                     done=carve(off[4], (n,), torch.uint8), flags=carve(off[5], (n,), torch.uint8), _block=blk)
             out = _lib.HostOut(*[ctypes.c_void_p(h[k].data_ptr()) for k in
                                  ("observation", "achieved_goal", "desired_goal", "reward", "done", "flags")])
-            npv = {k: v.numpy() for k, v in h.items()}
+            npv = {k: v.numpy() for k, v in h.items() if not k.startswith("_")}
             npv["done_bool"] = npv["done"].view(np.bool_)
             self._ring.append((h, out, npv))
         self._ring_pos = 0
@@ -191,11 +239,33 @@ class PandaVecEnv:
     def env_is_wrapped(self, wrapper_class, indices=None):
         return [False] * self.num_envs
 
+    # per-environment state readable through get_attr (what callbacks / evaluate.py read off env.task / env.robot)
+    _PER_ENV = {"goal": ("goal", 1), "joint_angles": ("q", 1), "joint_velocities": ("qd", 1), "is_collided": ("flags", 0),
+                "distances_closest_obstacles": ("d_link", 1), "step_count": ("step_count", 0)}
+
     def get_attr(self, attr_name, indices=None):
+        """SB3 ``VecEnv.get_attr``: one value per selected environment.  Per-env simulator state (``goal``,
+        ``joint_angles``, ``joint_velocities``, ``distances_closest_obstacles``, ``is_collided``, ``step_count``) is read
+        from the device; configuration attributes (``scenario``, ``config`` fields, spaces, ...) are shared by all
+        environments of the batch."""
         idx = self._indices(indices)
-        return [getattr(self, attr_name) if hasattr(self, attr_name) else getattr(self.config, attr_name) for _ in idx]
+        if attr_name in self._PER_ENV:
+            view, soa = self._PER_ENV[attr_name]
+            t = self.batch.view(view)
+            sel = torch.as_tensor(idx, dtype=torch.int64, device=t.device)
+            vals = (t.index_select(1, sel).t() if soa else t.index_select(0, sel)).cpu().numpy()
+            if attr_name == "is_collided":
+                vals = (vals & 4) != 0
+            return [v.copy() if isinstance(v, np.ndarray) else v for v in vals]
+        if hasattr(self, attr_name):
+            return [getattr(self, attr_name) for _ in idx]
+        return [getattr(self.config, attr_name) for _ in idx]
 
     def set_attr(self, attr_name, value, indices=None):
+        """SB3 ``VecEnv.set_attr``.  The batch shares one configuration: setting an attribute for a strict subset of the
+        environments cannot be honoured and raises instead of silently applying it to all."""
+        if len(self._indices(indices)) != self.num_envs:
+            raise _lib.PandaB200Error("set_attr on a subset of environments: the batched simulator shares its configuration")
         setattr(self, attr_name, value)
 
     def env_method(self, method_name, *args, indices=None, **kwargs):
@@ -230,10 +300,14 @@ class PandaVecEnv:
         st = sim.stage_from_scenario(scenario, max_episode_steps or self.batch.cfg.stage.max_episode_steps,
                                      ee_error_threshold, speed_threshold)
         old = self.batch.obs_dim
-        self.batch.set_stage(st)
+        self.batch.set_stage(st)  # swaps the block and resets every environment (the reference rebuilds the VecEnv)
         self.scenario = scenario
         if self.batch.obs_dim != old:
             self._alloc_host()
+        _, out, npv = self._next_buffers()
+        self.batch.copy_out(out)
+        self._last_desired = npv["desired_goal"]
+        return self._obs_dict(npv)
 
     # ------------------------------------------------------------------ device-native API (no host copies)
     def step_device(self, actions):

@@ -19,6 +19,31 @@ class HerOracle:
         self.her_ratio = 1 - (1.0 / (n_sampled_goal + 1))
         self.compute_reward = compute_reward
 
+    def add_vectorised(self, obs, next_obs, action, reward, done, timeouts):
+        """Same bookkeeping as ``add`` with the two per-environment loops replaced by masked numpy updates (the 1 M-transition
+        x 1 024-column test would spend minutes in the Python loops); tests/test_host_logic.py checks both forms agree."""
+        R, pos = self.buffer_size, self.pos
+        st, ln = self.ep_start[pos].copy(), self.ep_length[pos].copy()
+        cnt = np.where(ln > 0, st + ln - pos, 0)
+        for off in range(int(cnt.max()) if cnt.size else 0):
+            e = np.flatnonzero(off < cnt)
+            self.ep_length[(pos + off) % R, e] = 0
+        self.ep_start[pos] = self._current_ep_start.copy()
+        for k in self.obs:
+            self.obs[k][pos] = obs[k]; self.next_obs[k][pos] = next_obs[k]
+        self.actions[pos] = action; self.rewards[pos] = reward; self.dones[pos] = done; self.timeouts[pos] = timeouts
+        self.pos += 1
+        if self.pos == R:
+            self.full = True; self.pos = 0
+        d = np.asarray(done).astype(bool)
+        start = self._current_ep_start.copy()
+        end = np.where(self.pos < start, self.pos + R, self.pos)
+        length = np.where(d, end - start, 0)
+        for off in range(int(length.max()) if length.size else 0):
+            e = np.flatnonzero(off < length)
+            self.ep_length[(start[e] + off) % R, e] = length[e]
+        self._current_ep_start[d] = self.pos
+
     def add(self, obs, next_obs, action, reward, done, timeouts):
         for e in range(self.n_envs):
             st, ln = self.ep_start[self.pos, e], self.ep_length[self.pos, e]

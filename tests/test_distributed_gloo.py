@@ -57,6 +57,16 @@ def _gather_worker(rank, world, port, out):
     ok &= torch.equal(full.actions[sl], local.actions) and torch.equal(full.rewards[sl], local.rewards) and torch.equal(full.dones[sl], local.dones)
     other = 1 - rank                        # the other rank's block carries its rank offset
     ok &= bool((full.rewards[other * B:(other + 1) * B] >= 10.0 * other).all() and (full.rewards[other * B:(other + 1) * B] < 10.0 * other + 1).all())
+    # the packed form (HerReplayBuffer.last_packed(): one [B, 144] block in record order) goes out without a packing pass
+    from panda_gym_b200.sharding import allgather_packed
+    W = 144
+    blk = torch.arange(B * W, dtype=torch.float32).reshape(B, W) + 1000.0 * rank
+    fp = allgather_packed(blk, od, ad)
+    ok &= fp.observations["observation"].shape == (world * B, od) and fp.rewards.shape == (world * B, 1)
+    ok &= torch.equal(fp.observations["observation"][sl], blk[:, :od]) and torch.equal(fp.next_observations["observation"][sl], blk[:, od:2 * od])
+    ok &= torch.equal(fp.observations["desired_goal"][sl], blk[:, 2 * od + 3:2 * od + 6]) and torch.equal(fp.actions[sl], blk[:, 2 * od + 12:2 * od + 19])
+    ok &= torch.equal(fp.rewards[sl], blk[:, 2 * od + 19:2 * od + 20]) and torch.equal(fp.dones[sl], blk[:, 2 * od + 20:2 * od + 21])
+    ok &= bool((fp.actions[other * B:(other + 1) * B] >= 1000.0 * other).all())
     out[rank] = (bool(ok), float(full.actions.sum()))
     dist.barrier()
     dist.destroy_process_group()

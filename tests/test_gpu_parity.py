@@ -443,7 +443,8 @@ def test_vec_env_api_and_auto_reset(sim, oracle):
                 saw_done = True
                 episodes[i] += 1
                 assert np.abs(info["terminal_observation"]["observation"] - o["observation"]).max() < 1e-3
-                assert info["TimeLimit.truncated"] == (f["time_limit"] and not f["terminated"])
+                # SB3 worker rule: truncated (collision OR time limit) and not terminated
+                assert info["TimeLimit.truncated"] == ((f["time_limit"] or f["truncated"]) and not f["terminated"])
                 assert info["episode"]["l"] > 0
                 # the returned observation is already the first one of the next episode: arm back at neutral
                 assert np.abs(obs["observation"][i, 6:13] - np.array([0, -0.3, 0, -2.2, 0, 2.0, np.pi / 4])).max() < 1e-6
@@ -471,6 +472,73 @@ def test_stage_switch(sim):
     assert obs["observation"].shape == (64, 47)  # reach_ao.py:904: np.ones(27) without obstacles
     assert np.all(obs["observation"][:, 20:] == 1.0)
     env.close()
+
+
+def test_stage_switch_starts_fresh_episodes(sim):
+    """set_stage without an explicit reset (what bench.py --curriculum and a curriculum callback do): the reference
+    rebuilds the VecEnv per stage, so every environment must start a fresh episode in the new scene -- no collision
+    spike from newly enabled obstacle slots at stale positions, goals from the new sampler, new observation width."""
+    from panda_gym_b200.vec_env import PandaVecEnv
+    n = 512
+    env = PandaVecEnv("PandaReachAO-v3", n_envs=n, seed=3, scenario="reachao1", max_episode_steps=50)
+    env.reset()
+    rng = np.random.default_rng(0)
+    for _ in range(5):
+        env.step(rng.uniform(-1, 1, (n, 7)).astype(np.float32))
+    obs = env.set_stage("reachao3", max_episode_steps=100)
+    assert obs["observation"].shape == (n, 56)
+    assert np.abs(obs["observation"][:, 6:13] - np.array([0, -0.3, 0, -2.2, 0, 2.0, np.pi / 4], np.float32)).max() < 1e-6, "arms back at neutral"
+    assert (env.batch.view("step_count").cpu().numpy() == 0).all()
+    before = env.episode_stats()["collisions"]
+    obs, rew, dones, infos = env.step(np.zeros((n, 7), np.float32))
+    assert env.episode_stats()["collisions"] == before and not infos.is_truncated.any(), "no spurious collisions after the switch"
+    g = np.linalg.norm(obs["desired_goal"], axis=1)
+    assert (g > 0.49).all() and (g < 0.81).all(), "goals come from reachao3's shell sampler"
+    # width change reach1 <-> reachao*: ee control reads its cached EE from the observation at the NEW stride
+    env.close()
+    cfgc = sim_cfg_ee()
+    env = PandaVecEnv("PandaReachAO-v3", n_envs=64, seed=3, scenario="reach1", max_episode_steps=50, config=cfgc)
+    env.reset()
+    env.step(rng.uniform(-1, 1, (64, 3)).astype(np.float32))
+    obs = env.set_stage("reachao2", max_episode_steps=75)
+    assert obs["observation"].shape[1] == 56
+    ee0 = obs["observation"][:, :3].copy()
+    obs, _, _, infos = env.step(np.zeros((64, 3), np.float32))
+    assert np.abs(obs["observation"][:, :3] - ee0).max() < 0.05 and not infos.is_truncated.any()
+    env.close()
+
+
+def sim_cfg_ee():
+    from panda_gym_b200.config import TrainConfig
+    return TrainConfig(control_type="ee")
+
+
+def test_shard_determinism(sim):
+    """SURVEY section 4 'multi-GPU shard determinism': rank r of a job owns environments [r N, (r+1) N) and seeds them with
+    first_env_index = r N.  Two N-env handles (ranks 0 and 1) must reproduce, bit for bit, the two halves of one 2N-env
+    handle over 30 auto-reset steps -- observations, rewards, flags, episode statistics."""
+    from panda_gym_b200 import sim as S
+    N, steps = 448 + 61, 30   # not a multiple of the step kernel's block: block boundaries differ between the handles
+    def make(n, first):
+        cfg = S.make_config(1, n, scenario="reachao3", max_episode_steps=12, auto_reset=True)
+        b = S.PandaBatch(cfg)
+        b.seed(99, first)
+        b.reset()
+        return b
+    whole, lo, hi = make(2 * N, 0), make(N, 0), make(N, N)
+    rng = np.random.default_rng(5)
+    for k in range(steps):
+        A = torch.from_numpy(rng.uniform(-1, 1, (2 * N, 7)).astype(np.float32)).cuda()
+        whole.step(A); lo.step(A[:N].contiguous()); hi.step(A[N:].contiguous())
+        torch.cuda.synchronize()
+        for name in ("observation", "achieved_goal", "desired_goal", "reward", "done", "flags", "ep_return", "ep_length"):
+            w = whole.view(name).cpu().numpy()
+            assert np.array_equal(w[:N], lo.view(name).cpu().numpy()), (name, k)
+            assert np.array_equal(w[N:], hi.view(name).cpu().numpy()), (name, k)
+    sw = whole.view("stats").cpu().numpy()
+    assert sw[0] > 2 * N and np.array_equal(sw[:4], lo.view("stats").cpu().numpy()[:4] + hi.view("stats").cpu().numpy()[:4])
+    for b in (whole, lo, hi):
+        b.close()
 
 
 # ------------------------------------------------------------------------------------------ full-size properties

@@ -101,7 +101,13 @@ def test_lazy_infos():
     infos = LazyInfos(np.ones((4, 3), np.float32), flags, done, fetch, 1.5)
     assert len(infos) == 4 and "terminal_observation" not in infos[0] and calls == []
     assert infos[1]["is_success"] and infos[1]["episode"] == {"r": -3.0, "l": 4, "t": 1.5}
-    assert infos[2]["is_truncated"] and not infos[2]["TimeLimit.truncated"]
+    # SB3's SubprocVecEnv worker on gymnasium >= 0.26: TimeLimit.truncated = truncated and not terminated, and gymnasium's
+    # truncated is the task's is_truncated() (collision) OR the TimeLimit wrapper
+    assert infos[2]["is_truncated"] and infos[2]["TimeLimit.truncated"]
+    assert not infos[1]["TimeLimit.truncated"] and not infos[0]["TimeLimit.truncated"]
+    assert np.array_equal(infos.time_limit_truncated, [False, False, True, True])
+    assert np.array_equal(infos.finished, [1, 2, 3]) and np.array_equal(infos.episode_lengths, [4, 7, 50])
+    assert infos.terminal_observations()["observation"].shape == (3, 5)
     assert infos[3]["TimeLimit.truncated"] and np.array_equal(infos[3]["terminal_observation"]["observation"], term[2])
     assert [i["is_success"] for i in infos] == [False, True, False, False]
     assert calls == [[1, 2, 3]], "terminal rows are fetched once, and only for finished environments"
@@ -137,3 +143,25 @@ def test_benchmark_results_from_accumulators():
     assert r["mean_effort"] == 0.5 and r["mean_manipulability"] == 0.1 and r["mean_norm_jerk"] == 0.2 and r["mean_ee_speed"] == 0.3
     empty = benchmark_results([0.0] * 12)
     assert empty["num_episodes"] == 0.0 and empty["mean_effort"] != empty["mean_effort"]  # nan, like np.mean([])
+
+
+def test_her_oracle_vectorised_add_equals_loop():
+    """The numpy restatement of SB3's HerReplayBuffer has a loop form (reads like SB3) and a vectorised form (used at the
+    1 M-transition size): identical bookkeeping on a wrapping buffer with ragged episodes."""
+    from her_oracle import HerOracle
+    rng = np.random.default_rng(3)
+    E, R, od, ad = 13, 37, 5, 2
+    a, b = HerOracle(R * E, E, od, ad), HerOracle(R * E, E, od, ad)
+    remaining = rng.integers(3, 60, E)  # some episodes are longer than the buffer has rows
+    for step in range(150):
+        obs = {"observation": rng.random((E, od), np.float32), "achieved_goal": rng.random((E, 3), np.float32),
+               "desired_goal": rng.random((E, 3), np.float32)}
+        nobs = {k: v + 1 for k, v in obs.items()}
+        remaining -= 1
+        done = (remaining == 0)
+        remaining[done] = rng.integers(3, 60, int(done.sum()))
+        args = (obs, nobs, rng.random((E, ad), np.float32), rng.random(E, np.float32), done.astype(np.float32), np.zeros(E, np.float32))
+        a.add(*args); b.add_vectorised(*args)
+        assert np.array_equal(a.ep_start, b.ep_start) and np.array_equal(a.ep_length, b.ep_length), step
+        assert np.array_equal(a._current_ep_start, b._current_ep_start) and a.pos == b.pos and a.full == b.full
+    assert a.full and (a.ep_length > 0).any()
