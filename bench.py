@@ -371,8 +371,10 @@ def main():
     # a DIFFERENT action batch every step, like the device-timed loop: cycling a handful of batches is a periodic drive that
     # walks the arms into their joint limits (the solver's slow path) and would time a different workload
     host_actions = [a.cpu().numpy() for a in actions]
-    for k in range(3):
-        env.step(host_actions[k % len(host_actions)])
+    for k in range(3):  # warm-up of the whole host path, the consumers of `infos` included
+        obs, rew, dones, infos = env.step(host_actions[k % len(host_actions)])
+        if len(infos.finished):
+            infos.terminal_observations(); infos.episode_returns.sum()
     torch.cuda.synchronize()
     Ke = max(10, K // 2)
     if world > 1:

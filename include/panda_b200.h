@@ -117,6 +117,16 @@ typedef struct {
 } pg_host_out;
 int pg_step_host(pg_handle h, const float* actions_host, const pg_host_out* out, void* stream);
 int pg_reset_host(pg_handle h, const pg_host_out* out, void* stream);
+/* Episodes that ended in a step (what SB3 reads out of `infos`: terminal_observation, Monitor's episode r / l,
+ * TimeLimit.truncated).  The step kernel writes one compact row per finished episode into a 3-deep device ring:
+ *   [0] env index (int bits) [1] episode return [2] episode length (int bits) [3] flags (int bits, pg_host_out.flags)
+ *   [4..6] terminal achieved goal [7] - [8 ..] terminal observation;  *row_width floats per row, in completion order.
+ * pg_step_id: number of pg_step calls so far (the id of the latest step).  pg_finished_count: episodes that ended in step
+ * `step_id` (known on the host after pg_step_host of that step; negative pg_status when older than three steps).
+ * pg_fetch_finished: ONE device-to-host copy of those rows (at most max_rows) + a stream synchronise; returns the row count. */
+int64_t pg_step_id(pg_handle h);
+int pg_finished_count(pg_handle h, int64_t step_id);
+int pg_fetch_finished(pg_handle h, int64_t step_id, float* rows_host, int max_rows, int* row_width, void* stream);
 /* current results -> host buffers without stepping (synchronises the stream) */
 int pg_copy_out(pg_handle h, const pg_host_out* out, void* stream);
 /* The six results live in one device slab.  A caller that carves its six host buffers out of ONE (page-locked) block at

@@ -71,6 +71,9 @@ SYMBOLS = [
     ("pg_step_host", c_int, [P, P, P, P]),
     ("pg_reset_host", c_int, [P, P, P]),
     ("pg_copy_out", c_int, [P, P, P]),
+    ("pg_step_id", c_i64, [P]),
+    ("pg_finished_count", c_int, [P, c_i64]),
+    ("pg_fetch_finished", c_int, [P, c_i64, P, c_int, P, P]),
     ("pg_host_layout", c_int, [P, P, P]),
     ("pg_compute_reward", c_int, [P, P, P, P, c_i64, c_int, P]),
     ("pg_random_actions", c_int, [P, c_u64, c_u64, P, P]),

@@ -43,6 +43,10 @@ struct pg_env_s {
   int sm_count;                     // cudaDevAttrMultiProcessorCount (grid of the auto-reset kernel)
   uint8_t* out_slab;                // per-step results, one allocation (see pg_create)
   size_t slab_obs_off;
+  float* term_ring;                 // [3][n][term_w_max] compact rows of finished episodes (Params::term_rows points into it)
+  int term_w_max;
+  int64_t step_id;                  // pg_step calls so far; ring slot = step_id % 3
+  int* finished_host;               // page-locked [4]: finished-episode count of the last three steps (by ring slot) 
 };
 
 namespace {
@@ -68,6 +72,8 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   d.goal_upper = s->goal_upper_half; d.goal_front = s->goal_front_half; d.goal_34 = s->goal_three_quarter_front;
   d.nobs = s->n_obstacles;
   P.scene.nobs = s->n_obstacles;
+  P.scene.has_box = 0;
+  for (int j = 0; j < s->n_obstacles; j++) P.scene.has_box |= s->obstacle_type[j] == 1;
   for (int j = 0; j < pg::kMaxObst; j++) {
     d.obs_type[j] = j < s->n_obstacles ? s->obstacle_type[j] : 0;
     for (int k = 0; k < 3; k++) d.obs_size[j][k] = j < s->n_obstacles ? s->obstacle_size[j][k] : 0.0;
@@ -203,6 +209,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   pg_env_s* h = new pg_env_s();
   h->sm_count = sms;
   h->cfg = *cfg; h->device = device; h->launches = 0; h->first_env = 0; h->d_actions = nullptr; h->eval_metrics = 0;
+  h->finished_host = nullptr; h->term_ring = nullptr; h->out_slab = nullptr;
   pg::Params& P = h->P;
   memset(&P, 0, sizeof P);
   const int n = cfg->n_envs;
@@ -254,6 +261,12 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   }
   A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true)
   A(P.stats, 8, false) A(P.reset_list, n, false) A(P.reset_count, 1, false)
+  h->term_w_max = (8 + max_obs + 3) / 4 * 4;
+  A(h->term_ring, (size_t)3 * n * h->term_w_max, false)
+  P.term_rows = h->term_ring; P.term_w = (8 + P.obs_dim + 3) / 4 * 4;
+  h->step_id = 0;
+  if (cudaHostAlloc((void**)&h->finished_host, 4 * sizeof(int), cudaHostAllocDefault) != cudaSuccess) { pg_destroy(h); return fail(PG_ERR_CUDA, "cudaHostAlloc"); }
+  memset(h->finished_host, 0, 4 * sizeof(int));
   A(P.ev_acc, 4 * n, true) A(P.ev_len, n, true) A(P.ev_ret, n, true) A(P.ev, 12, false)
   A(h->d_actions, 8 * n, false)
 #undef A
@@ -276,6 +289,7 @@ int pg_destroy(pg_handle h) {
   cudaSetDevice(h->device);
   for (void* p : h->all_bufs) cudaFree(p);
   for (auto& kv : h->saved) for (void* p : kv.second) cudaFree(p);
+  if (h->finished_host) cudaFreeHost(h->finished_host);
   delete h;
   return PG_OK;
 }
@@ -312,7 +326,10 @@ int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, vo
 int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   if (!h || !actions_dev) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
-  if (h->P.auto_reset) PG_CUDA(cudaMemsetAsync(h->P.reset_count, 0, sizeof(int), (cudaStream_t)stream));
+  PG_CUDA(cudaMemsetAsync(h->P.reset_count, 0, sizeof(int), (cudaStream_t)stream));
+  h->step_id++;
+  h->P.term_w = (8 + h->P.obs_dim + 3) / 4 * 4;
+  h->P.term_rows = h->term_ring + (size_t)(h->step_id % 3) * h->P.n * h->term_w_max;
   if (h->P.task >= 2) pg::launch_step_obj(h->P, actions_dev, (cudaStream_t)stream);
   else pg::launch_step(h->P, actions_dev, (cudaStream_t)stream);
   h->launches++;
@@ -357,6 +374,29 @@ int pg_host_layout(pg_handle h, int64_t* offsets6, int64_t* total_bytes) {
   return PG_OK;
 }
 
+int64_t pg_step_id(pg_handle h) { return h ? h->step_id : 0; }
+
+int pg_finished_count(pg_handle h, int64_t step_id) {
+  if (!h || step_id > h->step_id || h->step_id - step_id >= 3 || step_id <= 0) return PG_ERR_STATE;
+  return h->finished_host[step_id % 3];
+}
+
+int pg_fetch_finished(pg_handle h, int64_t step_id, float* rows_host, int max_rows, int* row_width, void* stream) {
+  if (!h || !rows_host || !row_width) return fail(PG_ERR_ARG, "NULL argument");
+  if (step_id > h->step_id || step_id <= 0 || h->step_id - step_id >= 3)
+    return fail(PG_ERR_STATE, "the finished-episode rows of that step have been overwritten (the ring keeps the last three steps)");
+  PG_CUDA(cudaSetDevice(h->device));
+  int count = h->finished_host[step_id % 3];
+  if (count > max_rows) count = max_rows;
+  *row_width = h->P.term_w;
+  if (count > 0) {
+    const float* src = h->term_ring + (size_t)(step_id % 3) * h->P.n * h->term_w_max;
+    PG_CUDA(cudaMemcpyAsync(rows_host, src, (size_t)count * h->P.term_w * sizeof(float), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    PG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  }
+  return count;
+}
+
 int pg_copy_out(pg_handle h, const pg_host_out* out, void* stream) {
   if (!h || !out) return fail(PG_ERR_ARG, "NULL argument");
   PG_CUDA(cudaSetDevice(h->device));
@@ -370,6 +410,8 @@ int pg_step_host(pg_handle h, const float* actions_host, const pg_host_out* out,
   PG_CUDA(cudaMemcpyAsync(h->d_actions, actions_host, (size_t)h->P.n * h->P.act_dim * sizeof(float), cudaMemcpyHostToDevice, s));
   int rc = pg_step(h, h->d_actions, stream);
   if (rc != PG_OK) return rc;
+  // how many episodes ended in this step: rides along with the results (page-locked word, valid after the synchronise)
+  PG_CUDA(cudaMemcpyAsync(&h->finished_host[h->step_id % 3], h->P.reset_count, sizeof(int), cudaMemcpyDeviceToHost, s));
   if (out) return copy_out(h, out, s);
   PG_CUDA(cudaStreamSynchronize(s));
   return PG_OK;

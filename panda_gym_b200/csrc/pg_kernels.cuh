@@ -75,6 +75,12 @@ struct Params {
   uint8_t *done, *flags;
   double* stats;                 // [8]
   int *reset_list, *reset_count;   // compacted indices of environments that finished in the last step
+  // compact rows of the episodes that ended in this step, in the order of reset_list, term_w floats each:
+  //   [0] env index (int bits) [1] episode return [2] episode length (int bits) [3] flags (int bits) [4..6] achieved goal [7] -
+  //   [8 ..] terminal observation.  One slot of a 3-deep ring (pg_step rotates it): the host fetches the rows of a step it is
+  //   still interested in with ONE copy of count x term_w floats (LazyInfos), nothing is snapshotted per step.
+  float* term_rows;
+  int term_w;
   // evaluation metrics of perform_benchmark (evaluation/evaluate.py:131-300), filled by k_eval_metrics when enabled
   float* ev_acc;                 // [4][n] running sums of the current episode: effort, manipulability, jerk norm, ee speed
   int* ev_len;                   // [n] steps of the current episode
@@ -479,7 +485,14 @@ __device__ __forceinline__ void step_end(const Params& P, int e, const float* q,
     for (int k = 0; k < P.obs_dim; k++) t[k] = o[k];
     P.term_achieved[(size_t)e * 3] = ag[0]; P.term_achieved[(size_t)e * 3 + 1] = ag[1]; P.term_achieved[(size_t)e * 3 + 2] = ag[2];
     P.need_reset[e] = 1;
-    if (P.auto_reset) P.reset_list[atomicAdd(P.reset_count, 1)] = e;
+    {
+      const int slot = atomicAdd(P.reset_count, 1);
+      P.reset_list[slot] = e;
+      float* row = P.term_rows + (size_t)slot * P.term_w;
+      row[0] = __int_as_float(e); row[1] = ret; row[2] = __int_as_float(len); row[3] = __int_as_float((int)P.flags[e]);
+      row[4] = ag[0]; row[5] = ag[1]; row[6] = ag[2]; row[7] = 0.f;
+      for (int k = 0; k < P.obs_dim; k++) row[8 + k] = o[k];
+    }
     atomicAdd(&P.stats[0], 1.0);
     if (succ) atomicAdd(&P.stats[1], 1.0);
     if (truncated) atomicAdd(&P.stats[2], 1.0);

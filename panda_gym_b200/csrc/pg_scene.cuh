@@ -14,6 +14,7 @@ struct SceneParams {
   float obst_bound[kMaxObst];  // bounding radius of each obstacle shape
   float table_pos[3], table_core[3], table_margin;
   int has_table;
+  int has_box;                 // any cuboid obstacle in the scene (selects the barrier pattern of the flag pass)
 };
 
 // primitives of collision-link slot S: [first, first + count)
@@ -38,6 +39,39 @@ template <int K0> struct SlotBound<K0, 0> { static constexpr float value = 0.f; 
 // convergent GJK call per round (rounds = longest queue in the warp, typically 2-4).
 struct CylBoxCand { V3 c, a; float r, h, lb; int j, slot; };
 struct CylBoxQueue { static constexpr int kCap = 12; CylBoxCand q[kCap]; int n; };
+
+// Measured on B200 (profiles/r02_variants.txt), 65 536 envs: with box obstacles the per-substep flag pass is a long,
+// divergently-culled code path and the warps of a block drift apart in it (ncu: 56 % stall_no_inst); block barriers between
+// its link groups keep them inside one instruction-cache window: reachao_rand 3.28 -> 1.90 ms per step.  Sphere-only scenes
+// run 2 % slower with those barriers, so they are taken only when the scene has a box (a kernel parameter: uniform over the
+// block).  One shared copy of the cylinder-box sign test instead of ten inlined ones: reachao3 0.748 -> 0.717 ms.
+#ifndef PG_SCENE_SYNC
+#define PG_SCENE_SYNC 2   // 0 never, 1 always, 2 when the scene has box obstacles
+#endif
+#ifndef PG_CYLBOX_NOINLINE
+#define PG_CYLBOX_NOINLINE 1
+#endif
+// cylinder (centre rel to the box centre, unit axis a, radius r, half length h) vs box core, margin m: is the distance <= 0 ?
+// Decided in closed form except in the sliver between the two bounds (see cyl_box_bound).
+#if PG_CYLBOX_NOINLINE
+static __device__ __noinline__
+#else
+__device__ __forceinline__
+#endif
+bool cyl_box_hits(V3 rel, V3 a, float r, float h, V3 core, float margin) {
+  const float thr = kHullMargin + margin;
+  {  // bounding sphere of the cylinder against the core
+    V3 v = rel - box_clamp<float>(rel, core);
+    const float reach = r + h + thr;
+    if (dot(v, v) > reach * reach) return false;
+  }
+  CylBoxBoundT<float> bd = cyl_box_bound<float>(rel, a, r, h, core);
+  if (bd.lb > thr) return false;
+  if (bd.exact) return true;
+  V3 on;
+  if (point_cylinder<float>(bd.pb, rel, a, r, h, on) <= thr) return true;  // the box's closest point already reaches the cylinder
+  return cyl_box<float>(rel, a, r, h, v3(0.f, 0.f, 0.f), core, margin).d <= 0.f;
+}
 
 template <int K>
 __device__ __forceinline__ void prim_vs_obstacle(const Frame& F, V3 o, const Obst& ob, float& best, V3& bdir, CylBoxQueue* Q = nullptr,
@@ -85,20 +119,7 @@ __device__ __forceinline__ bool prim_hits_obstacle(const Frame& F, V3 o, const O
   }
   V3 a = frame_dir(F, Pm::ax, Pm::ay, Pm::az);
   if (ob.type == 0) { float best = 1e-6f; V3 dir; prim_vs_obstacle<K>(F, o, ob, best, dir); return best <= 0.f; }
-  // cylinder vs box, sign only: decided in closed form except in the sliver between the two bounds (see cyl_box_bound)
-  V3 core = v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), rel = c - o;
-  const float thr = kHullMargin + ob.margin;
-  {  // bounding sphere of the cylinder against the core
-    V3 v = rel - box_clamp<float>(rel, core);
-    const float reach = Pm::r + Pm::h + thr;
-    if (dot(v, v) > reach * reach) return false;
-  }
-  CylBoxBoundT<float> bd = cyl_box_bound<float>(rel, a, Pm::r, Pm::h, core);
-  if (bd.lb > thr) return false;
-  if (bd.exact) return true;
-  V3 on;
-  if (point_cylinder<float>(bd.pb, rel, a, Pm::r, Pm::h, on) <= thr) return true;  // the box's closest point already reaches the cylinder
-  return cyl_box<float>(c, a, Pm::r, Pm::h, o, core, ob.margin).d <= 0.f;
+  return cyl_box_hits(c - o, a, Pm::r, Pm::h, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
 }
 
 template <int K>
@@ -120,14 +141,21 @@ template <int K0, int N> struct PrimLoop {
     return fminf(PrimLoop<K0, N - 1>::table(F, S), prim_vs_table<K0 + N - 1>(F, S));
   }
   static __device__ __forceinline__ bool hits(const Frame& F, V3 o, const Obst& ob) {
-    // last primitive first: the spheres of a link come after its cylinder, and once a sphere hits the cylinder is not needed
-    return prim_hits_obstacle<K0 + N - 1>(F, o, ob) || PrimLoop<K0, N - 1>::hits(F, o, ob);
+    return PrimLoop<K0, N - 1>::hits(F, o, ob) | prim_hits_obstacle<K0 + N - 1>(F, o, ob);  // straight-line, no branches
+  }
+  // box obstacle: the spheres of the link first (cheap); the link colliders are capsules, so a slanted end contact reaches a
+  // sphere before the cylinder and the cylinder-box test is only needed while no sphere hits
+  static __device__ __forceinline__ bool hits_kind(const Frame& F, V3 o, const Obst& ob, int type) {
+    bool h = PrimLoop<K0, N - 1>::hits_kind(F, o, ob, type);
+    if (pgm::Prim<K0 + N - 1>::type == type) h |= prim_hits_obstacle<K0 + N - 1>(F, o, ob);
+    return h;
   }
 };
 template <int K0> struct PrimLoop<K0, 0> {
   static __device__ __forceinline__ void obstacle(const Frame&, V3, const Obst&, float&, V3&, CylBoxQueue*, int) {}
   static __device__ __forceinline__ float table(const Frame&, const SceneParams&) { return 3.0e38f; }
   static __device__ __forceinline__ bool hits(const Frame&, V3, const Obst&) { return false; }
+  static __device__ __forceinline__ bool hits_kind(const Frame&, V3, const Obst&, int) { return false; }
 };
 
 // One collision link.  FULL: exact per-link minimum distance + closest pair (observation); otherwise only
@@ -147,7 +175,8 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const float* __r
       V3 d = o - ctr;
       float rr = R + P.obst_bound[j];
       if (dot(d, d) > rr * rr) continue;
-      if (PrimLoop<K0, N>::hits(F, o, P.obst[j])) hit = true;
+      if (P.obst[j].type == 0) { if (PrimLoop<K0, N>::hits(F, o, P.obst[j])) hit = true; }
+      else if (PrimLoop<K0, N>::hits_kind(F, o, P.obst[j], 0) || PrimLoop<K0, N>::hits_kind(F, o, P.obst[j], 1)) hit = true;
       continue;
     }
     PrimLoop<K0, N>::obstacle(F, o, P.obst[j], best, dir, Q, j);
@@ -175,18 +204,18 @@ __device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, co
     F = frame_step<2>(F, cq[1], sq[1]); slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[1] = d; u_link[1] = u; }
     F = frame_step<3>(F, cq[2], sq[2]); slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[2] = d; u_link[2] = u; }
   }
-  if (SYNC && FULL) __syncthreads();
+  if (SYNC && (FULL || PG_SCENE_SYNC == 1 || (PG_SCENE_SYNC == 2 && P.has_box))) __syncthreads();
   if (active) {
     F = frame_step<4>(F, cq[3], sq[3]); slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[3] = d; u_link[3] = u; }
     F = frame_step<5>(F, cq[4], sq[4]); slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[4] = d; u_link[4] = u; }
   }
-  if (SYNC && FULL) __syncthreads();
+  if (SYNC && (FULL || PG_SCENE_SYNC == 1 || (PG_SCENE_SYNC == 2 && P.has_box))) __syncthreads();
   if (active) {
     F = frame_step<6>(F, cq[5], sq[5]); slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[5] = d; u_link[5] = u; }
     F = frame_step<7>(F, cq[6], sq[6]);
     slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[6] = d; u_link[6] = u; }
   }
-  if (SYNC && FULL) __syncthreads();
+  if (SYNC && (FULL || PG_SCENE_SYNC == 1 || (PG_SCENE_SYNC == 2 && P.has_box))) __syncthreads();
   if (active) {
     slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[7] = d; u_link[7] = u; }
     slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[8] = d; u_link[8] = u; }

@@ -159,6 +159,32 @@ class PandaBatch:
     def copy_out(self, out):
         _lib.check(self.lib.pg_copy_out(self.h, ctypes.byref(out), self._stream()))
 
+    def step_id(self):
+        return int(self.lib.pg_step_id(self.h))
+
+    def finished_count(self, step_id):
+        return int(self.lib.pg_finished_count(self.h, int(step_id)))
+
+    def fetch_finished(self, step_id):
+        """Compact rows of the episodes that ended in step ``step_id`` (one device-to-host copy): returns
+        ``(env_index[int32 k], episode_return[k], episode_length[int32 k], flags[int32 k], achieved[k, 3], observation[k, obs_dim])``
+        sorted by environment index."""
+        if getattr(self, "_fin_stage", None) is None or self._fin_stage.shape[1] < 8 + self.obs_dim:
+            w = (8 + 6 + 14 + 81 + 3) // 4 * 4
+            self._fin_stage = torch.empty((self.n, w), dtype=torch.float32).pin_memory()
+            self._fin_np = self._fin_stage.numpy().reshape(-1)
+        width = ctypes.c_int()
+        k = self.lib.pg_fetch_finished(self.h, int(step_id), ctypes.c_void_p(self._fin_stage.data_ptr()), self.n, ctypes.byref(width),
+                                       self._stream())
+        if k < 0:
+            _lib.check(k)
+        w = width.value
+        rows = self._fin_np[:k * w].reshape(k, w)
+        order = np.argsort(rows[:, 0].view(np.int32), kind="stable")
+        rows = rows[order]  # fancy indexing copies out of the staging buffer
+        iv = rows[:, :4].view(np.int32)
+        return iv[:, 0].copy(), rows[:, 1].copy(), iv[:, 2].copy(), iv[:, 3].copy(), rows[:, 4:7].copy(), rows[:, 8:8 + self.obs_dim].copy()
+
     def host_layout(self):
         """Byte offsets (observation, achieved_goal, desired_goal, reward, done, flags) and total size of the one-block
         host layout that pg_step_host fills with a single device-to-host copy."""

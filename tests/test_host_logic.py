@@ -94,9 +94,9 @@ def test_lazy_infos():
     term = np.arange(3 * 5, dtype=np.float32).reshape(3, 5); ag = np.zeros((3, 3), np.float32)
     calls = []
 
-    def fetch(idx):
-        calls.append(list(idx))
-        return term, ag, np.array([-3, -101, -50], np.float32), np.array([4, 7, 50])
+    def fetch():  # what PandaBatch.fetch_finished delivers: the finished rows of this step, sorted by environment index
+        calls.append(1)
+        return np.array([1, 2, 3]), term, ag, np.array([-3, -101, -50], np.float32), np.array([4, 7, 50])
 
     infos = LazyInfos(np.ones((4, 3), np.float32), flags, done, fetch, 1.5)
     assert len(infos) == 4 and "terminal_observation" not in infos[0] and calls == []
@@ -110,7 +110,7 @@ def test_lazy_infos():
     assert infos.terminal_observations()["observation"].shape == (3, 5)
     assert infos[3]["TimeLimit.truncated"] and np.array_equal(infos[3]["terminal_observation"]["observation"], term[2])
     assert [i["is_success"] for i in infos] == [False, True, False, False]
-    assert calls == [[1, 2, 3]], "terminal rows are fetched once, and only for finished environments"
+    assert calls == [1], "the finished rows are fetched once, on first use"
 
 
 def test_spaces_and_ids():
