@@ -198,6 +198,15 @@ int pg_get_eval_metrics(pg_handle h, double* out12_host, void* stream);
  * q_dev NULL: the handle's current joint angles, out_dev f32 [num_envs]; else q_dev f32 [7][n] -> out_dev f32 [n]. */
 int pg_manipulability(pg_handle h, const float* q_dev, int64_t n, float* out_dev, void* stream);
 
+/* RobotTaskEnv.render(mode="rgb_array", width, height, target_position, distance, yaw, pitch, roll) (core.py:373-414 ->
+ * pybullet.py:152-180: computeViewMatrixFromYawPitchRoll with upAxisIndex 2, computeProjectionMatrixFOV(60, w / h, 0.1, 100),
+ * getCameraImage).  The reference rasterises with OpenGL, which does not exist on the target machines; this is a CUDA
+ * ray-caster over the same analytic scene (plane, table, the robot's collision primitives, obstacles, object, translucent
+ * goal marker) of environment env_index.  rgba_dev: uint8 [height][width][4] on the device, like getCameraImage's pixels.
+ * target_position NULL = (0, 0, 0); angles in degrees. */
+int pg_render(pg_handle h, int env_index, int width, int height, const float* target_position, float distance, float yaw, float pitch,
+              float roll, uint8_t* rgba_dev, void* stream);
+
 /* ---- matched-state entry points used by the parity tests (pybullet getters/setters of pybullet.py) ---- */
 /* resetJointState for every env (pybullet.py:427-435): q_dev f32 [7][n]; velocities zeroed unless qd_dev given */
 int pg_set_joint_state(pg_handle h, const float* q_dev, const float* qd_dev, void* stream);

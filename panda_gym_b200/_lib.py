@@ -91,6 +91,7 @@ SYMBOLS = [
     ("pg_set_object_state", c_int, [P, P, P]),
     ("pg_observe", c_int, [P, P]),
     ("pg_manipulability", c_int, [P, P, c_i64, P, P]),
+    ("pg_render", c_int, [P, c_int, c_int, c_int, P, c_float, c_float, c_float, c_float, P, P]),
     ("pg_set_eval_metrics", c_int, [P, c_int, P]),
     ("pg_get_eval_metrics", c_int, [P, P, P]),
     ("pg_debug_substeps", c_int, [c_int, c_int, P, P, P, P, c_int, c_int, P]),

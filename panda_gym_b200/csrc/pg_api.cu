@@ -553,6 +553,48 @@ int pg_observe(pg_handle h, void* stream) {
   return PG_OK;
 }
 
+// computeViewMatrixFromYawPitchRoll(upAxisIndex = 2) + computeProjectionMatrixFOV(60, w / h, 0.1, 100) as Bullet builds them:
+// eye = target + Rz(yaw) Ry(roll) Rx(pitch) (0, -distance, 0), up = the same rotation of (0, 0, 1)
+static void build_camera(pg::Camera& cam, int width, int height, const float* target, float distance, float yaw_deg, float pitch_deg, float roll_deg) {
+  const double D2R = 0.017453292519943295;
+  const double y = yaw_deg * D2R, p = pitch_deg * D2R, r = roll_deg * D2R;
+  const double cy = cos(y), sy = sin(y), cp = cos(p), sp = sin(p), cr = cos(r), sr = sin(r);
+  // R = Rz(y) Ry(r) Rx(p)
+  const double R[3][3] = {{cy * cr, cy * sr * sp - sy * cp, cy * sr * cp + sy * sp},
+                          {sy * cr, sy * sr * sp + cy * cp, sy * sr * cp - cy * sp},
+                          {-sr, cr * sp, cr * cp}};
+  double eye[3], up[3], f[3], s[3], u[3];
+  for (int k = 0; k < 3; k++) { eye[k] = target[k] + R[k][1] * (-(double)distance); up[k] = R[k][2]; }
+  double fl = 0, sl = 0;
+  for (int k = 0; k < 3; k++) { f[k] = target[k] - eye[k]; fl += f[k] * f[k]; }
+  fl = sqrt(fl);
+  for (int k = 0; k < 3; k++) f[k] /= fl;
+  s[0] = f[1] * up[2] - f[2] * up[1]; s[1] = f[2] * up[0] - f[0] * up[2]; s[2] = f[0] * up[1] - f[1] * up[0];
+  for (int k = 0; k < 3; k++) sl += s[k] * s[k];
+  sl = sqrt(sl);
+  for (int k = 0; k < 3; k++) s[k] /= sl;
+  u[0] = s[1] * f[2] - s[2] * f[1]; u[1] = s[2] * f[0] - s[0] * f[2]; u[2] = s[0] * f[1] - s[1] * f[0];
+  for (int k = 0; k < 3; k++) { cam.eye[k] = (float)eye[k]; cam.fwd[k] = (float)f[k]; cam.right[k] = (float)s[k]; cam.up[k] = (float)u[k]; }
+  cam.tan_half_fov = (float)tan(0.5 * 60.0 * D2R); cam.aspect = (float)width / (float)height;
+  cam.near_plane = 0.1f; cam.far_plane = 100.0f; cam.width = width; cam.height = height;
+}
+
+int pg_render(pg_handle h, int env_index, int width, int height, const float* target_position, float distance, float yaw, float pitch,
+              float roll, uint8_t* rgba_dev, void* stream) {
+  if (!h || !rgba_dev) return fail(PG_ERR_ARG, "NULL argument");
+  if (env_index < 0 || env_index >= h->P.n) return fail(PG_ERR_ARG, "env_index out of range");
+  if (width <= 0 || height <= 0 || width > 8192 || height > 8192) return fail(PG_ERR_ARG, "bad image size");
+  if (!(distance > 0.f)) return fail(PG_ERR_ARG, "distance must be positive");
+  PG_CUDA(cudaSetDevice(h->device));
+  const float zero[3] = {0.f, 0.f, 0.f};
+  pg::Camera cam;
+  build_camera(cam, width, height, target_position ? target_position : zero, distance, yaw, pitch, roll);
+  pg::launch_render(h->P, cam, env_index, rgba_dev, (cudaStream_t)stream);
+  h->launches++;
+  PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
 int pg_set_eval_metrics(pg_handle h, int enable, void* stream) {
   if (!h) return fail(PG_ERR_ARG, "NULL handle");
   PG_CUDA(cudaSetDevice(h->device));

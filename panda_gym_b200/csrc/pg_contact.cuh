@@ -67,6 +67,12 @@ struct CStore {
     const int off = c < kPairContacts ? c * kCF0 : kPairContacts * kCF0 + (c - kPairContacts) * kCF1;
     return base[(off + k) * stride];
   }
+  // slot c as slot 0 of a shifted store: one address computation per contact, immediate offsets after it
+  __device__ __forceinline__ CStore view(int c) const {
+    CStore V; V.stride = stride;
+    V.base = base + (c < kPairContacts ? c * kCF0 : kPairContacts * kCF0 + (c - kPairContacts) * kCF1) * stride;
+    return V;
+  }
   __device__ __forceinline__ V3 vec(int c, int k) const { return v3(at(c, k), at(c, k + 1), at(c, k + 2)); }
   __device__ __forceinline__ void put(int c, int k, V3 v) const { at(c, k) = v.x; at(c, k + 1) = v.y; at(c, k + 2) = v.z; }
 };
@@ -397,31 +403,37 @@ __device__ __forceinline__ float solve_row(const CStore& S, const RowCtx& C, int
   return delta;
 }
 
+// The sweeps stay ROLLED (one copy of each row body per pair kind): the solver loop has to sit in the 32 KB instruction
+// cache the SM's four warps share, see profiles/r02_k_step_obj.md.
+#ifndef PG_OBJ_UNROLL
+#define PG_OBJ_UNROLL 1
+#endif
+constexpr int kObjUnroll = PG_OBJ_UNROLL;
 // normal rows of one pair, in contact order; `act` collects how far the object-table island still moves (pair 0)
 template <int KIND>
 __device__ __forceinline__ void sweep_normals(const CStore& S, const RowCtx& C, int cnt, float* V7, float* F7, V3& dvl, V3& dvw, float& res,
                                               float& act) {
-#pragma unroll
+#pragma unroll kObjUnroll
   for (int i = 0; i < kPairContacts; i++) {
-    if (i < cnt) {
-      const int c = KIND * kPairContacts + i;
-      const float delta = solve_row<KIND, 0>(S, C, c, 0.f, 1e10f, V7, F7, dvl, dvw, res);
-      if (KIND == 0) act = fmaxf(act, fabsf(delta) - 2.4e-7f * fabsf(S.at(c, 17)));
-    }
+    if (i >= cnt) break;
+    const CStore Sc = S.view(KIND * kPairContacts + i);
+    const float delta = solve_row<KIND, 0>(Sc, C, 0, 0.f, 1e10f, V7, F7, dvl, dvw, res);
+    if (KIND == 0) act = fmaxf(act, fabsf(delta) - 2.4e-7f * fabsf(Sc.at(0, 17)));
   }
 }
 // friction rows of one pair, bounded by mu x the normal impulse
 template <int KIND>
 __device__ __forceinline__ void sweep_frictions(const CStore& S, const RowCtx& C, int cnt, float* V7, float* F7, V3& dvl, V3& dvw, float& res,
                                                 float& act) {
-#pragma unroll
+#pragma unroll kObjUnroll
   for (int i = 0; i < kPairContacts; i++) {
-    const int c = KIND * kPairContacts + i;
-    const float tot = i < cnt ? S.at(c, 17) : 0.f;
+    if (i >= cnt) break;
+    const CStore Sc = S.view(KIND * kPairContacts + i);
+    const float tot = Sc.at(0, 17);
     if (tot > 0.f) {
-      const float lim = S.at(c, 10) * tot;
-      const float d1 = solve_row<KIND, 1>(S, C, c, -lim, lim, V7, F7, dvl, dvw, res);
-      const float d2 = solve_row<KIND, 2>(S, C, c, -lim, lim, V7, F7, dvl, dvw, res);
+      const float lim = Sc.at(0, 10) * tot;
+      const float d1 = solve_row<KIND, 1>(Sc, C, 0, -lim, lim, V7, F7, dvl, dvw, res);
+      const float d2 = solve_row<KIND, 2>(Sc, C, 0, -lim, lim, V7, F7, dvl, dvw, res);
       if (KIND == 0) act = fmaxf(act, fmaxf(fabsf(d1), fabsf(d2)) - 2.4e-7f * lim);
     }
   }
@@ -534,9 +546,9 @@ __device__ __forceinline__ void world_substep(bool active, bool velocity, bool u
 #pragma unroll
       for (int k = 0; k < 21; k++) G[k] = 0.f;
     }
-    for (int i = 0; i < nt; i++) setup_contact<0>(S, C, G, V7p, i);
-    for (int i = 0; i < nr; i++) setup_contact<1>(S, C, G, V7p, kPairContacts + i);
-    for (int i = 0; i < ns; i++) setup_contact<2>(S, C, G, V7p, 2 * kPairContacts + i);
+    for (int i = 0; i < nt; i++) setup_contact<0>(S.view(i), C, G, V7p, 0);
+    for (int i = 0; i < nr; i++) setup_contact<1>(S.view(kPairContacts + i), C, G, V7p, 0);
+    for (int i = 0; i < ns; i++) setup_contact<2>(S.view(2 * kPairContacts + i), C, G, V7p, 0);
   }
   if (SYNC) __syncthreads();
   if (active) {

@@ -9,6 +9,11 @@ namespace pg {
 struct Params;
 struct HerParams;
 struct HerBatch;
+struct Camera {          // built on the host (pg_api.cu), Bullet's view / projection conventions
+  float eye[3], fwd[3], right[3], up[3];
+  float tan_half_fov, aspect, near_plane, far_plane;
+  int width, height;
+};
 
 // pg_tu_step.cu
 void launch_step(const Params& P, const float* actions, cudaStream_t s);
@@ -30,6 +35,8 @@ void launch_debug_minv(int n, const float* q, float* out, cudaStream_t s);
 void launch_debug_ik(int n, const float* q, const float* tgt, float bx, float by, float bz, float* out, cudaStream_t s);
 void launch_fma_peak(int blocks, float* out, int iters, cudaStream_t s);
 
+// pg_tu_render.cu
+void launch_render(const Params& P, const Camera& cam, int env, uint8_t* out, cudaStream_t s);
 // pg_tu_her.cu
 void launch_her_add(const HerParams& H, const float* obs, const float* ag, const float* dg, const float* nobs, const float* nag,
                     const float* ndg, const float* act, const float* rew, const uint8_t* done, const uint8_t* timeout, cudaStream_t s);
