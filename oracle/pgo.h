@@ -155,6 +155,11 @@ void pgo_env_get_obs(pgo_env*, float* obs, float* achieved, float* desired);
 /* compute_reward(achieved, desired) vectorised over n rows, the HER relabel entry (core.py:282) */
 void pgo_env_compute_reward(pgo_env*, const float* ag, const float* dg, int n, float* out);
 int pgo_env_is_collided(const pgo_env*);
+void pgo_env_get_config(const pgo_env*, pgo_env_config* out);
+void pgo_env_get_table(const pgo_env*, double pos[3], double half[3]);
+/* render("rgb_array") restated (pgo_render.c): RGBA8 [height][width][4]; camera arguments as PyBullet.render (pybullet.py:117-180) */
+void pgo_render(pgo_env*, int width, int height, const double target[3], double distance, double yaw_deg, double pitch_deg,
+                double roll_deg, unsigned char* rgba);
 
 #ifdef __cplusplus
 }

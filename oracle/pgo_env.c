@@ -630,3 +630,11 @@ int pgo_bench_rollout(const pgo_env_config* cfg, uint64_t seed, int steps, doubl
 void pgo_test_distance(const float* a, const float* b, int n, float* out) {
   for (int i = 0; i < n; i++) out[i] = f32_distance(a + 3 * i, b + 3 * i);
 }
+
+/* accessors for the render oracle (pgo_render.c) */
+void pgo_env_get_config(const pgo_env* e, pgo_env_config* out) { *out = e->cfg; }
+void pgo_env_get_table(const pgo_env* e, double pos[3], double half[3]) {
+  const double* p = e->cfg.task >= 2 ? e->world.table_pos : e->table_pos;
+  const double* h = e->cfg.task >= 2 ? e->world.table_half : e->table_half;
+  for (int k = 0; k < 3; k++) { pos[k] = p[k]; half[k] = h[k]; }
+}

@@ -124,9 +124,13 @@ class RobotTaskEnv:
     def remove_state(self, state_id):
         self.batch.remove_state(state_id)
 
-    def render(self, mode="human", **kwargs):
-        # no graphics stack exists on the target machines: rendering is out of scope
-        return None
+    def render(self, mode="rgb_array", width=720, height=480, target_position=None, distance=1.4, yaw=45, pitch=-30, roll=0):
+        """core.py:370-389 -> PyBullet.render.  "rgb_array": the scene ray-cast on the GPU (pg_render), uint8 [height, width, 4]
+        like getCameraImage's pixels; "human" (a window paced in real time) has nothing to show on a headless machine."""
+        if mode != "rgb_array":
+            return None
+        img = self.batch.render(0, width, height, target_position, distance, yaw, pitch, roll)
+        return img.cpu().numpy()
 
     def close(self):
         self.batch.close()

@@ -230,6 +230,15 @@ class PandaBatch:
             _lib.check(self.lib.pg_manipulability(self.h, ctypes.c_void_p(q.data_ptr()), q.shape[1], ctypes.c_void_p(out.data_ptr()), self._stream()))
         return out
 
+    def render(self, env_index=0, width=720, height=480, target_position=None, distance=1.4, yaw=45.0, pitch=-30.0, roll=0.0):
+        """PyBullet.render(mode="rgb_array") (pybullet.py:117-180) for one environment: uint8 [height][width][4] on the
+        device, ray-cast by k_render (no graphics stack involved)."""
+        out = torch.empty((int(height), int(width), 4), dtype=torch.uint8, device=self.device)
+        tp = (ctypes.c_float * 3)(*(target_position if target_position is not None else (0.0, 0.0, 0.0)))
+        _lib.check(self.lib.pg_render(self.h, int(env_index), int(width), int(height), tp, float(distance), float(yaw), float(pitch),
+                                      float(roll), ctypes.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
     def save_state(self):
         sid = ctypes.c_int(-1)
         _lib.check(self.lib.pg_save_state(self.h, ctypes.byref(sid), self._stream()))

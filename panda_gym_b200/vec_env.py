@@ -234,6 +234,15 @@ class PandaVecEnv:
         from .sharding import benchmark_results
         return benchmark_results(self.batch.eval_metrics_raw(), n_substeps=self.batch.cfg.n_substeps, group=group)
 
+    def get_images(self, width=720, height=480, indices=None, **camera):
+        """SB3 VecEnv.get_images: one rgb_array frame per environment in `indices` (default: the first), uint8 [h, w, 4]."""
+        idx = [0] if indices is None else list(indices)
+        return [self.batch.render(i, width, height, **camera).cpu().numpy() for i in idx]
+
+    def render(self, mode="rgb_array", **kwargs):
+        """SB3 VecEnv.render("rgb_array") for the first environment (a tiled view of thousands of environments is not useful)."""
+        return self.get_images(**kwargs)[0] if mode == "rgb_array" else None
+
     def close(self):
         self.batch.close()
 

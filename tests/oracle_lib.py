@@ -117,6 +117,7 @@ def lib():
     sig("pgo_env_get_obs", None, P, P, P, P)
     sig("pgo_env_compute_reward", None, P, P, P, c_int, P)
     sig("pgo_env_is_collided", c_int, P)
+    sig("pgo_render", None, P, c_int, c_int, P, ctypes.c_double, ctypes.c_double, ctypes.c_double, ctypes.c_double, P)
     sig("pgo_bench_rollout", c_int, P, c_u64, c_int, P)
     sig("pgo_env_object", ctypes.POINTER(Body), P)
     sig("pgo_env_world", ctypes.POINTER(World), P)
@@ -310,6 +311,12 @@ class Env:
         n = self.L.pgo_world_contacts(self.L.pgo_env_arm(self.h), self.L.pgo_env_object(self.h), self.L.pgo_env_world(self.h), arr)
         return [dict(kind=c.kind, link=c.link, d=c.d, n=np.array(c.n[:]), pa=np.array(c.pa[:]), pb=np.array(c.pb[:]), mu=c.mu)
                 for c in arr[:n]]
+
+    def render(self, width=720, height=480, target_position=(0.0, 0.0, 0.0), distance=1.4, yaw=45.0, pitch=-30.0, roll=0.0):
+        out = np.zeros((height, width, 4), np.uint8)
+        tp = np.asarray(target_position, np.float64)
+        self.L.pgo_render(self.h, width, height, dp(tp), distance, yaw, pitch, roll, dp(out))
+        return out
 
     def compute_reward(self, ag, dg):
         ag = np.ascontiguousarray(ag, dtype=np.float32).reshape(-1, 3); dg = np.ascontiguousarray(dg, dtype=np.float32).reshape(-1, 3)

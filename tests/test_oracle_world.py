@@ -121,3 +121,33 @@ def test_push_moves_the_object_and_reward_follows(oracle):
         succ.append(f["is_success"])
     assert o["achieved_goal"][0] > start[0] + 0.02  # pushed along +x
     assert abs(o["achieved_goal"][2] - 0.02) < 2e-3  # still flat on the table
+
+
+def test_render_oracle_camera_and_scene():
+    """pgo_render (the checker of k_render): Bullet's yaw / pitch / roll camera and the scene content.
+    The camera target projects to the image centre; yaw 0 looks along +y, yaw 90 along -x (pybullet.py:152-180 defaults)."""
+    import oracle_lib as OL
+    e = OL.Env(task=1, scenario="reachao3")
+    e.reset(3)
+    g = np.array([0.35, 0.1, 0.3])
+    e.set_goal(g)
+    w, h = 121, 81
+    img = e.render(width=w, height=h, target_position=tuple(g), distance=0.5, yaw=30.0, pitch=-20.0, roll=0.0)
+    assert img.shape == (h, w, 4) and (img[..., 3] == 255).all()
+    c = img[h // 2, w // 2, :3].astype(int)
+    assert c[1] > c[0] + 40 and c[1] > c[2] + 40          # the green goal marker sits at the centre pixel
+    assert (img[..., :3] == (179, 179, 204)).all(axis=2).any()   # background (0.7, 0.7, 0.8) above the horizon
+    # deterministic
+    assert np.array_equal(img, e.render(width=w, height=h, target_position=tuple(g), distance=0.5, yaw=30.0, pitch=-20.0, roll=0.0))
+    # yaw turns the camera about the world z axis through the target: an obstacle-free Reach scene seen from yaw and
+    # yaw + 180 shows the goal at the centre both times, the table edge mirrored
+    e0 = OL.Env(task=0)
+    e0.reset(1)
+    e0.set_goal(np.array([0.4, 0.3, 0.5]))
+    for yaw in (0.0, 90.0, 180.0):
+        im = e0.render(width=w, height=h, target_position=(0.4, 0.3, 0.5), distance=0.4, yaw=yaw, pitch=-10.0)
+        c = im[h // 2, w // 2, :3].astype(int)
+        assert c[1] > c[0] + 15                        # 30 % green over the bluish background
+    # looking straight down from above the table: the floor / table fill the frame, no background
+    top = e0.render(width=w, height=h, target_position=(0.0, 0.0, 0.0), distance=2.0, yaw=0.0, pitch=-89.9)
+    assert not (top[..., :3] == (179, 179, 204)).all(axis=2).any()
