@@ -46,7 +46,9 @@ struct pg_env_s {
   float* term_ring;                 // [3][n][term_w_max] compact rows of finished episodes (Params::term_rows points into it)
   int term_w_max;
   int64_t step_id;                  // pg_step calls so far; ring slot = step_id % 3
-  int* finished_host;               // page-locked [4]: finished-episode count of the last three steps (by ring slot) 
+  int* finished_host;               // page-locked [4]: finished-episode count of the last three steps (by ring slot)
+  bool dlink_valid;                 // d_link / q_dl of EVERY environment come from an observation pass over the current obstacles
+  bool cull_enabled;                // PANDA_B200_SCENE_CULL != 0 (default on): temporal culling of the flag pass, see scene_skip_mask
 };
 
 namespace {
@@ -208,6 +210,8 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   PG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   pg_env_s* h = new pg_env_s();
   h->sm_count = sms;
+  h->dlink_valid = false;
+  { const char* v = getenv("PANDA_B200_SCENE_CULL"); h->cull_enabled = !(v && v[0] == '0'); }
   h->cfg = *cfg; h->device = device; h->launches = 0; h->first_env = 0; h->d_actions = nullptr; h->eval_metrics = 0;
   h->finished_host = nullptr; h->term_ring = nullptr; h->out_slab = nullptr;
   pg::Params& P = h->P;
@@ -246,7 +250,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
 #define A(ptr, count, st) if ((rc = alloc(h, &ptr, (size_t)(count), st)) != PG_OK) { pg_destroy(h); return rc; }
   A(P.q, 7 * n, true) A(P.qd, 7 * n, true) A(P.goal, 3 * n, true) A(P.obs_pos, (size_t)pg::kMaxObst * 3 * n, true) A(P.obs_pos_f, (size_t)pg::kMaxObst * 3 * n, true)
   A(P.recent, 7 * n, true) A(P.prev, 7 * n, true) A(P.cur_vel, 7 * n, true) A(P.cur_acc, 7 * n, true) A(P.jerk, 7 * n, true)
-  A(P.d_link, 9 * n, true) A(P.past_vec, 54 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
+  A(P.d_link, 9 * n, true) A(P.q_dl, 7 * n, true) A(P.past_vec, 54 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
   A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
   A(P.rng, 4 * n, true) A(P.episode, n, true) A(P.obj, 13 * n, true)
   {  // the six per-step results live in ONE slab so that the host-buffer step moves them with a single device-to-host copy:
@@ -318,6 +322,7 @@ int pg_reset(pg_handle h, const uint8_t* mask_dev, const uint64_t* seeds_dev, vo
   if (!h) return fail(PG_ERR_ARG, "NULL handle");
   PG_CUDA(cudaSetDevice(h->device));
   pg::launch_reset_all(h->P, mask_dev, seeds_dev, h->first_env, (cudaStream_t)stream);
+  if (!mask_dev) h->dlink_valid = true;
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;
@@ -330,8 +335,10 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   h->step_id++;
   h->P.term_w = (8 + h->P.obs_dim + 3) / 4 * 4;
   h->P.term_rows = h->term_ring + (size_t)(h->step_id % 3) * h->P.n * h->term_w_max;
+  h->P.scene.skip_far = h->cull_enabled && h->dlink_valid && h->P.task == 1 && h->P.obstacle_obs != 0 && h->P.scene.nobs > 0;
   if (h->P.task >= 2) pg::launch_step_obj(h->P, actions_dev, (cudaStream_t)stream);
   else pg::launch_step(h->P, actions_dev, (cudaStream_t)stream);
+  h->dlink_valid = true;  // the step ends with the observation pass of every environment
   h->launches++;
   if (h->eval_metrics) {  // perform_benchmark's bookkeeping, on the post-step state and before the auto-reset
     pg::launch_eval_metrics(h->P, (cudaStream_t)stream);
@@ -467,6 +474,7 @@ int pg_restore_state(pg_handle h, int state_id, void* stream) {
   auto it = h->saved.find(state_id);
   if (it == h->saved.end()) return fail(PG_ERR_STATE, "Couldn't restore state.");  // pybullet.error text
   PG_CUDA(cudaSetDevice(h->device));
+  h->dlink_valid = false;
   for (size_t i = 0; i < h->state_bufs.size(); i++)
     PG_CUDA(cudaMemcpyAsync(*h->state_bufs[i].slot, it->second[i], h->state_bufs[i].bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return PG_OK;
@@ -542,12 +550,14 @@ int pg_set_obstacles(pg_handle h, const double* pos_dev, void* stream) {
   PG_CUDA(cudaSetDevice(h->device));
   PG_CUDA(cudaMemcpyAsync(h->P.obs_pos, pos_dev, (size_t)h->P.st.nobs * 3 * h->P.n * sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   pg::launch_mirror_obstacles(h->P, (cudaStream_t)stream);
+  h->dlink_valid = false;  // until the next observation pass (pg_observe / pg_step / full pg_reset)
   return PG_OK;
 }
 int pg_observe(pg_handle h, void* stream) {
   if (!h) return fail(PG_ERR_ARG, "NULL handle");
   PG_CUDA(cudaSetDevice(h->device));
   pg::launch_observe(h->P, (cudaStream_t)stream);
+  h->dlink_valid = true;
   h->launches++;
   PG_CUDA(cudaGetLastError());
   return PG_OK;

@@ -63,6 +63,7 @@ struct Params {
   float *recent, *prev;          // [7][n] action history (panda.py:138-139)
   float *cur_vel, *cur_acc, *jerk; // [7][n] (panda.py:167-172)
   float* d_link;                 // [9][n]
+  float* q_dl;                   // [7][n] joint angles d_link was evaluated at (scene_skip_mask trusts d_link only at exactly this pose)
   float* obj;                    // [13][n] object position, quaternion xyzw, linear / angular velocity (tasks 2, 3)
   float* past_vec;               // [2][27][n] previous two vector observations ("vectors+past", reach_ao.py:918-922)
   uint8_t *have_recent, *have_prev, *collided, *goal_reached, *need_reset;
@@ -243,6 +244,8 @@ __device__ __forceinline__ void observe(const Params& P, int e, const float* q, 
       float mn = dl[0];
 #pragma unroll
       for (int i = 0; i < 9; i++) { P.d_link[(size_t)i * n + e] = dl[i]; mn = fminf(mn, dl[i]); }
+#pragma unroll
+      for (int d = 0; d < 7; d++) P.q_dl[(size_t)d * n + e] = q[d];
       if (P.obstacle_obs == 1) {
 #pragma unroll
         for (int i = 0; i < 9; i++) { o[off + i] = dl[i]; o[off + 9 + 3 * i] = ul[i].x; o[off + 10 + 3 * i] = ul[i].y; o[off + 11 + 3 * i] = ul[i].z; }

@@ -15,6 +15,7 @@ struct SceneParams {
   float table_pos[3], table_core[3], table_margin;
   int has_table;
   int has_box;                 // any cuboid obstacle in the scene (selects the barrier pattern of the flag pass)
+  int skip_far;                // d_link of every environment is current: the flag pass may cull links by it (scene_skip_mask)
 };
 
 // primitives of collision-link slot S: [first, first + count)
@@ -158,18 +159,60 @@ template <int K0> struct PrimLoop<K0, 0> {
   static __device__ __forceinline__ bool hits_kind(const Frame&, V3, const Obst&, int) { return false; }
 };
 
+// ---- temporal culling of the per-substep flag pass.
+// Obstacles do not move during a step, and the observation pass that ended the previous step (or the reset) left the exact
+// minimum distance d0 of every collision link to the obstacles at the pose q0 this step starts from.  Slot S lies inside the
+// ball of radius R_S about its centre c_S (first primitive), rigid with joint frame k.  Going from q0 to q, a point
+// c_S + v of it is displaced by at most
+//     M_S = |c_S(q) - c_S(q0)| + R_S * sum_{j <= k} |q_j - q0_j|
+// (translation of the centre plus |v| <= R_S times the angle the frame has turned by, which the joint angles bound).  While
+// d0_S - M_S stays positive no collider of the slot can touch an obstacle and its obstacle tests are skipped for this
+// substep: the flags are the ones the full test gives (tests/test_gpu_parity.py::test_flag_pass_culling_changes_nothing
+// compares whole rollouts bit for bit).  The table test has its own height cull and is not affected.
+constexpr float kSkipMargin = 2e-3f;  // fp32 error of d0 (GJK / closed forms: ~1e-5) with two orders of magnitude to spare
+struct CullState {                    // per-thread slices of the block's shared memory, element i at [i * stride]
+  const float* q; const float* q0;    // joint angles now / at the start of the step
+  const float* slack;                 // [9] d0_S - kSkipMargin (negative: do not cull)
+  const float* ctr0;                  // [9][3] slot centres at q0
+  int stride;
+};
+template <int S> __device__ __forceinline__ V3 slot_centre(const Frame& F) {
+  using P0 = pgm::Prim<slot_first(S)>;
+  return frame_point(F, P0::x, P0::y, P0::z);
+}
+// slot centres at the pose (cq, sq) into ctr0 (start of a step)
+__device__ __forceinline__ void scene_centres(V3 base, const float* cq, const float* sq, float* ctr0, int stride) {
+  Frame F = base_frame(base);
+  V3 c;
+#define PG_PUT(S) c = slot_centre<S>(F); ctr0[(3 * S) * stride] = c.x; ctr0[(3 * S + 1) * stride] = c.y; ctr0[(3 * S + 2) * stride] = c.z;
+  F = frame_step<1>(F, cq[0], sq[0]); PG_PUT(0)
+  F = frame_step<2>(F, cq[1], sq[1]); PG_PUT(1)
+  F = frame_step<3>(F, cq[2], sq[2]); PG_PUT(2)
+  F = frame_step<4>(F, cq[3], sq[3]); PG_PUT(3)
+  F = frame_step<5>(F, cq[4], sq[4]); PG_PUT(4)
+  F = frame_step<6>(F, cq[5], sq[5]); PG_PUT(5)
+  F = frame_step<7>(F, cq[6], sq[6]); PG_PUT(6) PG_PUT(7) PG_PUT(8)
+#undef PG_PUT
+}
+
 // One collision link.  FULL: exact per-link minimum distance + closest pair (observation); otherwise only
 // "is any distance <= 0", with bounding-sphere culling.  obs_pos: f32 [kMaxObst][3][n] (SoA), e = env.
 template <int S, bool FULL>
 __device__ __forceinline__ void slot_eval(const SceneParams& P, const float* __restrict__ obs_pos, int n, int e, const Frame& F,
-                                          bool& hit, float& d_out, V3& u_out, CylBoxQueue* Q) {
+                                          bool& hit, float& d_out, V3& u_out, CylBoxQueue* Q, const CullState* cull = nullptr, float turned = 0.f) {
   constexpr int K0 = slot_first(S), N = slot_count(S);
   using P0 = pgm::Prim<K0>;
   constexpr float R = SlotBound<K0, N>::value + 0.002f;
   float best = FULL ? 999.0f : 1e-6f;  // FULL: pyb_utils saturates at max_distance; flag-only: just the sign matters
   V3 dir = v3(0, 0, 0);
   V3 ctr = frame_point(F, P0::x, P0::y, P0::z);
-  for (int j = 0; j < P.nobs; j++) {
+  int nobs = P.nobs;
+  if (!FULL && cull) {  // temporal culling: the slot cannot have reached any obstacle yet
+    const int st = cull->stride;
+    const V3 d = ctr - v3(cull->ctr0[(3 * S) * st], cull->ctr0[(3 * S + 1) * st], cull->ctr0[(3 * S + 2) * st]);
+    if (cull->slack[S * st] > norm(d) + R * turned) nobs = 0;
+  }
+  for (int j = 0; j < nobs; j++) {
     V3 o = v3(obs_pos[(size_t)(j * 3 + 0) * n + e], obs_pos[(size_t)(j * 3 + 1) * n + e], obs_pos[(size_t)(j * 3 + 2) * n + e]);
     if (!FULL) {
       V3 d = o - ctr;
@@ -193,32 +236,34 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const float* __r
 // SYNC: called by every thread of the block (see substep) with block barriers between groups of links.
 template <bool FULL, bool SYNC>
 __device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, const float* __restrict__ obs_pos, int n, int e, V3 base,
-                                           const float* cq, const float* sq, float* d_link, V3* u_link) {
+                                           const float* cq, const float* sq, float* d_link, V3* u_link, const CullState* cull = nullptr) {
   bool hit = false;
+  float turned = 0.f;  // sum of |q_j - q0_j| over the joints up to the current frame
+#define PG_TURN(j) if (!FULL && cull) turned += fabsf(cull->q[(j) * cull->stride] - cull->q0[(j) * cull->stride]);
   float d; V3 u;
   CylBoxQueue queue; queue.n = 0;
   CylBoxQueue* Q = FULL ? &queue : nullptr;
   Frame F = base_frame(base);
   if (active) {
-    F = frame_step<1>(F, cq[0], sq[0]); slot_eval<0, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[0] = d; u_link[0] = u; }
-    F = frame_step<2>(F, cq[1], sq[1]); slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[1] = d; u_link[1] = u; }
-    F = frame_step<3>(F, cq[2], sq[2]); slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[2] = d; u_link[2] = u; }
+    F = frame_step<1>(F, cq[0], sq[0]); PG_TURN(0) slot_eval<0, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[0] = d; u_link[0] = u; }
+    F = frame_step<2>(F, cq[1], sq[1]); PG_TURN(1) slot_eval<1, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[1] = d; u_link[1] = u; }
+    F = frame_step<3>(F, cq[2], sq[2]); PG_TURN(2) slot_eval<2, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[2] = d; u_link[2] = u; }
   }
   if (SYNC && (FULL || PG_SCENE_SYNC == 1 || (PG_SCENE_SYNC == 2 && P.has_box))) __syncthreads();
   if (active) {
-    F = frame_step<4>(F, cq[3], sq[3]); slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[3] = d; u_link[3] = u; }
-    F = frame_step<5>(F, cq[4], sq[4]); slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[4] = d; u_link[4] = u; }
+    F = frame_step<4>(F, cq[3], sq[3]); PG_TURN(3) slot_eval<3, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[3] = d; u_link[3] = u; }
+    F = frame_step<5>(F, cq[4], sq[4]); PG_TURN(4) slot_eval<4, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[4] = d; u_link[4] = u; }
   }
   if (SYNC && (FULL || PG_SCENE_SYNC == 1 || (PG_SCENE_SYNC == 2 && P.has_box))) __syncthreads();
   if (active) {
-    F = frame_step<6>(F, cq[5], sq[5]); slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[5] = d; u_link[5] = u; }
-    F = frame_step<7>(F, cq[6], sq[6]);
-    slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[6] = d; u_link[6] = u; }
+    F = frame_step<6>(F, cq[5], sq[5]); PG_TURN(5) slot_eval<5, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[5] = d; u_link[5] = u; }
+    F = frame_step<7>(F, cq[6], sq[6]); PG_TURN(6)
+    slot_eval<6, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[6] = d; u_link[6] = u; }
   }
   if (SYNC && (FULL || PG_SCENE_SYNC == 1 || (PG_SCENE_SYNC == 2 && P.has_box))) __syncthreads();
   if (active) {
-    slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[7] = d; u_link[7] = u; }
-    slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u, Q); if (FULL) { d_link[8] = d; u_link[8] = u; }
+    slot_eval<7, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[7] = d; u_link[7] = u; }
+    slot_eval<8, FULL>(P, obs_pos, n, e, F, hit, d, u, Q, cull, turned); if (FULL) { d_link[8] = d; u_link[8] = u; }
   }
   if (FULL && active) {
     // drain the deferred cylinder-box queries, the whole warp together
@@ -243,6 +288,7 @@ __device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, co
       if (b <= 0.f) hit = true;
     }
   }
+#undef PG_TURN
   if (SYNC && PG_SYNC_E) __syncthreads();
   return hit;
 }

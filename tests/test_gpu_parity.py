@@ -829,3 +829,46 @@ def test_render_matches_oracle(sim, oracle, task, scenario):
         assert (diff <= 1).mean() > 0.995, (diff > 1).mean()
         assert (gpu[..., 3] == 255).all()
         assert len(np.unique(gpu[..., :3].reshape(-1, 3), axis=0)) > 50   # not a blank frame: robot, table, floor, sky
+
+
+# ---------------------------------------------------------------- temporal culling of the flag pass (scene_skip_mask)
+@pytest.mark.parametrize("scenario", ["reachao_rand", "reachao3", "wangexp-3"])
+def test_flag_pass_culling_changes_nothing(sim, scenario, monkeypatch):
+    """The per-substep collision test skips a link while its last exact obstacle distance exceeds a rigorous bound on how
+    far the link can have moved since (pg_scene.cuh).  With the culling switched off (PANDA_B200_SCENE_CULL=0, read by
+    pg_create) every output of a long auto-resetting rollout must be bit-identical."""
+    n, steps = 4096, 70
+    outs = []
+    for cull in ("0", "1"):
+        monkeypatch.setenv("PANDA_B200_SCENE_CULL", cull)
+        cfg = sim.make_config(1, n, scenario=scenario, max_episode_steps=50, auto_reset=True)
+        b = sim.PandaBatch(cfg); b.seed(99); b.reset()
+        rec = []
+        for k in range(steps):
+            b.step(b.random_actions(31, k))
+            rec.append((b.view("flags").clone(), b.view("reward").clone(), b.view("observation").clone(), b.view("q").clone()))
+        torch.cuda.synchronize()
+        outs.append(rec)
+        stats = b.view("stats").cpu().numpy()
+    collided = 0
+    for k in range(steps):
+        for a, c in zip(outs[0][k], outs[1][k]):
+            assert torch.equal(a, c), (scenario, k)
+        collided += int((outs[0][k][0] & 4).ne(0).sum())
+    assert collided > 50, "the rollout must actually contain collisions for the comparison to mean something"
+    # a state written behind the library's back (zero-copy view) without pg_observe: the stale distances are not trusted
+    monkeypatch.setenv("PANDA_B200_SCENE_CULL", "1")
+    res = []
+    for cull in ("0", "1"):
+        monkeypatch.setenv("PANDA_B200_SCENE_CULL", cull)
+        cfg = sim.make_config(1, 512, scenario=scenario, max_episode_steps=50, auto_reset=False)
+        b = sim.PandaBatch(cfg); b.seed(5); b.reset()
+        b.step(b.random_actions(1, 0))
+        g = torch.Generator(device="cpu").manual_seed(3)
+        qn = torch.tensor(Q_LO, dtype=torch.float32)[:, None] + torch.rand((7, 512), generator=g) * torch.tensor(Q_HI - Q_LO, dtype=torch.float32)[:, None]
+        b.view("q").copy_(qn.to(dev()))
+        b.step(torch.zeros((512, b.act_dim), device=dev()))
+        torch.cuda.synchronize()
+        res.append(b.view("flags").clone())
+    assert torch.equal(res[0], res[1])
+    assert int((res[0] & 4).ne(0).sum()) > 10
