@@ -31,6 +31,8 @@ import sys
 import threading
 import time
 
+import numpy as np
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 # Rank 0 must print exactly ONE JSON line on stdout.  Native libraries write there too (NCCL's "NCCL version ..." banner at
 # communicator creation, at any NCCL_DEBUG level >= VERSION), so file descriptor 1 points at stderr for the whole run and is
@@ -308,7 +310,7 @@ def main():
     dev = torch.device("cuda", local)
     # one process per GPU: run on (and take page-locked memory from) the NUMA node the GPU hangs off, BEFORE any pinned
     # allocation -- eight ranks pushing 17 MB per step through the far socket is what held the 8-GPU end-to-end number back
-    numa = sharding.bind_to_local_numa(local) if world > 1 else None
+    numa = sharding.bind_to_local_numa(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     N = args.envs_per_gpu
@@ -382,7 +384,11 @@ def main():
     consumed = 0.0
     t0 = time.perf_counter()
     for k in range(Ke):
-        obs, rew, dones, infos = env.step(host_actions[(k + 3) % len(host_actions)])
+        # the policy's output lands in the environment's page-locked action buffer (PandaVecEnv.action_buffer); the copy into
+        # it stands in for the policy writing there and is part of the timed step
+        abuf = env.action_buffer()
+        np.copyto(abuf, host_actions[(k + 3) % len(host_actions)])
+        obs, rew, dones, infos = env.step(abuf)
         # what a Monitor + replay buffer take from `infos` every step, in vectorised form: which episodes ended, their return and
         # length, whether the ending was a truncation, and the terminal observations (a device gather + copy of those rows)
         fin = infos.finished

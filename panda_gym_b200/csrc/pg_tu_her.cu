@@ -1,4 +1,5 @@
 // pg_tu_her.cu -- kernels of the on-device HER replay buffer (contract: pg_her.cuh)
+#include <cstdio>
 #include "pg_her.cuh"
 #include "pg_launch.h"
 
@@ -116,6 +117,23 @@ __device__ void mt_twist(uint32_t* mt) {
   __syncthreads();
 }
 
+// inclusive prefix sum of one int per thread over a 256-thread block: warp shuffles + one shared exchange of the 8 warp totals
+// (two barriers; s_w is reusable after the call returns); *total = the block's sum
+__device__ __forceinline__ int block_scan256(int v, int* s_w, int* total) {
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  int x = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+  if (lane == 31) s_w[w] = x;
+  __syncthreads();
+  int before = 0, all = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) { const int c = s_w[i]; all += c; if (i < w) before += c; }
+  __syncthreads();
+  *total = all;
+  return x + before;
+}
+
 constexpr int kHerChunk = 1024;  // phase-B elements staged in shared memory at a time
 // Index sampling, numpy-exact.  ONE block of 256 threads (blockDim >= 128 so each twist phase fits 3 values/thread).
 //   phase A: np.random.choice(valid, B) == randint(0, n_valid, B): masked rejection on 32-bit draws, all elements
@@ -129,6 +147,8 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
   __shared__ int s_count, s_stop, s_pos, s_tw_ok;
   __shared__ uint32_t s_rng[kHerChunk], s_tw[624];  // per-element range -> accepted draw; tempered words of the state
   __shared__ int s_cur[kHerChunk], s_st[kHerChunk];
+  __shared__ uint32_t s_msk[kHerChunk];   // per-element rejection mask
+  __shared__ int s_nzc[kHerChunk + 1];    // exclusive count of non-zero ranges before each element of the chunk
   const int t = threadIdx.x;
   for (int k = t; k < 625; k += blockDim.x) mt[k] = H.mt[k];
   __syncthreads();
@@ -137,6 +157,9 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
   if (t == 0) { H.status[0] = 0; s_count = 0; s_pos = (int)mt[624]; }
   __syncthreads();
   const int rows = H.rows, ne = H.n_envs;
+#ifdef PG_HER_TIMING
+  long long tA0 = clock64(), tStage = 0, tWalk = 0, tTwist = 0, tc, tLoop = 0; int nRounds = 0;
+#endif
   // ---- phase A
   const uint32_t rng = (uint32_t)(nv - 1);
   uint32_t mask = rng; mask |= mask >> 1; mask |= mask >> 2; mask |= mask >> 4; mask |= mask >> 8; mask |= mask >> 16;
@@ -149,21 +172,25 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
       int pos = s_pos, avail = 624 - pos, chunk = avail < 256 ? avail : 256;
       uint32_t w = 0; int f = 0;
       if (t < chunk) { w = mt_temper(mt[pos + t]) & mask; f = w <= rng; }
-      s_scan[t] = f;
-      __syncthreads();
-      for (int o = 1; o < 256; o <<= 1) { int x = t >= o ? s_scan[t - o] : 0; __syncthreads(); s_scan[t] += x; __syncthreads(); }
-      int before = s_count, mine = before + s_scan[t] - 1;  // index of this accepted draw
+      int tot;
+      const int incl = block_scan256(f, s_scan, &tot);
+      int before = s_count, mine = before + incl - 1;  // index of this accepted draw
       if (t == 0) s_stop = -1;
       __syncthreads();
-      if (f && mine < B) { int idx = H.valid[w]; H.s_row[mine] = idx / ne; H.s_env[mine] = idx % ne; if (mine == B - 1) s_stop = t; }
+      if (f && mine < B) { H.s_row[mine] = (int)w; if (mine == B - 1) s_stop = t; }  // the raw draw; resolved below, off this loop's critical path
       __syncthreads();
       if (t == 0) {
         if (s_stop >= 0) { s_pos = pos + s_stop + 1; s_count = B; }
-        else { s_pos = pos + chunk; s_count = before + s_scan[255]; }
+        else { s_pos = pos + chunk; s_count = before + tot; }
       }
       __syncthreads();
       if (s_count >= B) break;
     }
+    // draw -> transition: valid[] is a random gather over megabytes (a DRAM round trip each); done for all B at once, the
+    // loads of a thread independent of each other, instead of one dependent load per 256-word iteration above
+    __syncthreads();
+    for (int k = t; k < B; k += blockDim.x) { const int idx = H.valid[H.s_row[k]]; H.s_row[k] = idx / ne; H.s_env[k] = idx % ne; }
+    __syncthreads();
   }
   // ---- phase B (future strategy): t = randint(cur, ep_len) per virtual sample.  numpy draws element by element with a
   // PER-ELEMENT mask and an element whose range is 0 consumes nothing: a sequential automaton over the raw stream.  Only
@@ -171,45 +198,119 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
   // state words are done by the whole block, chunk by chunk; thread 0 walks shared memory only (a few ns per element).
   // The state is regenerated lazily, when a draw is needed and none is left, exactly like numpy.
   __syncthreads();
+#ifdef PG_HER_TIMING
+  long long tA1 = clock64();
+#endif
   if (t == 0) s_tw_ok = 0;
   for (int c0 = 0; c0 < nb_virtual; c0 += kHerChunk) {
+#ifdef PG_HER_TIMING
+    tc = clock64();
+#endif
     const int cn = nb_virtual - c0 < kHerChunk ? nb_virtual - c0 : kHerChunk;
     __syncthreads();
-    for (int k = t; k < cn; k += blockDim.x) {
-      const int row = H.s_row[c0 + k], env = H.s_env[c0 + k];
-      const int st = H.ep_start[(size_t)row * ne + env], len = H.ep_length[(size_t)row * ne + env];
-      const int cur = ((row - st) % rows + rows) % rows;
-      s_rng[k] = (uint32_t)(len - 1 - cur);  // high - 1 - low
-      s_cur[k] = cur; s_st[k] = st;
+    // staging, whole block: ranges, masks and the running count of elements that will draw at all.  Thread t owns the 4
+    // consecutive elements 4t .. 4t+3 so that the prefix count is one block scan of per-thread totals.
+    {
+      int nzl = 0;
+#pragma unroll
+      for (int j = 0; j < kHerChunk / 256; j++) {
+        const int k = t * (kHerChunk / 256) + j;
+        uint32_t r = 0;
+        if (k < cn) {
+          const int row = H.s_row[c0 + k], env = H.s_env[c0 + k];
+          const int st = H.ep_start[(size_t)row * ne + env], len = H.ep_length[(size_t)row * ne + env];
+          const int cur = ((row - st) % rows + rows) % rows;
+          r = (uint32_t)(len - 1 - cur);  // high - 1 - low
+          s_cur[k] = cur; s_st[k] = st;
+        }
+        uint32_t m = r; m |= m >> 1; m |= m >> 2; m |= m >> 4; m |= m >> 8; m |= m >> 16;
+        s_rng[k] = r; s_msk[k] = m;
+        nzl += r != 0u;
+      }
+      int tot;
+      int run = block_scan256(nzl, s_scan, &tot) - nzl;  // exclusive prefix of this thread's first element
+#pragma unroll
+      for (int j = 0; j < kHerChunk / 256; j++) {
+        const int k = t * (kHerChunk / 256) + j;
+        s_nzc[k] = run;
+        run += s_rng[k] != 0u;
+      }
+      if (t == 255) s_nzc[kHerChunk] = run;
     }
     if (t == 0) s_count = 0;
     __syncthreads();
+#ifdef PG_HER_TIMING
+    tStage += clock64() - tc;
+#endif
     while (s_count < cn) {
+#ifdef PG_HER_TIMING
+      tc = clock64();
+#endif
       if (!s_tw_ok) {
         __syncthreads();
         for (int k = t; k < 624; k += blockDim.x) s_tw[k] = mt_temper(mt[k]);
         if (t == 0) s_tw_ok = 1;
         __syncthreads();
       }
-      if (t == 0) {
-        int pos = s_pos, k = s_count;
-        bool need = false;
+      if (t < 32) {
+        // Warp 0 walks the automaton SPECULATIVELY, 32 elements per round.  Lane i takes element k + i and assumes that no
+        // element before it rejects a word: its first word is then pos + (non-zero ranges among k .. k+i-1), a difference
+        // of two staged prefix counts.  It tests that word and the two after it (shift 0, 1, 2).  Up to the first lane
+        // that rejects at shift 0 the assumption held; from that lane on everybody is one word late, so the round goes on
+        // at shift 1 up to the next rejection, then at shift 2.  A round so commits three runs of accepting elements
+        // (acceptance probability (r + 1) / (mask + 1) >= 1/2) for roughly the latency of one element of a sequential walk.
+        int pos = s_pos, k = s_count, need = 0;
+#ifdef PG_HER_TIMING
+        long long tw0 = clock64();
+#endif
         while (k < cn) {
-          const uint32_t r = s_rng[k];
-          uint32_t v = 0;
-          if (r != 0) {
-            uint32_t m = r; m |= m >> 1; m |= m >> 2; m |= m >> 4; m |= m >> 8; m |= m >> 16;
-            bool got = false;
-            while (pos < 624) { v = s_tw[pos++] & m; if (v <= r) { got = true; break; } }
-            if (!got) { need = true; break; }  // state exhausted mid-element: regenerate and retry this element
+#ifdef PG_HER_TIMING
+          nRounds++;
+#endif
+          const int idx = k + t;
+          const bool valid = idx < cn;
+          const int ic = valid ? idx : cn;
+          const uint32_t r = valid ? s_rng[idx] : 0u, m = valid ? s_msk[idx] : 0u;
+          const int p0 = pos + (s_nzc[ic] - s_nzc[k]);
+          const bool nz = r != 0u;
+          uint32_t v[3]; unsigned F[3], I[3];
+#pragma unroll
+          for (int sft = 0; sft < 3; sft++) {
+            const bool in = p0 + sft < 624;
+            v[sft] = (nz && in) ? (s_tw[p0 + sft] & m) : 0u;
+            F[sft] = __ballot_sync(0xffffffffu, valid && nz && !(in && v[sft] <= r));
+            I[sft] = __ballot_sync(0xffffffffu, in);
           }
-          s_rng[k] = v;  // the slot now holds the accepted draw
-          k++;
+          const unsigned nzm = __ballot_sync(0xffffffffu, nz);
+          const int nvalid = __popc(__ballot_sync(0xffffffffu, valid));
+          int cur = 0, rej = 0;
+#pragma unroll
+          for (int sft = 0; sft < 3; sft++) {
+            const unsigned Fs = F[sft] & ~((1u << cur) - 1u);  // rejections among the lanes not committed yet (cur < 32 here)
+            const int f = Fs ? __ffs(Fs) - 1 : nvalid;
+            if (t >= cur && t < f) s_rng[idx] = v[sft];          // the slot now holds the accepted draw (0 for a zero range)
+            cur = f;
+            if (!Fs) break;
+            if (!((I[sft] >> f) & 1u)) { need = 1; break; }      // no word left for element k + f: regenerate, retry it
+            rej++;                                               // the rejected word is consumed; element k + f tries the next one
+          }
+          pos += __popc(nzm & ((cur >= 32) ? 0xffffffffu : ((1u << cur) - 1u))) + rej;
+          k += cur;
+          if (need) { pos = 624; break; }
         }
-        s_pos = pos; s_count = k; s_stop = need ? 1 : 0;
+#ifdef PG_HER_TIMING
+        tLoop += clock64() - tw0;
+#endif
+        if (t == 0) { s_pos = pos; s_count = k; s_stop = need; }
       }
       __syncthreads();
+#ifdef PG_HER_TIMING
+      tWalk += clock64() - tc; tc = clock64();
+#endif
       if (s_stop) { mt_twist(mt); if (t == 0) { s_pos = 0; s_tw_ok = 0; } __syncthreads(); }
+#ifdef PG_HER_TIMING
+      tTwist += clock64() - tc;
+#endif
     }
     for (int k = t; k < cn; k += blockDim.x) {
       const int tt = s_cur[k] + (int)s_rng[k];
@@ -218,6 +319,9 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
     }
   }
   __syncthreads();
+#ifdef PG_HER_TIMING
+  if (t == 0) printf("her exact B=%d: phaseA %lld  stage %lld  walk(+temper) %lld  twist %lld  total %lld cycles; warp loop %lld cycles, %d rounds\n", B, tA1 - tA0, tStage, tWalk, tTwist, clock64() - tA0, tLoop, nRounds);
+#endif
   if (t == 0) mt[624] = (uint32_t)s_pos;
   __syncthreads();
   for (int k = t; k < 625; k += blockDim.x) H.mt[k] = mt[k];

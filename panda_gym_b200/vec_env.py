@@ -114,7 +114,7 @@ class LazyInfos:
 class PandaVecEnv:
     def __init__(self, env_id="PandaReachAO-v3", n_envs=8, seed=None, scenario="reachao1", config=None, device=0,
                  max_episode_steps=50, ee_error_threshold=0.05, speed_threshold=0.1, first_env_index=0, copy_outputs=False,
-                 n_host_buffers=3, **env_kwargs):
+                 n_host_buffers=3, numa_bind=True, **env_kwargs):
         if env_id not in ENV_IDS:
             raise _lib.PandaB200Error("unknown / out-of-scope env id %r (supported: %s)" % (env_id, sorted(ENV_IDS)))
         spec = dict(ENV_IDS[env_id])
@@ -126,6 +126,13 @@ class PandaVecEnv:
                               control_type=spec.get("control_type"), reward_type=spec.get("reward_type"),
                               max_episode_steps=max_episode_steps, ee_error_threshold=ee_error_threshold,
                               speed_threshold=speed_threshold, auto_reset=True)
+        # One process drives one GPU: run it (and allocate its page-locked result buffers) on the CPUs / memory node next to
+        # that GPU.  On a two-socket host the per-step result copy is otherwise 2-3x slower whenever the launcher happened
+        # to start the process on the far socket (profiles/r02_e2e.md).  numa_bind=False leaves the affinity alone.
+        self.numa = None
+        if numa_bind:
+            from .sharding import bind_to_local_numa
+            self.numa = bind_to_local_numa(device if isinstance(device, int) else torch.device(device).index or 0)
         self.batch = sim.PandaBatch(cfg, device=device)
         self.first_env_index = int(first_env_index)
         self.batch.seed(0 if seed is None else seed, self.first_env_index)
@@ -197,8 +204,14 @@ class PandaVecEnv:
     def step_async(self, actions):
         self._actions = actions
 
+    def action_buffer(self):
+        """The page-locked float32 [n_envs, act_dim] array the host-to-device copy of ``step`` reads from.  A policy that writes
+        its actions straight into it and passes it to ``step`` saves the staging copy (1.8 MB at 65 536 environments)."""
+        return self._np_actions
+
     def step_wait(self):
-        np.copyto(self._np_actions, np.asarray(self._actions, dtype=np.float32).reshape(self.num_envs, self.batch.act_dim))
+        if self._actions is not self._np_actions:
+            np.copyto(self._np_actions, np.asarray(self._actions, dtype=np.float32).reshape(self.num_envs, self.batch.act_dim))
         prev_desired = self._last_desired
         _, out, npv = self._next_buffers()
         self.batch.step_host(self._np_actions, out)
