@@ -63,13 +63,16 @@ constexpr int kCStoreFloats = kPairContacts * kCF0 + 2 * kPairContacts * kCF1;
 constexpr int kXG = 42;  // X = M^-1 S^T (7 x 6, row-major) in shared memory; G = S X lives in registers during the row setup
 struct CStore {
   float* base; int stride;
+  int cf = 0;  // a view(c) (one slot seen as slot 0): that slot's field count, for PG_CHECK only
   __device__ __forceinline__ float& at(int c, int k) const {
+    PG_CHECK(cf ? (c == 0 && k >= 0 && k < cf) : (c >= 0 && c < kMaxContacts && k >= 0 && k < (c < kPairContacts ? kCF0 : kCF1)));
     const int off = c < kPairContacts ? c * kCF0 : kPairContacts * kCF0 + (c - kPairContacts) * kCF1;
     return base[(off + k) * stride];
   }
   // slot c as slot 0 of a shifted store: one address computation per contact, immediate offsets after it
   __device__ __forceinline__ CStore view(int c) const {
-    CStore V; V.stride = stride;
+    PG_CHECK(c >= 0 && c < kMaxContacts);
+    CStore V; V.stride = stride; V.cf = c < kPairContacts ? kCF0 : kCF1;
     V.base = base + (c < kPairContacts ? c * kCF0 : kPairContacts * kCF0 + (c - kPairContacts) * kCF1) * stride;
     return V;
   }

@@ -8,6 +8,15 @@
 #pragma once
 #include "pg_dynamics.cuh"
 
+// PG_CHECK: index / invariant assertions of the debug build (-DPG_BOUNDS_CHECK, see tools/bounds_check_run.sh): every
+// run-time-indexed shared / global write site asserts its range and traps with the site's line.  Compiled out otherwise.
+#if defined(PG_BOUNDS_CHECK) && defined(__CUDA_ARCH__)
+#include <cstdio>
+#define PG_CHECK(cond) do { if (!(cond)) { printf("PG_CHECK failed: %s  (%s:%d, block %d thread %d)\n", #cond, __FILE__, __LINE__, (int)blockIdx.x, (int)threadIdx.x); __trap(); } } while (0)
+#else
+#define PG_CHECK(cond) do { } while (0)
+#endif
+
 namespace pg {
 
 constexpr float kHullMargin = 0.001f;

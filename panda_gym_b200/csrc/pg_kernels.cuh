@@ -490,6 +490,7 @@ __device__ __forceinline__ void step_end(const Params& P, int e, const float* q,
     P.need_reset[e] = 1;
     {
       const int slot = atomicAdd(P.reset_count, 1);
+      PG_CHECK(slot >= 0 && slot < P.n);
       P.reset_list[slot] = e;
       float* row = P.term_rows + (size_t)slot * P.term_w;
       row[0] = __int_as_float(e); row[1] = ret; row[2] = __int_as_float(len); row[3] = __int_as_float((int)P.flags[e]);

@@ -177,6 +177,7 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
       int before = s_count, mine = before + incl - 1;  // index of this accepted draw
       if (t == 0) s_stop = -1;
       __syncthreads();
+      PG_CHECK(!(f && mine < B) || (mine >= 0 && w <= rng));
       if (f && mine < B) { H.s_row[mine] = (int)w; if (mine == B - 1) s_stop = t; }  // the raw draw; resolved below, off this loop's critical path
       __syncthreads();
       if (t == 0) {
@@ -271,7 +272,9 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
           const bool valid = idx < cn;
           const int ic = valid ? idx : cn;
           const uint32_t r = valid ? s_rng[idx] : 0u, m = valid ? s_msk[idx] : 0u;
+          PG_CHECK(k >= 0 && k < kHerChunk && ic >= 0 && ic <= kHerChunk && pos >= 0 && pos <= 624);
           const int p0 = pos + (s_nzc[ic] - s_nzc[k]);
+          PG_CHECK(p0 >= pos);
           const bool nz = r != 0u;
           uint32_t v[3]; unsigned F[3], I[3];
 #pragma unroll
@@ -288,6 +291,7 @@ __global__ void __launch_bounds__(256) k_her_indices_exact(HerParams H, int B, i
           for (int sft = 0; sft < 3; sft++) {
             const unsigned Fs = F[sft] & ~((1u << cur) - 1u);  // rejections among the lanes not committed yet (cur < 32 here)
             const int f = Fs ? __ffs(Fs) - 1 : nvalid;
+            PG_CHECK(!(t >= cur && t < f) || (idx >= 0 && idx < cn));
             if (t >= cur && t < f) s_rng[idx] = v[sft];          // the slot now holds the accepted draw (0 for a zero range)
             cur = f;
             if (!Fs) break;
@@ -374,6 +378,8 @@ __global__ void __launch_bounds__(kGatherWarps * 32) k_her_gather(HerParams H, P
       v0[j] = make_float4(0.f, 0.f, 0.f, 0.f); v1[j] = v0[j]; fut[j] = 0.f;
       if (k < B) {
         const int row = H.s_row[k], env = H.s_env[k];
+        PG_CHECK(row >= 0 && row < H.rows && env >= 0 && env < ne && w4 <= 64);
+        PG_CHECK(!(k < nb_virtual) || (H.s_trow[k] >= 0 && H.s_trow[k] < H.rows));
         const float4* __restrict__ rec = reinterpret_cast<const float4*>(H.rec + ((size_t)row * ne + env) * w);
         if (lane < w4) v0[j] = __ldg(rec + lane);
         if (lane + 32 < w4) v1[j] = __ldg(rec + lane + 32);
@@ -410,6 +416,7 @@ __global__ void __launch_bounds__(kGatherWarps * 32) k_her_gather(HerParams H, P
       const int k = base + j;
       if (k < B) {
         const int out = k < nb_virtual ? (B - nb_virtual) + k : k - nb_virtual;  // torch.cat((real, virtual))
+        PG_CHECK(out >= 0 && out < B);
         float4* dst = reinterpret_cast<float4*>(O.packed + (size_t)out * w);
         if (lane < w4) dst[lane] = mine[j * w4 + lane];
         if (lane + 32 < w4) dst[lane + 32] = mine[j * w4 + lane + 32];

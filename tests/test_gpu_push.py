@@ -142,7 +142,12 @@ def test_sliding_and_falling_object(sim, oracle):
 
 
 def test_well_conditioned_push(sim, oracle):
-    """The lowered gripper bar pushes the box along the table: positions within 1 mm for the whole push."""
+    """The lowered gripper bar pushes the box along the table, ten steps free-running (no re-matching).
+    Frictional pushing amplifies perturbations: the ORACLE run twice, the second time with its start state perturbed by 1e-7
+    / 1e-6 (one / ten fp32 ulps of a joint angle), drifts apart by 0.13 mm / 3.2 mm over these ten steps (measured, DESIGN.md
+    "Push parity").  fp32 rounding over 200 substeps is a perturbation of that size, so the free-running bound is 3 mm; the
+    1 mm north-star tolerance is asserted where it is meaningful, from matched states
+    (test_matched_state_single_steps_under_aggressive_pushing)."""
     n = 16
     b, envs, _ = make_pair(sim, oracle, 2, n, seed=3, max_episode_steps=1000)
     down = np.tile(np.array([0.0, 0.0, -1.0], np.float32), (n, 1))
@@ -167,9 +172,9 @@ def test_well_conditioned_push(sim, oracle):
             o, r, f = e.step(a[i])
             # the arm presses on the table while it pushes: its redundant (elbow) self-motion is weakly determined,
             # task-space quantities stay within the north-star tolerance
-            assert np.abs(e.arm.q()[0] - qg[i]).max() < 5e-3, (s, i)
-            assert np.abs(o["observation"][6:9] - og[i][6:9]).max() < 1e-3, (s, i)
-            assert np.abs(o["observation"][:3] - og[i][:3]).max() < 2e-3, (s, i)
+            assert np.abs(e.arm.q()[0] - qg[i]).max() < 1e-2, (s, i)
+            assert np.abs(o["observation"][6:9] - og[i][6:9]).max() < 3e-3, (s, i)
+            assert np.abs(o["observation"][:3] - og[i][:3]).max() < 3e-3, (s, i)
     for i, e in enumerate(envs):
         moved += e.object_state()[0][0] - start[i][0] > 0.01
     assert moved >= n // 2

@@ -1,7 +1,7 @@
 """Small workload touching every kernel family, meant to run under compute-sanitizer (memcheck / racecheck / synccheck):
     compute-sanitizer --tool memcheck python tools/sanitize_run.py
 k_step (block barriers + shared-memory s_q / s_tgt), k_reset<true> (32 lanes of a warp on one environment's state),
-k_step_obj (sub-warp cooperative contact solver), k_her_indices_exact (shared MT19937 state), k_her_gather (shared staging)."""
+k_step_obj (contact store in dynamic shared memory), k_her_indices_exact (shared MT19937 state), k_her_gather (shared staging), k_render."""
 import os
 import sys
 
@@ -35,5 +35,7 @@ env.reset()
 for k in range(4):
     env.step(rng.uniform(-1, 1, (128, 3)).astype(np.float32))
 torch.cuda.synchronize()
-print("push ok", env.episode_stats()["episodes"])
+img = env.render(width=64, height=48)
+torch.cuda.synchronize()
+print("push ok", env.episode_stats()["episodes"], "render", img.shape)
 env.close()
