@@ -57,6 +57,9 @@ typedef struct {
   double ee_error_threshold;        /* reach_ao.py:71 / reach.py:15 */
   double speed_threshold;           /* reach_ao.py:72 */
   int pose_randomizer;              /* pg_pose_randomizer; used only with pg_config.randomize_robot_pose */
+  int custom_neutral;               /* 1: neutral_q replaces Panda.neutral_joint_values (panda.py:67) as the reset pose, the way */
+  double neutral_q[7];              /*    some benchmark-scene builders do (reach_ao.py:322, 343, 356-359, 424-425) */
+  int needs_scene;                  /* set by pg_stage_from_scenario for a benchmark scene: its boxes come from pg_set_scene */
 } pg_stage;
 
 /* Environment configuration.  Replaces the constructor arguments of PandaReachAOEnv / PandaReachEnv
@@ -204,6 +207,15 @@ int pg_manipulability(pg_handle h, const float* q_dev, int64_t n, float* out_dev
  * ray-caster over the same analytic scene (plane, table, the robot's collision primitives, obstacles, object, translucent
  * goal marker) of environment env_index.  rgba_dev: uint8 [height][width][4] on the device, like getCameraImage's pixels.
  * target_position NULL = (0, 0, 0); angles in degrees. */
+/* Static scene shared by all environments: the benchmark scenes of ReachAO.setup_benchmark_scenario (reach_ao.py:292-306,
+ * builders :308-516) as a set of axis-aligned boxes -- every collision link of the scene's URDF bodies (box geometry, or the
+ * cuboid hull of an OBJ mesh) already placed in the world frame by the host loader (panda_gym_b200/scenes.py).
+ * boxes_host: n_boxes x 7 floats = centre xyz, half extents xyz, collision margin (0.001 for URDF-imported shapes);
+ * n_boxes <= 64, 0 removes the scene.  The boxes take part in the per-substep collision flag, the per-link distance
+ * observation and the collision-free goal sampling of reset exactly like the obstacles of a stage; call pg_set_stage (or
+ * pg_reset) afterwards to start episodes in the new scene. */
+int pg_set_scene(pg_handle h, int n_boxes, const float* boxes_host, void* stream);
+
 int pg_render(pg_handle h, int env_index, int width, int height, const float* target_position, float distance, float yaw, float pitch,
               float roll, uint8_t* rgba_dev, void* stream);
 

@@ -20,7 +20,7 @@ extern "C" {
 
 #define PGO_MAXL 16 /* links  */
 #define PGO_MAXD 9  /* dofs   */
-#define PGO_MAXOBS 8 /* obstacle slots per env */
+#define PGO_MAXOBS 64 /* obstacle slots per env: <= 8 sampled obstacles of a training stage, or the boxes of a benchmark scene */
 #define PGO_NCL 9   /* ReachAO collision links: link1..link8, panda_ee (reach_ao.py:98-99) */
 
 /* ---------------------------------------------------------------- robot + Bullet multibody step */
@@ -60,12 +60,14 @@ double pgo_arm_manipulability(const pgo_arm*);
 
 /* ---------------------------------------------------------------- closest distances (getClosestPoints) */
 typedef struct {
-  int type;        /* 0 sphere, 1 box (axis aligned, world), -1 empty slot */
+  int type;        /* 0 sphere, 1 box (axis aligned, world; createCollisionShape: safe margin), 2 box imported from a URDF
+                      (margin gUrdfDefaultCollisionMargin = 0.001), -1 empty slot */
   double pos[3];
   double size[3];  /* sphere: size[0] = radius; box: half extents */
 } pgo_obstacle;
 /* Bullet box collision margin: min(0.04, 0.1 * min half extent) (btBoxShape::setSafeMargin) */
 double pgo_box_margin(const double half[3]);
+double pgo_obstacle_margin(const pgo_obstacle* ob); /* by type: safe margin (1) or 0.001 (2) */
 /* signed distance between one robot collision primitive (index into the model's primitive table,
  * placed by the arm's current FK) and an obstacle; pa/pb = closest points on robot / obstacle */
 double pgo_prim_obstacle_distance(const pgo_arm*, int prim, const pgo_obstacle*, double pa[3], double pb[3]);
@@ -124,10 +126,14 @@ typedef struct {
   int n_obstacles;       /* wang-N / wangexp-N */
   double base_pos[3];
   int randomize_robot_pose; /* train_config.py:26; restated only for set_random_robot_base (scenario wangexp-N, reach_ao.py:711) */
+  /* PGO_SCN_STATIC: a benchmark scene (reach_ao.py:292-516): goal box and neutral joint values of its builder; the scene's
+   * boxes are handed over with pgo_env_set_obstacles (type 2) after pgo_env_create and stay put (no obstacle sampling) */
+  double scene_goal_lo[3], scene_goal_hi[3];
+  int custom_neutral; double neutral_q[7];
 } pgo_env_config;
 
 enum { PGO_SCN_NONE = 0, PGO_SCN_REACH1, PGO_SCN_REACH2, PGO_SCN_REACH3, PGO_SCN_REACHAO1, PGO_SCN_REACHAO2,
-       PGO_SCN_REACHAO3, PGO_SCN_REACHAO_RAND, PGO_SCN_WANG, PGO_SCN_WANGEXP };
+       PGO_SCN_REACHAO3, PGO_SCN_REACHAO_RAND, PGO_SCN_WANG, PGO_SCN_WANGEXP, PGO_SCN_STATIC };
 
 void pgo_env_default_config(pgo_env_config*, int task);
 pgo_env* pgo_env_create(const pgo_env_config*);

@@ -41,6 +41,7 @@ struct pgo_env {
   int obs_sampler;         /* 0 goal box, 1 wang (70/20/10), 2 experimental (50/50), 3 wang-N (70/30) */
   int randomize_obstacles, allow_overlap, random_num_obs, size_lo, size_hi;
   double neutral0; /* Panda.neutral_joint_values[0], mutated by set_random_robot_base */
+  double neutral[7]; /* Panda.neutral_joint_values (panda.py:67), replaced by some benchmark-scene builders */
   double table_pos[3], table_half[3];
   /* Push / PickAndPlace (tasks 2, 3): the free object and its world */
   pgo_body obj;
@@ -133,6 +134,9 @@ static void setup_scenario(pgo_env* e) {
       goal_shell(e, 0.5, 0.8, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 1;
       for (int i = 0; i < c->n_obstacles; i++) add_sphere(e, 0.05);
       break;
+    case PGO_SCN_STATIC:                                                                                     /* :292-516 */
+      goal_box(e, c->scene_goal_lo[0], c->scene_goal_hi[0], c->scene_goal_lo[1], c->scene_goal_hi[1], c->scene_goal_lo[2], c->scene_goal_hi[2]);
+      break;
     default: break;
   }
 }
@@ -141,6 +145,7 @@ pgo_env* pgo_env_create(const pgo_env_config* c) {
   pgo_env* e = (pgo_env*)calloc(1, sizeof *e);
   e->cfg = *c;
   e->arm = pgo_arm_create(0, c->base_pos);
+  for (int d = 0; d < N_ARM; d++) e->neutral[d] = c->custom_neutral ? c->neutral_q[d] : NEUTRAL[d];
   setup_scenario(e);
   pgo_world_default(&e->world);
   e->obj.quat[3] = 1.0; e->obj.pos[2] = e->world.half[2];
@@ -205,13 +210,13 @@ static int body_body_collision(const pgo_obstacle* a, const pgo_obstacle* b, dou
     double d[3] = {a->pos[0] - b->pos[0], a->pos[1] - b->pos[1], a->pos[2] - b->pos[2]};
     return margin >= sqrt(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]) - a->size[0] - b->size[0];
   }
-  if (a->type == 1 && b->type == 1) {
+  if (a->type >= 1 && b->type >= 1) {
     for (int k = 0; k < 3; k++) if (fabs(a->pos[k] - b->pos[k]) > a->size[k] + b->size[k]) return 0;
     return 1;
   }
   const pgo_obstacle* s = a->type == 0 ? a : b;
   const pgo_obstacle* bx = a->type == 0 ? b : a;
-  double m = pgo_box_margin(bx->size), v[3], d2 = 0, rel[3];
+  double m = pgo_obstacle_margin(bx), v[3], d2 = 0, rel[3];
   for (int k = 0; k < 3; k++) {
     double ek = bx->size[k] - m;
     rel[k] = s->pos[k] - bx->pos[k];
@@ -435,7 +440,7 @@ int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, i
   const int rbase = e->cfg.task == 1 && e->cfg.randomize_robot_pose && e->cfg.scenario == PGO_SCN_WANGEXP;
   pgo_pcg64_seed(&e->rng, seed);                       /* core.py:302 */
   if (rbase) random_robot_base(e);                     /* robot.reset = robot_pose_randomizer (reach_ao.py:132-133) */
-  else for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, NEUTRAL[d]); /* panda.py:290-298 */
+  else for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, e->neutral[d]); /* panda.py:290-298 */
   e->steps = 0;
   if (e->cfg.task == 0) {
     for (int k = 0; k < 3; k++) e->goal[k] = pgo_pcg64_uniform(&e->rng, e->goal_lo[k], e->goal_hi[k]); /* reach.py:75-78 */

@@ -34,6 +34,7 @@ static void cross3(const double* a, const double* b, double* o) {
   o[0] = t[0]; o[1] = t[1]; o[2] = t[2];
 }
 
+double pgo_obstacle_margin(const pgo_obstacle* ob) { return ob->type == 2 ? 0.001 : pgo_box_margin(ob->size); }
 double pgo_box_margin(const double half[3]) {
   double mn = half[0] < half[1] ? half[0] : half[1];
   if (half[2] < mn) mn = half[2];
@@ -212,7 +213,7 @@ static double prim_obstacle(const double c[3], const double ax[3], const pgo_pri
       for (int k = 0; k < 3; k++) { n[k] = L > 1.1920929e-07 ? d[k] / L : (k == 0); pa[k] = c[k] + n[k] * p->radius; pb[k] = ob->pos[k] - n[k] * ob->size[0]; }
       return L - p->radius - ob->size[0];
     }
-    double m = pgo_box_margin(ob->size), e[3] = {ob->size[0] - m, ob->size[1] - m, ob->size[2] - m}, onb[3];
+    double m = pgo_obstacle_margin(ob), e[3] = {ob->size[0] - m, ob->size[1] - m, ob->size[2] - m}, onb[3];
     double d = point_corebox(c, ob->pos, e, onb, n);
     for (int k = 0; k < 3; k++) { pb[k] = onb[k] + n[k] * m; pa[k] = c[k] - n[k] * p->radius; }
     return d - m - p->radius;
@@ -227,7 +228,7 @@ static double prim_obstacle(const double c[3], const double ax[3], const pgo_pri
     for (int k = 0; k < 3; k++) { n[k] = L > 1e-300 ? v[k] / L : (k == 0); pa[k] = onc[k] + n[k] * HULL_MARGIN; pb[k] = ob->pos[k] - n[k] * ob->size[0]; }
     return d - HULL_MARGIN - ob->size[0];
   }
-  double m = pgo_box_margin(ob->size), e[3] = {ob->size[0] - m, ob->size[1] - m, ob->size[2] - m}, qa[3], qb[3];
+  double m = pgo_obstacle_margin(ob), e[3] = {ob->size[0] - m, ob->size[1] - m, ob->size[2] - m}, qa[3], qb[3];
   double d = pgo_gjk_cyl_box(c, ax, p->radius, p->half_len, ob->pos, e, qa, qb);
   double v[3]; sub3(qb, qa, v);
   double L = sqrt(dot3(v, v));

@@ -127,7 +127,7 @@ void pgo_render(pgo_env* env, int width, int height, const double target[3], dou
   const double thf = tan(0.5 * 60.0 * D2R), aspect = (double)width / (double)height, near_plane = 0.1, far_plane = 100.0;
 
   /* ---- scene */
-  rprim prims[96], goal;
+  rprim prims[8 + 36 + PGO_MAXOBS], goal;
   int np = 0;
   const double z3[3] = {0, 0, 0};
   pgo_env_config cfg; pgo_env_get_config(env, &cfg);
@@ -147,7 +147,8 @@ void pgo_render(pgo_env* env, int width, int height, const double target[3], dou
     for (int j = 0; j < nobs; j++) {
       if (ob[j].type < 0 || ob[j].pos[2] < -50.0) continue;
       if (ob[j].type == 0) set_prim(&prims[np++], 0, ob[j].pos, z3, ob[j].size[0], 0, z3, 1, 0, 0, 0);
-      else set_prim(&prims[np++], 2, ob[j].pos, z3, 0, 0, ob[j].size, 1, 0.5, 0, 0);
+      else if (ob[j].type == 1) set_prim(&prims[np++], 2, ob[j].pos, z3, 0, 0, ob[j].size, 1, 0.5, 0, 0);
+      else set_prim(&prims[np++], 2, ob[j].pos, z3, 0, 0, ob[j].size, 0.6, 0.6, 0.6, 0);  /* benchmark-scene box */
     }
   }
   double g[3]; pgo_env_get_goal(env, g);

@@ -24,7 +24,7 @@ class Stage(ctypes.Structure):
         ("obstacle_sampler", c_int), ("randomize_obstacle_position", c_int), ("allow_overlapping_obstacles", c_int),
         ("random_num_obs", c_int), ("sample_size_lo", c_int), ("sample_size_hi", c_int),
         ("max_episode_steps", c_int), ("ee_error_threshold", c_double), ("speed_threshold", c_double),
-        ("pose_randomizer", c_int),
+        ("pose_randomizer", c_int), ("custom_neutral", c_int), ("neutral_q", c_double * 7), ("needs_scene", c_int),
     ]
 
 
@@ -91,6 +91,7 @@ SYMBOLS = [
     ("pg_set_object_state", c_int, [P, P, P]),
     ("pg_observe", c_int, [P, P]),
     ("pg_manipulability", c_int, [P, P, c_i64, P, P]),
+    ("pg_set_scene", c_int, [P, c_int, P, P]),
     ("pg_render", c_int, [P, c_int, c_int, c_int, P, c_float, c_float, c_float, c_float, P, P]),
     ("pg_set_eval_metrics", c_int, [P, c_int, P]),
     ("pg_get_eval_metrics", c_int, [P, P, P]),

@@ -47,6 +47,7 @@ struct pg_env_s {
   int term_w_max;
   int64_t step_id;                  // pg_step calls so far; ring slot = step_id % 3
   int* finished_host;               // page-locked [4]: finished-episode count of the last three steps (by ring slot)
+  float* sbox;                      // static scene boxes (pg_set_scene), [64][8] floats
   bool dlink_valid;                 // d_link / q_dl of EVERY environment come from an observation pass over the current obstacles
   bool cull_enabled;                // PANDA_B200_SCENE_CULL != 0 (default on): temporal culling of the flag pass, see scene_skip_mask
 };
@@ -74,7 +75,7 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   d.goal_upper = s->goal_upper_half; d.goal_front = s->goal_front_half; d.goal_34 = s->goal_three_quarter_front;
   d.nobs = s->n_obstacles;
   P.scene.nobs = s->n_obstacles;
-  P.scene.has_box = 0;
+  P.scene.has_box = P.scene.nstatic > 0;
   for (int j = 0; j < s->n_obstacles; j++) P.scene.has_box |= s->obstacle_type[j] == 1;
   for (int j = 0; j < pg::kMaxObst; j++) {
     d.obs_type[j] = j < s->n_obstacles ? s->obstacle_type[j] : 0;
@@ -94,7 +95,7 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   // observation width (reach_ao.py:902-932: np.ones(27) when the scenario has no obstacles)
   int t = 0;
   if (P.task == 1 && P.obstacle_obs != 0) {
-    if (s->n_obstacles == 0) t = 27;
+    if (s->n_obstacles == 0 && !s->needs_scene) t = 27;  // a benchmark scene's bodies are obstacles (reach_ao.py:300-306)
     else t = P.obstacle_obs == 1 ? 36 : (P.obstacle_obs == 2 ? 27 : (P.obstacle_obs == 3 ? 9 : (P.obstacle_obs == 5 ? 81 : 1)));
   }
   if (P.task >= 2) t = 12;  // push.py:49-63
@@ -172,7 +173,30 @@ int pg_stage_from_scenario(pg_stage* s, const char* scenario) {
     for (int i = 0; i < count; i++) add_sphere(s, 0.05);
     s->pose_randomizer = PG_POSE_RANDOM_BASE;  // :711
   } else {
-    return fail(PG_ERR_ARG, std::string("Scenario ") + scenario + " not found!");  // reach_ao.py:262-264
+    // benchmark scenes (reach_ao.py:308-516): goal box and, where the builder replaces it, the neutral pose; the scene's
+    // boxes are loaded on the host (panda_gym_b200/scenes.py) and handed over with pg_set_scene
+    struct SceneDef { const char* name; double lo[3], hi[3]; int neutral; };
+    static const double kNeutralSets[4][7] = {
+        {0, 0, 0, 0, 0, 0, 0},
+        {-1.0, -0.3, 0.0, -2.2, 0.0, 2.0, 0.7853981633974483},                                        // tunnel / narrow_tunnel
+        {0.00887326, -0.05377409, -0.03621967, -1.9094068, 0.08791409, 2.00265486, 0.76681184},        // workshop*
+        {0.0, 0.12001979, 0.0, -1.64029458, 0.02081271, 3.1, 0.77979846}};                             // library*
+    static const SceneDef kScenes[] = {
+        {"bookshelves", {0.6, -0.35, 0.2}, {0.7, 0.35, 0.8}, 0},      {"warehouse", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},
+        {"countertop", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},        {"kitchen", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},
+        {"raised_shelves", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},    {"tabletop", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},
+        {"tabletop2", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},         {"industrial", {0.5, -0.1, 0.55}, {0.6, 0.1, 0.75}, 0},
+        {"tunnel", {0.55, 0.2, 0.2}, {0.75, 0.4, 0.75}, 1},           {"narrow_tunnel", {0.55, 0.2, 0.2}, {0.75, 0.4, 0.75}, 1},
+        {"workshop", {-0.7, -0.7, 0.4}, {0.1, -0.4, 0.7}, 2},         {"workshop2", {0.5, -0.15, 0.4}, {0.6, 0.15, 0.5}, 2},
+        {"workshop3", {-0.7, -0.7, 0.4}, {0.1, -0.4, 0.7}, 2},        {"library", {0.2, -0.3, 0.0}, {0.7, 0.3, 0.6}, 3},
+        {"library1", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 3},          {"library2", {-0.7, -0.4, 0.4}, {-0.55, 0.4, 0.85}, 3}};
+    const SceneDef* def = nullptr;
+    for (const SceneDef& d : kScenes) if (full == d.name) def = &d;
+    if (full == "kasys") return fail(PG_ERR_UNSUPPORTED, "Scenario kasys: its meshes (trolley.obj, wall.obj) are not part of the reference repository");
+    if (!def) return fail(PG_ERR_ARG, std::string("Scenario ") + scenario + " not found!");  // reach_ao.py:262-264
+    set_goal_box(s, def->lo[0], def->hi[0], def->lo[1], def->hi[1], def->lo[2], def->hi[2]);
+    s->needs_scene = 1;
+    if (def->neutral) { s->custom_neutral = 1; for (int d = 0; d < 7; d++) s->neutral_q[d] = kNeutralSets[def->neutral][d]; }
   }
   return PG_OK;
 }
@@ -210,7 +234,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   PG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
   pg_env_s* h = new pg_env_s();
   h->sm_count = sms;
-  h->dlink_valid = false;
+  h->dlink_valid = false; h->sbox = nullptr;
   { const char* v = getenv("PANDA_B200_SCENE_CULL"); h->cull_enabled = !(v && v[0] == '0'); }
   h->cfg = *cfg; h->device = device; h->launches = 0; h->first_env = 0; h->d_actions = nullptr; h->eval_metrics = 0;
   h->finished_host = nullptr; h->term_ring = nullptr; h->out_slab = nullptr;
@@ -250,6 +274,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
 #define A(ptr, count, st) if ((rc = alloc(h, &ptr, (size_t)(count), st)) != PG_OK) { pg_destroy(h); return rc; }
   A(P.q, 7 * n, true) A(P.qd, 7 * n, true) A(P.goal, 3 * n, true) A(P.obs_pos, (size_t)pg::kMaxObst * 3 * n, true) A(P.obs_pos_f, (size_t)pg::kMaxObst * 3 * n, true)
   A(P.recent, 7 * n, true) A(P.prev, 7 * n, true) A(P.cur_vel, 7 * n, true) A(P.cur_acc, 7 * n, true) A(P.jerk, 7 * n, true)
+  A(P.nprims, pgm::kNumNeutralPrim, false) A(P.nextra, 13, false)
   A(P.d_link, 9 * n, true) A(P.q_dl, 7 * n, true) A(P.past_vec, 54 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
   A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
   A(P.rng, 4 * n, true) A(P.episode, n, true) A(P.obj, 13 * n, true)
@@ -283,6 +308,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
     if (e2 != cudaSuccess) { pg_destroy(h); return fail(PG_ERR_CUDA, cudaGetErrorString(e2)); }
     pg::launch_mirror_obstacles(P, 0);
   }
+  pg::launch_neutral_table(P, cfg->stage.custom_neutral ? cfg->stage.neutral_q : nullptr, 0);
   P.base_seed = 0;
   *out = h;
   return PG_OK;
@@ -304,6 +330,7 @@ int pg_set_stage(pg_handle h, const pg_stage* s, void* stream) {
   if (int rc = check_pose_randomizer(&h->cfg, s)) return rc;
   h->cfg.stage = *s;
   fill_stage(h, s);
+  pg::launch_neutral_table(h->P, s->custom_neutral ? s->neutral_q : nullptr, (cudaStream_t)stream);
   // The reference rebuilds the whole VecEnv for a new stage (setup_training.py:233-252), so every environment starts a
   // fresh episode in the new scene.  Same here: running episodes would otherwise meet newly enabled obstacle slots at
   // stale positions, goals of the old sampler and (when the observation width changes) a cached EE at the old stride.
@@ -335,7 +362,7 @@ int pg_step(pg_handle h, const float* actions_dev, void* stream) {
   h->step_id++;
   h->P.term_w = (8 + h->P.obs_dim + 3) / 4 * 4;
   h->P.term_rows = h->term_ring + (size_t)(h->step_id % 3) * h->P.n * h->term_w_max;
-  h->P.scene.skip_far = h->cull_enabled && h->dlink_valid && h->P.task == 1 && h->P.obstacle_obs != 0 && h->P.scene.nobs > 0;
+  h->P.scene.skip_far = h->cull_enabled && h->dlink_valid && h->P.task == 1 && h->P.obstacle_obs != 0 && h->P.scene.nobs + h->P.scene.nstatic > 0;
   if (h->P.task >= 2) pg::launch_step_obj(h->P, actions_dev, (cudaStream_t)stream);
   else pg::launch_step(h->P, actions_dev, (cudaStream_t)stream);
   h->dlink_valid = true;  // the step ends with the observation pass of every environment
@@ -560,6 +587,29 @@ int pg_observe(pg_handle h, void* stream) {
   h->dlink_valid = true;
   h->launches++;
   PG_CUDA(cudaGetLastError());
+  return PG_OK;
+}
+
+int pg_set_scene(pg_handle h, int n_boxes, const float* boxes_host, void* stream) {
+  if (!h || n_boxes < 0 || n_boxes > pg::kMaxStaticBoxes || (n_boxes > 0 && !boxes_host)) return fail(PG_ERR_ARG, "pg_set_scene: 0..64 boxes");
+  if (h->P.task != PG_TASK_REACH_AO) return fail(PG_ERR_UNSUPPORTED, "pg_set_scene: benchmark scenes belong to ReachAO");
+  PG_CUDA(cudaSetDevice(h->device));
+  std::vector<float> tab((size_t)pg::kMaxStaticBoxes * 8, 0.f);
+  for (int j = 0; j < n_boxes; j++) {
+    const float* b = boxes_host + 7 * j;
+    if (!(b[3] > 0.f && b[4] > 0.f && b[5] > 0.f) || !(b[6] >= 0.f) || b[6] >= fminf(b[3], fminf(b[4], b[5])))
+      return fail(PG_ERR_ARG, "pg_set_scene: half extents must be positive and larger than the margin");
+    float* t = &tab[(size_t)8 * j];
+    t[0] = b[0]; t[1] = b[1]; t[2] = b[2]; t[3] = b[6];
+    t[4] = b[3]; t[5] = b[4]; t[6] = b[5]; t[7] = sqrtf(b[3] * b[3] + b[4] * b[4] + b[5] * b[5]);
+  }
+  if (!h->sbox) { PG_CUDA(cudaMalloc((void**)&h->sbox, tab.size() * sizeof(float))); h->all_bufs.push_back(h->sbox); }
+  PG_CUDA(cudaMemcpyAsync(h->sbox, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, (cudaStream_t)stream));
+  PG_CUDA(cudaStreamSynchronize((cudaStream_t)stream));  // tab is a local
+  h->P.scene.nstatic = n_boxes;
+  h->P.scene.sbox = (const float4*)h->sbox;
+  if (n_boxes > 0) h->P.scene.has_box = 1;
+  h->dlink_valid = false;
   return PG_OK;
 }
 

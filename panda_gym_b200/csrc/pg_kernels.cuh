@@ -4,6 +4,7 @@
 #pragma once
 #include <stdint.h>
 #include "pg_scene.cuh"
+#include "pg_neutral.h"
 #include "pg_contact.cuh"
 
 namespace pg {
@@ -63,6 +64,11 @@ struct Params {
   float *recent, *prev;          // [7][n] action history (panda.py:138-139)
   float *cur_vel, *cur_acc, *jerk; // [7][n] (panda.py:167-172)
   float* d_link;                 // [9][n]
+  // reset pose: collision primitives of the robot at Panda.neutral_joint_values (base at the origin), EE position, COM of
+  // panda_link1 and the joint values themselves -- the generated constants of pg_neutral.h, or the same quantities for the
+  // neutral pose a benchmark-scene builder installs (pg_stage.custom_neutral), filled by k_neutral_table
+  pgm::NeutralPrim* nprims;      // [36]
+  double* nextra;                // ee[3] | link0[3] | q[7]
   float* q_dl;                   // [7][n] joint angles d_link was evaluated at (scene_skip_mask trusts d_link only at exactly this pose)
   float* obj;                    // [13][n] object position, quaternion xyzw, linear / angular velocity (tasks 2, 3)
   float* past_vec;               // [2][27][n] previous two vector observations ("vectors+past", reach_ao.py:918-922)
@@ -236,7 +242,7 @@ __device__ __forceinline__ void observe(const Params& P, int e, const float* q, 
     ag_out[0] = b[0]; ag_out[1] = b[1]; ag_out[2] = b[2];  // push.py:65-67
   }
   if (P.task == 1 && P.obstacle_obs != 0) {
-    if (P.scene.nobs == 0) {  // reach_ao.py:904
+    if (P.scene.nobs + P.scene.nstatic == 0) {  // reach_ao.py:904
       for (int k = 0; k < 27; k++) o[off + k] = 1.0f;
     } else {
       float dl[9]; V3 ul[9];

@@ -25,6 +25,7 @@ void launch_step_obj(const Params& P, const float* actions, cudaStream_t s);
 void launch_reset_all(const Params& P, const uint8_t* mask, const uint64_t* seeds, uint64_t first_env, cudaStream_t s);
 void launch_reset_list(const Params& P, uint64_t first_env, int sm_count, cudaStream_t s);
 void launch_observe(const Params& P, cudaStream_t s);
+void launch_neutral_table(const Params& P, const double* q7 /* nullptr = panda.py:67 */, cudaStream_t s);
 // pg_tu_misc.cu
 void launch_mirror_obstacles(const Params& P, cudaStream_t s);
 void launch_reward(const Params& P, const float* ag, const float* dg, float* out, int64_t n, int src, cudaStream_t s);

@@ -24,18 +24,7 @@ struct RPrim {
   float e[3];            // box half extents
   float rgb[3];
 };
-constexpr int kMaxRPrims = 64;
-
-struct PrimRT { int frame, type; float x, y, z, ax, ay, az, r, h; };
-template <int K> __host__ __device__ constexpr PrimRT prim_rt() {
-  using P = pgm::Prim<K>;
-  return PrimRT{P::frame, P::type, P::x, P::y, P::z, P::ax, P::ay, P::az, P::r, P::h};
-}
-static __device__ __constant__ PrimRT kPrimRT[pgm::kNumPrim] = {
-    prim_rt<0>(),  prim_rt<1>(),  prim_rt<2>(),  prim_rt<3>(),  prim_rt<4>(),  prim_rt<5>(),  prim_rt<6>(),  prim_rt<7>(),  prim_rt<8>(),
-    prim_rt<9>(),  prim_rt<10>(), prim_rt<11>(), prim_rt<12>(), prim_rt<13>(), prim_rt<14>(), prim_rt<15>(), prim_rt<16>(), prim_rt<17>(),
-    prim_rt<18>(), prim_rt<19>(), prim_rt<20>(), prim_rt<21>(), prim_rt<22>(), prim_rt<23>(), prim_rt<24>(), prim_rt<25>(), prim_rt<26>(),
-    prim_rt<27>(), prim_rt<28>(), prim_rt<29>(), prim_rt<30>(), prim_rt<31>(), prim_rt<32>()};
+constexpr int kMaxRPrims = 5 + pgm::kNumPrim + kMaxObst + kMaxStaticBoxes + 2;
 
 constexpr float kLight[3] = {0.40824829f, -0.40824829f, 0.81649658f};  // normalize(1, -1, 2)
 constexpr float kAmbient = 0.35f, kDiffuse = 0.65f;
@@ -145,8 +134,8 @@ __global__ void __launch_bounds__(256) k_render(const Params P, const Camera cam
   if (t == 0) set(s_prims[0], 2, v3(0.f, 0.f, -0.41f), z3, 0.f, 0.f, v3(3.f, 3.f, 0.01f), 0.15f, 0.15f, 0.15f, 0);  // create_plane(z_offset = -0.4)
   if (t == 1) set(s_prims[1], 2, v3((float)P.table_pos[0], (float)P.table_pos[1], (float)P.table_pos[2]), z3, 0.f, 0.f,
                   v3((float)P.table_half[0], (float)P.table_half[1], (float)P.table_half[2]), 0.3f, 0.3f, 0.3f, 0);
-  if (t >= 2 && t < 5) {  // panda_link0 (fixed to the base)
-    const pgm::NeutralPrim& np = pgm::kNeutralPrims[t - 2];
+  if (t >= 2 && t < 5) {  // panda_link0 (fixed to the base): the last three rows of the neutral-pose table
+    const pgm::NeutralPrim& np = pgm::kNeutralPrims[pgm::kNumPrim + t - 2];
     set(s_prims[t], np.type, v3((float)np.c[0] + P.base[0], (float)np.c[1] + P.base[1], (float)np.c[2] + P.base[2]),
         v3((float)np.a[0], (float)np.a[1], (float)np.a[2]), (float)np.r, (float)np.h, z3, 1.f, 1.f, 1.f, 0);
   }
@@ -164,6 +153,13 @@ __global__ void __launch_bounds__(256) k_render(const Params P, const Camera cam
         const Obst& ob = P.scene.obst[j];
         if (ob.type == 0) set(s_prims[k++], 0, o, z3, ob.sx, 0.f, z3, 1.f, 0.f, 0.f, 0);
         else set(s_prims[k++], 2, o, z3, 0.f, 0.f, v3(ob.sx, ob.sy, ob.sz), 1.f, 0.5f, 0.f, 0);
+      }
+    }
+    if (P.task == 1) {  // benchmark scene (pg_set_scene): URDF default grey
+      for (int j = 0; j < P.scene.nstatic; j++) {
+        V3 o;
+        const Obst ob = static_obst(P.scene, j, o);
+        set(s_prims[k++], 2, o, z3, 0.f, 0.f, v3(ob.sx, ob.sy, ob.sz), 0.6f, 0.6f, 0.6f, 0);
       }
     }
     if (P.task >= 2) {

@@ -25,7 +25,7 @@ __device__ __noinline__ double robot_body_distance(const Params& P, const Body& 
   double m = b.type == 1 ? box_margin_d(b.sx, b.sy, b.sz) : 0.0;
   D3 core = v3t<double>(b.sx - m, b.sy - m, b.sz - m);
   for (int k = k0; k < pgm::kNumNeutralPrim; k += kstep) {
-    const pgm::NeutralPrim& np = pgm::kNeutralPrims[k];
+    const pgm::NeutralPrim& np = P.nprims[k];
     D3 c = v3t<double>(np.c[0], np.c[1], np.c[2]);
     double d;
     if (b.type == 0) {

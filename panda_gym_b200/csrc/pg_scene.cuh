@@ -16,7 +16,30 @@ struct SceneParams {
   int has_table;
   int has_box;                 // any cuboid obstacle in the scene (selects the barrier pattern of the flag pass)
   int skip_far;                // d_link of every environment is current: the flag pass may cull links by it (scene_skip_mask)
+  // static scene shared by all environments (benchmark scenes, pg_set_scene): axis-aligned boxes, two float4 per box
+  // = (centre xyz, collision margin), (half extents xyz, bounding radius)
+  int nstatic;
+  const float4* sbox;
 };
+constexpr int kMaxStaticBoxes = 64;
+__device__ __forceinline__ Obst static_obst(const SceneParams& P, int j, V3& pos) {
+  const float4 a = __ldg(P.sbox + 2 * j), b = __ldg(P.sbox + 2 * j + 1);
+  pos = v3(a.x, a.y, a.z);
+  Obst ob; ob.type = 1; ob.sx = b.x; ob.sy = b.y; ob.sz = b.z; ob.margin = a.w;
+  return ob;
+}
+
+// run-time copy of the compile-time primitive table (render, neutral-pose table of a custom reset pose)
+struct PrimRT { int frame, type; float x, y, z, ax, ay, az, r, h; };
+template <int K> __host__ __device__ constexpr PrimRT prim_rt() {
+  using P = pgm::Prim<K>;
+  return PrimRT{P::frame, P::type, P::x, P::y, P::z, P::ax, P::ay, P::az, P::r, P::h};
+}
+static __device__ __constant__ PrimRT kPrimRT[pgm::kNumPrim] = {
+    prim_rt<0>(),  prim_rt<1>(),  prim_rt<2>(),  prim_rt<3>(),  prim_rt<4>(),  prim_rt<5>(),  prim_rt<6>(),  prim_rt<7>(),  prim_rt<8>(),
+    prim_rt<9>(),  prim_rt<10>(), prim_rt<11>(), prim_rt<12>(), prim_rt<13>(), prim_rt<14>(), prim_rt<15>(), prim_rt<16>(), prim_rt<17>(),
+    prim_rt<18>(), prim_rt<19>(), prim_rt<20>(), prim_rt<21>(), prim_rt<22>(), prim_rt<23>(), prim_rt<24>(), prim_rt<25>(), prim_rt<26>(),
+    prim_rt<27>(), prim_rt<28>(), prim_rt<29>(), prim_rt<30>(), prim_rt<31>(), prim_rt<32>()};
 
 // primitives of collision-link slot S: [first, first + count)
 __host__ __device__ constexpr int slot_first(int s) { return s <= 4 ? 3 * s : 3 * s + 3; }
@@ -207,10 +230,11 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const float* __r
   V3 dir = v3(0, 0, 0);
   V3 ctr = frame_point(F, P0::x, P0::y, P0::z);
   int nobs = P.nobs;
+  bool culled = false;
   if (!FULL && cull) {  // temporal culling: the slot cannot have reached any obstacle yet
     const int st = cull->stride;
     const V3 d = ctr - v3(cull->ctr0[(3 * S) * st], cull->ctr0[(3 * S + 1) * st], cull->ctr0[(3 * S + 2) * st]);
-    if (cull->slack[S * st] > norm(d) + R * turned) nobs = 0;
+    if (cull->slack[S * st] > norm(d) + R * turned) { nobs = 0; culled = true; }
   }
   for (int j = 0; j < nobs; j++) {
     V3 o = v3(obs_pos[(size_t)(j * 3 + 0) * n + e], obs_pos[(size_t)(j * 3 + 1) * n + e], obs_pos[(size_t)(j * 3 + 2) * n + e]);
@@ -223,6 +247,22 @@ __device__ __forceinline__ void slot_eval(const SceneParams& P, const float* __r
       continue;
     }
     PrimLoop<K0, N>::obstacle(F, o, P.obst[j], best, dir, Q, j);
+  }
+  const int nst = culled ? 0 : P.nstatic;  // culled slots skip the static boxes too (d_link covers them)
+  for (int j = 0; j < nst; j++) {
+    V3 o;
+    const Obst ob = static_obst(P, j, o);
+    {  // the slot's bounding sphere against the box itself (a long thin shelf has a useless bounding sphere)
+      const V3 rel = ctr - o;
+      const V3 v = v3(rel.x - fminf(fmaxf(rel.x, -ob.sx), ob.sx), rel.y - fminf(fmaxf(rel.y, -ob.sy), ob.sy), rel.z - fminf(fmaxf(rel.z, -ob.sz), ob.sz));
+      const float reach = FULL ? R + best : R;  // FULL: a box farther than the running minimum cannot lower it
+      if (dot(v, v) > reach * reach) continue;
+    }
+    if (!FULL) {
+      if (PrimLoop<K0, N>::hits_kind(F, o, ob, 0) || PrimLoop<K0, N>::hits_kind(F, o, ob, 1)) hit = true;
+      continue;
+    }
+    PrimLoop<K0, N>::obstacle(F, o, ob, best, dir, Q, kMaxObst + j);
   }
   if (S >= 1 && P.has_table) {  // table: panda_link0 / panda_link1 ignored (reach_ao.py:898)
     bool near = true;
@@ -273,8 +313,12 @@ __device__ __forceinline__ bool scene_pass(bool active, const SceneParams& P, co
       if (has) {
         const CylBoxCand cd = queue.q[it];
         if (cd.lb < d_link[cd.slot]) {
-          const Obst& ob = P.obst[cd.j];
-          V3 o = v3(obs_pos[(size_t)(cd.j * 3 + 0) * n + e], obs_pos[(size_t)(cd.j * 3 + 1) * n + e], obs_pos[(size_t)(cd.j * 3 + 2) * n + e]);
+          Obst ob; V3 o;
+          if (cd.j >= kMaxObst) ob = static_obst(P, cd.j - kMaxObst, o);
+          else {
+            ob = P.obst[cd.j];
+            o = v3(obs_pos[(size_t)(cd.j * 3 + 0) * n + e], obs_pos[(size_t)(cd.j * 3 + 1) * n + e], obs_pos[(size_t)(cd.j * 3 + 2) * n + e]);
+          }
           Closest k = cyl_box<float>(cd.c, cd.a, cd.r, cd.h, o, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
           if (k.d < d_link[cd.slot]) { d_link[cd.slot] = k.d; u_link[cd.slot] = k.dir; }
         }

@@ -25,20 +25,21 @@ __global__ void __launch_bounds__(kBlock) k_reset(const __grid_constant__ Params
   // Panda.reset (panda.py:290-298) -- or, with randomize_robot_pose, the scenario's randomizer in its place
   // (reach_ao.py:132-133): set_random_robot_base draws joint 1 from its limits (panda.py:77-79) and keeps the rest neutral
   const bool rbase = P.task == 1 && st.random_base;
-  double q0 = pgm::kNeutralQ[0], c0 = 1.0, s0 = 0.0;
-  if (rbase) { q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - pgm::kNeutralQ[0]); s0 = sin(q0 - pgm::kNeutralQ[0]); }
+  const double* __restrict__ NX = P.nextra;  // ee[3] | link0[3] | q[7] of the reset pose
+  double q0 = NX[6], c0 = 1.0, s0 = 0.0;
+  if (rbase) { q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - NX[6]); s0 = sin(q0 - NX[6]); }
   float q[7], qd[7], cq[7], sq[7];
   P.steps[e] = 0; P.ep_ret[e] = 0.f; P.ep_len[e] = 0;
   double goal[3], ee[6];  // ee[0..2] = get_ee_position(), ee[3..5] = get_link_position(0), both at the reset pose
   int status = 0;
 #define PG_EE_AT_POSE()                                                                                   \
   do {                                                                                                    \
-    ee[0] = c0 * pgm::kNeutralEE[0] - s0 * pgm::kNeutralEE[1] + P.based[0];                               \
-    ee[1] = s0 * pgm::kNeutralEE[0] + c0 * pgm::kNeutralEE[1] + P.based[1];                               \
-    ee[2] = pgm::kNeutralEE[2] + P.based[2];                                                              \
-    ee[3] = c0 * pgm::kNeutralLink0[0] - s0 * pgm::kNeutralLink0[1] + P.based[0];                         \
-    ee[4] = s0 * pgm::kNeutralLink0[0] + c0 * pgm::kNeutralLink0[1] + P.based[1];                         \
-    ee[5] = pgm::kNeutralLink0[2] + P.based[2];                                                           \
+    ee[0] = c0 * NX[0] - s0 * NX[1] + P.based[0];                               \
+    ee[1] = s0 * NX[0] + c0 * NX[1] + P.based[1];                               \
+    ee[2] = NX[2] + P.based[2];                                                              \
+    ee[3] = c0 * NX[3] - s0 * NX[4] + P.based[0];                         \
+    ee[4] = s0 * NX[3] + c0 * NX[4] + P.based[1];                         \
+    ee[5] = NX[5] + P.based[2];                                                           \
   } while (0)
   PG_EE_AT_POSE();
   if (P.task == 0) {
@@ -72,7 +73,16 @@ __global__ void __launch_bounds__(kBlock) k_reset(const __grid_constant__ Params
         i++;
         probe.px = goal[0]; probe.py = goal[1]; probe.pz = goal[2];
         bool coll = false;
-        if (pass == 1) for (int j = 0; j < st.nobs; j++) coll |= body_body_collision(probe, obstacle_body(P, j, e), margin);
+        if (pass == 1) {
+          for (int j = 0; j < st.nobs; j++) coll |= body_body_collision(probe, obstacle_body(P, j, e), margin);
+          for (int j = 0; j < P.scene.nstatic && !coll; j++) {  // the scene's URDF bodies are obstacles like any other (reach_ao.py:986-988)
+            V3 o;
+            const Obst ob = static_obst(P.scene, j, o);
+            const double m = ob.margin;
+            coll |= margin >= sphere_box<double>(v3t<double>(probe.px, probe.py, probe.pz), probe.sx, v3t<double>(o.x, o.y, o.z),
+                                                 v3t<double>(ob.sx - m, ob.sy - m, ob.sz - m), m).d;
+          }
+        }
         coll |= body_body_collision(probe, table, margin);
         if (!coll) coll |= (margin >= robot_body_distance<WARP>(P, probe, margin, c0, s0));
         if (!coll) break;
@@ -108,7 +118,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const __grid_constant__ Params
         while (0.05 >= robot_body_distance<WARP>(P, ob, 0.05, c0, s0)) {
           if (i > 9999) { status |= 4; break; }  // set_joint_neutral: neutral_joint_values[0] already holds the last draw
           i++;
-          q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - pgm::kNeutralQ[0]); s0 = sin(q0 - pgm::kNeutralQ[0]);
+          q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - NX[6]); s0 = sin(q0 - NX[6]);
         }
       }
     }
@@ -129,7 +139,7 @@ __global__ void __launch_bounds__(kBlock) k_reset(const __grid_constant__ Params
 #undef PG_EE_AT_POSE
 #pragma unroll
   for (int d = 0; d < 7; d++) {
-    q[d] = (float)(d == 0 ? q0 : pgm::kNeutralQ[d]); qd[d] = 0.f;
+    q[d] = (float)(d == 0 ? q0 : NX[6 + d]); qd[d] = 0.f;
     P.q[(size_t)d * n + e] = q[d]; P.qd[(size_t)d * n + e] = 0.f;
     sincosf(q[d], &sq[d], &cq[d]);
   }
@@ -163,6 +173,47 @@ void launch_reset_all(const Params& P, const uint8_t* mask, const uint64_t* seed
 }
 void launch_reset_list(const Params& P, uint64_t first_env, int sm_count, cudaStream_t s) {
   k_reset<true><<<sm_count * 8, kBlock, 0, s>>>(P, nullptr, nullptr, first_env);  // 32 warps per SM, grid-stride over the list
+}
+// The reset-pose table (Params::nprims / nextra).  q == nullptr: the generated constants of pg_neutral.h (panda.py:67).
+// Otherwise the same quantities at the joint values q[7] a benchmark-scene builder installs (reach_ao.py:322, 343, 356,
+// 424), by the fp32 forward kinematics of the step kernel -- 1e-7 m from the fp64 oracle, which only matters for a goal
+// sample that lands within that distance of its rejection threshold.
+struct NeutralQ { double q[7]; int custom; };
+__global__ void k_neutral_table(const Params P, const NeutralQ nq) {
+  const int k = threadIdx.x;
+  if (!nq.custom) {
+    if (k < pgm::kNumNeutralPrim) P.nprims[k] = pgm::kNeutralPrims[k];
+    if (k < 3) { P.nextra[k] = pgm::kNeutralEE[k]; P.nextra[3 + k] = pgm::kNeutralLink0[k]; }
+    if (k < 7) P.nextra[6 + k] = pgm::kNeutralQ[k];
+    return;
+  }
+  if (k >= pgm::kNumNeutralPrim) return;
+  float cq[7], sq[7];
+  for (int d = 0; d < 7; d++) { cq[d] = (float)cos(nq.q[d]); sq[d] = (float)sin(nq.q[d]); }
+  Frame F[8];
+  F[0] = base_frame(v3(0.f, 0.f, 0.f));
+  F[1] = frame_step<1>(F[0], cq[0], sq[0]); F[2] = frame_step<2>(F[1], cq[1], sq[1]); F[3] = frame_step<3>(F[2], cq[2], sq[2]);
+  F[4] = frame_step<4>(F[3], cq[3], sq[3]); F[5] = frame_step<5>(F[4], cq[4], sq[4]); F[6] = frame_step<6>(F[5], cq[5], sq[5]);
+  F[7] = frame_step<7>(F[6], cq[6], sq[6]);
+  pgm::NeutralPrim np;
+  if (k < pgm::kNumPrim) {
+    const PrimRT& pr = kPrimRT[k];
+    const V3 c = frame_point(F[pr.frame], pr.x, pr.y, pr.z), a = frame_dir(F[pr.frame], pr.ax, pr.ay, pr.az);
+    np.type = pr.type; np.c[0] = c.x; np.c[1] = c.y; np.c[2] = c.z; np.a[0] = a.x; np.a[1] = a.y; np.a[2] = a.z; np.r = pr.r; np.h = pr.h;
+  } else np = pgm::kNeutralPrims[k];  // panda_link0: fixed to the base
+  P.nprims[k] = np;
+  if (k == 0) {
+    const V3 ee = frame_point(F[7], pgm::kEEx, pgm::kEEy, pgm::kEEz);
+    const V3 l0 = frame_point(F[1], pgm::Link<1>::cx, pgm::Link<1>::cy, pgm::Link<1>::cz);
+    P.nextra[0] = ee.x; P.nextra[1] = ee.y; P.nextra[2] = ee.z; P.nextra[3] = l0.x; P.nextra[4] = l0.y; P.nextra[5] = l0.z;
+    for (int d = 0; d < 7; d++) P.nextra[6 + d] = nq.q[d];
+  }
+}
+void launch_neutral_table(const Params& P, const double* q7, cudaStream_t s) {
+  NeutralQ nq;
+  nq.custom = q7 != nullptr;
+  for (int d = 0; d < 7; d++) nq.q[d] = q7 ? q7[d] : 0.0;
+  k_neutral_table<<<1, 64, 0, s>>>(P, nq);
 }
 void launch_observe(const Params& P, cudaStream_t s) { k_observe<<<(P.n + kBlock - 1) / kBlock, kBlock, 0, s>>>(P); }
 }  // namespace pg

@@ -5,6 +5,7 @@ This is the B200 replacement of the reference's L0-L2 stack (``panda_gym/pybulle
 view library-owned device buffers and for streams; all arithmetic happens in the CUDA kernels.
 """
 import ctypes
+import os
 
 import numpy as np
 import torch
@@ -33,6 +34,7 @@ def make_config(task, n_envs, scenario=None, config=None, control_type=None, rew
     _lib.check(lib.pg_default_config(ctypes.byref(cfg), task, scenario.encode() if scenario else None))
     cfg.n_envs = int(n_envs)
     cfg.auto_reset = 1 if auto_reset else 0
+    cfg._scenario = scenario  # remembered for PandaBatch: a benchmark scene needs its boxes (pg_set_scene)
     if task == 1:
         c = config if config is not None else TrainConfig()
         cfg.control = CONTROL[control_type or c.control_type]
@@ -77,6 +79,7 @@ def stage_from_scenario(scenario, max_episode_steps=50, ee_error_threshold=0.05,
     st.max_episode_steps = int(max_episode_steps)
     st.ee_error_threshold = float(ee_error_threshold)
     st.speed_threshold = float(speed_threshold)
+    st._scenario = scenario
     return st
 
 
@@ -91,6 +94,10 @@ class PandaBatch:
         h = ctypes.c_void_p()
         _lib.check(self.lib.pg_create(ctypes.byref(cfg), self.device_index, ctypes.byref(h)))
         self.h = h
+        self._scene_boxes = None
+        if cfg.stage.needs_scene:
+            from . import scenes
+            self.set_scene(scenes.scene_boxes(getattr(cfg, "_scenario", None), os.environ.get("PANDA_GYM_SCENARIOS")))
         self.n = self.lib.pg_num_envs(h)
         self.act_dim = self.lib.pg_act_dim(h)
         self._views = {}
@@ -131,8 +138,21 @@ class PandaBatch:
     def seed(self, seed, first_env_index=0):
         _lib.check(self.lib.pg_seed(self.h, int(seed), int(first_env_index)))
 
+    def set_scene(self, boxes):
+        """Static boxes shared by all environments (pg_set_scene): float [n, 7] = centre, half extents, margin, e.g.
+        ``scenes.scene_boxes("kitchen")``; None or an empty array removes the scene.  Takes effect with the next reset."""
+        b = np.ascontiguousarray(boxes if boxes is not None else np.zeros((0, 7)), dtype=np.float32).reshape(-1, 7)
+        _lib.check(self.lib.pg_set_scene(self.h, int(b.shape[0]), b.ctypes.data_as(ctypes.c_void_p) if len(b) else None, self._stream()))
+        self._scene_boxes = b if len(b) else None
+
     def set_stage(self, stage):
-        """Swap the scenario block; every environment is reset into the new scene (pg_set_stage)."""
+        """Swap the scenario block; every environment is reset into the new scene (pg_set_stage).  A benchmark-scene stage
+        (``stage_from_scenario("kitchen")``) brings its boxes along; any other stage removes them."""
+        if stage.needs_scene:
+            from . import scenes
+            self.set_scene(scenes.scene_boxes(getattr(stage, "_scenario", None), os.environ.get("PANDA_GYM_SCENARIOS")))
+        elif self._scene_boxes is not None:
+            self.set_scene(None)
         _lib.check(self.lib.pg_set_stage(self.h, ctypes.byref(stage), self._stream()))
         self._views = {}
 

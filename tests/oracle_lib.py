@@ -23,6 +23,7 @@ class EnvConfig(ctypes.Structure):
         ("collision_reward", c_double), ("ee_error_threshold", c_double), ("speed_threshold", c_double),
         ("safety_distance", c_double), ("max_episode_steps", c_int), ("scenario", c_int), ("n_obstacles", c_int),
         ("base_pos", c_double * 3), ("randomize_robot_pose", c_int),
+        ("scene_goal_lo", c_double * 3), ("scene_goal_hi", c_double * 3), ("custom_neutral", c_int), ("neutral_q", c_double * 7),
     ]
 
 
@@ -50,7 +51,7 @@ class Pcg64(ctypes.Structure):
 
 
 SCENARIOS = {"none": 0, "reach1": 1, "reach2": 2, "reach3": 3, "reachao1": 4, "reachao2": 5, "reachao3": 6,
-             "reachao_rand": 7, "wang": 8, "wangexp": 9}
+             "reachao_rand": 7, "wang": 8, "wangexp": 9, "static": 10}
 
 
 def build():
@@ -206,7 +207,7 @@ class Arm:
 
 def make_obstacle(kind, pos, size):
     o = Obstacle()
-    o.type = 0 if kind == "sphere" else 1
+    o.type = {"sphere": 0, "urdf_box": 2}.get(kind, 1)
     for k in range(3):
         o.pos[k] = float(pos[k])
     if kind == "sphere":
@@ -230,9 +231,9 @@ class Env:
                 self.cfg.scenario = SCENARIOS[name]
                 if n:
                     self.cfg.n_obstacles = int(n)
-            elif k == "base_pos":
-                for i in range(3):
-                    self.cfg.base_pos[i] = float(v[i])
+            elif k in ("base_pos", "scene_goal_lo", "scene_goal_hi", "neutral_q"):
+                for i in range(len(v)):
+                    getattr(self.cfg, k)[i] = float(v[i])
             else:
                 setattr(self.cfg, k, v)
         self.h = self.L.pgo_env_create(ctypes.byref(self.cfg))
@@ -273,13 +274,14 @@ class Env:
         self.L.pgo_env_set_goal(self.h, dp(np.asarray(g, dtype=np.float64)))
 
     def obstacles(self):
-        arr = (Obstacle * 8)()
+        arr = (Obstacle * 64)()
         n = self.L.pgo_env_get_obstacles(self.h, arr)
         return [(arr[i].type, np.array(arr[i].pos[:]), np.array(arr[i].size[:])) for i in range(n)]
 
     def set_obstacles(self, obs_list):
         arr = (Obstacle * max(1, len(obs_list)))(*obs_list)
         self.L.pgo_env_set_obstacles(self.h, len(obs_list), arr)
+        self.obs_dim = self.L.pgo_env_obs_dim(self.h)  # reach_ao.py:904: the obstacle part is np.ones(27) only while there is no obstacle
 
     def step_metrics(self):
         out = np.zeros(4)

@@ -165,3 +165,27 @@ def test_her_oracle_vectorised_add_equals_loop():
         assert np.array_equal(a.ep_start, b.ep_start) and np.array_equal(a.ep_length, b.ep_length), step
         assert np.array_equal(a._current_ep_start, b._current_ep_start) and a.pos == b.pos and a.full == b.full
     assert a.full and (a.ep_length > 0).any()
+
+
+def test_benchmark_scene_loader():
+    """scenes.py: shipped numbers (data/benchmark_scenes.json) = what the loader extracts from the reference assets, where
+    those exist (not on the GPU box); counts and extents of the shipped table always."""
+    import os
+    import importlib.util
+    import numpy as np
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("pg_scenes", os.path.join(root, "panda_gym_b200", "scenes.py"))
+    scenes = importlib.util.module_from_spec(spec); spec.loader.exec_module(scenes)
+    counts = {"bookshelves": 6, "warehouse": 50, "countertop": 52, "kitchen": 50, "raised_shelves": 10, "tabletop": 47, "tabletop2": 50,
+              "industrial": 16, "tunnel": 3, "narrow_tunnel": 3, "workshop": 6, "library": 7}
+    for name, k in counts.items():
+        b = scenes.builtin_scene_boxes(name)
+        assert b.shape == (k, 7) and (b[:, 3:6] > b[:, 6:7]).all() and (b[:, 6] == 0.001).all()
+        assert k <= 64
+    # the URDFs give every link's joint AND collision origin: a box sits at their sum times globalScaling (tabletop: 1.4)
+    t = scenes.builtin_scene_boxes("bookshelves")
+    assert np.allclose(t[0], [0.765, 0.0, 0.14, 0.21, 0.385, 0.007, 0.001])
+    assets = "/root/reference/panda_gym/assets/scenarios"
+    if os.path.isdir(assets):
+        for name in scenes.SCENES:
+            assert np.allclose(scenes.load_scene_boxes(assets, name), scenes.builtin_scene_boxes(name), atol=1e-9), name
