@@ -83,6 +83,8 @@ typedef struct {
   int randomize_robot_pose;  /* train_config.py:26: Panda.reset <- the scenario's robot_pose_randomizer, then
                                 set_coll_free_robot (reach_ao.py:991-992, 1035-1060) */
   pg_stage stage;
+  int has_fixed_target;      /* train_config.py:29 fixed_target: ReachAO.reset skips its first set_coll_free_goal (reach_ao.py:981) */
+  double fixed_target[3];    /*   and the goal keeps this value unless the scenario re-samples it (:986-988, obstacle positions fixed) */
 } pg_config;
 
 /* fill cfg with the reference defaults: task PG_TASK_REACH -> PandaReachJoints-v3 (sparse);

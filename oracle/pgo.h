@@ -130,6 +130,7 @@ typedef struct {
    * boxes are handed over with pgo_env_set_obstacles (type 2) after pgo_env_create and stay put (no obstacle sampling) */
   double scene_goal_lo[3], scene_goal_hi[3];
   int custom_neutral; double neutral_q[7];
+  int has_fixed_target; double fixed_target[3]; /* train_config.py:29, consumed at reach_ao.py:981 */
 } pgo_env_config;
 
 enum { PGO_SCN_NONE = 0, PGO_SCN_REACH1, PGO_SCN_REACH2, PGO_SCN_REACH3, PGO_SCN_REACHAO1, PGO_SCN_REACHAO2,

@@ -460,7 +460,8 @@ int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, i
     e->obj.quat[3] = 1.0;
   } else {
     e->goal_reached = 0; e->is_collided = 0;
-    status |= set_coll_free_goal(e, 0, 0.1);           /* fixed_target None */
+    if (e->cfg.has_fixed_target) memcpy(e->goal, e->cfg.fixed_target, 24); /* self.goal = config.fixed_target (:381, 410, 418) */
+    else status |= set_coll_free_goal(e, 0, 0.1);      /* reach_ao.py:981-982 */
     if (e->randomize_obstacles) status |= set_coll_free_obs(e, 0.03);
     else status |= set_coll_free_goal(e, 1, 0.03);
     if (rbase) status |= set_coll_free_robot(e);       /* reach_ao.py:991-992 */

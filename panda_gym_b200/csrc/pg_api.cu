@@ -176,11 +176,12 @@ int pg_stage_from_scenario(pg_stage* s, const char* scenario) {
     // benchmark scenes (reach_ao.py:308-516): goal box and, where the builder replaces it, the neutral pose; the scene's
     // boxes are loaded on the host (panda_gym_b200/scenes.py) and handed over with pg_set_scene
     struct SceneDef { const char* name; double lo[3], hi[3]; int neutral; };
-    static const double kNeutralSets[4][7] = {
+    static const double kNeutralSets[5][7] = {
         {0, 0, 0, 0, 0, 0, 0},
         {-1.0, -0.3, 0.0, -2.2, 0.0, 2.0, 0.7853981633974483},                                        // tunnel / narrow_tunnel
         {0.00887326, -0.05377409, -0.03621967, -1.9094068, 0.08791409, 2.00265486, 0.76681184},        // workshop*
-        {0.0, 0.12001979, 0.0, -1.64029458, 0.02081271, 3.1, 0.77979846}};                             // library*
+        {0.0, 0.12001979, 0.0, -1.64029458, 0.02081271, 3.1, 0.77979846},                              // library*
+        {0.94551719, 0.65262327, 0.12742699, -1.74347465, -0.16996126, 1.97424632, 0.88058222}};       // wall (create_stage_wall :457-468)
     static const SceneDef kScenes[] = {
         {"bookshelves", {0.6, -0.35, 0.2}, {0.7, 0.35, 0.8}, 0},      {"warehouse", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},
         {"countertop", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},        {"kitchen", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 0},
@@ -189,7 +190,8 @@ int pg_stage_from_scenario(pg_stage* s, const char* scenario) {
         {"tunnel", {0.55, 0.2, 0.2}, {0.75, 0.4, 0.75}, 1},           {"narrow_tunnel", {0.55, 0.2, 0.2}, {0.75, 0.4, 0.75}, 1},
         {"workshop", {-0.7, -0.7, 0.4}, {0.1, -0.4, 0.7}, 2},         {"workshop2", {0.5, -0.15, 0.4}, {0.6, 0.15, 0.5}, 2},
         {"workshop3", {-0.7, -0.7, 0.4}, {0.1, -0.4, 0.7}, 2},        {"library", {0.2, -0.3, 0.0}, {0.7, 0.3, 0.6}, 3},
-        {"library1", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 3},          {"library2", {-0.7, -0.4, 0.4}, {-0.55, 0.4, 0.85}, 3}};
+        {"library1", {0.5, -0.3, 0.0}, {0.85, 0.3, 0.3}, 3},          {"library2", {-0.7, -0.4, 0.4}, {-0.55, 0.4, 0.85}, 3},
+        {"wall", {0.45, -0.6, 0.1}, {0.7, -0.1, 0.3}, 4}};  // its one cuboid stays where create_obstacle_cuboid puts it: a static box
     const SceneDef* def = nullptr;
     for (const SceneDef& d : kScenes) if (full == d.name) def = &d;
     if (full == "kasys") return fail(PG_ERR_UNSUPPORTED, "Scenario kasys: its meshes (trolley.obj, wall.obj) are not part of the reference repository");
@@ -249,6 +251,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   P.act_dim = (cfg->control == PG_CTRL_EE ? 3 : 7) + (cfg->task == PG_TASK_PICK_AND_PLACE ? 1 : 0);
   P.n_substeps = cfg->n_substeps; P.truncate_on_collision = cfg->truncate_on_collision; P.terminate_on_success = cfg->terminate_on_success;
   P.auto_reset = cfg->auto_reset; P.collision_reward = (float)cfg->collision_reward; P.safety_distance = cfg->safety_distance;
+  P.has_fixed_target = cfg->has_fixed_target; for (int k = 0; k < 3; k++) P.fixed_target[k] = cfg->fixed_target[k];
   for (int k = 0; k < 3; k++) { P.base[k] = (float)cfg->base_position[k]; P.based[k] = cfg->base_position[k]; }
   if (cfg->task != PG_TASK_REACH_AO) {  // table 1.1 x 0.7 x 0.4 at x = -0.3 (reach.py:33, push.py:31); Reach never queries it
     P.table_pos[0] = -0.3; P.table_half[0] = 0.55; P.table_half[1] = 0.35;

@@ -48,6 +48,7 @@ struct Params {
   int n_substeps, truncate_on_collision, terminate_on_success, auto_reset;
   float collision_reward;
   double safety_distance;
+  int has_fixed_target; double fixed_target[3];  // train_config.py:29
   float base[3];
   double based[3];
   double table_pos[3], table_half[3];

@@ -63,8 +63,11 @@ __global__ void __launch_bounds__(kBlock) k_reset(const __grid_constant__ Params
     table.sx = P.table_half[0]; table.sy = P.table_half[1]; table.sz = P.table_half[2];
     Body probe; probe.type = 0; probe.sx = 0.05; probe.sy = probe.sz = 0;
     // set_coll_free_goal: pass 0 = (["table","robot"], 0.1); pass 1 (only without obstacle randomisation) = all bodies, 0.03
+    // config.fixed_target (reach_ao.py:981): the first pass is skipped (no draws), the goal keeps the configured value unless
+    // the second pass -- taken whenever the obstacles are not re-sampled -- replaces it
     const int passes = st.randomize_obstacles ? 1 : 2;
-    for (int pass = 0; pass < passes; pass++) {
+    if (P.has_fixed_target) for (int k = 0; k < 3; k++) goal[k] = P.fixed_target[k];
+    for (int pass = P.has_fixed_target ? 1 : 0; pass < passes; pass++) {
       const double margin = pass == 0 ? 0.1 : 0.03;
       int i = 0;
       for (;;) {

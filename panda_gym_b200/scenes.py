@@ -49,6 +49,11 @@ SCENES = {
     "library2":       dict(asset="library", goal_lo=(-0.7, -0.4, 0.4), goal_hi=(-0.55, 0.4, 0.85),
                            neutral=(0.0, 0.12001979, 0.0, -1.64029458, 0.02081271, 3.1, 0.77979846)),
 }
+# create_stage_wall (reach_ao.py:457-468): one cuboid from create_obstacle_cuboid (half extents = `size`, btBoxShape safe margin),
+# never re-sampled -- a one-box static scene
+SCENES["wall"] = dict(asset=None, goal_lo=(0.45, -0.6, 0.1), goal_hi=(0.7, -0.1, 0.3),
+                      neutral=(0.94551719, 0.65262327, 0.12742699, -1.74347465, -0.16996126, 1.97424632, 0.88058222),
+                      boxes=((0.0, 0.0, 0.1, 0.2, 0.05, 0.3, 0.005),))
 # kasys (reach_ao.py:413-420) references ../meshes/trolley.obj and wall.obj, which the reference repository does not ship:
 # the reference cannot load it either.
 
@@ -130,6 +135,8 @@ def urdf_boxes(path, base_position=(0, 0, 0), base_orientation=(0, 0, 0, 1), glo
 def load_scene_boxes(assets_dir, scenario):
     """All collision boxes of benchmark scenario ``scenario`` from a panda_gym ``assets/scenarios`` directory:
     float64 array [n, 7] = centre, half extents, collision margin."""
+    if SCENES[scenario].get("boxes") is not None:
+        return np.array(SCENES[scenario]["boxes"], dtype=np.float64)
     asset = SCENES[scenario]["asset"]
     d = os.path.join(assets_dir, asset)
     with open(os.path.join(d, asset + ".json")) as f:
@@ -146,6 +153,8 @@ _DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "benchm
 
 
 def builtin_scene_boxes(scenario):
+    if SCENES[scenario].get("boxes") is not None:
+        return np.array(SCENES[scenario]["boxes"], dtype=np.float64)
     with open(_DATA) as f:
         return np.array(json.load(f)[SCENES[scenario]["asset"]], dtype=np.float64)
 

@@ -53,7 +53,9 @@ def make_config(task, n_envs, scenario=None, config=None, control_type=None, rew
                                       "ik_lm_chan (panda.py:220-224), which is not built; only set_random_robot_base "
                                       "(scenario wangexp-N) is (SURVEY section 8f, N2)")
         if c.fixed_target is not None:
-            raise _lib.PandaB200Error("fixed_target is not supported yet")
+            cfg.has_fixed_target = 1
+            for k in range(3):
+                cfg.fixed_target[k] = float(c.fixed_target[k])
         cfg.n_substeps = int(c.n_substeps)
         cfg.truncate_on_collision = int(bool(c.truncate_on_collision))
         cfg.terminate_on_success = int(bool(c.terminate_on_success))

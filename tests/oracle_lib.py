@@ -24,6 +24,7 @@ class EnvConfig(ctypes.Structure):
         ("safety_distance", c_double), ("max_episode_steps", c_int), ("scenario", c_int), ("n_obstacles", c_int),
         ("base_pos", c_double * 3), ("randomize_robot_pose", c_int),
         ("scene_goal_lo", c_double * 3), ("scene_goal_hi", c_double * 3), ("custom_neutral", c_int), ("neutral_q", c_double * 7),
+        ("has_fixed_target", c_int), ("fixed_target", c_double * 3),
     ]
 
 
@@ -231,7 +232,7 @@ class Env:
                 self.cfg.scenario = SCENARIOS[name]
                 if n:
                     self.cfg.n_obstacles = int(n)
-            elif k in ("base_pos", "scene_goal_lo", "scene_goal_hi", "neutral_q"):
+            elif k in ("base_pos", "scene_goal_lo", "scene_goal_hi", "neutral_q", "fixed_target"):
                 for i in range(len(v)):
                     getattr(self.cfg, k)[i] = float(v[i])
             else:

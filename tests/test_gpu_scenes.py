@@ -24,12 +24,13 @@ def oracle_env(oracle, scenes, name, **kw):
     sc = scenes.SCENES[name]
     extra = dict(custom_neutral=1, neutral_q=sc["neutral"]) if sc["neutral"] is not None else {}
     e = oracle.Env(task=1, scenario="static", scene_goal_lo=sc["goal_lo"], scene_goal_hi=sc["goal_hi"], **extra, **kw)
-    e.set_obstacles([oracle.make_obstacle("urdf_box", b[:3], b[3:6]) for b in scenes.builtin_scene_boxes(name)])
+    kind = "box" if name == "wall" else "urdf_box"   # wall: a create_obstacle_cuboid body (safe margin), not a URDF import
+    e.set_obstacles([oracle.make_obstacle(kind, b[:3], b[3:6]) for b in scenes.builtin_scene_boxes(name)])
     return e
 
 
 ALL = ["bookshelves", "warehouse", "countertop", "kitchen", "raised_shelves", "tabletop", "tabletop2", "industrial", "tunnel",
-       "narrow_tunnel", "workshop", "workshop2", "workshop3", "library", "library1", "library2"]
+       "narrow_tunnel", "workshop", "workshop2", "workshop3", "library", "library1", "library2", "wall"]
 
 
 @pytest.mark.parametrize("name", ALL)
@@ -78,8 +79,8 @@ def test_scene_reset_distances_and_flags(sim, oracle, name):
         k = np.abs(o - og[i])
         # unit vectors flip between equally close features; distances and the robot part must agree
         assert k[:6].max() < 2e-5
-    if name in ("warehouse", "tabletop2"):   # tabletop2.urdf as placed by its json puts a table top through the robot's base link
-        assert n_coll == n
+    if name in ("warehouse", "tabletop2", "wall"):   # tabletop2.urdf as placed by its json puts a table top through the robot's
+        assert n_coll == n                           # base link, and so does the cuboid of create_stage_wall
     else:
         assert 0 < n_coll < n, "poses must cover both outcomes"
 
@@ -127,3 +128,24 @@ def test_scene_swap_and_removal(sim):
     assert b._scene_boxes is None
     img = b.render(0, 96, 64).cpu().numpy()
     assert img.shape == (64, 96, 4)
+
+
+def test_fixed_target(sim, oracle):
+    """TrainConfig.fixed_target (train_config.py:29): with re-sampled obstacles the goal IS the fixed target and the first
+    goal-sampling pass draws nothing (the obstacle draws that follow start at the same stream position on both sides);
+    with fixed obstacles the second pass replaces it (reach_ao.py:981-988)."""
+    from panda_gym_b200.config import TrainConfig
+    tgt = [0.55, 0.05, 0.4]
+    for scenario, kept in (("reachao3", True), ("reach1", False)):
+        c = TrainConfig(); c.fixed_target = tgt
+        cfg = sim.make_config(1, 16, scenario=scenario, config=c, max_episode_steps=50, auto_reset=False)
+        b = sim.PandaBatch(cfg); b.seed(40); b.reset()
+        torch.cuda.synchronize()
+        goal = b.view("goal").cpu().numpy(); opos = b.view("obstacle_pos").cpu().numpy()
+        for i in range(16):
+            e = oracle.Env(task=1, scenario=scenario, has_fixed_target=1, fixed_target=tgt, max_episode_steps=50)
+            e.reset(40 + i)
+            assert np.allclose(e.goal(), goal[:, i], rtol=0, atol=1e-12)
+            assert np.array_equal(e.goal(), np.array(tgt)) == kept
+            for j, (_, p, _) in enumerate(e.obstacles()):
+                assert np.allclose(p, opos[j, :, i], rtol=0, atol=1e-9), (scenario, i, j)

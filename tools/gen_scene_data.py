@@ -9,7 +9,7 @@ scenes = importlib.util.module_from_spec(spec); spec.loader.exec_module(scenes)
 assets = sys.argv[1]
 out = {}
 for name, s in scenes.SCENES.items():
-    if s["asset"] in out:
+    if s["asset"] is None or s["asset"] in out:
         continue
     b = scenes.load_scene_boxes(assets, name)
     out[s["asset"]] = [[round(float(v), 9) for v in row] for row in b]
