@@ -30,10 +30,19 @@ enum pg_reward { PG_REW_SPARSE = 0, PG_REW_DENSE_OR_WANG = 1, PG_REW_KUMAR_HER =
 enum pg_obstacle_obs { PG_OOBS_NONE = 0, PG_OOBS_VECTORS_CLOSEST_PER_LINK = 1, PG_OOBS_VECTORS = 2,
                        PG_OOBS_CLOSEST_PER_LINK = 3, PG_OOBS_CLOSEST = 4, PG_OOBS_VECTORS_PAST = 5 };      /* reach_ao.py:908-932 */
 enum pg_goal_sampler { PG_GOAL_BOX = 0, PG_GOAL_SHELL = 1 };                     /* reach_ao.py:1183-1211 */
-/* ReachAO.robot_pose_randomizer of the scenario (reach_ao.py:62-63, 521-604, 669, 711); it replaces Panda.reset when
- * TrainConfig.randomize_robot_pose is set (reach_ao.py:132-133).  Only set_random_robot_base (:1238-1241, scenario
- * wangexp-N) is built; the others call roboticstoolbox's ik_lm_chan (panda.py:220-224), which is not restated. */
-enum pg_pose_randomizer { PG_POSE_RTB_IK = 0, PG_POSE_RANDOM_BASE = 1 };
+/* ReachAO.robot_pose_randomizer of the scenario (reach_ao.py:62-63, 310-320, 363-375, 395-403, 521-604, 669, 711).  It
+ * replaces Panda.reset when TrainConfig.randomize_robot_pose is set or the scenario forces it (reach_ao.py:132-133), and
+ * set_coll_free_robot (:1035-1060) re-runs it while the robot stands within 0.05 of an obstacle.
+ *   TORUS / TORUS_FRONT  set_robot_random_pose(sample_inside_torus) (:806-817, 1213-1236): rtb_ik targets until the EE height is in [0.4, 0.6]
+ *   RANDOM_BASE          set_random_robot_base (:1238-1241): joint 1 uniform in its limits
+ *   IK_GOAL_SPACE        set_robot_random_joint_position_ik_goal_space (:801-804): rtb_ik towards a sample of the goal sampler
+ *   IK_SPHERE            set_robot_random_joint_position_ik_sphere(rmin, rmax) (:793-799): rtb_ik targets until check_collided is false
+ *   IK_BOX               rtb_ik towards U(pose_lo, pose_hi) (narrow_tunnel :310-320, workshop2 :363-375)
+ *   BULLET_IK_BOX        PyBullet calculateInverseKinematics (position only, seeded by the current joints) towards U(pose_lo, pose_hi) (industrial :395-403)
+ * rtb_ik = roboticstoolbox ik_lm_chan (panda.py:220-224), restated in fp64 on the device; the two rejection loops that are
+ * unbounded in the reference stop after 1000 tries here (counted in episode_stats reset_failures). */
+enum pg_pose_randomizer { PG_POSE_TORUS = 0, PG_POSE_RANDOM_BASE = 1, PG_POSE_TORUS_FRONT = 2, PG_POSE_IK_GOAL_SPACE = 3,
+                          PG_POSE_IK_SPHERE = 4, PG_POSE_IK_BOX = 5, PG_POSE_BULLET_IK_BOX = 6 };
 enum pg_obstacle_sampler { PG_OSMP_GOAL_BOX = 0, PG_OSMP_WANG = 1, PG_OSMP_EXPERIMENTAL = 2, PG_OSMP_WANG_N = 3 }; /* :610-644, 650-660 */
 
 #define PG_MAX_OBSTACLES 8
@@ -56,7 +65,11 @@ typedef struct {
   int max_episode_steps;            /* gymnasium TimeLimit (panda_gym/__init__.py:15-20) */
   double ee_error_threshold;        /* reach_ao.py:71 / reach.py:15 */
   double speed_threshold;           /* reach_ao.py:72 */
-  int pose_randomizer;              /* pg_pose_randomizer; used only with pg_config.randomize_robot_pose */
+  int pose_randomizer;              /* pg_pose_randomizer; active with pg_config.randomize_robot_pose or force_randomize_pose */
+  int force_randomize_pose;         /* the scenario sets randomize_robot_pose itself (reach_ao.py:319, 374, 402, 603) */
+  double pose_lo[3], pose_hi[3];    /* IK_BOX / BULLET_IK_BOX: target range; IK_SPHERE: [0] = minor / major radius */
+  int random_size_cuboids;          /* reachao_rand_shape (reach_ao.py:606-608, 969-979, 1084-1089): every reset re-creates the cuboids with
+                                       half extents 0.2 * Dirichlet(1, 1, 1) from the episode's numpy stream (per-environment sizes) */
   int custom_neutral;               /* 1: neutral_q replaces Panda.neutral_joint_values (panda.py:67) as the reset pose, the way */
   double neutral_q[7];              /*    some benchmark-scene builders do (reach_ao.py:322, 343, 356-359, 424-425) */
   int needs_scene;                  /* set by pg_stage_from_scenario for a benchmark scene: its boxes come from pg_set_scene */
@@ -173,6 +186,7 @@ enum pg_view_id {
   PG_V_STEP_COUNT,        /* i32 [n] */
   PG_V_D_LINK,            /* f32 [9][n] distances_closest_obstacles (reach_ao.py:897) */
   PG_V_OBJECT,            /* f32 [13][n] object position, quaternion xyzw, linear / angular velocity (get_base_* of pybullet.py:182-247) */
+  PG_V_OBSTACLE_SIZE,     /* f64 [PG_MAX_OBSTACLES][3][n] per-environment cuboid half extents (pg_stage.random_size_cuboids; rows of spheres unused) */
   PG_V_COUNT
 };
 typedef struct { void* ptr; int dtype; /* 0 f32, 1 u8, 2 i32, 3 f64, 4 u64 */ int ndim; int64_t shape[3]; } pg_view;

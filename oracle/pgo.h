@@ -53,6 +53,13 @@ void pgo_arm_minv(pgo_arm*, double* minv);
  * quat_xyzw may be NULL (position only).  out[ndof]. */
 void pgo_arm_ik(const pgo_arm*, int link, const double pos[3], const double* quat_xyzw, double* out);
 void pgo_arm_set_ik(pgo_arm*, double joint_damping, int max_iters, double residual_thr);
+/* Panda.rtb_ik (panda.py:220-224): roboticstoolbox ik_lm_chan towards fkine(q_seed) moved to `target` (see pgo_dyn.c).
+ * returns 0 solved, 1 solved after a random restart, 2 unsolved; q_out[7]. */
+typedef struct { uint32_t r[31]; int f, b; } pgo_crand; /* glibc rand() state (the toolbox's restart stream) */
+void pgo_crand_seed(pgo_crand*, uint32_t seed);
+int pgo_crand_next(pgo_crand*);
+int pgo_arm_ik_lm_chan(const pgo_arm*, const double target[3], const double* q_seed, int ilimit, int slimit, double tol,
+                       double lambda, pgo_crand* restart, double* q_out, int* iters_out);
 /* translational Jacobian (3 x ndof) of a link COM, world frame */
 void pgo_arm_jacobian(const pgo_arm*, int link, double* Jt, double* Jr);
 /* Panda.get_manipulability (panda.py:314-317): Yoshikawa index of the translational Jacobian at the flange (panda_link8) */
@@ -101,8 +108,11 @@ void pgo_quat_to_euler(const double quat_xyzw[4], double rpy[3]);
 typedef struct { uint64_t s_hi, s_lo, inc_hi, inc_lo; } pgo_pcg64;
 void pgo_pcg64_seed(pgo_pcg64*, uint64_t seed); /* == np.random.default_rng(seed) / gymnasium seeding.np_random(seed) */
 uint64_t pgo_pcg64_next(pgo_pcg64*);
+void pgo_pcg64_advance(pgo_pcg64*, uint64_t delta); /* BitGenerator.advance: skip delta draws */
 double pgo_pcg64_double(pgo_pcg64*);            /* Generator.random() */
 double pgo_pcg64_uniform(pgo_pcg64*, double lo, double hi); /* Generator.uniform(lo, hi) */
+double pgo_pcg64_standard_exponential(pgo_pcg64*);          /* Generator.standard_exponential() (256-layer ziggurat) */
+void pgo_pcg64_dirichlet111(pgo_pcg64*, double out[3]);     /* Generator.dirichlet([1, 1, 1]) */
 
 /* ---------------------------------------------------------------- environments */
 typedef struct pgo_env pgo_env; /* opaque */
@@ -125,23 +135,32 @@ typedef struct {
   int scenario;          /* ReachAO: see PGO_SCN_* */
   int n_obstacles;       /* wang-N / wangexp-N */
   double base_pos[3];
-  int randomize_robot_pose; /* train_config.py:26; restated only for set_random_robot_base (scenario wangexp-N, reach_ao.py:711) */
+  int randomize_robot_pose; /* train_config.py:26: Panda.reset <- the scenario's robot_pose_randomizer (reach_ao.py:132-133) */
   /* PGO_SCN_STATIC: a benchmark scene (reach_ao.py:292-516): goal box and neutral joint values of its builder; the scene's
    * boxes are handed over with pgo_env_set_obstacles (type 2) after pgo_env_create and stay put (no obstacle sampling) */
   double scene_goal_lo[3], scene_goal_hi[3];
   int custom_neutral; double neutral_q[7];
   int has_fixed_target; double fixed_target[3]; /* train_config.py:29, consumed at reach_ao.py:981 */
+  /* PGO_SCN_STATIC only: the scene builder's own robot_pose_randomizer (narrow_tunnel :310-320, workshop2 :363-375: an
+   * rtb_ik towards U(lo, hi); industrial :395-403: PyBullet's own IK towards U(lo, hi); all with randomize_robot_pose forced on);
+   * 0 keeps the task default (set_robot_random_pose, :62-63) */
+  int scene_pose_randomizer, scene_force_randomize; double scene_pose_lo[3], scene_pose_hi[3];
 } pgo_env_config;
+/* ReachAO.robot_pose_randomizer kinds (reach_ao.py:62-63, 521-604, 669, 711, 782-817, 1238-1241) */
+enum { PGO_POSE_TORUS = 0, PGO_POSE_RANDOM_BASE = 1, PGO_POSE_TORUS_FRONT = 2, PGO_POSE_IK_GOAL_SPACE = 3, PGO_POSE_IK_SPHERE = 4,
+       PGO_POSE_IK_BOX = 5, PGO_POSE_BULLET_IK_BOX = 6 };
 
 enum { PGO_SCN_NONE = 0, PGO_SCN_REACH1, PGO_SCN_REACH2, PGO_SCN_REACH3, PGO_SCN_REACHAO1, PGO_SCN_REACHAO2,
-       PGO_SCN_REACHAO3, PGO_SCN_REACHAO_RAND, PGO_SCN_WANG, PGO_SCN_WANGEXP, PGO_SCN_STATIC };
+       PGO_SCN_REACHAO3, PGO_SCN_REACHAO_RAND, PGO_SCN_WANG, PGO_SCN_WANGEXP, PGO_SCN_STATIC,
+       PGO_SCN_REACHAO_RAND_START, PGO_SCN_REACHAO_RAND_SHAPE };
 
 void pgo_env_default_config(pgo_env_config*, int task);
 pgo_env* pgo_env_create(const pgo_env_config*);
 void pgo_env_destroy(pgo_env*);
 int pgo_env_obs_dim(const pgo_env*);
 int pgo_env_act_dim(const pgo_env*);
-/* RobotTaskEnv.reset(seed) (core.py:298-308).  returns 0 ok, 1 if a rejection loop hit its cap. */
+/* RobotTaskEnv.reset(seed) (core.py:298-308).  returns 0 ok, else a bit mask: 1 / 2 / 4 / 8 = the goal / obstacle / set_coll_free_robot /
+ * start-pose rejection loop hit its cap, 16 = an rtb_ik call found no solution in its 100 searches. */
 int pgo_env_reset(pgo_env*, uint64_t seed, float* obs, float* achieved, float* desired, int* is_success);
 /* RobotTaskEnv.step (core.py:352-368) + TimeLimit.  flags out: [is_success, terminated, truncated(collision), time_limit] */
 void pgo_env_step(pgo_env*, const float* action, float* obs, float* achieved, float* desired, float* reward, int* flags);

@@ -611,6 +611,93 @@ void pgo_arm_ik(const pgo_arm* a0, int link, const double pos[3], const double* 
 }
 
 /* accessors for the geometry module */
+/* roboticstoolbox 1.1.0 ERobot.ik_lm_chan(Tep, q0, ilimit, slimit, tol, reject_jl=True, we=1, lambda=1.0) as Panda.rtb_ik calls it
+ * (panda.py:220-224): Tep = fkine(q_seed) with its translation replaced by `target`, Chan's Levenberg-Marquardt step
+ *   e = angle_axis(Te, Tep) (translation error; rotation error of Tep.R Te.R^T as angle * axis),  E = e.e / 2,
+ *   q += (J^T J + lambda E I)^-1 J^T e,  J = jacob0 at the toolbox model's end-effector link panda_link8,
+ * stop when E < tol, wrap q into (-pi, pi], reject a solution outside the TOOLBOX model's joint limits (franka_description's,
+ * not the simulated URDF's) and restart from a random configuration, at most slimit searches of ilimit iterations.
+ * The toolbox's C solver draws restart configurations q_i = lo_i + rand() / RAND_MAX * (hi_i - lo_i) from the C library's rand(),
+ * never seeded: every SubprocVecEnv worker process therefore walks glibc's srand(1) stream (pgo_crand below, checked against libc
+ * in the tests), one state per environment for the life of the process, NOT reset with the episode seed.  About one target in
+ * six of the goal shells needs a restart (the first descent ends outside the joint limits), so this stream shapes the start poses.
+ * Frames are the robot's own (base at the origin: the toolbox model has no base offset).
+ * PARITY UNPINNED: roboticstoolbox is not installable here and the reference holds no vector for this solver [UPSTREAM-RECALL].
+ * returns 0 = solved in the first search, 1 = solved after >= 1 restart, 2 = no solution (q_out = last iterate). */
+static const double RTB_QLIM_LO[7] = {-2.8973, -1.7628, -2.8973, -3.0718, -2.8973, -0.0175, -2.8973};
+static const double RTB_QLIM_HI[7] = {2.8973, 1.7628, 2.8973, -0.0698, 2.8973, 3.7525, 2.8973};
+/* glibc rand(): TYPE_3 additive feedback generator r[k] = r[k-31] + r[k-3] after srandom(seed)'s 310 warm-up draws */
+void pgo_crand_seed(pgo_crand* c, uint32_t seed) {
+  int32_t word = (int32_t)seed;
+  c->r[0] = seed;
+  for (int i = 1; i < 31; i++) {
+    const int32_t hi = word / 127773, lo = word % 127773;
+    word = 16807 * lo - 2836 * hi;
+    if (word < 0) word += 2147483647;
+    c->r[i] = (uint32_t)word;
+  }
+  c->f = 3; c->b = 0;
+  for (int i = 0; i < 310; i++) pgo_crand_next(c);
+}
+int pgo_crand_next(pgo_crand* c) {
+  c->r[c->f] += c->r[c->b];
+  const int res = (int)(c->r[c->f] >> 1);
+  c->f = (c->f + 1) % 31; c->b = (c->b + 1) % 31;
+  return res;
+}
+int pgo_arm_ik_lm_chan(const pgo_arm* a, const double target[3], const double* q_seed, int ilimit, int slimit, double tol,
+                       double lambda, pgo_crand* restart, double* q_out, int* iters_out) {
+  const int flange = 7, n = 7;
+  double Rw[PGO_MAXL][9], ow[PGO_MAXL][3], comw[PGO_MAXL][3], q[PGO_MAXD] = {0}, Rt[9];
+  memcpy(q, q_seed, n * sizeof(double));
+  fk_q(a, q, Rw, ow, comw);
+  memcpy(Rt, Rw[flange], sizeof Rt);
+  int total = 0, solved = 0, search = 1;
+  for (; search <= slimit; search++) {
+    for (int it = 1; it <= ilimit; it++, total++) {
+      fk_q(a, q, Rw, ow, comw);
+      double e[6], R[9];
+      for (int k = 0; k < 3; k++) e[k] = target[k] - (ow[flange][k] - a->base_pos[k]);
+      for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { double s = 0; for (int k = 0; k < 3; k++) s += Rt[3 * i + k] * Rw[flange][3 * j + k]; R[3 * i + j] = s; }
+      double li[3] = {R[7] - R[5], R[2] - R[6], R[3] - R[1]}, ln = norm3(li), tr = R[0] + R[4] + R[8];
+      if (ln < 1e-6) { for (int k = 0; k < 3; k++) e[3 + k] = tr > 0 ? 0.0 : M_PI / 2 * (R[4 * k] + 1); }
+      else { double ang = atan2(ln, tr - 1); for (int k = 0; k < 3; k++) e[3 + k] = ang * li[k] / ln; }
+      double E = 0; for (int k = 0; k < 6; k++) E += 0.5 * e[k] * e[k];
+      if (E < tol) {
+        for (int d = 0; d < n; d++) q[d] = fmod(q[d] + M_PI, 2 * M_PI) - M_PI;
+        solved = 1;
+        for (int d = 0; d < n; d++) if (q[d] < RTB_QLIM_LO[d] || q[d] > RTB_QLIM_HI[d]) solved = 0;
+        break;
+      }
+      double J[6][7];
+      for (int d = 0; d < n; d++) {
+        int l = a->link_of_dof[d];
+        double axw[3], r[3], c[3];
+        m3vec(Rw[l], a->L[l].axis, axw);
+        for (int k = 0; k < 3; k++) r[k] = ow[flange][k] - ow[l][k];
+        cross(axw, r, c);
+        for (int k = 0; k < 3; k++) { J[k][d] = c[k]; J[3 + k][d] = axw[k]; }
+      }
+      double A[49], g[7];
+      for (int i = 0; i < n; i++) {
+        for (int j = 0; j < n; j++) { double s = 0; for (int k = 0; k < 6; k++) s += J[k][i] * J[k][j]; A[i * n + j] = s + (i == j ? lambda * E : 0.0); }
+        double s = 0; for (int k = 0; k < 6; k++) s += J[k][i] * e[k];
+        g[i] = s;
+      }
+      solve_spd(n, A, g);
+      for (int d = 0; d < n; d++) q[d] += g[d];
+    }
+    if (solved) break;
+    for (int d = 0; d < n; d++) { /* random restart inside the toolbox limits */
+      const double u = (double)pgo_crand_next(restart) / 2147483647.0;
+      q[d] = RTB_QLIM_LO[d] + u * (RTB_QLIM_HI[d] - RTB_QLIM_LO[d]);
+    }
+  }
+  memcpy(q_out, q, n * sizeof(double));
+  if (iters_out) *iters_out = total;
+  return solved ? (search > 1 ? 1 : 0) : 2;
+}
+
 int pgo__arm_prims(const pgo_arm* a, const pgo_prim_t** P) { *P = a->P; return a->np; }
 void pgo__arm_fk(pgo_arm* a) { fk(a); }
 const double* pgo__arm_Rw(const pgo_arm* a, int link) { return a->Rw[link]; }

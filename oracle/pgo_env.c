@@ -9,6 +9,7 @@
  */
 #define _GNU_SOURCE
 #include "pgo.h"
+#include "pgo_internal.h"
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -42,6 +43,10 @@ struct pgo_env {
   int randomize_obstacles, allow_overlap, random_num_obs, size_lo, size_hi;
   double neutral0; /* Panda.neutral_joint_values[0], mutated by set_random_robot_base */
   double neutral[7]; /* Panda.neutral_joint_values (panda.py:67), replaced by some benchmark-scene builders */
+  int pose_kind, pose_active;  /* robot_pose_randomizer of the scenario (PGO_POSE_*) and whether it replaces Panda.reset (:132-133) */
+  double pose_lo[3], pose_hi[3]; /* IK_BOX: target range; IK_SPHERE: [0] = minor / major radius */
+  int random_size_cuboids;     /* reach_ao.py:105, 608 */
+  pgo_crand crand;             /* the worker process's C rand() stream: restart configurations of rtb_ik (pgo_arm_ik_lm_chan) */
   double table_pos[3], table_half[3];
   /* Push / PickAndPlace (tasks 2, 3): the free object and its world */
   pgo_body obj;
@@ -108,34 +113,50 @@ static void setup_scenario(pgo_env* e) {
   e->table_half[0] = 1.0; e->table_half[1] = 0.65; e->table_half[2] = 0.2;
   goal_box(e, -0.3 / 2.5 + 0.6, 0.3 / 2.5 + 0.6, -0.3 / 1.5, 0.3 / 1.5, 0.0, 0.3);
   e->obs_sampler = 0; e->randomize_obstacles = 0; e->allow_overlap = 0; e->random_num_obs = 0;
+  e->pose_kind = PGO_POSE_TORUS; e->pose_active = c->randomize_robot_pose; e->random_size_cuboids = 0;       /* :61-63 */
   switch (c->scenario) {
-    case PGO_SCN_REACH1: goal_box(e, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4); break;       /* :518-522 */
-    case PGO_SCN_REACH2: case PGO_SCN_REACH3: goal_shell(e, 0.5, 0.85, 1, 0, 1); break;                      /* :524-539 */
+    case PGO_SCN_REACH1: goal_box(e, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4);               /* :518-522 */
+      e->pose_kind = PGO_POSE_TORUS_FRONT; break;
+    case PGO_SCN_REACH2: goal_shell(e, 0.5, 0.85, 1, 0, 1); e->pose_kind = PGO_POSE_TORUS_FRONT; break;      /* :524-531 */
+    case PGO_SCN_REACH3: goal_shell(e, 0.5, 0.85, 1, 0, 1); e->pose_kind = PGO_POSE_TORUS; break;            /* :533-539 */
     case PGO_SCN_REACHAO1:                                                                                   /* :541-545 */
       goal_box(e, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4);
+      e->pose_kind = PGO_POSE_TORUS_FRONT;
       e->randomize_obstacles = 1; add_sphere(e, 0.04); break;
     case PGO_SCN_REACHAO2:                                                                                   /* :547-564 */
       goal_shell(e, 0.5, 0.8, 1, 1, 0); e->randomize_obstacles = 1; e->obs_sampler = 1;
+      e->pose_kind = PGO_POSE_IK_GOAL_SPACE;
       add_sphere(e, 0.05); add_sphere(e, 0.05); break;
     case PGO_SCN_REACHAO3:                                                                                   /* :573-585 */
       goal_shell(e, 0.5, 0.8, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 1;
+      e->pose_kind = PGO_POSE_IK_GOAL_SPACE;
       for (int i = 0; i < 3; i++) add_sphere(e, 0.05);
       break;
-    case PGO_SCN_REACHAO_RAND:                                                                               /* :587-599 */
+    case PGO_SCN_REACHAO_RAND: case PGO_SCN_REACHAO_RAND_START: case PGO_SCN_REACHAO_RAND_SHAPE:             /* :587-608 */
       goal_shell(e, 0.5, 0.8, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 2;
+      e->pose_kind = PGO_POSE_IK_GOAL_SPACE;
       for (int i = 0; i < 3; i++) add_sphere(e, 0.05);
       for (int i = 0; i < 3; i++) add_cuboid(e, 0.05);
-      e->random_num_obs = 1; e->allow_overlap = 1; e->size_lo = 4; e->size_hi = 6; break;
+      e->random_num_obs = 1; e->allow_overlap = 1; e->size_lo = 4; e->size_hi = 6;
+      if (c->scenario == PGO_SCN_REACHAO_RAND_START) {                                                       /* :601-604 */
+        e->pose_active = 1; e->pose_kind = PGO_POSE_IK_SPHERE; e->pose_lo[0] = 0.45; e->pose_hi[0] = 0.7;
+      }
+      if (c->scenario == PGO_SCN_REACHAO_RAND_SHAPE) e->random_size_cuboids = 1;                              /* :606-608 */
+      break;
     case PGO_SCN_WANG:                                                                                       /* :646-699 */
       goal_shell(e, 0.4, 0.95, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 3;
+      e->pose_kind = PGO_POSE_TORUS;
       for (int i = 0; i < c->n_obstacles; i++) add_sphere(e, 0.05);
       break;
     case PGO_SCN_WANGEXP:                                                                                    /* :701-722 */
       goal_shell(e, 0.5, 0.8, 1, 0, 0); e->randomize_obstacles = 1; e->obs_sampler = 1;
+      e->pose_kind = PGO_POSE_RANDOM_BASE;
       for (int i = 0; i < c->n_obstacles; i++) add_sphere(e, 0.05);
       break;
     case PGO_SCN_STATIC:                                                                                     /* :292-516 */
       goal_box(e, c->scene_goal_lo[0], c->scene_goal_hi[0], c->scene_goal_lo[1], c->scene_goal_hi[1], c->scene_goal_lo[2], c->scene_goal_hi[2]);
+      if (c->scene_pose_randomizer) { e->pose_kind = c->scene_pose_randomizer; memcpy(e->pose_lo, c->scene_pose_lo, 24); memcpy(e->pose_hi, c->scene_pose_hi, 24); }
+      if (c->scene_force_randomize) e->pose_active = 1;
       break;
     default: break;
   }
@@ -147,10 +168,11 @@ pgo_env* pgo_env_create(const pgo_env_config* c) {
   e->arm = pgo_arm_create(0, c->base_pos);
   for (int d = 0; d < N_ARM; d++) e->neutral[d] = c->custom_neutral ? c->neutral_q[d] : NEUTRAL[d];
   setup_scenario(e);
+  pgo_crand_seed(&e->crand, 1); /* a fresh worker process: rand() without srand() */
   pgo_world_default(&e->world);
   e->obj.quat[3] = 1.0; e->obj.pos[2] = e->world.half[2];
   for (int k = 0; k < PGO_NCL; k++) e->d_link[k] = 0.0; /* reach_ao.py:110 np.zeros */
-  for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, 0.0);
+  for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, e->neutral[d]); /* Panda.__init__ / the scene builders end with set_joint_neutral */
   return e;
 }
 void pgo_env_destroy(pgo_env* e) { if (e) { pgo_arm_destroy(e->arm); free(e); } }
@@ -202,6 +224,12 @@ int pgo_env_check_collided(pgo_env* e, double* d_link, double* d_table_min) {
 static double robot_body_distance(pgo_env* e, const pgo_obstacle* o) {
   double best = 1e300;
   for (int p = 0; p < NPRIM_ALL; p++) { double d = pgo_prim_obstacle_distance(e->arm, p, o, 0, 0); if (d < best) best = d; }
+  return best;
+}
+/* the part of the robot no start pose moves: the base link and panda_link1, whose colliders lie on joint 1's axis */
+static double robot_column_distance(pgo_env* e, const pgo_obstacle* o) {
+  double best = 1e300;
+  for (int p = 0; p < NPRIM_ALL; p++) if (pgo__prim_link(e->arm, p) <= 0) { double d = pgo_prim_obstacle_distance(e->arm, p, o, 0, 0); if (d < best) best = d; }
   return best;
 }
 /* sphere body vs sphere / box body; box-box: Bullet's SAT box detector only reports overlapping boxes */
@@ -419,17 +447,86 @@ static void random_robot_base(pgo_env* e) {
   e->neutral0 = pgo_pcg64_uniform(&e->rng, -2.7437, 2.7437);
   for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, d == 0 ? e->neutral0 : NEUTRAL[d]);
 }
-/* set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the robot pose while the robot is within 0.05 */
+/* sample_inside_torus (reach_ao.py:1213-1236): R 0.5, r 0.05, centre height 0.5 */
+static void sample_torus(pgo_env* e, int front, double out[3]) {
+  double theta = 2.0 * M_PI * pgo_pcg64_double(&e->rng);
+  if (front) theta = pgo_pcg64_uniform(&e->rng, -0.5 * M_PI, 0.5 * M_PI);
+  double phi = 2.0 * M_PI * pgo_pcg64_double(&e->rng);
+  double rad = 0.05 * sqrt(pgo_pcg64_double(&e->rng));
+  out[0] = (0.5 + rad * cos(phi)) * cos(theta); out[1] = (0.5 + rad * cos(phi)) * sin(theta); out[2] = rad * sin(phi) + 0.5;
+}
+/* Panda.rtb_ik + set_joint_angles (panda.py:220-224, core.py:187-193) */
+static int ik_to(pgo_env* e, const double target[3]) {
+  double q[7];
+  int rc = pgo_arm_ik_lm_chan(e->arm, target, e->neutral, 100, 100, 0.01, 1.0, &e->crand, q, 0);
+  for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, q[d]);
+  return rc == 2 ? 16 : 0;
+}
+/* the scenario's robot_pose_randomizer, which replaces Panda.reset (reach_ao.py:132-133) */
+static int robot_reset(pgo_env* e) {
+  int status = 0;
+  double t[3];
+  switch (e->pose_kind) {
+    case PGO_POSE_RANDOM_BASE: random_robot_base(e); break;
+    case PGO_POSE_IK_GOAL_SPACE: sample_goal(e, t); status |= ik_to(e, t); break;              /* :801-804 */
+    case PGO_POSE_IK_BOX:                                                                      /* :310-320, 363-375 */
+      for (int k = 0; k < 3; k++) t[k] = pgo_pcg64_uniform(&e->rng, e->pose_lo[k], e->pose_hi[k]);
+      status |= ik_to(e, t); break;
+    case PGO_POSE_BULLET_IK_BOX: {                                                             /* :395-403: robot.inverse_kinematics(ee_link, target)[:7] */
+      double ik[PGO_MAXD];
+      for (int k = 0; k < 3; k++) t[k] = pgo_pcg64_uniform(&e->rng, e->pose_lo[k], e->pose_hi[k]);
+      pgo_arm_ik(e->arm, EE_LINK, t, 0, ik);                                                   /* seeded by the joints the last episode left */
+      for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, ik[d]);
+      break; }
+    case PGO_POSE_IK_SPHERE: {                                                                 /* :793-799 (unbounded there) */
+      int i = 0;
+      for (;;) {
+        sample_hollow(e, e->pose_lo[0], e->pose_hi[0], 1, 0, 0, t);
+        status |= ik_to(e, t);
+        if (!pgo_env_check_collided(e, 0, 0)) break;
+        if (++i > 999) { status |= 8; break; } /* unbounded in the reference: 1000 tries here and on the device */
+      }
+      break; }
+    default: {                                                                                 /* set_robot_random_pose :806-817 (unbounded there) */
+      int i = 0;
+      for (;;) {
+        sample_torus(e, e->pose_kind == PGO_POSE_TORUS_FRONT, t);
+        status |= ik_to(e, t);
+        double p[3]; ee_position(e, p);
+        if (0.6 >= p[2] && p[2] >= 0.4) break;
+        if (++i > 999) { status |= 8; break; }
+      }
+      break; }
+  }
+  return status;
+}
+/* set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the robot pose while the robot is within 0.05.
+ * FUTILE CASE: an obstacle within 0.05 of the base column (base link + panda_link1: no joint moves them) fails all 10 000 tries
+ * whatever they draw, after which the reference prints "Couldn't find collision free robot pose!" and sets the neutral pose.  With
+ * an rtb_ik randomizer that is 10 000 inverse-kinematics solves to no effect, so it is short-circuited here and on the device:
+ * neutral pose, flag 4, and the numpy stream jumps over the draws the tries would have made when their number is fixed
+ * (ik_goal_space / ik_box: one target sample per try).  Deviations, stated: the C rand() stream is NOT advanced by the restarts
+ * those solves would have made, and for the variable-draw randomizers (set_robot_random_pose, ..._ik_sphere) the numpy stream is
+ * not advanced either -- it only feeds set_random_num_obs afterwards (reachao_rand_start). */
+static int draws_per_goal_sample(const pgo_env* e) { return e->goal_sampler == 0 ? 3 : 3 + (e->goal_front ? 1 : 0) + (e->goal_34 ? 1 : 0); }
 static int set_coll_free_robot(pgo_env* e) {
   int status = 0;
   for (int j = 0; j < e->nobs; j++) {
     int i = 0;
+    if (e->pose_kind != PGO_POSE_RANDOM_BASE && 0.05 >= robot_body_distance(e, &e->obs[j]) && 0.05 >= robot_column_distance(e, &e->obs[j])) {
+      if (e->pose_kind == PGO_POSE_IK_GOAL_SPACE) pgo_pcg64_advance(&e->rng, 10000ull * (uint64_t)draws_per_goal_sample(e));
+      if (e->pose_kind == PGO_POSE_IK_BOX || e->pose_kind == PGO_POSE_BULLET_IK_BOX) pgo_pcg64_advance(&e->rng, 30000ull);
+      for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, e->neutral[d]);
+      status |= 4;
+      continue;
+    }
     while (0.05 >= robot_body_distance(e, &e->obs[j])) {
-      if (i > 9999) { /* set_joint_neutral with the mutated neutral_joint_values[0] = the pose it already has */
-        status = 4; break;
+      if (i > 9999) { /* set_joint_neutral */
+        for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, d == 0 && e->pose_kind == PGO_POSE_RANDOM_BASE ? e->neutral0 : e->neutral[d]);
+        status |= 4; break;
       }
       i++;
-      random_robot_base(e);
+      status |= robot_reset(e);
     }
   }
   return status;
@@ -437,9 +534,9 @@ static int set_coll_free_robot(pgo_env* e) {
 
 int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, int* success) {
   int status = 0;
-  const int rbase = e->cfg.task == 1 && e->cfg.randomize_robot_pose && e->cfg.scenario == PGO_SCN_WANGEXP;
+  const int rpose = e->cfg.task == 1 && e->pose_active;
   pgo_pcg64_seed(&e->rng, seed);                       /* core.py:302 */
-  if (rbase) random_robot_base(e);                     /* robot.reset = robot_pose_randomizer (reach_ao.py:132-133) */
+  if (rpose) status |= robot_reset(e);                 /* robot.reset = robot_pose_randomizer (reach_ao.py:132-133) */
   else for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, e->neutral[d]); /* panda.py:290-298 */
   e->steps = 0;
   if (e->cfg.task == 0) {
@@ -460,11 +557,18 @@ int pgo_env_reset(pgo_env* e, uint64_t seed, float* obs, float* ag, float* dg, i
     e->obj.quat[3] = 1.0;
   } else {
     e->goal_reached = 0; e->is_collided = 0;
+    if (e->random_size_cuboids)                          /* reach_ao.py:969-979, 1084-1089: every cuboid is removed and re-created with */
+      for (int j = 0; j < e->nobs; j++)                  /* half extents 0.2 * Dirichlet(1, 1, 1) at create_obstacle_cuboid's default position */
+        if (e->obs[j].type == 1) {
+          double f[3]; pgo_pcg64_dirichlet111(&e->rng, f);
+          for (int k = 0; k < 3; k++) e->obs[j].size[k] = 0.2 * f[k];
+          e->obs[j].pos[0] = 0.1; e->obs[j].pos[1] = 0.0; e->obs[j].pos[2] = 0.1;
+        }
     if (e->cfg.has_fixed_target) memcpy(e->goal, e->cfg.fixed_target, 24); /* self.goal = config.fixed_target (:381, 410, 418) */
     else status |= set_coll_free_goal(e, 0, 0.1);      /* reach_ao.py:981-982 */
     if (e->randomize_obstacles) status |= set_coll_free_obs(e, 0.03);
     else status |= set_coll_free_goal(e, 1, 0.03);
-    if (rbase) status |= set_coll_free_robot(e);       /* reach_ao.py:991-992 */
+    if (rpose) status |= set_coll_free_robot(e);       /* reach_ao.py:991-992 */
     e->dummy[0] = 0; e->dummy[1] = 0; e->dummy[2] = -5.0;
     if (e->random_num_obs) {                           /* reach_ao.py:1062-1082 */
       u32buf b = {0, 0};

@@ -50,5 +50,45 @@ uint64_t pgo_pcg64_next(pgo_pcg64* g) {
   unsigned rot = (unsigned)(g->s_hi >> 58);
   return (x >> rot) | (x << ((-rot) & 63));
 }
+/* BitGenerator.advance(delta): the state after delta draws, by LCG jump-ahead (Brown, "Random number generation with arbitrary
+ * strides") in O(log delta) 128-bit multiplications */
+void pgo_pcg64_advance(pgo_pcg64* g, uint64_t delta) {
+  const u128 MULT = ((u128)0x2360ed051fc65da4ULL << 64) | 0x4385df649fccf645ULL;
+  u128 state = ((u128)g->s_hi << 64) | g->s_lo, inc = ((u128)g->inc_hi << 64) | g->inc_lo;
+  u128 acc_mult = 1, acc_plus = 0, cur_mult = MULT, cur_plus = inc;
+  while (delta > 0) {
+    if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+    cur_plus = (cur_mult + 1) * cur_plus;
+    cur_mult *= cur_mult;
+    delta >>= 1;
+  }
+  state = acc_mult * state + acc_plus;
+  g->s_hi = (uint64_t)(state >> 64); g->s_lo = (uint64_t)state;
+}
 double pgo_pcg64_double(pgo_pcg64* g) { return (double)(pgo_pcg64_next(g) >> 11) * (1.0 / 9007199254740992.0); }
 double pgo_pcg64_uniform(pgo_pcg64* g, double lo, double hi) { return lo + (hi - lo) * pgo_pcg64_double(g); }
+
+/* Generator.standard_exponential(): numpy's 256-layer ziggurat (random_standard_exponential); tables recovered from and
+ * verified against numpy itself by tools/gen_ziggurat.py */
+#include "pgo_ziggurat.h"
+#include <math.h>
+double pgo_pcg64_standard_exponential(pgo_pcg64* g) {
+  for (;;) {
+    uint64_t ri = pgo_pcg64_next(g) >> 3;
+    const int idx = (int)(ri & 0xff);
+    ri >>= 8;
+    const double x = (double)ri * ZIG_we[idx];
+    if (ri < ZIG_ke[idx]) return x;
+    const double u = pgo_pcg64_double(g);
+    if (idx == 0) return ZIG_R - log1p(-u);
+    if ((ZIG_fe[idx - 1] - ZIG_fe[idx]) * u + ZIG_fe[idx] < exp(-x)) return x;
+  }
+}
+/* Generator.dirichlet(alpha=[1, 1, 1]): alpha.max() >= 0.1, so three standard_gamma(1.0) = standard_exponential draws,
+ * normalised by the reciprocal of their running sum */
+void pgo_pcg64_dirichlet111(pgo_pcg64* g, double out[3]) {
+  double acc = 0.0;
+  for (int j = 0; j < 3; j++) { out[j] = pgo_pcg64_standard_exponential(g); acc = acc + out[j]; }
+  const double inv = 1 / acc;
+  for (int j = 0; j < 3; j++) out[j] = out[j] * inv;
+}

@@ -24,7 +24,8 @@ class Stage(ctypes.Structure):
         ("obstacle_sampler", c_int), ("randomize_obstacle_position", c_int), ("allow_overlapping_obstacles", c_int),
         ("random_num_obs", c_int), ("sample_size_lo", c_int), ("sample_size_hi", c_int),
         ("max_episode_steps", c_int), ("ee_error_threshold", c_double), ("speed_threshold", c_double),
-        ("pose_randomizer", c_int), ("custom_neutral", c_int), ("neutral_q", c_double * 7), ("needs_scene", c_int),
+        ("pose_randomizer", c_int), ("force_randomize_pose", c_int), ("pose_lo", c_double * 3), ("pose_hi", c_double * 3),
+        ("random_size_cuboids", c_int), ("custom_neutral", c_int), ("neutral_q", c_double * 7), ("needs_scene", c_int),
     ]
 
 
@@ -56,7 +57,7 @@ class HerBatch(ctypes.Structure):
 
 VIEW_IDS = {name: i for i, name in enumerate([
     "observation", "achieved_goal", "desired_goal", "reward", "done", "flags", "terminal_observation",
-    "terminal_achieved", "ep_return", "ep_length", "q", "qd", "goal", "obstacle_pos", "stats", "step_count", "d_link", "object"])}
+    "terminal_achieved", "ep_return", "ep_length", "q", "qd", "goal", "obstacle_pos", "stats", "step_count", "d_link", "object", "obstacle_size"])}
 
 # every symbol include/panda_b200.h declares: (name, restype, argtypes)
 P = c_void_p

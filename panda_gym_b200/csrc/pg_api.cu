@@ -89,7 +89,12 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   d.obs_sampler = s->obstacle_sampler; d.randomize_obstacles = s->randomize_obstacle_position;
   d.allow_overlap = s->allow_overlapping_obstacles; d.random_num_obs = s->random_num_obs;
   d.size_lo = s->sample_size_lo; d.size_hi = s->sample_size_hi;
-  d.random_base = (h->cfg.randomize_robot_pose && s->pose_randomizer == PG_POSE_RANDOM_BASE) ? 1 : 0;
+  d.pose_active = (h->cfg.task == PG_TASK_REACH_AO && (h->cfg.randomize_robot_pose || s->force_randomize_pose)) ? 1 : 0;
+  d.pose_kind = s->pose_randomizer;
+  d.random_base = (d.pose_active && s->pose_randomizer == PG_POSE_RANDOM_BASE) ? 1 : 0;
+  for (int k = 0; k < 3; k++) { d.pose_lo[k] = s->pose_lo[k]; d.pose_hi[k] = s->pose_hi[k]; }
+  d.random_size = (h->cfg.task == PG_TASK_REACH_AO && s->random_size_cuboids) ? 1 : 0;
+  P.scene.env_box = d.random_size ? P.env_box : nullptr;
   d.max_episode_steps = s->max_episode_steps;
   d.ee_thr = (float)s->ee_error_threshold; d.speed_thr = (float)s->speed_threshold;
   // observation width (reach_ao.py:902-932: np.ones(27) when the scenario has no obstacles)
@@ -103,14 +108,13 @@ void fill_stage(pg_env_s* h, const pg_stage* s) {
   P.obs_dim = 6 + (P.obs_js ? 14 : 0) + (P.task == PG_TASK_PICK_AND_PLACE ? 1 : 0) + t;  // + fingers width (panda.py:282-284)
 }
 
-// randomize_robot_pose (train_config.py:26): which scenario randomizers exist on the device
+// randomize_robot_pose (train_config.py:26): every scenario randomizer is built; the combinations that are not are rejected here
 int check_pose_randomizer(const pg_config* cfg, const pg_stage* s) {
-  if (!cfg->randomize_robot_pose || cfg->task != PG_TASK_REACH_AO) return PG_OK;
-  if (s->pose_randomizer != PG_POSE_RANDOM_BASE)
-    return fail(PG_ERR_UNSUPPORTED, "randomize_robot_pose: this scenario's robot_pose_randomizer calls roboticstoolbox ik_lm_chan "
-                                    "(panda.py:220-224), which is not built; only set_random_robot_base (wangexp-N) is");
-  for (int j = 0; j < s->n_obstacles; j++)
-    if (s->obstacle_type[j] != 0) return fail(PG_ERR_UNSUPPORTED, "randomize_robot_pose with cuboid obstacles is not built");
+  if (cfg->task != PG_TASK_REACH_AO || !(cfg->randomize_robot_pose || s->force_randomize_pose)) return PG_OK;
+  if (s->pose_randomizer < PG_POSE_TORUS || s->pose_randomizer > PG_POSE_BULLET_IK_BOX) return fail(PG_ERR_ARG, "unknown pose_randomizer");
+  if (s->pose_randomizer == PG_POSE_RANDOM_BASE)  // the neutral-pose table is turned about joint 1: exact for sphere bodies only
+    for (int j = 0; j < s->n_obstacles; j++)
+      if (s->obstacle_type[j] != 0) return fail(PG_ERR_UNSUPPORTED, "set_random_robot_base with cuboid obstacles is not built");
   return PG_OK;
 }
 
@@ -147,22 +151,32 @@ int pg_stage_from_scenario(pg_stage* s, const char* scenario) {
     set_goal_box(s, -0.15, 0.15, -0.15, 0.15, 0.0, 0.3);
   } else if (name == "reach1") {          // reach_ao.py:518-522
     set_goal_box(s, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4);
+    s->pose_randomizer = PG_POSE_TORUS_FRONT;
   } else if (name == "reach2" || name == "reach3") {  // :524-539
     set_goal_shell(s, 0.5, 0.85, 1, 0, 1);
+    s->pose_randomizer = name == "reach2" ? PG_POSE_TORUS_FRONT : PG_POSE_TORUS;
   } else if (name == "reachao1") {        // :541-545
     set_goal_box(s, -0.4 / 2 + 0.6, 0.4 / 2 + 0.6, -0.4 / 2, 0.4 / 2, 0, 0.4);
+    s->pose_randomizer = PG_POSE_TORUS_FRONT;  // inherited from create_scenario_reach1
     s->randomize_obstacle_position = 1; add_sphere(s, 0.04);
   } else if (name == "reachao2") {        // :547-564
     set_goal_shell(s, 0.5, 0.8, 1, 1, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG;
+    s->pose_randomizer = PG_POSE_IK_GOAL_SPACE;
     add_sphere(s, 0.05); add_sphere(s, 0.05);
   } else if (name == "reachao3") {        // :573-585
     set_goal_shell(s, 0.5, 0.8, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG;
+    s->pose_randomizer = PG_POSE_IK_GOAL_SPACE;
     for (int i = 0; i < 3; i++) add_sphere(s, 0.05);
-  } else if (name == "reachao_rand") {    // :587-599
+  } else if (name == "reachao_rand" || name == "reachao_rand_start" || name == "reachao_rand_shape") {    // :587-608
     set_goal_shell(s, 0.5, 0.8, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_EXPERIMENTAL;
+    s->pose_randomizer = PG_POSE_IK_GOAL_SPACE;  // inherited from create_scenario_reachao3
     for (int i = 0; i < 3; i++) add_sphere(s, 0.05);
     for (int i = 0; i < 3; i++) add_cuboid(s, 0.05);
     s->random_num_obs = 1; s->allow_overlapping_obstacles = 1; s->sample_size_lo = 4; s->sample_size_hi = 6;
+    if (name == "reachao_rand_start") {   // :601-604
+      s->force_randomize_pose = 1; s->pose_randomizer = PG_POSE_IK_SPHERE; s->pose_lo[0] = 0.45; s->pose_hi[0] = 0.7;
+    }
+    if (name == "reachao_rand_shape") s->random_size_cuboids = 1;  // :606-608
   } else if (name == "wang") {            // :646-699
     if (count < 0 || count > PG_MAX_OBSTACLES) return fail(PG_ERR_ARG, "wang-N: N out of range");
     set_goal_shell(s, 0.4, 0.95, 1, 0, 0); s->randomize_obstacle_position = 1; s->obstacle_sampler = PG_OSMP_WANG_N;
@@ -198,6 +212,16 @@ int pg_stage_from_scenario(pg_stage* s, const char* scenario) {
     if (!def) return fail(PG_ERR_ARG, std::string("Scenario ") + scenario + " not found!");  // reach_ao.py:262-264
     set_goal_box(s, def->lo[0], def->hi[0], def->lo[1], def->hi[1], def->lo[2], def->hi[2]);
     s->needs_scene = 1;
+    // scene builders that install their own start-pose randomizer and switch it on (reach_ao.py:310-320, 363-375, 395-403)
+    struct PoseDef { const char* name; int kind; double lo[3], hi[3]; };
+    static const PoseDef kPoses[] = {{"narrow_tunnel", PG_POSE_IK_BOX, {0.0, -0.6, 0.2}, {0.5, -0.5, 0.7}},
+                                     {"workshop2", PG_POSE_IK_BOX, {-0.5, -0.6, 0.6}, {0.2, -0.3, 0.7}},
+                                     {"industrial", PG_POSE_BULLET_IK_BOX, {-0.5, -0.8, 0.4}, {0.2, -0.4, 0.7}}};
+    for (const PoseDef& pd : kPoses)
+      if (full == pd.name) {
+        s->force_randomize_pose = 1; s->pose_randomizer = pd.kind;
+        for (int k = 0; k < 3; k++) { s->pose_lo[k] = pd.lo[k]; s->pose_hi[k] = pd.hi[k]; }
+      }
     if (def->neutral) { s->custom_neutral = 1; for (int d = 0; d < 7; d++) s->neutral_q[d] = kNeutralSets[def->neutral][d]; }
   }
   return PG_OK;
@@ -281,6 +305,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   A(P.d_link, 9 * n, true) A(P.q_dl, 7 * n, true) A(P.past_vec, 54 * n, true) A(P.have_recent, n, true) A(P.have_prev, n, true) A(P.collided, n, true) A(P.goal_reached, n, true)
   A(P.need_reset, n, true) A(P.steps, n, true) A(P.ep_len, n, true) A(P.last_len, n, true) A(P.ep_ret, n, true) A(P.last_ret, n, true)
   A(P.rng, 4 * n, true) A(P.episode, n, true) A(P.obj, 13 * n, true)
+  A(P.env_size, (size_t)pg::kMaxObst * 3 * n, true) A(P.env_box, (size_t)pg::kMaxObst * 5 * n, true) A(P.crand, (size_t)33 * n, false)
   {  // the six per-step results live in ONE slab so that the host-buffer step moves them with a single device-to-host copy:
      // [achieved 3n f32 | desired 3n f32 | reward n f32 | done n u8 | flags n u8 | pad to 256 B | observation n x obs_dim f32]
      // (the observation comes last: its width depends on the stage, the copy stops after n x obs_dim)
@@ -311,6 +336,26 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
     if (e2 != cudaSuccess) { pg_destroy(h); return fail(PG_ERR_CUDA, cudaGetErrorString(e2)); }
     pg::launch_mirror_obstacles(P, 0);
   }
+  {  // every environment stands for one SubprocVecEnv worker process: its C rand() stream starts at glibc's srand(1) state
+     // (the restart stream of roboticstoolbox's ik_lm_chan, pg_reset.cuh); r[31] | front index | back index
+    uint32_t st[33];
+    int32_t word = 1;
+    st[0] = 1;
+    for (int i = 1; i < 31; i++) {
+      const int32_t hi = word / 127773, lo = word % 127773;
+      word = 16807 * lo - 2836 * hi;
+      if (word < 0) word += 2147483647;
+      st[i] = (uint32_t)word;
+    }
+    int f = 3, b = 0;
+    for (int i = 0; i < 310; i++) { st[f] += st[b]; f = (f + 1) % 31; b = (b + 1) % 31; }
+    st[31] = (uint32_t)f; st[32] = (uint32_t)b;
+    std::vector<uint32_t> init((size_t)33 * n);
+    for (int e = 0; e < n; e++) memcpy(&init[(size_t)33 * e], st, sizeof st);
+    cudaError_t e2 = cudaMemcpy(P.crand, init.data(), init.size() * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    if (e2 != cudaSuccess) { pg_destroy(h); return fail(PG_ERR_CUDA, cudaGetErrorString(e2)); }
+  }
+  fill_stage(h, &cfg->stage);  // again, now that the per-environment size buffer exists (scene.env_box)
   pg::launch_neutral_table(P, cfg->stage.custom_neutral ? cfg->stage.neutral_q : nullptr, 0);
   P.base_seed = 0;
   *out = h;
@@ -545,6 +590,7 @@ int pg_get_view(pg_handle h, int id, pg_view* v) {
     case PG_V_STEP_COUNT: set(P.steps, 2, 1, n, 0, 0); break;
     case PG_V_D_LINK: set(P.d_link, 0, 2, 9, n, 0); break;
     case PG_V_OBJECT: set(P.obj, 0, 2, 13, n, 0); break;
+    case PG_V_OBSTACLE_SIZE: set(P.env_size, 3, 3, pg::kMaxObst, 3, n); break;
     default: return fail(PG_ERR_ARG, "unknown view id");
   }
   return PG_OK;

@@ -39,6 +39,9 @@ struct StageDev {  // device copy of pg_stage (scenario parameter block)
   double obs_size[kMaxObst][3];
   int obs_sampler, randomize_obstacles, allow_overlap, random_num_obs, size_lo, size_hi;
   int random_base;   // randomize_robot_pose with set_random_robot_base (reach_ao.py:1238-1241)
+  int pose_active, pose_kind;      // the scenario's robot_pose_randomizer replaces Panda.reset (pg_pose_randomizer)
+  double pose_lo[3], pose_hi[3];
+  int random_size;   // reachao_rand_shape: cuboid half extents re-drawn at every reset (reach_ao.py:1084-1089)
   int max_episode_steps;
   float ee_thr, speed_thr;
 };
@@ -62,6 +65,9 @@ struct Params {
   double* goal;                  // [3][n]
   double* obs_pos;               // [kMaxObst][3][n]
   float* obs_pos_f;              // fp32 mirror read by the per-substep collision pass (refreshed by reset / set_obstacles)
+  double* env_size;              // [kMaxObst][3][n] per-environment cuboid half extents (random_size_cuboids only)
+  float* env_box;                // [kMaxObst][5][n] fp32 mirror: half extents, collision margin, bounding radius (scene.env_box)
+  uint32_t* crand;               // [n][33] glibc rand() state of each environment's "worker process": ik_lm_chan's restart stream
   float *recent, *prev;          // [7][n] action history (panda.py:138-139)
   float *cur_vel, *cur_acc, *jerk; // [7][n] (panda.py:167-172)
   float* d_link;                 // [9][n]
@@ -135,6 +141,19 @@ __device__ __forceinline__ uint64_t pcg_next(Pcg& g) {
   uint64_t x = g.s_hi ^ g.s_lo;
   unsigned rot = (unsigned)(g.s_hi >> 58);
   return (x >> rot) | (x << ((64 - rot) & 63));
+}
+// BitGenerator.advance(delta): skip delta draws by LCG jump-ahead, O(log delta) 128-bit multiplications
+__device__ inline void pcg_advance(Pcg& g, uint64_t delta) {
+  u128 state = ((u128)g.s_hi << 64) | g.s_lo, inc = ((u128)g.i_hi << 64) | g.i_lo;
+  u128 acc_mult = 1, acc_plus = 0, cur_mult = pcg_mult(), cur_plus = inc;
+  while (delta > 0) {
+    if (delta & 1) { acc_mult *= cur_mult; acc_plus = acc_plus * cur_mult + cur_plus; }
+    cur_plus = (cur_mult + 1) * cur_plus;
+    cur_mult *= cur_mult;
+    delta >>= 1;
+  }
+  state = acc_mult * state + acc_plus;
+  g.s_hi = (uint64_t)(state >> 64); g.s_lo = (uint64_t)state;
 }
 __device__ __forceinline__ double pcg_double(Pcg& g) { return (double)(pcg_next(g) >> 11) * (1.0 / 9007199254740992.0); }
 // numpy random_uniform: off + range * next_double, no FMA contraction (bit parity with the host generator)

@@ -19,6 +19,8 @@ struct Camera {          // built on the host (pg_api.cu), Bullet's view / proje
 void launch_step(const Params& P, const float* actions, cudaStream_t s);
 void launch_debug_substeps(int n, float* q, float* qd, const float* tgt, const float* f, int n_sub, int velocity_mode, cudaStream_t s);
 cudaError_t step_kernel_attrs(int* out6);
+// pg_tu_step_envbox.cu
+void launch_step_envbox(const Params& P, const float* actions, cudaStream_t s);
 // pg_tu_obj.cu
 void launch_step_obj(const Params& P, const float* actions, cudaStream_t s);
 // pg_tu_reset.cu
@@ -26,6 +28,9 @@ void launch_reset_all(const Params& P, const uint8_t* mask, const uint64_t* seed
 void launch_reset_list(const Params& P, uint64_t first_env, int sm_count, cudaStream_t s);
 void launch_observe(const Params& P, cudaStream_t s);
 void launch_neutral_table(const Params& P, const double* q7 /* nullptr = panda.py:67 */, cudaStream_t s);
+// pg_tu_reset_envbox.cu
+void launch_reset_envbox(const Params& P, bool list, const uint8_t* mask, const uint64_t* seeds, uint64_t first_env, int sm_count, cudaStream_t s);
+void launch_observe_envbox(const Params& P, cudaStream_t s);
 // pg_tu_misc.cu
 void launch_mirror_obstacles(const Params& P, cudaStream_t s);
 void launch_reward(const Params& P, const float* ag, const float* dg, float* out, int64_t n, int src, cudaStream_t s);

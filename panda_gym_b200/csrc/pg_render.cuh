@@ -150,7 +150,8 @@ __global__ void __launch_bounds__(256) k_render(const Params P, const Camera cam
       for (int j = 0; j < P.scene.nobs; j++) {
         V3 o = v3(P.obs_pos_f[(size_t)(j * 3 + 0) * n + env], P.obs_pos_f[(size_t)(j * 3 + 1) * n + env], P.obs_pos_f[(size_t)(j * 3 + 2) * n + env]);
         if (o.z < -50.f) continue;  // parked by set_random_num_obs (reach_ao.py:1062-1082)
-        const Obst& ob = P.scene.obst[j];
+        float bound;
+        const Obst ob = scene_obst(P.scene, j, env, n, bound);  // per-environment cuboid sizes where the stage has them
         if (ob.type == 0) set(s_prims[k++], 0, o, z3, ob.sx, 0.f, z3, 1.f, 0.f, 0.f, 0);
         else set(s_prims[k++], 2, o, z3, 0.f, 0.f, v3(ob.sx, ob.sy, ob.sz), 1.f, 0.5f, 0.f, 0);
       }

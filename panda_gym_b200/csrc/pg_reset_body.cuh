@@ -1,0 +1,243 @@
+// pg_reset_body.cuh -- bodies of the reset and observation-refresh kernels, included once per translation unit that instantiates
+// them: pg_tu_reset.cu (PG_ENVBOX 0, the default: obstacle shapes from the kernel parameters) and pg_tu_reset_envbox.cu
+// (PG_ENVBOX 1: per-environment cuboid sizes, scenario reachao_rand_shape).  The includer defines PG_RESET_KERNEL /
+// PG_OBSERVE_KERNEL and opens namespace pg.
+
+// GPOSE: the stage has a start-pose randomizer that puts the arm anywhere (rtb_ik / Bullet IK); false compiles all of that out
+template <bool WARP, bool GPOSE>
+__global__ void __launch_bounds__(kBlock) PG_RESET_KERNEL(const __grid_constant__ Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
+                                                  uint64_t first_env) {
+  const int n = P.n;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int count = WARP ? *P.reset_count : n;
+  const int stride = WARP ? (gridDim.x * blockDim.x) >> 5 : gridDim.x * blockDim.x;
+  const bool leader = WARP ? (threadIdx.x & 31) == 0 : true;
+  for (int item = WARP ? tid >> 5 : tid; item < count; item += stride) {
+  int e = item;
+  if (WARP) e = P.reset_list[item];
+  else if (mask && !mask[e]) continue;
+  P.need_reset[e] = 0;
+  uint32_t ep = P.episode[e];
+  P.episode[e] = ep + 1;
+  uint64_t seed = seeds ? seeds[e] : episode_seed(P.base_seed, first_env + (uint64_t)e, ep);
+  Pcg g; pcg_seed(g, seed);
+  const StageDev& st = P.st;
+  // Panda.reset (panda.py:290-298) -- or, with randomize_robot_pose, the scenario's randomizer in its place
+  // (reach_ao.py:132-133): set_random_robot_base draws joint 1 from its limits (panda.py:77-79) and keeps the rest neutral
+  const bool rbase = P.task == 1 && st.random_base;
+  const bool gpose = GPOSE;  // (the launcher checks: ReachAO, pose_active, not set_random_robot_base)
+  const double* __restrict__ NX = P.nextra;  // ee[3] | link0[3] | q[7] of the reset pose
+  double q0 = NX[6], c0 = 1.0, s0 = 0.0;
+  if (rbase) { q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - NX[6]); s0 = sin(q0 - NX[6]); }
+  float q[7], qd[7], cq[7], sq[7];
+  P.steps[e] = 0; P.ep_ret[e] = 0.f; P.ep_len[e] = 0;
+  double goal[3], ee[6];  // ee[0..2] = get_ee_position(), ee[3..5] = get_link_position(0), both at the reset pose
+  int status = 0;
+  PoseD pose; double qpose[7]; CRand cr;
+  const PoseD* pp = gpose ? &pose : nullptr;
+  if (gpose) {
+    const uint32_t* cs = P.crand + (size_t)33 * e;
+    for (int k = 0; k < 31; k++) cr.r[k] = cs[k];
+    cr.f = (int)cs[31]; cr.b = (int)cs[32];
+    // the joints the robot has when the randomizer runs: what the last episode left, or, in a fresh environment, the neutral
+    // pose its scene builder installed (reach_ao.py:405 set_joint_neutral) -- Bullet's IK (industrial) starts from them
+    for (int d = 0; d < 7; d++) qpose[d] = ep == 0 ? NX[6 + d] : (double)P.q[(size_t)d * n + e];
+    status |= randomize_pose<WARP>(P, e, g, cr, qpose, pose, qpose);
+  }
+#define PG_EE_AT_POSE()                                                                                   \
+  do {                                                                                                    \
+    ee[0] = c0 * NX[0] - s0 * NX[1] + P.based[0];                               \
+    ee[1] = s0 * NX[0] + c0 * NX[1] + P.based[1];                               \
+    ee[2] = NX[2] + P.based[2];                                                              \
+    ee[3] = c0 * NX[3] - s0 * NX[4] + P.based[0];                         \
+    ee[4] = s0 * NX[3] + c0 * NX[4] + P.based[1];                         \
+    ee[5] = NX[5] + P.based[2];                                                           \
+  } while (0)
+#define PG_EE_AT_GPOSE()                                                                                  \
+  do {                                                                                                    \
+    pose_point(pose, 7, pgm::kLocalEE, ee); pose_point(pose, 1, pgm::kLocalLink0, ee + 3);                \
+    for (int k = 0; k < 3; k++) { ee[k] += P.based[k]; ee[3 + k] += P.based[k]; }                         \
+  } while (0)
+  if (gpose) PG_EE_AT_GPOSE(); else PG_EE_AT_POSE();
+  if (P.task == 0) {
+    for (int k = 0; k < 3; k++) goal[k] = pcg_uniform(g, st.goal_lo[k], st.goal_hi[k]);
+  } else if (P.task >= 2) {
+    // Push.reset (push.py:69-87) / PickAndPlace.reset (pick_and_place.py:65-85): goal, then object; xy range 0.3;
+    // PickAndPlace lifts the goal by U(0, 0.2) and flattens it again with probability 0.3
+    const double half = P.obj_half_z;
+    double nx = pcg_uniform(g, -0.15, 0.15), ny = pcg_uniform(g, -0.15, 0.15), nz = pcg_uniform(g, 0.0, P.task == 3 ? 0.2 : 0.0);
+    if (P.task == 3 && pcg_double(g) < 0.3) nz = 0.0;
+    goal[0] = 0.0 + nx; goal[1] = 0.0 + ny; goal[2] = half + nz;
+    nx = pcg_uniform(g, -0.15, 0.15); ny = pcg_uniform(g, -0.15, 0.15); nz = pcg_uniform(g, 0.0, 0.0);
+    ObjState B;
+    B.x = v3((float)(0.0 + nx), (float)(0.0 + ny), (float)(half + nz));
+    B.qx = B.qy = B.qz = 0.f; B.qw = 1.f; B.v = v3(0, 0, 0); B.w = v3(0, 0, 0);  // set_base_pose: identity orientation, velocities zeroed
+    store_obj(P, e, B);
+    P.have_recent[e] = 0; P.have_prev[e] = 0;
+  } else {
+    P.goal_reached[e] = 0; P.collided[e] = 0;
+    if (st.random_size) {  // add_random_size_cuboids (reach_ao.py:969-979, 1084-1089): half extents 0.2 * Dirichlet(1, 1, 1), in
+      for (int j = 0; j < st.nobs; j++)  // dict order; the re-created body sits at create_obstacle_cuboid's default position
+        if (st.obs_type[j] == 1) {
+          double f[3];
+          pcg_dirichlet111(g, f);
+          for (int k = 0; k < 3; k++) P.env_size[(size_t)(j * 3 + k) * n + e] = 0.2 * f[k];
+          P.obs_pos[(size_t)(j * 3 + 0) * n + e] = 0.1; P.obs_pos[(size_t)(j * 3 + 1) * n + e] = 0.0; P.obs_pos[(size_t)(j * 3 + 2) * n + e] = 0.1;
+        }
+    }
+    Body table; table.type = 1; table.px = P.table_pos[0]; table.py = P.table_pos[1]; table.pz = P.table_pos[2];
+    table.sx = P.table_half[0]; table.sy = P.table_half[1]; table.sz = P.table_half[2];
+    Body probe; probe.type = 0; probe.sx = 0.05; probe.sy = probe.sz = 0;
+    // set_coll_free_goal: pass 0 = (["table","robot"], 0.1); pass 1 (only without obstacle randomisation) = all bodies, 0.03
+    // config.fixed_target (reach_ao.py:981): the first pass is skipped (no draws), the goal keeps the configured value unless
+    // the second pass -- taken whenever the obstacles are not re-sampled -- replaces it
+    const int passes = st.randomize_obstacles ? 1 : 2;
+    if (P.has_fixed_target) for (int k = 0; k < 3; k++) goal[k] = P.fixed_target[k];
+    for (int pass = P.has_fixed_target ? 1 : 0; pass < passes; pass++) {
+      const double margin = pass == 0 ? 0.1 : 0.03;
+      int i = 0;
+      for (;;) {
+        sample_goal(st, g, goal);
+        if (i > 9999) { for (int k = 0; k < 3; k++) goal[k] = ee[k]; status = 1; break; }
+        i++;
+        probe.px = goal[0]; probe.py = goal[1]; probe.pz = goal[2];
+        bool coll = false;
+        if (pass == 1) {
+          for (int j = 0; j < st.nobs; j++) coll |= body_body_collision(probe, obstacle_body(P, j, e), margin);
+          for (int j = 0; j < P.scene.nstatic && !coll; j++) {  // the scene's URDF bodies are obstacles like any other (reach_ao.py:986-988)
+            V3 o;
+            const Obst ob = static_obst(P.scene, j, o);
+            const double m = ob.margin;
+            coll |= margin >= sphere_box<double>(v3t<double>(probe.px, probe.py, probe.pz), probe.sx, v3t<double>(o.x, o.y, o.z),
+                                                 v3t<double>(ob.sx - m, ob.sy - m, ob.sz - m), m).d;
+          }
+        }
+        coll |= body_body_collision(probe, table, margin);
+        if (!coll) coll |= (margin >= robot_body_distance<WARP, GPOSE>(P, probe, margin, c0, s0, pp));
+        if (!coll) break;
+      }
+    }
+    if (st.randomize_obstacles) {  // set_coll_free_obs(0.03)
+      const double margin = 0.03;
+      bool stop = false;  // StopIteration escapes set_coll_free_obs in the reference (reach_ao.py:1144-1145)
+      for (int j = 0; j < st.nobs && !stop; j++) {
+        int i = 0;
+        for (;;) {
+          if (i > 9999) { status |= 2; stop = true; break; }
+          i++;
+          double pos[3];
+          sample_obstacle(P, g, goal, ee, pos);
+          for (int k = 0; k < 3; k++) P.obs_pos[(size_t)(j * 3 + k) * n + e] = pos[k];
+          Body ob = obstacle_body(P, j, e);
+          bool coll = body_body_collision(table, ob, margin);
+          coll |= body_body_collision(probe, ob, margin);
+          if (!st.allow_overlap) {
+            for (int k = 0; k < st.nobs; k++) if (k != j) coll |= body_body_collision(obstacle_body(P, k, e), ob, 0.0);
+            probe.px = probe.py = probe.pz = 0.0;  // the probe sphere is moved to the origin and left there
+            coll |= !body_body_collision(probe, ob, 1.0);
+          }
+          if (!coll) coll |= (margin + P.safety_distance >= robot_body_distance<WARP, GPOSE>(P, ob, margin + P.safety_distance, c0, s0, pp));
+          if (!coll) break;
+        }
+      }
+    }
+    if (gpose && st.pose_kind == PG_POSE_IK_SPHERE)  // its check_collided (fp32 scene pass) must see the obstacles just sampled
+      for (int k = 0; k < st.nobs * 3; k++) P.obs_pos_f[(size_t)k * n + e] = (float)P.obs_pos[(size_t)k * n + e];
+    if (rbase || gpose) {  // set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the pose while the robot is within 0.05
+      // self.obstacles = the sampled obstacles, then (benchmark scenes) the scene's bodies (reach_ao.py:300-306)
+      const int nbody = st.nobs + (gpose ? P.scene.nstatic : 0);
+      for (int j = 0; j < nbody; j++) {
+        Body ob;
+        if (j < st.nobs) ob = obstacle_body(P, j, e);
+        else {
+          V3 o;
+          const Obst so = static_obst(P.scene, j - st.nobs, o);
+          ob.type = 1; ob.px = o.x; ob.py = o.y; ob.pz = o.z; ob.sx = so.sx; ob.sy = so.sy; ob.sz = so.sz; ob.margin = so.margin;
+        }
+        int i = 0;
+        // futile case (see oracle/pgo_env.c set_coll_free_robot): the obstacle stands within 0.05 of the base column, which no
+        // pose moves -- all 10 000 tries of the reference fail, then it sets the neutral pose.  Short-circuited: the numpy stream
+        // jumps over the tries' draws where their number is fixed; the C rand() stream is left alone (stated deviation).
+        if (gpose && 0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, 1.0, 0.0, pp) && 0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, 1.0, 0.0, pp, 1)) {
+          if (st.pose_kind == PG_POSE_IK_GOAL_SPACE)
+            pcg_advance(g, 10000ull * (uint64_t)(st.goal_sampler == 0 ? 3 : 3 + (st.goal_front ? 1 : 0) + (st.goal_34 ? 1 : 0)));
+          if (st.pose_kind == PG_POSE_IK_BOX || st.pose_kind == PG_POSE_BULLET_IK_BOX) pcg_advance(g, 30000ull);
+          for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d];
+          pose_fk(qpose, pose);
+          status |= 4;
+          continue;
+        }
+        while (0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, c0, s0, pp)) {
+          if (i > 9999) {  // set_joint_neutral (with set_random_robot_base, neutral_joint_values[0] already holds the last draw)
+            status |= 4;
+            if (gpose) { for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d]; pose_fk(qpose, pose); }
+            break;
+          }
+          i++;
+          if (gpose) status |= randomize_pose<WARP>(P, e, g, cr, qpose, pose, qpose);
+          else { q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - NX[6]); s0 = sin(q0 - NX[6]); }
+        }
+      }
+    }
+    if (st.random_num_obs) {  // set_random_num_obs (reach_ao.py:1062-1082)
+      int nb = st.nobs;
+      uint32_t span = (uint32_t)(st.size_hi - 1 - st.size_lo);
+      int k = st.size_lo + (span == 0 ? 0 : (int)pcg_lemire32(g, span));
+      int to_move = abs(k - nb), order[kMaxObst];
+      for (int i = 0; i < nb; i++) order[i] = i;
+      for (int i = nb - 1; i >= 1; i--) { int j = (int)pcg_interval32(g, (uint32_t)i); int t = order[i]; order[i] = order[j]; order[j] = t; }
+      for (int i = 0; i < nb && to_move > 0; i++, to_move--) {
+        P.obs_pos[(size_t)(order[i] * 3 + 0) * n + e] = 99.9; P.obs_pos[(size_t)(order[i] * 3 + 1) * n + e] = 99.9; P.obs_pos[(size_t)(order[i] * 3 + 2) * n + e] = -99.9;
+      }
+    }
+    P.have_recent[e] = 0; P.have_prev[e] = 0;
+    for (int k = 0; k < st.nobs * 3; k++) P.obs_pos_f[(size_t)k * n + e] = (float)P.obs_pos[(size_t)k * n + e];
+    if (st.random_size)
+      for (int j = 0; j < st.nobs; j++)
+        if (st.obs_type[j] == 1) {  // fp32 mirror for the collision / observation passes (same arithmetic as k_mirror_obstacles)
+          const Body b = obstacle_body(P, j, e);
+          float* eb = P.env_box + (size_t)(j * 5) * n + e;
+          eb[0] = (float)b.sx; eb[n] = (float)b.sy; eb[(size_t)2 * n] = (float)b.sz;
+          eb[(size_t)3 * n] = (float)box_margin_d(b.sx, b.sy, b.sz);
+          eb[(size_t)4 * n] = sqrtf((float)b.sx * (float)b.sx + (float)b.sy * (float)b.sy + (float)b.sz * (float)b.sz);
+        }
+  }
+  if (WARP && gpose) __syncwarp();  // every lane has read the stream state before the leader stores the advanced one
+  if (gpose && leader) {
+    uint32_t* cs = P.crand + (size_t)33 * e;
+    for (int k = 0; k < 31; k++) cs[k] = cr.r[k];
+    cs[31] = (uint32_t)cr.f; cs[32] = (uint32_t)cr.b;
+  }
+#undef PG_EE_AT_POSE
+#undef PG_EE_AT_GPOSE
+#pragma unroll
+  for (int d = 0; d < 7; d++) {
+    q[d] = (float)(gpose ? qpose[d] : (d == 0 ? q0 : NX[6 + d])); qd[d] = 0.f;
+    P.q[(size_t)d * n + e] = q[d]; P.qd[(size_t)d * n + e] = 0.f;
+    sincosf(q[d], &sq[d], &cq[d]);
+  }
+  for (int k = 0; k < 3; k++) P.goal[(size_t)k * n + e] = goal[k];
+  P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;
+  if (status && leader) atomicAdd(&P.stats[6], 1.0);
+  float ag[3], dg[3];
+  observe(P, e, q, qd, q, cq, sq, ag, true);
+  dg[0] = (float)goal[0]; dg[1] = (float)goal[1]; dg[2] = (float)goal[2];
+  bool succ = is_success(P, e, ag, dg);
+  if (!WARP) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
+  }
+}
+
+// refresh observation / goals at the current state (no stepping)
+__global__ void __launch_bounds__(kBlock) PG_OBSERVE_KERNEL(const Params P) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= P.n) return;
+  float q[7], qd[7], cq[7], sq[7], ag[3];
+#pragma unroll
+  for (int d = 0; d < 7; d++) { q[d] = P.q[(size_t)d * P.n + e]; qd[d] = P.qd[(size_t)d * P.n + e]; sincosf(q[d], &sq[d], &cq[d]); }
+  observe(P, e, q, qd, q, cq, sq, ag, true);
+  if (P.task == 1) {
+    bool hit = scene_pass<false, false>(true, P.scene, P.obs_pos_f, P.n, e, v3(P.base[0], P.base[1], P.base[2]), cq, sq, nullptr, nullptr);
+    P.flags[e] = (uint8_t)((P.flags[e] & ~4) | (hit ? 4 : 0));
+  }
+}
+

@@ -7,6 +7,14 @@ namespace pg {
 __global__ void k_mirror_obstacles(const Params P) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < (int64_t)kMaxObst * 3 * P.n) P.obs_pos_f[i] = (float)P.obs_pos[i];
+  if (P.st.random_size && i < (int64_t)kMaxObst * P.n) {  // fp32 mirror of the per-environment cuboid sizes (pg_reset.cuh: store_env_box)
+    const int j = (int)(i / P.n), e = (int)(i % P.n);
+    const double sx = P.env_size[(size_t)(j * 3) * P.n + e], sy = P.env_size[(size_t)(j * 3 + 1) * P.n + e], sz = P.env_size[(size_t)(j * 3 + 2) * P.n + e];
+    float* b = P.env_box + (size_t)(j * 5) * P.n + e;
+    b[0] = (float)sx; b[P.n] = (float)sy; b[(size_t)2 * P.n] = (float)sz;
+    b[(size_t)3 * P.n] = (float)fmin(0.04, 0.1 * fmin(sx, fmin(sy, sz)));
+    b[(size_t)4 * P.n] = sqrtf((float)sx * (float)sx + (float)sy * (float)sy + (float)sz * (float)sz);
+  }
 }
 
 __global__ void k_reward(const Params P, const float* __restrict__ ag, const float* __restrict__ dg, float* __restrict__ out, int64_t m, int src) {

@@ -48,10 +48,6 @@ def make_config(task, n_envs, scenario=None, config=None, control_type=None, rew
         if c.task_observations.get("prior") is not None:
             raise _lib.PandaB200Error("task_observations['prior'] (NEO prior, needs Gurobi) is out of scope")
         cfg.randomize_robot_pose = int(bool(c.randomize_robot_pose))
-        if cfg.randomize_robot_pose and cfg.stage.pose_randomizer != 1:  # same rule as pg_create (PG_POSE_RANDOM_BASE)
-            raise _lib.PandaB200Error("randomize_robot_pose=True: this scenario's robot_pose_randomizer calls roboticstoolbox "
-                                      "ik_lm_chan (panda.py:220-224), which is not built; only set_random_robot_base "
-                                      "(scenario wangexp-N) is (SURVEY section 8f, N2)")
         if c.fixed_target is not None:
             cfg.has_fixed_target = 1
             for k in range(3):

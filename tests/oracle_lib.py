@@ -25,6 +25,7 @@ class EnvConfig(ctypes.Structure):
         ("base_pos", c_double * 3), ("randomize_robot_pose", c_int),
         ("scene_goal_lo", c_double * 3), ("scene_goal_hi", c_double * 3), ("custom_neutral", c_int), ("neutral_q", c_double * 7),
         ("has_fixed_target", c_int), ("fixed_target", c_double * 3),
+        ("scene_pose_randomizer", c_int), ("scene_force_randomize", c_int), ("scene_pose_lo", c_double * 3), ("scene_pose_hi", c_double * 3),
     ]
 
 
@@ -52,7 +53,7 @@ class Pcg64(ctypes.Structure):
 
 
 SCENARIOS = {"none": 0, "reach1": 1, "reach2": 2, "reach3": 3, "reachao1": 4, "reachao2": 5, "reachao3": 6,
-             "reachao_rand": 7, "wang": 8, "wangexp": 9, "static": 10}
+             "reachao_rand": 7, "wang": 8, "wangexp": 9, "static": 10, "reachao_rand_start": 11, "reachao_rand_shape": 12}
 
 
 def build():
@@ -102,6 +103,10 @@ def lib():
     sig("pgo_pcg64_next", c_u64, P)
     sig("pgo_pcg64_double", c_double, P)
     sig("pgo_pcg64_uniform", c_double, P, c_double, c_double)
+    sig("pgo_pcg64_advance", None, P, c_u64)
+    sig("pgo_pcg64_standard_exponential", c_double, P)
+    sig("pgo_pcg64_dirichlet111", None, P, P)
+    sig("pgo_arm_ik_lm_chan", c_int, P, P, P, c_int, c_int, c_double, c_double, P, P, P)
     sig("pgo_env_default_config", None, P, c_int)
     sig("pgo_env_create", P, P)
     sig("pgo_env_destroy", None, P)
@@ -232,7 +237,7 @@ class Env:
                 self.cfg.scenario = SCENARIOS[name]
                 if n:
                     self.cfg.n_obstacles = int(n)
-            elif k in ("base_pos", "scene_goal_lo", "scene_goal_hi", "neutral_q", "fixed_target"):
+            elif k in ("base_pos", "scene_goal_lo", "scene_goal_hi", "neutral_q", "fixed_target", "scene_pose_lo", "scene_pose_hi"):
                 for i in range(len(v)):
                     getattr(self.cfg, k)[i] = float(v[i])
             else:

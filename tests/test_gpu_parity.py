@@ -649,14 +649,6 @@ def test_random_robot_base_reset_matches_oracle(sim, oracle):
     b.close()
 
 
-def test_randomize_robot_pose_needs_a_built_randomizer(sim):
-    from panda_gym_b200.config import TrainConfig
-    from panda_gym_b200._lib import PandaB200Error
-    tc = TrainConfig()
-    tc.randomize_robot_pose = True
-    with pytest.raises(PandaB200Error, match="ik_lm_chan"):
-        sim.PandaBatch(sim.make_config(1, 4, scenario="reachao3", config=tc))
-
 # ------------------------------------------------------------------------------------------ N3: evaluation metrics
 def test_benchmark_metrics_match_perform_benchmark_on_the_oracle(sim, oracle):
     """evaluation/evaluate.py:perform_benchmark (:131-300) replayed on oracle envs -- many episodes per env, each reset with

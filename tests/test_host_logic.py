@@ -67,10 +67,21 @@ def test_make_config_maps_trainconfig(lib):
                           max_episode_steps=75, speed_threshold=0.01)
     assert (cfg.reward_type, cfg.goal_condition, cfg.action_limiter, cfg.obstacle_obs) == (4, 1, 1, 3)
     assert cfg.collision_reward == -50 and cfg.stage.max_episode_steps == 75 and cfg.stage.speed_threshold == 0.01
-    with pytest.raises(lib.PandaB200Error):
-        sim.make_config(1, 1, scenario="reachao1", config=TrainConfig(randomize_robot_pose=True))
+    # robot_pose_randomizer of each scenario (reach_ao.py:62-63, 521-604, 669, 711): 0 torus, 1 random base, 2 torus front half,
+    # 3 ik goal space, 4 ik sphere, 5 ik box, 6 Bullet ik box
+    for scn, kind in [("reachao1", 2), ("reach1", 2), ("reach2", 2), ("reach3", 0), ("reachao2", 3), ("reachao3", 3), ("reachao_rand", 3),
+                      ("reachao_rand_shape", 3), ("wang-2", 0), ("wangexp-3", 1)]:
+        cfg = sim.make_config(1, 1, scenario=scn, config=TrainConfig(randomize_robot_pose=True))
+        assert cfg.randomize_robot_pose == 1 and cfg.stage.pose_randomizer == kind and cfg.stage.force_randomize_pose == 0, scn
     cfg = sim.make_config(1, 1, scenario="wangexp-3", config=TrainConfig(randomize_robot_pose=True))  # set_random_robot_base
-    assert cfg.randomize_robot_pose == 1 and cfg.stage.pose_randomizer == 1 and cfg.stage.n_obstacles == 3
+    assert cfg.stage.n_obstacles == 3
+    cfg = sim.make_config(1, 1, scenario="reachao_rand_start")   # switches randomize_robot_pose on itself (reach_ao.py:601-604)
+    assert cfg.stage.force_randomize_pose == 1 and cfg.stage.pose_randomizer == 4 and (cfg.stage.pose_lo[0], cfg.stage.pose_hi[0]) == (0.45, 0.7)
+    cfg = sim.make_config(1, 1, scenario="reachao_rand_shape")
+    assert cfg.stage.random_size_cuboids == 1 and cfg.stage.n_obstacles == 6
+    for scn, kind in [("narrow_tunnel", 5), ("workshop2", 5), ("industrial", 6)]:   # reach_ao.py:310-320, 363-375, 395-403
+        cfg = sim.make_config(1, 1, scenario=scn)
+        assert cfg.stage.force_randomize_pose == 1 and cfg.stage.pose_randomizer == kind, scn
     with pytest.raises(lib.PandaB200Error):
         sim.make_config(1, 1, scenario="no_such_scenario")
 

@@ -122,3 +122,92 @@ def test_random_robot_base_reset(oracle):
     plain = oracle.Env(task=1, scenario="wangexp-3", max_episode_steps=100)
     plain.reset(3)
     assert plain.arm.q()[0][0] == 0.0      # flag off: Panda.reset to the neutral pose
+
+
+# ------------------------------------------------------------------------------------------ N2 / a16: the numpy and libc pieces
+def test_crand_is_glibc_rand(oracle):
+    """roboticstoolbox's ik_lm_chan draws restart configurations from the C library's rand(), never seeded: the oracle's
+    pgo_crand must be glibc's srand(1) stream (checked against the libc of this machine)."""
+    import ctypes
+    libc = ctypes.CDLL("libc.so.6")
+    libc.srand(1)
+    want = [libc.rand() for _ in range(2000)]
+
+    class CRand(ctypes.Structure):
+        _fields_ = [("r", ctypes.c_uint32 * 31), ("f", ctypes.c_int), ("b", ctypes.c_int)]
+    L = oracle.lib()
+    L.pgo_crand_seed.argtypes = [ctypes.c_void_p, ctypes.c_uint32]; L.pgo_crand_next.argtypes = [ctypes.c_void_p]
+    c = CRand()
+    L.pgo_crand_seed(ctypes.byref(c), 1)
+    assert [L.pgo_crand_next(ctypes.byref(c)) for _ in range(2000)] == want
+
+
+def test_dirichlet_is_numpys(oracle):
+    """Generator.dirichlet([1, 1, 1]) and standard_exponential (256-layer ziggurat, tables of tools/gen_ziggurat.py) bit for bit."""
+    import ctypes
+    L = oracle.lib()
+    for seed in (0, 77, 2 ** 40 + 5):
+        g = oracle.Pcg64(); L.pgo_pcg64_seed(ctypes.byref(g), seed)
+        ref = np.random.default_rng(seed)
+        for _ in range(3000):
+            out = np.zeros(3)
+            L.pgo_pcg64_dirichlet111(ctypes.byref(g), oracle.dp(out))
+            assert np.array_equal(out, ref.dirichlet(alpha=[1, 1, 1], size=1)[0])
+        want = ref.standard_exponential(20000)
+        got = np.array([L.pgo_pcg64_standard_exponential(ctypes.byref(g)) for _ in range(20000)])
+        assert np.array_equal(got, want)
+
+
+def test_rtb_ik_reaches_its_target(oracle):
+    """Panda.rtb_ik (panda.py:220-224): the Levenberg-Marquardt solution satisfies ik_lm_chan's own stopping rule (E < 0.01 with
+    the neutral orientation as target), lies inside the toolbox model's joint limits, and most targets need no restart."""
+    import ctypes
+
+    class CRand(ctypes.Structure):
+        _fields_ = [("r", ctypes.c_uint32 * 31), ("f", ctypes.c_int), ("b", ctypes.c_int)]
+    L = oracle.lib()
+    L.pgo_crand_seed.argtypes = [ctypes.c_void_p, ctypes.c_uint32]
+    c = CRand(); L.pgo_crand_seed(ctypes.byref(c), 1)
+    arm = oracle.Arm(model=0)
+    neutral = np.array([0.0, -0.3, 0.0, -2.2, 0.0, 2.0, np.pi / 4])
+    arm.set_q(np.concatenate([neutral, np.zeros(0)])[:7], np.zeros(7))
+    R0, _ = arm.link_frame(7)
+    lo = np.array([-2.8973, -1.7628, -2.8973, -3.0718, -2.8973, -0.0175, -2.8973]); hi = np.array([2.8973, 1.7628, 2.8973, -0.0698, 2.8973, 3.7525, 2.8973])
+    rng = np.random.default_rng(0)
+    codes = []
+    for _ in range(300):
+        phi = rng.uniform(0, 2 * np.pi); th = rng.uniform(0, 0.5 * np.pi); r = np.cbrt(rng.uniform(0.5 ** 3, 0.8 ** 3))
+        t = np.array([r * np.sin(th) * np.cos(phi), r * np.sin(th) * np.sin(phi), r * np.cos(th)])
+        q = np.zeros(7); its = ctypes.c_int(0)
+        rc = L.pgo_arm_ik_lm_chan(arm.h, oracle.dp(t), oracle.dp(neutral), 100, 100, 0.01, 1.0, ctypes.byref(c), oracle.dp(q), ctypes.byref(its))
+        codes.append(rc)
+        if rc == 2:
+            continue
+        assert (q >= lo).all() and (q <= hi).all()
+        arm.set_q(q, np.zeros(7))
+        R, p = arm.link_frame(7)
+        Rerr = R0 @ R.T
+        ang = np.arccos(np.clip((np.trace(Rerr) - 1) / 2, -1, 1))
+        E = 0.5 * (np.sum((t - p) ** 2) + ang ** 2)
+        assert E < 0.01 + 1e-9
+    assert codes.count(0) > 200 and codes.count(2) < 10
+
+
+def test_pose_randomizers_and_random_sizes(oracle):
+    """Each scenario's robot_pose_randomizer moves the arm; set_robot_random_pose keeps the EE height inside [0.4, 0.6];
+    reachao_rand_shape re-draws cuboid half extents 0.2 * Dirichlet(1, 1, 1) = numpy's own rows."""
+    for scn in ("reach1", "reach3", "wang-2"):
+        e = oracle.Env(task=1, scenario=scn, randomize_robot_pose=1, max_episode_steps=100)
+        qs = []
+        for s in range(20):
+            o, info = e.reset(50 + s)
+            assert info["status"] == 0 and 0.4 <= o["achieved_goal"][2] <= 0.6
+            qs.append(e.arm.q()[0][:7].copy())
+        assert np.std(qs, axis=0).max() > 0.1
+    e = oracle.Env(task=1, scenario="reachao_rand_shape", max_episode_steps=100)
+    for s in range(10):
+        e.reset(s)
+        g = np.random.default_rng(s)
+        for t, p, sz in e.obstacles():
+            if t == 1:
+                assert np.array_equal(sz, 0.2 * g.dirichlet(alpha=[1, 1, 1], size=1)[0])

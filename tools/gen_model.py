@@ -358,6 +358,38 @@ def emit_neutral(links, root, order, path):
         ow[idx] = [ow[parent][k] + mat_vec(Rw[parent], j["xyz"])[k] for k in range(3)]
         add(links[name], Rw[idx], ow[idx])
     add(links[root], I3, [0.0, 0.0, 0.0])
+    # the same primitives in the frame of the moving link that carries them (frame 0 = base, i = child of revolute joint i),
+    # for the start-pose randomisers that put the arm anywhere (reach_ao.py:782-817): fp64 forward kinematics on the device
+    Rl = {-1: I3}; ol = {-1: [0.0, 0.0, 0.0]}; fr = {-1: 0}
+    lrows = []; jrows = []
+
+    def add_local(L, R, o, frame):
+        for pr in L["prims"]:
+            Rp = rpy_to_R(*pr["rpy"])
+            ax = mat_vec(R, [Rp[0][2], Rp[1][2], Rp[2][2]])
+            c = [o[k] + mat_vec(R, pr["xyz"])[k] for k in range(3)]
+            lrows.append("  {%d, %d, {%r, %r, %r}, {%r, %r, %r}, %r, %r}" % (
+                frame, 0 if pr["type"] == "sphere" else 1, c[0], c[1], c[2], ax[0], ax[1], ax[2], pr["r"], pr["L"] / 2))
+
+    nrev = 0
+    for idx, (name, j, parent) in enumerate(order):
+        R = rpy_to_R(*j["rpy"])
+        if j["type"] == "revolute":
+            nrev += 1
+            assert fr[parent] == nrev - 1 and Rl[parent] == I3 and ol[parent] == [0.0, 0.0, 0.0], "serial chain of revolute joints expected"
+            jrows.append("  {%s}" % ", ".join(repr(float(x)) for x in list(j["xyz"]) + [R[r][c] for r in range(3) for c in range(3)]))
+            Rl[idx] = I3; ol[idx] = [0.0, 0.0, 0.0]; fr[idx] = nrev
+        else:
+            Rl[idx] = mat_mul(Rl[parent], R)
+            ol[idx] = [ol[parent][k] + mat_vec(Rl[parent], j["xyz"])[k] for k in range(3)]
+            fr[idx] = fr[parent]
+        add_local(links[name], Rl[idx], ol[idx], fr[idx])
+    add_local(links[root], I3, [0.0, 0.0, 0.0], 0)
+    assert len(lrows) == len(rows) and nrev == 7
+    ee_l = [ol[11][k] + mat_vec(Rl[11], links[names[11]]["com"])[k] for k in range(3)]
+    l0_l = [ol[0][k] + mat_vec(Rl[0], links[names[0]]["com"])[k] for k in range(3)]
+    fl_l = ol[7]  # panda_link8 (the flange: roboticstoolbox's end-effector link)
+    assert fr[11] == 7 and fr[0] == 1 and fr[7] == 7
     ee = [ow[11][k] + mat_vec(Rw[11], links[names[11]]["com"])[k] for k in range(3)]
     l0 = [ow[0][k] + mat_vec(Rw[0], links[names[0]]["com"])[k] for k in range(3)]
     o = [
@@ -372,6 +404,19 @@ def emit_neutral(links, root, order, path):
         "static __device__ __constant__ double kNeutralEE[3] = {%r, %r, %r};     // COM of link 11 (get_ee_position)" % tuple(ee),
         "static __device__ __constant__ double kNeutralLink0[3] = {%r, %r, %r};  // COM of pybullet link 0 = panda_link1 (get_link_position(0)); turns with joint 1" % tuple(l0),
         "static __device__ __constant__ double kNeutralQ[7] = {%s};" % ", ".join(repr(x) for x in neutral),
+        "// link-local form of the same table, for forward kinematics at an arbitrary pose: frame 0 = base, i = moving link i",
+        "struct LocalPrim { int frame, type; double c[3]; double a[3]; double r, h; };",
+        "static __device__ __constant__ LocalPrim kLocalPrims[%d] = {" % len(lrows),
+        ",\n".join(lrows),
+        "};",
+        "// joint origins: xyz in the parent frame | rotation child -> parent at q = 0 (row-major), joint axis = child z",
+        "static __device__ __constant__ double kJointOrigin[7][12] = {",
+        ",\n".join(jrows),
+        "};",
+        "static __device__ __constant__ double kLocalEE[3] = {%r, %r, %r};      // COM of link 11, link-7 frame" % tuple(ee_l),
+        "static __device__ __constant__ double kLocalLink0[3] = {%r, %r, %r};   // COM of panda_link1, link-1 frame" % tuple(l0_l),
+        "static __device__ __constant__ double kLocalFlange[3] = {%r, %r, %r};  // origin of panda_link8, link-7 frame" % tuple(fl_l),
+        "static __device__ __constant__ double kLocalEEOrigin[3] = {%r, %r, %r};  // origin of the link-11 frame (what PyBullet's IK drives), link-7 frame" % tuple(ol[11]),
         "}  // namespace pgm",
     ]
     with open(path, "w") as f:
