@@ -53,9 +53,11 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 # Algorithmic FLOPs per env-step of the step kernel AS IMPLEMENTED: 20 substeps of
 # RNEA + CRBA + 7x7 Cholesky inverse + 50-sweep PGS + collider frames + link-obstacle tests, + one observation pass.
-# Frozen from ncu per-opcode thread-instruction counts of a real rollout launch (2*FFMA + FADD + FMUL), see
-# profiles/r01_k_step_summary.md.  A scenario WITHOUT a frozen count reports frac = null and says so (flops_source).
-FLOPS_PER_ENV_STEP = {"reachao3": 0.191e6}
+# Frozen from ncu per-opcode predicated-on thread-instruction counts (2*FFMA + FADD + FMUL) of one k_step launch at the stationary
+# mix of episode phases the bench times (the 156th step; profiles/r02_k_step_traffic.json, r02_k_step_summary.md) -- the round-1
+# figure, 0.191 MFLOP, was counted a few steps after a cold start, when every arm still stands near the neutral pose.
+# A scenario WITHOUT a frozen count reports frac = null and says so (flops_source).
+FLOPS_PER_ENV_STEP = {"reachao3": 0.1604e6}
 BYTES_PER_ENV_STEP = 750.0       # ~308 B read + ~440 B written
 HER_BYTES_PER_SAMPLE = 1080.0    # ~544 B read + ~532 B written per sampled transition
 
@@ -131,6 +133,7 @@ def config_block(args, stage_switches=0):
             "envs_per_gpu": n, "scenario": args.scenario, "sharding": "envs partitioned contiguously, no data-path collective",
             "l2": "flushed between timed steps (256 MiB write); per-step CUDA-event timing on the launch stream",
             "actions": "U(-1,1), counter-based, pre-generated in HBM",
+            "preroll_steps": args.preroll,
             "curriculum": ({"stages": STAGES, "every": args.stage_every,
                             "note": "BASELINE configs[2]: stage parameter block swapped (and every env reset) inside the timed region"}
                            if args.curriculum else None)}
@@ -182,12 +185,14 @@ def timed_steps(torch, b, actions, W, K, flush, extra_per_step=None):
     return sum(a.elapsed_time(bb) for a, bb in ev)
 
 
-def extra_env_record(torch, local, env_id, scenario, n, K, W, flush, fp32_peak, hbm_peak, label, **kw):
+def extra_env_record(torch, local, env_id, scenario, n, K, W, flush, fp32_peak, hbm_peak, label, preroll=0, **kw):
     """One bounded extra record: another BASELINE config timed like the main one (device events, L2 flush, resident actions)."""
     from panda_gym_b200.vec_env import PandaVecEnv
     env = PandaVecEnv(env_id, n_envs=n, seed=4321, scenario=scenario, device=local, max_episode_steps=kw.pop("max_episode_steps", 100), **kw)
     b = env.batch
     b.reset()
+    for k in range(preroll):  # untimed: to the stationary mix of episode phases (Push: arms in contact with the object)
+        b.step(b.random_actions(555, k))
     actions = [b.random_actions(977, k) for k in range(K + W)]
     l0 = b.launch_count()
     with Clocks(local) as ck:
@@ -196,7 +201,7 @@ def extra_env_record(torch, local, env_id, scenario, n, K, W, flush, fp32_peak, 
     flops = FLOPS_PER_ENV_STEP.get(label)
     ach = (flops * n / (ms / K * 1e-3) / 1e12) if flops else None
     hbm = BYTES_PER_ENV_STEP * n / (ms / K * 1e-3) / 1e9
-    rec = {"workload": label, "env_id": env_id, "scenario": scenario, "envs": n, "steps": K, "warmup": W, "ms_per_step": ms / K,
+    rec = {"workload": label, "env_id": env_id, "scenario": scenario, "envs": n, "steps": K, "warmup": W, "preroll_steps": preroll, "ms_per_step": ms / K,
            "value": n * K / (ms * 1e-3), "unit": "env-steps/s", "gpu_launches": launches * K // (K + W),
            "roofline": {"bound": "fp32", "achieved": ach, "peak": fp32_peak, "unit": "TFLOP/s",
                         "frac": (ach / fp32_peak) if (ach and fp32_peak) else None,
@@ -278,6 +283,9 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=65536)
     ap.add_argument("--ref-steps-per-env", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--preroll", type=int, default=150,
+                    help="untimed vector steps before the warm-up: freshly reset arms all stand at the neutral pose and step ~25 %% faster "
+                         "than the stationary mix of episode phases the workload settles into after ~1.5 mean episode lengths")
     ap.add_argument("--no-extra", action="store_true", help="skip the bounded extra records (other BASELINE configs)")
     ap.add_argument("--curriculum", action="store_true",
                     help="BASELINE configs[2]: cycle the stage block reachao1 -> reachao2 -> reachao3 -> wangexp-3 every "
@@ -326,6 +334,8 @@ def main():
     actions = [b.random_actions(1234 + rank, k) for k in range(K + W)]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stats_buf = b.view("stats")
+    for k in range(args.preroll):  # to the stationary mix of episode phases (untimed, own action batches)
+        b.step(b.random_actions(99 + rank, k))
     for k in range(W):
         b.step(actions[k])
     if world > 1:  # warm the one collective of the path up too (communicator / first-call cost stays out of the timed region)
@@ -359,7 +369,8 @@ def main():
         dist.barrier()
     t_wall = time.perf_counter() - t_wall0
     launches = b.launch_count() - launches0
-    dev_ms = sum(a.elapsed_time(bb) for a, bb in ev)
+    step_ms = [a.elapsed_time(bb) for a, bb in ev]
+    dev_ms = sum(step_ms)
     t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -448,12 +459,15 @@ def main():
             "roofline": {"bound": "fp32", "achieved": achieved_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
                          "frac": (achieved_tflops / fp32_peak) if (achieved_tflops and fp32_peak) else None, "traffic": traffic,
                          "kernel": "k_step", "flops_per_env_step": flops,
-                         "flops_source": ("frozen ncu opcode count for %s" % args.scenario) if flops else
+                         "flops_source": ("frozen ncu opcode count for %s at steady state (profiles/r02_k_step_traffic.json)" % args.scenario) if flops else
                                          "none: no frozen FLOP count for this scenario, frac not claimed",
                          "peak_source": "FP32 FMA micro-benchmark measured in this run (pg_debug_fma_peak); MEASURED_PEAKS.json has no FP32 figure",
                          "hbm": {"achieved": hbm_achieved, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_achieved / hbm_peak,
                                  "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6650"}},
             "episode_stats": stats,
+            "step_ms": {"min": min(step_ms), "median": sorted(step_ms)[len(step_ms) // 2], "max": max(step_ms),
+                        "first_tenth_mean": sum(step_ms[:max(1, K // 10)]) / max(1, K // 10),
+                        "last_tenth_mean": sum(step_ms[-max(1, K // 10):]) / max(1, K // 10)},
             "wall_s_timed_region": t_wall,
             "numa": numa,
         }
@@ -465,9 +479,9 @@ def main():
             Kx, Wx = 10, 3
             try:
                 extra["reachao_rand"] = extra_env_record(torch, local, "PandaReachAO-v3", "reachao_rand", N, Kx, Wx, flush, fp32_peak, hbm_peak,
-                                                         "reachao_rand")
+                                                         "reachao_rand", preroll=min(args.preroll, 100))
                 extra["push"] = extra_env_record(torch, local, "PandaPush-v3", None, 16384, Kx, Wx, flush, fp32_peak, hbm_peak, "push",
-                                                 max_episode_steps=50)
+                                                 preroll=min(args.preroll, 75), max_episode_steps=50)
                 del flush
                 extra["her"] = extra_her_record(torch, local, hbm_peak)
             except Exception as ex:  # an extra record must never cost the main line

@@ -28,9 +28,12 @@ void launch_reset_all(const Params& P, const uint8_t* mask, const uint64_t* seed
 void launch_reset_list(const Params& P, uint64_t first_env, int sm_count, cudaStream_t s);
 void launch_observe(const Params& P, cudaStream_t s);
 void launch_neutral_table(const Params& P, const double* q7 /* nullptr = panda.py:67 */, cudaStream_t s);
-// pg_tu_reset_envbox.cu
-void launch_reset_envbox(const Params& P, bool list, const uint8_t* mask, const uint64_t* seeds, uint64_t first_env, int sm_count, cudaStream_t s);
-void launch_observe_envbox(const Params& P, cudaStream_t s);
+// pg_tu_reset_e{0,1}g{0,1}.cu: e = per-environment cuboid sizes, g = general start-pose randomizer; list = the auto-reset list
+#define PG_DECL_RESET(tag) void launch_reset_##tag(const Params& P, bool list, const uint8_t* mask, const uint64_t* seeds, uint64_t first_env, int sm_count, cudaStream_t s);
+PG_DECL_RESET(e0g0) PG_DECL_RESET(e0g1) PG_DECL_RESET(e1g0) PG_DECL_RESET(e1g1)
+#undef PG_DECL_RESET
+void launch_observe_e0(const Params& P, cudaStream_t s);
+void launch_observe_e1(const Params& P, cudaStream_t s);
 // pg_tu_misc.cu
 void launch_mirror_obstacles(const Params& P, cudaStream_t s);
 void launch_reward(const Params& P, const float* ag, const float* dg, float* out, int64_t n, int src, cudaStream_t s);

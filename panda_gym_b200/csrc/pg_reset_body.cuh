@@ -1,21 +1,16 @@
-// pg_reset_body.cuh -- bodies of the reset and observation-refresh kernels, included once per translation unit that instantiates
-// them: pg_tu_reset.cu (PG_ENVBOX 0, the default: obstacle shapes from the kernel parameters) and pg_tu_reset_envbox.cu
-// (PG_ENVBOX 1: per-environment cuboid sizes, scenario reachao_rand_shape).  The includer defines PG_RESET_KERNEL /
-// PG_OBSERVE_KERNEL and opens namespace pg.
+// pg_reset_body.cuh -- bodies of the reset and observation-refresh kernels, included (through pg_reset_variant.inc) by the four
+// translation units pg_tu_reset_e{0,1}g{0,1}.cu: e = PG_ENVBOX (0: obstacle shapes from the kernel parameters, the default; 1:
+// per-environment cuboid sizes, scenario reachao_rand_shape), g = start-pose randomizer that puts the arm anywhere.  One unit per
+// variant so that they compile in parallel (each is ~1 minute of nvcc).
 
+// One environment's reset.  WARP: the 32 lanes of a warp run it together on the same environment (same streams, same control
+// flow; the 36-primitive robot distance query is split across the lanes).  AUTO: auto-reset of an environment that finished in
+// the step just taken (done / flags / reward of that step stay); otherwise a reset the caller asked for.
 // GPOSE: the stage has a start-pose randomizer that puts the arm anywhere (rtb_ik / Bullet IK); false compiles all of that out
-template <bool WARP, bool GPOSE>
-__global__ void __launch_bounds__(kBlock) PG_RESET_KERNEL(const __grid_constant__ Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
-                                                  uint64_t first_env) {
+template <bool WARP, bool GPOSE, bool AUTO>
+__device__ __forceinline__ void reset_env(const Params& P, const int e, const uint64_t* __restrict__ seeds, const uint64_t first_env) {
   const int n = P.n;
-  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-  const int count = WARP ? *P.reset_count : n;
-  const int stride = WARP ? (gridDim.x * blockDim.x) >> 5 : gridDim.x * blockDim.x;
   const bool leader = WARP ? (threadIdx.x & 31) == 0 : true;
-  for (int item = WARP ? tid >> 5 : tid; item < count; item += stride) {
-  int e = item;
-  if (WARP) e = P.reset_list[item];
-  else if (mask && !mask[e]) continue;
   P.need_reset[e] = 0;
   uint32_t ep = P.episode[e];
   P.episode[e] = ep + 1;
@@ -223,10 +218,34 @@ __global__ void __launch_bounds__(kBlock) PG_RESET_KERNEL(const __grid_constant_
   observe(P, e, q, qd, q, cq, sq, ag, true);
   dg[0] = (float)goal[0]; dg[1] = (float)goal[1]; dg[2] = (float)goal[2];
   bool succ = is_success(P, e, ag, dg);
-  if (!WARP) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
+  if (!AUTO) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
+}
+
+// LIST = false: every environment (or those of `mask`), one thread each.  LIST = true: the environments k_step appended to the
+// compact list, grid-stride -- one WARP per environment while the list is short (the usual 1 % of the batch: latency matters,
+// the lanes split the distance queries), one THREAD per environment when it is long (all environments were reset together, so
+// ~80 % of them time out in the same step every max_episode_steps: 32 lanes repeating the same fp64 sampling code made those
+// steps 15 ms; a thread each finishes them in under a millisecond).
+constexpr int kWarpResetMax = 2048;
+template <bool LIST, bool GPOSE>
+__global__ void __launch_bounds__(kBlock) PG_RESET_KERNEL(const __grid_constant__ Params P, const uint8_t* __restrict__ mask, const uint64_t* __restrict__ seeds,
+                                                  uint64_t first_env) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int total = gridDim.x * blockDim.x;
+  if (LIST) {
+    const int count = *P.reset_count;
+    if (count <= kWarpResetMax) {
+      for (int item = tid >> 5; item < count; item += total >> 5) reset_env<true, GPOSE, true>(P, P.reset_list[item], nullptr, first_env);
+    } else {
+      for (int item = tid; item < count; item += total) reset_env<false, GPOSE, true>(P, P.reset_list[item], nullptr, first_env);
+    }
+  } else {
+    for (int e = tid; e < P.n; e += total)
+      if (!mask || mask[e]) reset_env<false, GPOSE, false>(P, e, seeds, first_env);
   }
 }
 
+#ifdef PG_OBSERVE_LAUNCH
 // refresh observation / goals at the current state (no stepping)
 __global__ void __launch_bounds__(kBlock) PG_OBSERVE_KERNEL(const Params P) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -240,4 +259,4 @@ __global__ void __launch_bounds__(kBlock) PG_OBSERVE_KERNEL(const Params P) {
     P.flags[e] = (uint8_t)((P.flags[e] & ~4) | (hit ? 4 : 0));
   }
 }
-
+#endif

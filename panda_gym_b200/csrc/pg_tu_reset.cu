@@ -1,25 +1,19 @@
-// pg_tu_reset.cu -- domain-randomised reset (RobotTaskEnv.reset, core.py:298-308) and the observation refresh
-#define PG_ENVBOX 0  // shapes of the obstacles from the kernel parameters; pg_tu_reset_envbox.cu is the per-environment-size twin
+// pg_tu_reset.cu -- dispatch to the reset / observation-refresh kernel variants (pg_tu_reset_e?g?.cu) and the reset-pose table
 #include "pg_reset.cuh"
 #include "pg_launch.h"
 
 namespace pg {
 
-#define PG_RESET_KERNEL k_reset
-#define PG_OBSERVE_KERNEL k_observe
-#include "pg_reset_body.cuh"
-
-static bool general_pose(const Params& P) { return P.task == 1 && P.st.pose_active && !P.st.random_base; }
 void launch_reset_all(const Params& P, const uint8_t* mask, const uint64_t* seeds, uint64_t first_env, cudaStream_t s) {
-  if (P.scene.env_box) { launch_reset_envbox(P, false, mask, seeds, first_env, 0, s); return; }
-  if (general_pose(P)) k_reset<false, true><<<(P.n + kBlock - 1) / kBlock, kBlock, 0, s>>>(P, mask, seeds, first_env);
-  else k_reset<false, false><<<(P.n + kBlock - 1) / kBlock, kBlock, 0, s>>>(P, mask, seeds, first_env);
+  const bool g = P.task == 1 && P.st.pose_active && !P.st.random_base;  // a start-pose randomizer that puts the arm anywhere
+  (P.scene.env_box ? (g ? launch_reset_e1g1 : launch_reset_e1g0) : (g ? launch_reset_e0g1 : launch_reset_e0g0))(P, false, mask, seeds, first_env, 0, s);
 }
-void launch_reset_list(const Params& P, uint64_t first_env, int sm_count, cudaStream_t s) {  // 32 warps per SM, grid-stride over the list
-  if (P.scene.env_box) { launch_reset_envbox(P, true, nullptr, nullptr, first_env, sm_count, s); return; }
-  if (general_pose(P)) k_reset<true, true><<<sm_count * 8, kBlock, 0, s>>>(P, nullptr, nullptr, first_env);
-  else k_reset<true, false><<<sm_count * 8, kBlock, 0, s>>>(P, nullptr, nullptr, first_env);
+void launch_reset_list(const Params& P, uint64_t first_env, int sm_count, cudaStream_t s) {
+  const bool g = P.task == 1 && P.st.pose_active && !P.st.random_base;
+  (P.scene.env_box ? (g ? launch_reset_e1g1 : launch_reset_e1g0) : (g ? launch_reset_e0g1 : launch_reset_e0g0))(P, true, nullptr, nullptr, first_env, sm_count, s);
 }
+void launch_observe(const Params& P, cudaStream_t s) { (P.scene.env_box ? launch_observe_e1 : launch_observe_e0)(P, s); }
+
 // The reset-pose table (Params::nprims / nextra).  q == nullptr: the generated constants of pg_neutral.h (panda.py:67).
 // Otherwise the same quantities at the joint values q[7] a benchmark-scene builder installs (reach_ao.py:322, 343, 356,
 // 424), by the fp32 forward kinematics of the step kernel -- 1e-7 m from the fp64 oracle, which only matters for a goal
@@ -60,9 +54,5 @@ void launch_neutral_table(const Params& P, const double* q7, cudaStream_t s) {
   nq.custom = q7 != nullptr;
   for (int d = 0; d < 7; d++) nq.q[d] = q7 ? q7[d] : 0.0;
   k_neutral_table<<<1, 64, 0, s>>>(P, nq);
-}
-void launch_observe(const Params& P, cudaStream_t s) {
-  if (P.scene.env_box) { launch_observe_envbox(P, s); return; }
-  k_observe<<<(P.n + kBlock - 1) / kBlock, kBlock, 0, s>>>(P);
 }
 }  // namespace pg
