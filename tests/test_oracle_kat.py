@@ -4,9 +4,17 @@
 import numpy as np
 
 
-def test_dt():
-    # test/pybullet_test.py:30-35: dt == timestep * n_substeps == 0.04
-    assert (1.0 / 500) * 20 == 0.04
+def test_dt(oracle):
+    # test/pybullet_test.py:30-35: dt == timestep * n_substeps == 0.04.  Measured on the oracle: a free box (no contact) under
+    # gravity gains v_z = -g * t over one env step (n_substeps substeps of the oracle's own timestep), so t = -v_z / g.
+    e = oracle.Env(task=2)
+    e.reset(0)
+    e.set_object_state([0.0, 0.0, 1.0])
+    for _ in range(e.cfg.n_substeps):
+        e.world_substep()
+    v = e.object_state()[2]
+    # per-substep damping m v (k + k |v|) with k = 0.04 shaves 4e-5 relative: well inside the reference's atol
+    assert abs(-v[2] / 9.81 - 0.04) < 1e-4 and e.cfg.n_substeps == 20
 
 
 def test_link_position_stock(oracle):
@@ -67,12 +75,17 @@ def test_inverse_kinematics_kat(oracle):
     assert np.allclose(out, [1.000, 1.223, -1.113, -0.021, -0.917, 0.666, -0.499, 0.0, 0.0], atol=1e-3)
 
 
-def test_free_fall():
-    # test/pybullet_test.py:56-64: semi-implicit Euler, g = 9.81, 20 substeps of 1/500 -> v_z = -0.392
-    v = 0.0
+def test_free_fall(oracle):
+    # test/pybullet_test.py:56-64: a box created at z = 1 has get_base_velocity == [0, 0, -0.392] after one step()
+    # (20 substeps of semi-implicit Euler at g = 9.81); the oracle's free body is the Push / PickAndPlace object
+    e = oracle.Env(task=2)
+    e.reset(0)
+    e.set_object_state([0.0, 0.0, 1.0])
     for _ in range(20):
-        v += -9.81 * (1.0 / 500)
-    assert np.allclose(v, -0.392, atol=1e-3)
+        e.world_substep()
+    p, q, v, w = e.object_state()
+    assert np.allclose(v, [0.0, 0.0, -0.392], atol=1e-3)
+    assert np.allclose(q, [0.0, 0.0, 0.0, 1.0], atol=1e-3) and np.allclose(w, 0.0, atol=1e-3)   # :67-100
 
 
 def test_neutral_pose_golden(oracle):
