@@ -187,6 +187,8 @@ enum pg_view_id {
   PG_V_D_LINK,            /* f32 [9][n] distances_closest_obstacles (reach_ao.py:897) */
   PG_V_OBJECT,            /* f32 [13][n] object position, quaternion xyzw, linear / angular velocity (get_base_* of pybullet.py:182-247) */
   PG_V_OBSTACLE_SIZE,     /* f64 [PG_MAX_OBSTACLES][3][n] per-environment cuboid half extents (pg_stage.random_size_cuboids; rows of spheres unused) */
+  PG_V_JOINT_ACC,         /* f32 [7][n] Panda.current_joint_acceleration (panda.py:167-172: previous velocity - velocity, as written) */
+  PG_V_JOINT_JERK,        /* f32 [7][n] Panda.current_joint_jerk */
   PG_V_COUNT
 };
 typedef struct { void* ptr; int dtype; /* 0 f32, 1 u8, 2 i32, 3 f64, 4 u64 */ int ndim; int64_t shape[3]; } pg_view;

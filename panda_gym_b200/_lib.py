@@ -57,7 +57,7 @@ class HerBatch(ctypes.Structure):
 
 VIEW_IDS = {name: i for i, name in enumerate([
     "observation", "achieved_goal", "desired_goal", "reward", "done", "flags", "terminal_observation",
-    "terminal_achieved", "ep_return", "ep_length", "q", "qd", "goal", "obstacle_pos", "stats", "step_count", "d_link", "object", "obstacle_size"])}
+    "terminal_achieved", "ep_return", "ep_length", "q", "qd", "goal", "obstacle_pos", "stats", "step_count", "d_link", "object", "obstacle_size", "joint_acc", "joint_jerk"])}
 
 # every symbol include/panda_b200.h declares: (name, restype, argtypes)
 P = c_void_p

@@ -591,6 +591,8 @@ int pg_get_view(pg_handle h, int id, pg_view* v) {
     case PG_V_D_LINK: set(P.d_link, 0, 2, 9, n, 0); break;
     case PG_V_OBJECT: set(P.obj, 0, 2, 13, n, 0); break;
     case PG_V_OBSTACLE_SIZE: set(P.env_size, 3, 3, pg::kMaxObst, 3, n); break;
+    case PG_V_JOINT_ACC: set(P.cur_acc, 0, 2, 7, n, 0); break;
+    case PG_V_JOINT_JERK: set(P.jerk, 0, 2, 7, n, 0); break;
     default: return fail(PG_ERR_ARG, "unknown view id");
   }
   return PG_OK;

@@ -48,6 +48,122 @@ class _Namespace:
     pass
 
 
+class _Robot:
+    """The part of ``Panda`` (envs/robots/panda.py) that callers above the step path read: evaluation/evaluate.py:246-259,
+    the success / collision callbacks.  Getters read the device state of environment 0 of the (one-environment) batch."""
+
+    ee_link = 11                                                  # panda.py:68
+    joint_forces = np.array([87.0, 87.0, 87.0, 87.0, 12.0, 120.0, 120.0, 170.0, 170.0])  # panda.py:63
+    joint_lim_min = np.array([-2.7437, -1.7837, -2.9007, -3.0421, -2.8065, 0.5445, -3.0159])  # panda.py:77
+    joint_lim_max = np.array([2.7437, 1.7837, 2.9007, -0.1518, 2.8065, 4.5169, 3.0159])       # panda.py:78
+
+    def __init__(self, env):
+        self._env = env
+        nq = env.batch.cfg.stage.neutral_q
+        self.neutral_joint_values = (np.array(list(nq) + [0.0, 0.0]) if env.batch.cfg.stage.custom_neutral else
+                                     np.array([0.0, -0.3, 0.0, -2.2, 0.0, 2.0, np.pi / 4, 0.0, 0.0]))  # panda.py:67
+
+    def _v(self, name):
+        return self._env.batch.view(name)
+
+    def get_ee_position(self):                                    # panda.py:300-302
+        return self._v("observation")[0, 0:3].cpu().numpy().astype(np.float64)
+
+    def get_ee_velocity(self):                                    # panda.py:304-306
+        return self._v("observation")[0, 3:6].cpu().numpy().astype(np.float64)
+
+    def get_joint_angles(self, joints=None):                      # core.py:146-155
+        q = self._v("q")[:, 0].cpu().numpy().astype(np.float64)
+        return q if joints is None else q[np.asarray(joints)]
+
+    def get_joint_angle(self, joint):
+        return float(self.get_joint_angles()[joint])
+
+    def get_joint_velocities(self, joints=None):
+        qd = self._v("qd")[:, 0].cpu().numpy().astype(np.float64)
+        return qd if joints is None else qd[np.asarray(joints)]
+
+    def get_joint_velocity(self, joint):
+        return float(self.get_joint_velocities()[joint])
+
+    def get_fingers_width(self):                                  # panda.py:309-312: the loaded URDF's finger joints are fixed
+        return 0.0
+
+    def get_manipulability(self):                                 # panda.py:314-317
+        return float(self._env.batch.manipulability()[0])
+
+    @property
+    def current_joint_acceleration(self):                         # panda.py:167-172
+        return self._v("joint_acc")[:, 0].cpu().numpy().astype(np.float64)
+
+    @property
+    def current_joint_jerk(self):
+        return self._v("joint_jerk")[:, 0].cpu().numpy().astype(np.float64)
+
+    def get_obs(self):                                            # panda.py:264-288
+        b = self._env.batch
+        w = 6 + (14 if b.cfg.obs_js else 0) + (1 if b.cfg.task == 3 else 0)
+        return self._v("observation")[0, :w].cpu().numpy()
+
+
+class _Task:
+    """The part of ``ReachAO`` / ``Reach`` / ``Push`` (envs/tasks/*.py) that callers above the step path read."""
+
+    def __init__(self, env):
+        self._env = env
+        self.scenario = getattr(env.batch.cfg, "_scenario", None)
+        st = env.batch.cfg.stage
+        # reach_ao.py:819-860: obstacles are named "<shape>_<index in creation order>"
+        self.obstacles = {("cuboid_%d" if st.obstacle_type[j] else "sphere_%d") % j: j for j in range(st.n_obstacles)}
+
+    def _v(self, name):
+        return self._env.batch.view(name)
+
+    @property
+    def goal(self):
+        return self._env.get_goal()
+
+    def get_goal(self):
+        return self._env.get_goal()
+
+    def get_achieved_goal(self):
+        return self._v("achieved_goal")[0].cpu().numpy().astype(np.float64)
+
+    def compute_reward(self, achieved_goal, desired_goal, info=None):
+        return self._env.compute_reward(achieved_goal, desired_goal, info)
+
+    def is_success(self, achieved_goal, desired_goal):          # reach.py:80-82, reach_ao.py:1243-1261 ("reach" condition)
+        a, b = np.asarray(achieved_goal), np.asarray(desired_goal)
+        assert a.shape == b.shape
+        d = np.round(np.linalg.norm(a - b, axis=-1), 6)          # utils.distance (panda_gym/utils.py:4-16), in the inputs' dtype
+        return np.array(d < np.float32(self._env.batch.cfg.stage.ee_error_threshold), dtype=bool)
+
+    @property
+    def is_collided(self):                                        # reach_ao.py:109, 186
+        return bool(int(self._v("flags")[0]) & 4)
+
+    def is_truncated(self):                                       # reach_ao.py:1263-1264
+        return self.is_collided if self._env.batch.cfg.truncate_on_collision else ()
+
+    @property
+    def distances_closest_obstacles(self):                        # reach_ao.py:897
+        return self._v("d_link")[:, 0].cpu().numpy().astype(np.float64)
+
+    @property
+    def manipulability(self):                                     # reach_ao.py:1311, refreshed by every compute_reward
+        return float(self._env.batch.manipulability()[0])
+
+    def get_norm_effort(self):                                    # reach_ao.py:1299-1302
+        return float(np.linalg.norm(self._env.robot.current_joint_acceleration))
+
+    def get_norm_jerk(self):                                      # reach_ao.py:1304-1305
+        return float(np.linalg.norm(self._env.robot.current_joint_jerk))
+
+    def get_obs(self):                                            # reach_ao.py:902-959, push.py:49-63
+        w = len(self._env.robot.get_obs())
+        return self._v("observation")[0, w:].cpu().numpy()
+
+
 class RobotTaskEnv:
     """Shared implementation; subclasses only build the pg_config."""
 
@@ -65,16 +181,14 @@ class RobotTaskEnv:
             desired_goal=spaces.Box(-10.0, 10.0, shape=obs["achieved_goal"].shape, dtype=np.float32),
             achieved_goal=spaces.Box(-10.0, 10.0, shape=obs["achieved_goal"].shape, dtype=np.float32)))
         self.action_space = spaces.Box(-1.0, 1.0, shape=(self.batch.act_dim,), dtype=np.float32)
-        # attribute surface callers poke at (evaluation/evaluate.py uses env.task.* / env.robot.*)
-        self.task = _Namespace()
-        self.task.get_goal = self.get_goal
-        self.task.compute_reward = self.compute_reward
-        self.robot = _Namespace()
-        self.robot.get_joint_angles = lambda: self.batch.view("q")[:, 0].cpu().numpy().astype(np.float64)
-        self.robot.get_joint_velocities = lambda: self.batch.view("qd")[:, 0].cpu().numpy().astype(np.float64)
-        self.robot.get_manipulability = lambda: float(self.batch.manipulability()[0])  # panda.py:314-317
+        # attribute surface callers poke at (evaluation/evaluate.py:131-268 uses env.task.* / env.robot.*)
+        self.robot = _Robot(self)
+        self.task = _Task(self)
         self.sim = _Namespace()
-        self.sim.dt = (1.0 / 500) * self.batch.cfg.n_substeps  # PyBullet.dt (pybullet.py:63-66)
+        self.sim.timestep = 1.0 / 500                           # pybullet.py:50
+        self.sim.n_substeps = self.batch.cfg.n_substeps
+        self.sim.dt = self.sim.timestep * self.sim.n_substeps   # PyBullet.dt (pybullet.py:63-66)
+        self.task.sim = self.sim
 
     def _obs(self):
         v = self.batch.view

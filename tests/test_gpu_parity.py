@@ -864,3 +864,36 @@ def test_flag_pass_culling_changes_nothing(sim, scenario, monkeypatch):
         res.append(b.view("flags").clone())
     assert torch.equal(res[0], res[1])
     assert int((res[0] & 4).ne(0).sum()) > 10
+
+
+# ------------------------------------------------------------------------------------------ attribute surface of the single env
+def test_env_task_and_robot_surface(sim, oracle):
+    """What evaluation/evaluate.py:perform_benchmark reads off ``env.task`` / ``env.robot`` after every step (:246-259) against
+    the oracle's per-step readings (pgo_env_step_metrics): effort, jerk norm, manipulability, EE speed, plus the goal,
+    collision state and per-link distances."""
+    from panda_gym_b200 import envs
+    envs.register_reach_ao(100)
+    env = envs.make("PandaReachAO-v3", scenario="reachao3")
+    e = oracle.Env(task=1, scenario="reachao3", max_episode_steps=100)
+    obs, info = env.reset(seed=31)
+    e.reset(31)
+    assert np.allclose(env.task.goal, e.goal(), atol=1e-12) and set(env.task.obstacles) == {"sphere_0", "sphere_1", "sphere_2"}
+    assert env.robot.ee_link == 11 and env.sim.dt == 0.04 and env.robot.get_fingers_width() == 0.0
+    rng = np.random.default_rng(4)
+    for k in range(6):
+        a = rng.uniform(-1, 1, 7).astype(np.float32)
+        o, r, term, trunc, inf = env.step(a)
+        oo, ro, f = e.step(a)
+        m = e.step_metrics()
+        assert abs(env.task.get_norm_effort() - m[0]) < 2e-4 and abs(env.task.get_norm_jerk() - m[1]) < 2e-4
+        assert abs(env.task.manipulability - m[2]) < 1e-4 and abs(env.robot.get_manipulability() - m[2]) < 1e-4
+        assert abs(np.linalg.norm(env.robot.get_ee_velocity()) - m[3]) < 1e-4
+        assert np.abs(env.robot.get_ee_position() - oo["achieved_goal"]).max() < 1e-5
+        assert np.abs(env.robot.get_joint_angles() - e.arm.q()[0][:7]).max() < 1e-4
+        assert env.task.is_collided == f["truncated"] and bool(env.task.is_truncated()) == f["truncated"]
+        assert np.abs(env.task.distances_closest_obstacles - np.asarray(e.check_collided()[1])).max() < 1e-4
+        assert np.abs(np.concatenate([env.robot.get_obs(), env.task.get_obs()]) - o["observation"]).max() == 0.0
+        assert bool(env.task.is_success(o["achieved_goal"], o["desired_goal"])) == inf["is_success"]
+        if trunc or term:
+            break
+    env.close()
