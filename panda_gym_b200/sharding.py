@@ -57,6 +57,45 @@ def allreduce_stats(stats, group=None):
     return out
 
 
+class AsyncStats:
+    """The episode-statistics all-reduce off the step stream: a snapshot of the 8-entry vector is taken on the current stream,
+    the collective runs on a side stream behind an event, and the simulation carries on -- a rank that reaches the collective
+    early no longer stalls its step kernels until the slowest rank arrives (at 8 ranks that wait, not the 64-byte transfer, was
+    the whole cost of the collective).  ``result()`` waits and returns the summed dict of the LAST ``start()``."""
+
+    def __init__(self, device, group=None):
+        self.side = torch.cuda.Stream(device=device)
+        self.group = group
+        self.pending = None
+
+    def start(self, stats):
+        s = stats.detach().clone().to(torch.float64)      # snapshot on the caller's stream
+        ev = torch.cuda.Event()
+        ev.record()
+        work = None
+        if dist.is_available() and dist.is_initialized():
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(ev)
+                work = dist.all_reduce(s, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        self.pending = (s, work, ev)
+
+    def result(self):
+        if self.pending is None:
+            return None
+        s, work, ev = self.pending
+        if work is not None:
+            work.wait()                                    # orders the current stream after the collective
+            self.side.synchronize()
+        else:
+            ev.synchronize()
+        v = s.cpu().tolist()
+        out = {k: float(v[i]) for i, k in enumerate(STAT_KEYS[:7])}
+        ep = max(out["episodes"], 1.0)
+        out.update(success_rate=out["successes"] / ep, collision_rate=out["collisions"] / ep,
+                   mean_return=out["sum_return"] / ep, mean_length=out["sum_length"] / ep)
+        return out
+
+
 def allgather_packed(packed, obs_dim, act_dim, group=None):
     """Replay all-gather of a batch that already IS one ``[B, W]`` block -- ``HerReplayBuffer.last_packed()``, rows in the
     stored record's field order -- with ONE ``all_gather_into_tensor`` and no packing pass; the nine fields come back as
