@@ -214,23 +214,32 @@ struct StepOut { float ag[3]; bool success; };
 // q_fk: joint angles behind PyBullet's cached link transforms (one substep old, see oracle/pgo_dyn.c);
 // cq/sq: cos/sin of the CURRENT q.
 // fresh: first observation of an episode (the reference pre-fills the "vectors+past" history at reset).
+// AT_REST (the observation a reset ends with: joints just teleported, velocities zero, cached pose = current pose): the frame
+// chain reuses (cq, sq) and the velocity chain is skipped -- same numbers, ~1 k fewer instructions on the auto-reset's
+// instruction-fetch-bound path.
+template <bool AT_REST = false>
 __device__ __forceinline__ void observe(const Params& P, int e, const float* q, const float* qd, const float* q_fk, const float* cq,
                                         const float* sq, float* ag_out, bool fresh) {
   const int n = P.n;
   V3 base = v3(P.base[0], P.base[1], P.base[2]);
-  // end-effector pose from the cached transforms
-  float cf[7], sf[7];
+  Frame Fc;
+  V3 ev = v3(0.f, 0.f, 0.f);
+  if (AT_REST) Fc = link7_frame(base, cq, sq);
+  else {
+    // end-effector pose from the cached transforms
+    float cf[7], sf[7];
 #pragma unroll
-  for (int d = 0; d < 7; d++) sincosf(q_fk[d], &sf[d], &cf[d]);
-  Frame Fc = link7_frame(base, cf, sf);
+    for (int d = 0; d < 7; d++) sincosf(q_fk[d], &sf[d], &cf[d]);
+    Fc = link7_frame(base, cf, sf);
+    // link-local COM velocity of link 11 from the current state, rotated by the cached basis
+    V3 w = v3(0, 0, 0), v = v3(0, 0, 0);
+    vel_step<1>(w, v, cq[0], sq[0], qd[0]); vel_step<2>(w, v, cq[1], sq[1], qd[1]); vel_step<3>(w, v, cq[2], sq[2], qd[2]);
+    vel_step<4>(w, v, cq[3], sq[3], qd[3]); vel_step<5>(w, v, cq[4], sq[4], qd[4]); vel_step<6>(w, v, cq[5], sq[5], qd[5]);
+    vel_step<7>(w, v, cq[6], sq[6], qd[6]);
+    V3 vl = v + cross(w, v3(pgm::kEEx, pgm::kEEy, pgm::kEEz));
+    ev = frame_dir(Fc, vl.x, vl.y, vl.z);
+  }
   V3 ee = frame_point(Fc, pgm::kEEx, pgm::kEEy, pgm::kEEz);
-  // link-local COM velocity of link 11 from the current state, rotated by the cached basis
-  V3 w = v3(0, 0, 0), v = v3(0, 0, 0);
-  vel_step<1>(w, v, cq[0], sq[0], qd[0]); vel_step<2>(w, v, cq[1], sq[1], qd[1]); vel_step<3>(w, v, cq[2], sq[2], qd[2]);
-  vel_step<4>(w, v, cq[3], sq[3], qd[3]); vel_step<5>(w, v, cq[4], sq[4], qd[4]); vel_step<6>(w, v, cq[5], sq[5], qd[5]);
-  vel_step<7>(w, v, cq[6], sq[6], qd[6]);
-  V3 vl = v + cross(w, v3(pgm::kEEx, pgm::kEEy, pgm::kEEz));
-  V3 ev = frame_dir(Fc, vl.x, vl.y, vl.z);
   float* o = P.obs + (size_t)e * P.obs_dim;
   o[0] = ee.x; o[1] = ee.y; o[2] = ee.z; o[3] = ev.x; o[4] = ev.y; o[5] = ev.z;
   int off = 6;
@@ -382,11 +391,10 @@ __device__ __forceinline__ void ik_dls(V3 base, const float* q0, V3 target, floa
       else if (m11 > m22) { float S = sqrtf(1.f + m11 - m00 - m22) * 2.f; qw = (ez.x - ex.z) / S; qx = (ey.x + ex.y) / S; qy = 0.25f * S; qz = (ez.y + ey.z) / S; }
       else { float S = sqrtf(1.f + m22 - m00 - m11) * 2.f; qw = (ex.y - ey.x) / S; qx = (ez.x + ex.z) / S; qy = (ez.y + ey.z) / S; qz = 0.25f * S; }
     }
-    // (1,0,0,0) * conj(q):  a = (1,0,0,0) xyzw, b = (-qx,-qy,-qz,qw)
-    float dx = qw, dy = -qz, dz = qy, dw = qx;  // aw*b + ... with ax = 1: x = bw, y = -bz... see oracle formula
-    // oracle: dq = {aw*bx + ax*bw + ay*bz - az*by, aw*by + ay*bw + az*bx - ax*bz, aw*bz + az*bw + ax*by - ay*bx, aw*bw - ax*bx - ay*by - az*bz}
-    // with a = (1,0,0,0): dq = {bw, -bz, by, -bx} = {qw, qz, -qy, qx}
-    dx = qw; dy = qz; dz = -qy; dw = qx;
+    // deltaQ = a * conj(q) with a = (1,0,0,0) xyzw, b = conj(q) = (-qx,-qy,-qz,qw):
+    //   {aw*bx + ax*bw + ay*bz - az*by, aw*by + ay*bw + az*bx - ax*bz, aw*bz + az*bw + ax*by - ay*bx, aw*bw - ax*bx - ay*by - az*bz}
+    //   = {bw, -bz, by, -bx} = {qw, qz, -qy, qx}   (oracle/pgo_dyn.c pgo_arm_ik)
+    const float dx = qw, dy = qz, dz = -qy, dw = qx;
     // angle * axis with angle = 2 acos(w) (btQuaternion::getAngle/getAxis); evaluated as 2 atan2(|xyz|, w), which
     // is the same number in exact arithmetic but well conditioned in fp32 for the small angles met here
     float sn = sqrtf(dx * dx + dy * dy + dz * dz);
