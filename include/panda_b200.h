@@ -98,6 +98,9 @@ typedef struct {
   pg_stage stage;
   int has_fixed_target;      /* train_config.py:29 fixed_target: ReachAO.reset skips its first set_coll_free_goal (reach_ao.py:981) */
   double fixed_target[3];    /*   and the goal keeps this value unless the scenario re-samples it (:986-988, obstacle positions fixed) */
+  int pose_retry_limit;      /* tries of set_coll_free_robot per obstacle (reach_ao.py:1047: 10 000); 0 = as the reference.  A knob for
+                                large batches: one environment in a few thousand whose every start pose fails (for a reason the
+                                fixed-core test of pg_reset_body.cuh does not see) otherwise holds the whole step for 10 000 IK solves */
 } pg_config;
 
 /* fill cfg with the reference defaults: task PG_TASK_REACH -> PandaReachJoints-v3 (sparse);

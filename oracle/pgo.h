@@ -145,6 +145,8 @@ typedef struct {
    * rtb_ik towards U(lo, hi); industrial :395-403: PyBullet's own IK towards U(lo, hi); all with randomize_robot_pose forced on);
    * 0 keeps the task default (set_robot_random_pose, :62-63) */
   int scene_pose_randomizer, scene_force_randomize; double scene_pose_lo[3], scene_pose_hi[3];
+  int pose_retry_limit;  /* tries of set_coll_free_robot per obstacle; 0 = the reference's 10 000 (reach_ao.py:1047) */
+  int no_shortcuts;      /* 1: run the futile rejection loops as written instead of short-circuiting them (pgo_env.c set_coll_free_robot) */
 } pgo_env_config;
 /* ReachAO.robot_pose_randomizer kinds (reach_ao.py:62-63, 521-604, 669, 711, 782-817, 1238-1241) */
 enum { PGO_POSE_TORUS = 0, PGO_POSE_RANDOM_BASE = 1, PGO_POSE_TORUS_FRONT = 2, PGO_POSE_IK_GOAL_SPACE = 3, PGO_POSE_IK_SPHERE = 4,

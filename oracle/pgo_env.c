@@ -226,12 +226,6 @@ static double robot_body_distance(pgo_env* e, const pgo_obstacle* o) {
   for (int p = 0; p < NPRIM_ALL; p++) { double d = pgo_prim_obstacle_distance(e->arm, p, o, 0, 0); if (d < best) best = d; }
   return best;
 }
-/* the part of the robot no start pose moves: the base link and panda_link1, whose colliders lie on joint 1's axis */
-static double robot_column_distance(pgo_env* e, const pgo_obstacle* o) {
-  double best = 1e300;
-  for (int p = 0; p < NPRIM_ALL; p++) if (pgo__prim_link(e->arm, p) <= 0) { double d = pgo_prim_obstacle_distance(e->arm, p, o, 0, 0); if (d < best) best = d; }
-  return best;
-}
 /* sphere body vs sphere / box body; box-box: Bullet's SAT box detector only reports overlapping boxes */
 static int body_body_collision(const pgo_obstacle* a, const pgo_obstacle* b, double margin) {
   if (a->type == 0 && b->type == 0) {
@@ -258,6 +252,18 @@ static int body_body_collision(const pgo_obstacle* a, const pgo_obstacle* b, dou
     d = -best;
   } else d = sqrt(d2);
   return margin >= d - m - s->size[0];
+}
+
+/* The part of the robot no start pose moves: the base link, panda_link1 (its colliders lie on joint 1's axis) and the ball of
+ * radius 0.06 about the shoulder (the origin of panda_link2, on both joint axes): panda_link2's cylinder (r 0.06, half length 0.06,
+ * centred there) contains it whatever joints 1 and 2 do.  An obstacle within `margin` of this set is within `margin` of the robot
+ * in EVERY pose. */
+static int robot_core_within(pgo_env* e, const pgo_obstacle* o, double margin) {
+  for (int p = 0; p < NPRIM_ALL; p++)
+    if (pgo__prim_link(e->arm, p) <= 0 && margin >= pgo_prim_obstacle_distance(e->arm, p, o, 0, 0)) return 1;
+  pgo_obstacle sh; sh.type = 0; sh.size[0] = 0.06; sh.size[1] = sh.size[2] = 0;
+  sh.pos[0] = e->cfg.base_pos[0]; sh.pos[1] = e->cfg.base_pos[1]; sh.pos[2] = e->cfg.base_pos[2] + 0.333;
+  return body_body_collision(&sh, o, margin);
 }
 
 /* ------------------------------------------------------------------ samplers (reach_ao.py:1183-1211, 610-644) */
@@ -501,27 +507,38 @@ static int robot_reset(pgo_env* e) {
   return status;
 }
 /* set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the robot pose while the robot is within 0.05.
- * FUTILE CASE: an obstacle within 0.05 of the base column (base link + panda_link1: no joint moves them) fails all 10 000 tries
- * whatever they draw, after which the reference prints "Couldn't find collision free robot pose!" and sets the neutral pose.  With
- * an rtb_ik randomizer that is 10 000 inverse-kinematics solves to no effect, so it is short-circuited here and on the device:
- * neutral pose, flag 4, and the numpy stream jumps over the draws the tries would have made when their number is fixed
- * (ik_goal_space / ik_box: one target sample per try).  Deviations, stated: the C rand() stream is NOT advanced by the restarts
- * those solves would have made, and for the variable-draw randomizers (set_robot_random_pose, ..._ik_sphere) the numpy stream is
- * not advanced either -- it only feeds set_random_num_obs afterwards (reachao_rand_start). */
+ * FUTILE CASE: an obstacle within 0.05 of the robot's fixed core (robot_core_within: base link, panda_link1, the shoulder ball) fails
+ * all 10 000 tries whatever they draw, after which the reference prints "Couldn't find collision free robot pose!" and sets the
+ * neutral pose.  Short-circuited here and on the device (cfg.no_shortcuts = 1 runs the loop as written, for the tests):
+ *   set_random_robot_base: one uniform draw per try and the loop ends on its last draw -- the numpy stream jumps 9 999 draws
+ *     (BitGenerator.advance) and draws the 10 000th: IDENTICAL to running the loop;
+ *   rtb_ik randomizers: 10 000 inverse-kinematics solves to no effect -- neutral pose, flag 4, the numpy stream jumps over the
+ *     draws the tries would have made when their number is fixed (ik_goal_space / ik_box: one target sample per try).  Deviations,
+ *     stated: the C rand() stream is NOT advanced by the restarts those solves would have made, and for the variable-draw
+ *     randomizers (set_robot_random_pose, ..._ik_sphere) the numpy stream is not advanced either -- it only feeds
+ *     set_random_num_obs afterwards (reachao_rand_start).
+ * cfg.pose_retry_limit > 0 replaces the 10 000 (a knob for large batches, where the one environment in a thousand whose every
+ * pose fails for a reason the core test does not see holds a whole step for 10 000 solves; 0 = as the reference). */
 static int draws_per_goal_sample(const pgo_env* e) { return e->goal_sampler == 0 ? 3 : 3 + (e->goal_front ? 1 : 0) + (e->goal_34 ? 1 : 0); }
 static int set_coll_free_robot(pgo_env* e) {
   int status = 0;
+  const int limit = e->cfg.pose_retry_limit > 0 ? e->cfg.pose_retry_limit : 10000; /* reach_ao.py:1047: i > 9999 */
   for (int j = 0; j < e->nobs; j++) {
     int i = 0;
-    if (e->pose_kind != PGO_POSE_RANDOM_BASE && 0.05 >= robot_body_distance(e, &e->obs[j]) && 0.05 >= robot_column_distance(e, &e->obs[j])) {
-      if (e->pose_kind == PGO_POSE_IK_GOAL_SPACE) pgo_pcg64_advance(&e->rng, 10000ull * (uint64_t)draws_per_goal_sample(e));
-      if (e->pose_kind == PGO_POSE_IK_BOX || e->pose_kind == PGO_POSE_BULLET_IK_BOX) pgo_pcg64_advance(&e->rng, 30000ull);
-      for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, e->neutral[d]);
+    if (!e->cfg.no_shortcuts && 0.05 >= robot_body_distance(e, &e->obs[j]) && robot_core_within(e, &e->obs[j], 0.05)) {
+      if (e->pose_kind == PGO_POSE_RANDOM_BASE) {      /* one draw per try: the pose the loop ends with is its last draw -- EXACT */
+        pgo_pcg64_advance(&e->rng, (uint64_t)limit - 1);
+        random_robot_base(e);
+      } else {
+        if (e->pose_kind == PGO_POSE_IK_GOAL_SPACE) pgo_pcg64_advance(&e->rng, (uint64_t)limit * (uint64_t)draws_per_goal_sample(e));
+        if (e->pose_kind == PGO_POSE_IK_BOX || e->pose_kind == PGO_POSE_BULLET_IK_BOX) pgo_pcg64_advance(&e->rng, 3ull * (uint64_t)limit);
+        for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, e->neutral[d]);
+      }
       status |= 4;
       continue;
     }
     while (0.05 >= robot_body_distance(e, &e->obs[j])) {
-      if (i > 9999) { /* set_joint_neutral */
+      if (i > limit - 1) { /* set_joint_neutral */
         for (int d = 0; d < N_ARM; d++) pgo_arm_reset_joint(e->arm, d, d == 0 && e->pose_kind == PGO_POSE_RANDOM_BASE ? e->neutral0 : e->neutral[d]);
         status |= 4; break;
       }

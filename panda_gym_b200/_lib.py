@@ -37,7 +37,7 @@ class Config(ctypes.Structure):
         ("truncate_on_collision", c_int), ("terminate_on_success", c_int),
         ("collision_reward", c_double), ("safety_distance", c_double), ("base_position", c_double * 3),
         ("auto_reset", c_int), ("randomize_robot_pose", c_int), ("stage", Stage),
-        ("has_fixed_target", c_int), ("fixed_target", c_double * 3),
+        ("has_fixed_target", c_int), ("fixed_target", c_double * 3), ("pose_retry_limit", c_int),
     ]
 
 

@@ -275,6 +275,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
   P.act_dim = (cfg->control == PG_CTRL_EE ? 3 : 7) + (cfg->task == PG_TASK_PICK_AND_PLACE ? 1 : 0);
   P.n_substeps = cfg->n_substeps; P.truncate_on_collision = cfg->truncate_on_collision; P.terminate_on_success = cfg->terminate_on_success;
   P.auto_reset = cfg->auto_reset; P.collision_reward = (float)cfg->collision_reward; P.safety_distance = cfg->safety_distance;
+  P.pose_retry_limit = cfg->pose_retry_limit;
   P.has_fixed_target = cfg->has_fixed_target; for (int k = 0; k < 3; k++) P.fixed_target[k] = cfg->fixed_target[k];
   for (int k = 0; k < 3; k++) { P.base[k] = (float)cfg->base_position[k]; P.based[k] = cfg->base_position[k]; }
   if (cfg->task != PG_TASK_REACH_AO) {  // table 1.1 x 0.7 x 0.4 at x = -0.3 (reach.py:33, push.py:31); Reach never queries it

@@ -52,6 +52,7 @@ struct Params {
   float collision_reward;
   double safety_distance;
   int has_fixed_target; double fixed_target[3];  // train_config.py:29
+  int pose_retry_limit;          // tries of set_coll_free_robot per obstacle, 0 = the reference's 10 000
   float base[3];
   double based[3];
   double table_pos[3], table_half[3];

@@ -62,10 +62,16 @@ __device__ __noinline__ double robot_body_distance(const Params& P, const Body& 
   double best = 1e300;
   const int k0 = WARP ? (threadIdx.x & 31) : 0, kstep = WARP ? 32 : 1;
   const double ox = b.px - P.based[0], oy = b.py - P.based[1];
-  D3 o = v3t<double>(c0 * ox + s0 * oy, -s0 * ox + c0 * oy, b.pz - P.based[2]);
+  const D3 o_turned = v3t<double>(c0 * ox + s0 * oy, -s0 * ox + c0 * oy, b.pz - P.based[2]);
+  const D3 o_fixed = v3t<double>(ox, oy, b.pz - P.based[2]);
   double m = b.type == 1 ? (b.margin >= 0.0 ? b.margin : box_margin_d(b.sx, b.sy, b.sz)) : 0.0;
   D3 core = v3t<double>(b.sx - m, b.sy - m, b.sz - m);
   for (int k = k0; k < pgm::kNumNeutralPrim; k += kstep) {
+    // table order: primitives of the moving links (panda_link1's first: 0..2), then the base link's (kNumPrim ..): the base does
+    // not turn with joint 1, so it meets the body where it is
+    const bool base_prim = k >= pgm::kNumPrim;
+    if (!(GPOSE && pose) && frame_max < 7 && !(k < 3 || base_prim)) continue;
+    const D3 o = base_prim ? o_fixed : o_turned;
     pgm::NeutralPrim np;
     if (GPOSE && pose) {
       const pgm::LocalPrim& lp = pgm::kLocalPrims[k];
@@ -116,9 +122,21 @@ __device__ inline bool body_body_collision(const Body& a, const Body& b, double 
     return fabs(a.px - b.px) <= a.sx + b.sx && fabs(a.py - b.py) <= a.sy + b.sy && fabs(a.pz - b.pz) <= a.sz + b.sz;
   const Body& s = a.type == 0 ? a : b;
   const Body& x = a.type == 0 ? b : a;
-  double m = box_margin_d(x.sx, x.sy, x.sz);
+  double m = x.margin >= 0.0 ? x.margin : box_margin_d(x.sx, x.sy, x.sz);
   double d = sphere_box<double>(v3t<double>(s.px, s.py, s.pz), s.sx, v3t<double>(x.px, x.py, x.pz), v3t<double>(x.sx - m, x.sy - m, x.sz - m), m).d;
   return margin >= d;
+}
+
+// The part of the robot no start pose moves: the base link, panda_link1 (colliders on joint 1's axis) and the ball of radius 0.06
+// about the shoulder (origin of panda_link2: panda_link2's cylinder, r 0.06 / half length 0.06 centred there, contains it whatever
+// joints 1 and 2 do).  An obstacle within `margin` of this set is within `margin` of the robot in EVERY pose (oracle twin:
+// pgo_env.c robot_core_within).
+template <bool WARP, bool GPOSE>
+__device__ inline bool robot_core_within(const Params& P, const Body& b, double margin, const PoseD* pose) {
+  if (margin >= robot_body_distance<WARP, GPOSE>(P, b, margin, 1.0, 0.0, pose, 1)) return true;
+  Body sh; sh.type = 0; sh.sx = 0.06; sh.sy = sh.sz = 0.0;
+  sh.px = P.based[0]; sh.py = P.based[1]; sh.pz = P.based[2] + pgm::kJointOrigin[0][2];
+  return body_body_collision(sh, b, margin);
 }
 
 __device__ inline void sample_hollow(Pcg& g, double rmin, double rmax, int upper, int front, int q34, double* out) {

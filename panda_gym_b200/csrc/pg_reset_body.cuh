@@ -141,6 +141,7 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
     if (rbase || gpose) {  // set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the pose while the robot is within 0.05
       // self.obstacles = the sampled obstacles, then (benchmark scenes) the scene's bodies (reach_ao.py:300-306)
       const int nbody = st.nobs + (gpose ? P.scene.nstatic : 0);
+      const int limit = P.pose_retry_limit > 0 ? P.pose_retry_limit : 10000;  // reach_ao.py:1047: i > 9999
       for (int j = 0; j < nbody; j++) {
         Body ob;
         if (j < st.nobs) ob = obstacle_body(P, j, e);
@@ -150,20 +151,27 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
           ob.type = 1; ob.px = o.x; ob.py = o.y; ob.pz = o.z; ob.sx = so.sx; ob.sy = so.sy; ob.sz = so.sz; ob.margin = so.margin;
         }
         int i = 0;
-        // futile case (see oracle/pgo_env.c set_coll_free_robot): the obstacle stands within 0.05 of the base column, which no
-        // pose moves -- all 10 000 tries of the reference fail, then it sets the neutral pose.  Short-circuited: the numpy stream
-        // jumps over the tries' draws where their number is fixed; the C rand() stream is left alone (stated deviation).
-        if (gpose && 0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, 1.0, 0.0, pp) && 0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, 1.0, 0.0, pp, 1)) {
-          if (st.pose_kind == PG_POSE_IK_GOAL_SPACE)
-            pcg_advance(g, 10000ull * (uint64_t)(st.goal_sampler == 0 ? 3 : 3 + (st.goal_front ? 1 : 0) + (st.goal_34 ? 1 : 0)));
-          if (st.pose_kind == PG_POSE_IK_BOX || st.pose_kind == PG_POSE_BULLET_IK_BOX) pcg_advance(g, 30000ull);
-          for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d];
-          pose_fk(qpose, pose);
+        // futile case (see oracle/pgo_env.c set_coll_free_robot): the obstacle stands within 0.05 of the robot's fixed core, which
+        // no pose moves -- all `limit` tries of the reference fail, then it sets the neutral pose.  Short-circuited.  Random base:
+        // one draw per try and the loop ends on its last draw, so the numpy stream jumps limit - 1 draws and draws the last one
+        // (identical to running the loop).  rtb_ik randomizers: the numpy stream jumps over the tries' draws where their number is
+        // fixed; the C rand() stream is left alone (stated deviation).
+        if (0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, c0, s0, pp) && robot_core_within<WARP, GPOSE>(P, ob, 0.05, pp)) {
+          if (gpose) {
+            if (st.pose_kind == PG_POSE_IK_GOAL_SPACE)
+              pcg_advance(g, (uint64_t)limit * (uint64_t)(st.goal_sampler == 0 ? 3 : 3 + (st.goal_front ? 1 : 0) + (st.goal_34 ? 1 : 0)));
+            if (st.pose_kind == PG_POSE_IK_BOX || st.pose_kind == PG_POSE_BULLET_IK_BOX) pcg_advance(g, 3ull * (uint64_t)limit);
+            for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d];
+            pose_fk(qpose, pose);
+          } else {
+            pcg_advance(g, (uint64_t)limit - 1);
+            q0 = pcg_uniform(g, -2.7437, 2.7437); c0 = cos(q0 - NX[6]); s0 = sin(q0 - NX[6]);
+          }
           status |= 4;
           continue;
         }
         while (0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, c0, s0, pp)) {
-          if (i > 9999) {  // set_joint_neutral (with set_random_robot_base, neutral_joint_values[0] already holds the last draw)
+          if (i > limit - 1) {  // set_joint_neutral (with set_random_robot_base, neutral_joint_values[0] already holds the last draw)
             status |= 4;
             if (gpose) { for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d]; pose_fk(qpose, pose); }
             break;

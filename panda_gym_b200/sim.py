@@ -27,8 +27,10 @@ class _CudaArray:
 
 
 def make_config(task, n_envs, scenario=None, config=None, control_type=None, reward_type=None,
-                max_episode_steps=50, ee_error_threshold=0.05, speed_threshold=0.1, auto_reset=True, base_position=None):
-    """Build a pg_config from reference-style arguments (TrainConfig + gym kwargs)."""
+                max_episode_steps=50, ee_error_threshold=0.05, speed_threshold=0.1, auto_reset=True, base_position=None,
+                pose_retry_limit=0):
+    """Build a pg_config from reference-style arguments (TrainConfig + gym kwargs).  pose_retry_limit: tries of
+    set_coll_free_robot per obstacle, 0 = the reference's 10 000 (pg_config.pose_retry_limit)."""
     lib = _lib.load()
     cfg = _lib.Config()
     _lib.check(lib.pg_default_config(ctypes.byref(cfg), task, scenario.encode() if scenario else None))
@@ -67,6 +69,7 @@ def make_config(task, n_envs, scenario=None, config=None, control_type=None, rew
     cfg.stage.max_episode_steps = int(max_episode_steps)
     cfg.stage.ee_error_threshold = float(ee_error_threshold)
     cfg.stage.speed_threshold = float(speed_threshold)
+    cfg.pose_retry_limit = int(pose_retry_limit)
     return cfg
 
 

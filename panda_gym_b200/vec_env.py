@@ -114,7 +114,7 @@ class LazyInfos:
 class PandaVecEnv:
     def __init__(self, env_id="PandaReachAO-v3", n_envs=8, seed=None, scenario="reachao1", config=None, device=0,
                  max_episode_steps=50, ee_error_threshold=0.05, speed_threshold=0.1, first_env_index=0, copy_outputs=False,
-                 n_host_buffers=3, numa_bind=True, **env_kwargs):
+                 n_host_buffers=3, numa_bind=True, pose_retry_limit=0, **env_kwargs):
         if env_id not in ENV_IDS:
             raise _lib.PandaB200Error("unknown / out-of-scope env id %r (supported: %s)" % (env_id, sorted(ENV_IDS)))
         spec = dict(ENV_IDS[env_id])
@@ -125,7 +125,7 @@ class PandaVecEnv:
         cfg = sim.make_config(spec["task"], n_envs, scenario=self.scenario if spec["task"] == 1 else None, config=self.config,
                               control_type=spec.get("control_type"), reward_type=spec.get("reward_type"),
                               max_episode_steps=max_episode_steps, ee_error_threshold=ee_error_threshold,
-                              speed_threshold=speed_threshold, auto_reset=True)
+                              speed_threshold=speed_threshold, auto_reset=True, pose_retry_limit=pose_retry_limit)
         # One process drives one GPU: run it (and allocate its page-locked result buffers) on the CPUs / memory node next to
         # that GPU.  On a two-socket host the per-step result copy is otherwise 2-3x slower whenever the launcher happened
         # to start the process on the far socket (profiles/r02_e2e.md).  numa_bind=False leaves the affinity alone.

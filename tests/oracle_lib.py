@@ -26,6 +26,7 @@ class EnvConfig(ctypes.Structure):
         ("scene_goal_lo", c_double * 3), ("scene_goal_hi", c_double * 3), ("custom_neutral", c_int), ("neutral_q", c_double * 7),
         ("has_fixed_target", c_int), ("fixed_target", c_double * 3),
         ("scene_pose_randomizer", c_int), ("scene_force_randomize", c_int), ("scene_pose_lo", c_double * 3), ("scene_pose_hi", c_double * 3),
+        ("pose_retry_limit", c_int), ("no_shortcuts", c_int),
     ]
 
 

@@ -155,3 +155,42 @@ def test_pose_randomizer_under_auto_reset(sim):
     seen = np.concatenate(seen)
     assert len(seen) >= 2 * n and seen.std(axis=0).min() > 0.02
     env.close()
+
+
+def test_futile_robot_loop_short_circuit_is_exact_for_random_base(sim, oracle):
+    """set_coll_free_robot with set_random_robot_base (wangexp-N): an obstacle within 0.05 of the robot's fixed core fails all
+    10 000 re-draws.  The device (and the oracle by default) jump the numpy stream instead of looping; the oracle with
+    no_shortcuts=1 runs the loop as the reference writes it -- joint 1, goal, obstacles and the draws that follow must be the same."""
+    from panda_gym_b200.config import TrainConfig
+    n = 600
+    tc = TrainConfig(); tc.randomize_robot_pose = True
+    b = sim.PandaBatch(sim.make_config(1, n, scenario="wangexp-3", config=tc, max_episode_steps=100, auto_reset=False))
+    seeds = 7000 + np.arange(n)
+    b.reset(seeds=torch.tensor(seeds, dtype=torch.int64, device=b.device)); torch.cuda.synchronize()
+    q = b.view("q").cpu().numpy(); goal = b.view("goal").cpu().numpy(); opos = b.view("obstacle_pos").cpu().numpy()
+    futile = 0
+    for i in range(n):
+        # a fresh oracle environment per seed, like device environment i: the obstacles not yet re-sampled stand at their creation pose
+        e = oracle.Env(task=1, scenario="wangexp-3", randomize_robot_pose=1, max_episode_steps=100, no_shortcuts=1)
+        o, info = e.reset(int(seeds[i]))
+        futile += info["status"] != 0
+        assert np.float32(e.arm.q()[0][0]) == q[0, i], (i, info)
+        assert np.abs(e.goal() - goal[:, i]).max() < 1e-13
+        for j, (_, p, _) in enumerate(e.obstacles()):
+            assert np.abs(p - opos[j, :, i]).max() < 1e-12
+    assert futile >= 3 and int(b.view("stats").cpu().numpy()[6]) == futile
+    b.close()
+
+
+def test_pose_retry_limit(sim, oracle):
+    """pg_config.pose_retry_limit caps set_coll_free_robot's tries on both sides the same way."""
+    from panda_gym_b200.config import TrainConfig
+    n = 64
+    tc = TrainConfig(); tc.randomize_robot_pose = True
+    b = sim.PandaBatch(sim.make_config(1, n, scenario="reachao2", config=tc, max_episode_steps=100, auto_reset=False, pose_retry_limit=5))
+    envs = [oracle.Env(task=1, scenario="reachao2", randomize_robot_pose=1, max_episode_steps=100, pose_retry_limit=5) for _ in range(n)]
+    for episode in range(2):
+        seeds = 300 + 100 * episode + np.arange(n)
+        b.reset(seeds=torch.tensor(seeds, dtype=torch.int64, device=b.device)); torch.cuda.synchronize()
+        _compare_reset(b, envs, seeds, ("limit", episode))
+    b.close()

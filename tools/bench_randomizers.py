@@ -5,16 +5,19 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from panda_gym_b200 import sim
 from panda_gym_b200.config import TrainConfig
-N, P, K = 65536, 150, 100
+N, P, K = 65536, 120, 60
 out = {"envs": N, "preroll": P, "steps": K, "cases": {}}
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-for name, scenario, randomize in [("reachao3", "reachao3", False), ("reachao3 + randomize_robot_pose (ik_goal_space)", "reachao3", True),
-                                  ("reachao1 + randomize_robot_pose (torus, z window)", "reachao1", True),
-                                  ("wang-3 + randomize_robot_pose (torus)", "wang-3", True), ("wangexp-3 + randomize_robot_pose (random base)", "wangexp-3", True),
-                                  ("reachao_rand", "reachao_rand", False), ("reachao_rand_shape", "reachao_rand_shape", False),
-                                  ("reachao_rand_start (ik_sphere)", "reachao_rand_start", False)]:
+for name, scenario, randomize, limit in [
+        ("reachao3", "reachao3", False, 0), ("reachao3 + randomize_robot_pose (ik_goal_space)", "reachao3", True, 0),
+        ("reachao3 + randomize_robot_pose, pose_retry_limit 100", "reachao3", True, 100),
+        ("reachao1 + randomize_robot_pose (torus, z window)", "reachao1", True, 0),
+        ("wang-3 + randomize_robot_pose (torus)", "wang-3", True, 0), ("wang-3 + randomize_robot_pose, pose_retry_limit 100", "wang-3", True, 100),
+        ("wangexp-3 + randomize_robot_pose (random base)", "wangexp-3", True, 0),
+        ("reachao_rand", "reachao_rand", False, 0), ("reachao_rand_shape", "reachao_rand_shape", False, 0),
+        ("reachao_rand_start (ik_sphere), pose_retry_limit 100", "reachao_rand_start", False, 100)]:
     tc = TrainConfig(); tc.randomize_robot_pose = randomize
-    b = sim.PandaBatch(sim.make_config(1, N, scenario=scenario, config=tc, max_episode_steps=100, auto_reset=True))
+    b = sim.PandaBatch(sim.make_config(1, N, scenario=scenario, config=tc, max_episode_steps=100, auto_reset=True, pose_retry_limit=limit))
     b.seed(5)
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     e0.record(); b.reset(); e1.record(); torch.cuda.synchronize()
