@@ -170,11 +170,53 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
           status |= 4;
           continue;
         }
+        // Warp-cooperative reset, randomizers that draw a fixed number of values per try (ik_goal_space, ik_box): the 32 lanes run
+        // the next 32 tries at once -- lane L on the numpy stream advanced by L tries, FIRST search of ik_lm_chan only (it needs no
+        // C rand() draw), then the robot-obstacle distance of its own pose.  The lowest lane that either found a free pose or needs
+        // a restart decides: all tries before it failed without touching the C rand() stream, exactly as in sequence; a free pose
+        // ends the loop, a restart is replayed the sequential way (randomize_pose, which owns the restart stream) and speculation
+        // resumes after it.  Same poses, same streams as one try at a time; the 10 000-try loop of an obstacle every pose happens to
+        // touch (0.1 % of resets, not seen by the fixed-core test) takes ~1 / 25 of the time.
+        const bool spec = WARP && GPOSE && (st.pose_kind == PG_POSE_IK_GOAL_SPACE || st.pose_kind == PG_POSE_IK_BOX);
+        const int draws = st.pose_kind == PG_POSE_IK_BOX || st.goal_sampler == 0 ? 3 : 3 + (st.goal_front ? 1 : 0) + (st.goal_34 ? 1 : 0);
+        double Rt[9];
+        if (spec) { double ax_[7][3], org_[7][3], o7_[3]; chain7(NX + 6, ax_, org_, Rt, o7_); }
         while (0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, c0, s0, pp)) {
           if (i > limit - 1) {  // set_joint_neutral (with set_random_robot_base, neutral_joint_values[0] already holds the last draw)
             status |= 4;
             if (gpose) { for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d]; pose_fk(qpose, pose); }
             break;
+          }
+          if (spec) {
+            const int lane = threadIdx.x & 31, left = limit - i, nvalid = left < 32 ? left : 32;
+            Pcg gl = g;
+            pcg_advance(gl, (uint64_t)lane * (uint64_t)draws);
+            double t[3], ql[7];
+            if (st.pose_kind == PG_POSE_IK_BOX) { for (int k = 0; k < 3; k++) t[k] = pcg_uniform(gl, st.pose_lo[k], st.pose_hi[k]); }
+            else sample_goal(st, gl, t);
+            int ok = 0, freep = 0;
+            if (lane < nvalid) {
+              for (int d = 0; d < 7; d++) ql[d] = NX[6 + d];
+              ok = lm_search(ql, t, Rt);
+              if (ok) {
+                PoseD pl;
+                pose_fk(ql, pl);
+                freep = !(0.05 >= robot_body_distance<false, GPOSE>(P, ob, 0.05, 1.0, 0.0, &pl));
+              }
+            }
+            const unsigned m_restart = __ballot_sync(0xffffffffu, lane < nvalid && !ok);
+            const unsigned m_free = __ballot_sync(0xffffffffu, freep != 0);
+            const unsigned first = m_restart | m_free;
+            const int w = first ? __ffs(first) - 1 : nvalid - 1;  // the try whose pose the robot has afterwards
+            if (!first || ((m_free >> w) & 1u)) {                 // tries i+1 .. i+w+1 done: all failed, or the last one is free
+              for (int d = 0; d < 7; d++) qpose[d] = __shfl_sync(0xffffffffu, ql[d], w);
+              pose_fk(qpose, pose);
+              pcg_advance(g, (uint64_t)(w + 1) * (uint64_t)draws);
+              i += w + 1;
+              continue;
+            }
+            pcg_advance(g, (uint64_t)w * (uint64_t)draws);        // tries before lane w failed; try w needs the restart stream
+            i += w;
           }
           i++;
           if (gpose) status |= randomize_pose<WARP>(P, e, g, cr, qpose, pose, qpose);

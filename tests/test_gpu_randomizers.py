@@ -194,3 +194,42 @@ def test_pose_retry_limit(sim, oracle):
         b.reset(seeds=torch.tensor(seeds, dtype=torch.int64, device=b.device)); torch.cuda.synchronize()
         _compare_reset(b, envs, seeds, ("limit", episode))
     b.close()
+
+
+def _episode_seed(base, g, k):
+    """pg_kernels.cuh episode_seed: seed of episode k of global environment g (auto-resets after the first episode)."""
+    M = (1 << 64) - 1
+    if k == 0:
+        return (base + g) & M
+    x = (base + g + 0x9E3779B97F4A7C15 * k) & M
+    x = (x + 0x9E3779B97F4A7C15) & M
+    x = ((x ^ (x >> 30)) * 0xBF58476D1CE4E5B9) & M
+    x = ((x ^ (x >> 27)) * 0x94D049BB133111EB) & M
+    return x ^ (x >> 31)
+
+
+@pytest.mark.parametrize("scenario", ["reachao2", "reachao3"])
+def test_warp_cooperative_auto_reset_matches_oracle(sim, oracle, scenario):
+    """The auto-reset path (k_reset list mode, one warp per environment: warp-parallel ik_lm_chan restarts and the speculative
+    32-tries-at-once form of set_coll_free_robot) against the oracle, which does one try at a time: every environment is reset at
+    every step (TimeLimit 1) with the library's per-episode seeds, over enough episodes to meet re-draws and restarts."""
+    from panda_gym_b200.config import TrainConfig
+    n, base = 384, 4100
+    tc = TrainConfig(); tc.randomize_robot_pose = True
+    b = sim.PandaBatch(sim.make_config(1, n, scenario=scenario, config=tc, max_episode_steps=1, auto_reset=True))
+    b.seed(base); b.reset(); torch.cuda.synchronize()
+    envs = [oracle.Env(task=1, scenario=scenario, randomize_robot_pose=1, max_episode_steps=1) for _ in range(n)]
+    for i, e in enumerate(envs):
+        e.reset(_episode_seed(base, i, 0))
+    moved = 0
+    for k in range(1, 5):
+        b.step(torch.zeros((n, 7), device=b.device)); torch.cuda.synchronize()   # every episode ends, every environment auto-resets
+        q = b.view("q").cpu().numpy(); goal = b.view("goal").cpu().numpy(); opos = b.view("obstacle_pos").cpu().numpy()
+        for i, e in enumerate(envs):
+            o, info = e.reset(_episode_seed(base, i, k))
+            assert np.abs(e.arm.q()[0][:7] - q[:, i]).max() < 1e-6, (scenario, k, i, info)
+            assert np.abs(e.goal() - goal[:, i]).max() < 1e-9
+            for j, (_, p, _) in enumerate(e.obstacles()):
+                assert np.abs(p - opos[j, :, i]).max() < 1e-9, (scenario, k, i, j)
+            moved += info["status"] != 0
+    b.close()
