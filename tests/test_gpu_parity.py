@@ -897,3 +897,24 @@ def test_env_task_and_robot_surface(sim, oracle):
         if trunc or term:
             break
     env.close()
+
+
+def test_async_stats_single_process(sim):
+    """sharding.AsyncStats without a process group: the snapshot taken at start() is what result() returns (the side-stream
+    all-reduce itself runs in bench.py under NCCL; profiles/r02_bench_8gpu.json)."""
+    from panda_gym_b200.sharding import AsyncStats
+    from panda_gym_b200.vec_env import PandaVecEnv
+    env = PandaVecEnv("PandaReachAO-v3", n_envs=256, seed=2, scenario="reachao3", max_episode_steps=3)
+    env.reset()
+    a = AsyncStats(env.batch.device)
+    rng = np.random.default_rng(0)
+    for _ in range(4):
+        env.step(rng.uniform(-1, 1, (256, 7)).astype(np.float32))
+    a.start(env.batch.view("stats"))
+    snap = env.episode_stats()
+    for _ in range(4):
+        env.step(rng.uniform(-1, 1, (256, 7)).astype(np.float32))
+    got = a.result()
+    assert got["episodes"] == snap["episodes"] >= 256 and got["sum_length"] == snap["sum_length"]
+    assert env.episode_stats()["episodes"] > got["episodes"]
+    env.close()
