@@ -187,6 +187,20 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
             if (gpose) { for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d]; pose_fk(qpose, pose); }
             break;
           }
+          if (WARP && !GPOSE && rbase) {  // set_random_robot_base: one draw per try, no other stream -- 32 tries per round, a lane each
+            const int lane = threadIdx.x & 31, left = limit - i, nvalid = left < 32 ? left : 32;
+            Pcg gl = g;
+            pcg_advance(gl, (uint64_t)lane);
+            const double ql0 = pcg_uniform(gl, -2.7437, 2.7437);
+            const bool freep = lane < nvalid &&
+                               !(0.05 >= robot_body_distance<false, GPOSE>(P, ob, 0.05, cos(ql0 - NX[6]), sin(ql0 - NX[6]), nullptr));
+            const unsigned m_free = __ballot_sync(0xffffffffu, freep);
+            const int w = m_free ? __ffs(m_free) - 1 : nvalid - 1;  // the try whose pose the robot has afterwards
+            q0 = __shfl_sync(0xffffffffu, ql0, w); c0 = cos(q0 - NX[6]); s0 = sin(q0 - NX[6]);
+            pcg_advance(g, (uint64_t)(w + 1));
+            i += w + 1;
+            continue;
+          }
           if (spec) {
             const int lane = threadIdx.x & 31, left = limit - i, nvalid = left < 32 ? left : 32;
             Pcg gl = g;

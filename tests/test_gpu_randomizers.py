@@ -208,7 +208,7 @@ def _episode_seed(base, g, k):
     return x ^ (x >> 31)
 
 
-@pytest.mark.parametrize("scenario", ["reachao2", "reachao3"])
+@pytest.mark.parametrize("scenario", ["reachao2", "reachao3", "wangexp-3"])
 def test_warp_cooperative_auto_reset_matches_oracle(sim, oracle, scenario):
     """The auto-reset path (k_reset list mode, one warp per environment: warp-parallel ik_lm_chan restarts and the speculative
     32-tries-at-once form of set_coll_free_robot) against the oracle, which does one try at a time: every environment is reset at
