@@ -218,6 +218,7 @@ __device__ inline void sample_torus(Pcg& g, int front, double* out) {
 // glibc rand() of the environment's worker process: r[k] = r[k-31] + r[k-3] (TYPE_3), 31-word ring + front / back index
 struct CRand { uint32_t r[31]; int f, b; };
 __device__ inline int crand_next(CRand& c) {
+  PG_CHECK(c.f >= 0 && c.f < 31 && c.b >= 0 && c.b < 31);
   c.r[c.f] += c.r[c.b];
   const int res = (int)(c.r[c.f] >> 1);
   c.f = c.f == 30 ? 0 : c.f + 1; c.b = c.b == 30 ? 0 : c.b + 1;

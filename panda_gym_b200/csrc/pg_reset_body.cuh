@@ -11,6 +11,7 @@ template <bool WARP, bool GPOSE, bool AUTO>
 __device__ __forceinline__ void reset_env(const Params& P, const int e, const uint64_t* __restrict__ seeds, const uint64_t first_env) {
   const int n = P.n;
   const bool leader = WARP ? (threadIdx.x & 31) == 0 : true;
+  PG_CHECK(e >= 0 && e < n);
   P.need_reset[e] = 0;
   uint32_t ep = P.episode[e];
   P.episode[e] = ep + 1;
@@ -222,6 +223,7 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
             const unsigned m_free = __ballot_sync(0xffffffffu, freep != 0);
             const unsigned first = m_restart | m_free;
             const int w = first ? __ffs(first) - 1 : nvalid - 1;  // the try whose pose the robot has afterwards
+            PG_CHECK(w >= 0 && w < nvalid && nvalid >= 1 && nvalid <= 32 && i + w + 1 <= limit);
             if (!first || ((m_free >> w) & 1u)) {                 // tries i+1 .. i+w+1 done: all failed, or the last one is free
               for (int d = 0; d < 7; d++) qpose[d] = __shfl_sync(0xffffffffu, ql[d], w);
               pose_fk(qpose, pose);

@@ -29,6 +29,7 @@ struct SceneParams {
 #define PG_ENVBOX 1
 #endif
 __device__ __forceinline__ Obst scene_obst(const SceneParams& P, int j, int e, int n, float& bound) {
+  PG_CHECK(j >= 0 && j < kMaxObst && e >= 0 && e < n);
   Obst ob = P.obst[j];
   bound = P.obst_bound[j];
 #if PG_ENVBOX
