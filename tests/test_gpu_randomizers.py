@@ -208,7 +208,7 @@ def _episode_seed(base, g, k):
     return x ^ (x >> 31)
 
 
-@pytest.mark.parametrize("scenario", ["reachao2", "reachao3", "wangexp-3"])
+@pytest.mark.parametrize("scenario", ["reachao2", "reachao3", "wangexp-3", "reachao_rand_start", "reachao_rand_shape"])
 def test_warp_cooperative_auto_reset_matches_oracle(sim, oracle, scenario):
     """The auto-reset path (k_reset list mode, one warp per environment: warp-parallel ik_lm_chan restarts and the speculative
     32-tries-at-once form of set_coll_free_robot) against the oracle, which does one try at a time: every environment is reset at
@@ -216,6 +216,8 @@ def test_warp_cooperative_auto_reset_matches_oracle(sim, oracle, scenario):
     from panda_gym_b200.config import TrainConfig
     n, base = 384, 4100
     tc = TrainConfig(); tc.randomize_robot_pose = True
+    if scenario == "reachao_rand_start":
+        n = 96   # its first reset runs the 1 000-try loop in every environment (test_ik_sphere_randomizer)
     b = sim.PandaBatch(sim.make_config(1, n, scenario=scenario, config=tc, max_episode_steps=1, auto_reset=True))
     b.seed(base); b.reset(); torch.cuda.synchronize()
     envs = [oracle.Env(task=1, scenario=scenario, randomize_robot_pose=1, max_episode_steps=1) for _ in range(n)]
@@ -232,4 +234,10 @@ def test_warp_cooperative_auto_reset_matches_oracle(sim, oracle, scenario):
             for j, (_, p, _) in enumerate(e.obstacles()):
                 assert np.abs(p - opos[j, :, i]).max() < 1e-9, (scenario, k, i, j)
             moved += info["status"] != 0
+        if scenario == "reachao_rand_shape":   # per-environment cuboids together with a start-pose randomizer (k_reset_envbox<., true>)
+            size = b.view("obstacle_size").cpu().numpy()
+            for i, e in enumerate(envs):
+                for j, (t, _, sz) in enumerate(e.obstacles()):
+                    if t == 1:
+                        assert np.abs(size[j, :, i] - sz).max() < 1e-15
     b.close()
