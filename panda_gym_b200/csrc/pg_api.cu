@@ -318,7 +318,7 @@ int pg_create(const pg_config* cfg, int device, pg_handle* out) {
     P.obs = (float*)(h->out_slab + h->slab_obs_off);
   }
   A(P.term_obs, (size_t)max_obs * n, true) A(P.term_achieved, 3 * n, true)
-  A(P.stats, 8, false) A(P.reset_list, n, false) A(P.reset_count, 1, false)
+  A(P.stats, 8, false) A(P.reset_list, n, false) A(P.reset_count, 1, false) A(P.hard_list, n, false) A(P.hard_count, 1, false)
   h->term_w_max = (8 + max_obs + 3) / 4 * 4;
   A(h->term_ring, (size_t)3 * n * h->term_w_max, false)
   P.term_rows = h->term_ring; P.term_w = (8 + P.obs_dim + 3) / 4 * 4;

@@ -90,6 +90,7 @@ struct Params {
   uint8_t *done, *flags;
   double* stats;                 // [8]
   int *reset_list, *reset_count;   // compacted indices of environments that finished in the last step
+  int *hard_list, *hard_count;     // environments a one-thread reset deferred to the warp-cooperative pass (pg_reset_body.cuh kDeferTries)
   // compact rows of the episodes that ended in this step, in the order of reset_list, term_w floats each:
   //   [0] env index (int bits) [1] episode return [2] episode length (int bits) [3] flags (int bits) [4..6] achieved goal [7] -
   //   [8 ..] terminal observation.  One slot of a 3-deep ring (pg_step rotates it): the host fetches the rows of a step it is

@@ -441,7 +441,8 @@ static __device__ __noinline__ void ik_bullet_position(const double* q_seed, con
 // streams (same result in every lane).  Returns reset-status bits: 8 = an unbounded rejection loop of the reference stopped
 // after 1000 tries, 16 = rtb_ik found no solution.
 template <bool WARP>
-__device__ __noinline__ int randomize_pose(const Params& P, int e, Pcg& g, CRand& cr, double* qpose, PoseD& pose, const double* q_cur) {
+__device__ __noinline__ int randomize_pose(const Params& P, int e, Pcg& g, CRand& cr, double* qpose, PoseD& pose, const double* q_cur,
+                                           int tries_done = 0) {  // tries_done: set_robot_random_pose tries this call has already made
   const StageDev& st = P.st;
   const double* seed = P.nextra + 6;  // Panda.neutral_joint_values of the stage (q0 and the orientation target of rtb_ik)
   int status = 0;
@@ -475,7 +476,7 @@ __device__ __noinline__ int randomize_pose(const Params& P, int e, Pcg& g, CRand
       }
       break; }
     default: {                     // set_robot_random_pose: until the EE height is inside [0.4, 0.6]
-      for (int i = 0;; i++) {
+      for (int i = tries_done;; i++) {
         sample_torus(g, st.pose_kind == PG_POSE_TORUS_FRONT, t);
         if (ik_lm_chan<WARP>(seed, t, cr, qpose) == 2) status |= 16;
         pose_fk(qpose, pose);

@@ -7,8 +7,13 @@
 // flow; the 36-primitive robot distance query is split across the lanes).  AUTO: auto-reset of an environment that finished in
 // the step just taken (done / flags / reward of that step stay); otherwise a reset the caller asked for.
 // GPOSE: the stage has a start-pose randomizer that puts the arm anywhere (rtb_ik / Bullet IK); false compiles all of that out
-template <bool WARP, bool GPOSE, bool AUTO>
-__device__ __forceinline__ void reset_env(const Params& P, const int e, const uint64_t* __restrict__ seeds, const uint64_t first_env) {
+// A one-thread reset whose set_coll_free_robot loop runs long (an obstacle most start poses touch) gives up after kDeferTries tries,
+// puts the environment on Params::hard_list and leaves it to the warp-cooperative pass that follows (PG_RESET_HARD_KERNEL), which
+// redoes the reset from its seed with the 32-tries-per-round forms: at a time-out wave (50 000 one-thread resets) the handful of
+// such environments no longer holds the step for 10 000 sequential inverse-kinematics solves.
+constexpr int kDeferTries = 64;
+template <bool WARP, bool GPOSE>
+__device__ __forceinline__ void reset_env(const Params& P, const int e, const uint64_t* __restrict__ seeds, const uint64_t first_env, const bool AUTO) {
   const int n = P.n;
   const bool leader = WARP ? (threadIdx.x & 31) == 0 : true;
   PG_CHECK(e >= 0 && e < n);
@@ -28,6 +33,9 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
   float q[7], qd[7], cq[7], sq[7];
   P.steps[e] = 0; P.ep_ret[e] = 0.f; P.ep_len[e] = 0;
   double goal[3], ee[6];  // ee[0..2] = get_ee_position(), ee[3..5] = get_link_position(0), both at the reset pose
+  double old_pos[kMaxObst * 3];  // obstacle positions before this reset, for a one-thread reset that defers itself (kDeferTries)
+  if (!WARP && P.task == 1 && (GPOSE || st.random_base))
+    for (int k = 0; k < st.nobs * 3; k++) old_pos[k] = P.obs_pos[(size_t)k * n + e];
   int status = 0;
   PoseD pose; double qpose[7]; CRand cr;
   const PoseD* pp = gpose ? &pose : nullptr;
@@ -182,11 +190,68 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
         const int draws = st.pose_kind == PG_POSE_IK_BOX || st.goal_sampler == 0 ? 3 : 3 + (st.goal_front ? 1 : 0) + (st.goal_34 ? 1 : 0);
         double Rt[9];
         if (spec) { double ax_[7][3], org_[7][3], o7_[3]; chain7(NX + 6, ax_, org_, Rt, o7_); }
+        // set_robot_random_pose (torus kinds) draws a fixed number of values per TRY, several tries per call (until the EE height
+        // fits): the same speculation one level down -- the lowest lane that needs a restart or whose pose passes the height test
+        // decides; lanes before it are tries of the running call that failed the height test.
+        const bool spec_torus = WARP && GPOSE && (st.pose_kind == PG_POSE_TORUS || st.pose_kind == PG_POSE_TORUS_FRONT);
+        const int draws_torus = st.pose_kind == PG_POSE_TORUS_FRONT ? 4 : 3;
+        if (spec_torus) { double ax_[7][3], org_[7][3], o7_[3]; chain7(NX + 6, ax_, org_, Rt, o7_); }
+        bool in_call = false;  // a robot.reset() call of the loop below is under way (torus speculation only)
+        int inner = 0;         // height-test tries it has made
         while (0.05 >= robot_body_distance<WARP, GPOSE>(P, ob, 0.05, c0, s0, pp)) {
+          if (!WARP && i >= kDeferTries && limit > kDeferTries && st.pose_kind != PG_POSE_IK_SPHERE && st.pose_kind != PG_POSE_BULLET_IK_BOX) {
+            // as if this reset had not started: the episode counter and the obstacle positions it has overwritten go back (the
+            // overlap test of set_coll_free_obs reads the obstacles not yet re-sampled where the last episode left them);
+            // nothing else it wrote survives the redo
+            P.episode[e] = ep;
+            for (int k = 0; k < st.nobs * 3; k++) P.obs_pos[(size_t)k * n + e] = old_pos[k];
+            P.hard_list[atomicAdd(P.hard_count, 1)] = e;
+            return;
+          }
+          if (spec_torus && in_call) {}  // the try budget is checked when a call starts
+          else
           if (i > limit - 1) {  // set_joint_neutral (with set_random_robot_base, neutral_joint_values[0] already holds the last draw)
             status |= 4;
             if (gpose) { for (int d = 0; d < 7; d++) qpose[d] = NX[6 + d]; pose_fk(qpose, pose); }
             break;
+          }
+          if (spec_torus) {
+            if (!in_call) { i++; in_call = true; inner = 0; }
+            const int lane = threadIdx.x & 31, nvalid = 32;
+            Pcg gl = g;
+            pcg_advance(gl, (uint64_t)lane * (uint64_t)draws_torus);
+            double t[3], ql[7];
+            sample_torus(gl, st.pose_kind == PG_POSE_TORUS_FRONT, t);
+            for (int d = 0; d < 7; d++) ql[d] = NX[6 + d];
+            const int ok = lm_search(ql, t, Rt);
+            bool zpass = false;
+            if (ok) {
+              PoseD pl;
+              pose_fk(ql, pl);
+              double eel[3];
+              pose_point(pl, 7, pgm::kLocalEE, eel);
+              const double z = eel[2] + P.based[2];
+              zpass = 0.6 >= z && z >= 0.4;
+            }
+            const unsigned m_restart = __ballot_sync(0xffffffffu, !ok);
+            const unsigned m_z = __ballot_sync(0xffffffffu, zpass);
+            const unsigned first = m_restart | m_z;
+            const int w = first ? __ffs(first) - 1 : nvalid;
+            if (inner + w >= 990 || (first && ((m_restart >> w) & 1u))) {
+              // a try that needs the restart stream (or the call nears its 1 000-try bound): the tries before it failed the height
+              // test; the rest of the call runs the sequential way
+              const int skip = (first && w < nvalid) ? w : 0;
+              pcg_advance(g, (uint64_t)skip * (uint64_t)draws_torus);
+              status |= randomize_pose<WARP>(P, e, g, cr, qpose, pose, qpose, inner + skip);
+              in_call = false;
+              continue;
+            }
+            if (!first) { pcg_advance(g, (uint64_t)nvalid * (uint64_t)draws_torus); inner += nvalid; continue; }  // 32 more failed tries
+            for (int d = 0; d < 7; d++) qpose[d] = __shfl_sync(0xffffffffu, ql[d], w);  // try w passes the height test: the call returns
+            pose_fk(qpose, pose);
+            pcg_advance(g, (uint64_t)(w + 1) * (uint64_t)draws_torus);
+            in_call = false;
+            continue;
           }
           if (WARP && !GPOSE && rbase) {  // set_random_robot_base: one draw per try, no other stream -- 32 tries per round, a lane each
             const int lane = threadIdx.x & 31, left = limit - i, nvalid = left < 32 ? left : 32;
@@ -301,14 +366,22 @@ __global__ void __launch_bounds__(kBlock) PG_RESET_KERNEL(const __grid_constant_
   if (LIST) {
     const int count = *P.reset_count;
     if (count <= kWarpResetMax) {
-      for (int item = tid >> 5; item < count; item += total >> 5) reset_env<true, GPOSE, true>(P, P.reset_list[item], nullptr, first_env);
+      for (int item = tid >> 5; item < count; item += total >> 5) reset_env<true, GPOSE>(P, P.reset_list[item], nullptr, first_env, true);
     } else {
-      for (int item = tid; item < count; item += total) reset_env<false, GPOSE, true>(P, P.reset_list[item], nullptr, first_env);
+      for (int item = tid; item < count; item += total) reset_env<false, GPOSE>(P, P.reset_list[item], nullptr, first_env, true);
     }
   } else {
     for (int e = tid; e < P.n; e += total)
-      if (!mask || mask[e]) reset_env<false, GPOSE, false>(P, e, seeds, first_env);
+      if (!mask || mask[e]) reset_env<false, GPOSE>(P, e, seeds, first_env, false);
   }
+}
+// the environments the one-thread resets deferred (see kDeferTries), a warp each
+template <bool GPOSE>
+__global__ void __launch_bounds__(kBlock) PG_RESET_HARD_KERNEL(const __grid_constant__ Params P, const uint64_t* __restrict__ seeds, uint64_t first_env,
+                                                               int auto_reset) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, total = gridDim.x * blockDim.x;
+  const int count = *P.hard_count;
+  for (int item = tid >> 5; item < count; item += total >> 5) reset_env<true, GPOSE>(P, P.hard_list[item], seeds, first_env, auto_reset != 0);
 }
 
 #ifdef PG_OBSERVE_LAUNCH

@@ -1,6 +1,7 @@
 // pg_tu_reset_e0g0.cu -- reset kernels, variant PG_ENVBOX 0 (obstacle shapes from the kernel parameters), arm at the stage's reset pose (see pg_reset_body.cuh)
 #define PG_ENVBOX 0
 #define PG_RESET_KERNEL k_reset
+#define PG_RESET_HARD_KERNEL k_reset_deferred
 #define PG_RESET_GPOSE false
 #define PG_RESET_LAUNCH launch_reset_e0g0
 #define PG_OBSERVE_KERNEL k_observe

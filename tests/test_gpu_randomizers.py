@@ -208,7 +208,7 @@ def _episode_seed(base, g, k):
     return x ^ (x >> 31)
 
 
-@pytest.mark.parametrize("scenario", ["reachao2", "reachao3", "wangexp-3", "reachao_rand_start", "reachao_rand_shape"])
+@pytest.mark.parametrize("scenario", ["reachao2", "reachao3", "wangexp-3", "reachao_rand_start", "reachao_rand_shape", "wang-3", "reachao1"])
 def test_warp_cooperative_auto_reset_matches_oracle(sim, oracle, scenario):
     """The auto-reset path (k_reset list mode, one warp per environment: warp-parallel ik_lm_chan restarts and the speculative
     32-tries-at-once form of set_coll_free_robot) against the oracle, which does one try at a time: every environment is reset at
@@ -241,3 +241,38 @@ def test_warp_cooperative_auto_reset_matches_oracle(sim, oracle, scenario):
                     if t == 1:
                         assert np.abs(size[j, :, i] - sz).max() < 1e-15
     b.close()
+
+
+@pytest.mark.parametrize("scenario", ["wangexp-3", "reachao3", "wang-3"])
+def test_one_thread_and_warp_resets_agree(sim, scenario):
+    """The auto-reset gives every environment a warp while the finished list is short and a thread each when it is long (with the
+    long rejection loops deferred to a warp pass): the same environments, seeded alike, must come out identical either way.
+    One batch of 4 096 (every step resets all of them: one-thread mode) against four shards of 1 024 (warp mode)."""
+    from panda_gym_b200.config import TrainConfig
+    tc = TrainConfig(); tc.randomize_robot_pose = True
+    N, S = 4096, 1024
+    big = sim.PandaBatch(sim.make_config(1, N, scenario=scenario, config=tc, max_episode_steps=1, auto_reset=True))
+    big.seed(90, 0); big.reset()
+    shards = []
+    for r in range(N // S):
+        b = sim.PandaBatch(sim.make_config(1, S, scenario=scenario, config=tc, max_episode_steps=1, auto_reset=True))
+        b.seed(90, r * S); b.reset()
+        shards.append(b)
+    for k in range(4):
+        a = torch.zeros((N, 7), device=big.device)
+        big.step(a)
+        for b in shards:
+            b.step(a[:S])
+        torch.cuda.synchronize()
+        for name in ("q", "goal", "obstacle_pos"):
+            full = big.view(name).cpu().numpy()
+            for r, b in enumerate(shards):
+                part = b.view(name).cpu().numpy()
+                assert np.array_equal(full[..., r * S:(r + 1) * S], part), (scenario, k, name, r)
+        # the observation is fp32 arithmetic compiled twice (warp / one-thread instantiation): equal to rounding, not bit for bit
+        d = np.abs(big.view("observation").cpu().numpy() - np.concatenate([b.view("observation").cpu().numpy() for b in shards]))
+        assert d[:, :29].max() < 2e-6 and d.max() < 1e-4, (scenario, k, d[:, :29].max(), d.max())
+    assert sum(int(b.view("stats").cpu().numpy()[6]) for b in shards) == int(big.view("stats").cpu().numpy()[6])
+    big.close()
+    for b in shards:
+        b.close()
