@@ -492,6 +492,105 @@ __device__ __noinline__ int randomize_pose(const Params& P, int e, Pcg& g, CRand
   return status;
 }
 
+// ------------------------------------------------------------------------------------------------ reset observation, one warp
+// The observation a warp-cooperative reset ends with (ReachAO with obstacles; arm at rest, cached pose = current pose).  observe()
+// runs the unrolled per-link scene pass on every lane alike: 52 of the auto-reset kernel's 100 us, all of it instruction fetch
+// (~2.5 k instructions walked once).  Here the 9 links x M obstacles are dealt out to the lanes, one (link, obstacle) pair each,
+// and ONE loop over the run-time copy of the primitive table does the closest-distance work of every pair at once; the per-link
+// minimum over the obstacles is gathered with shuffles.  Same closed forms as prim_vs_obstacle<K> (no deferred queue: a pair's
+// cylinder-box GJK runs in place), so the numbers equal the unrolled pass to fp32 rounding.
+__device__ __forceinline__ void prim_vs_obstacle_rt(const Frame& F, const PrimRT& pr, V3 o, const Obst& ob, float& best, V3& bdir) {
+  const V3 c = frame_point(F, pr.x, pr.y, pr.z);
+  Closest k;
+  if (pr.type == 0) {
+    if (ob.type == 0) k = sphere_sphere<float>(c, pr.r, o, ob.sx);
+    else k = sphere_box<float>(c, pr.r, o, v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin), ob.margin);
+  } else {
+    const V3 a = frame_dir(F, pr.ax, pr.ay, pr.az);
+    if (ob.type == 0) k = cyl_sphere<float>(c, a, pr.r, pr.h, o, ob.sx);
+    else {
+      const V3 core = v3(ob.sx - ob.margin, ob.sy - ob.margin, ob.sz - ob.margin);
+      CylBoxBoundT<float> bd = cyl_box_bound<float>(c - o, a, pr.r, pr.h, core);
+      const float lb = bd.lb - kHullMargin - ob.margin;
+      if (lb >= best) return;
+      if (bd.exact) { best = lb; bdir = bd.lb > 0.f ? bd.u : v3(0.f, 0.f, 0.f); return; }
+      k = cyl_box<float>(c, a, pr.r, pr.h, o, core, ob.margin);
+    }
+  }
+  if (k.d < best) { best = k.d; bdir = k.dir; }
+}
+// all 32 lanes call it with the same arguments; returns the achieved goal (EE position) in ag on every lane
+static __device__ __noinline__ void observe_reset_warp(const Params& P, int e, const float* q, const float* cq, const float* sq, float* ag) {
+  const int n = P.n, lane = threadIdx.x & 31;
+  const V3 base = v3(P.base[0], P.base[1], P.base[2]);
+  Frame Fr[8];
+  Fr[0] = base_frame(base);
+  Fr[1] = frame_step<1>(Fr[0], cq[0], sq[0]); Fr[2] = frame_step<2>(Fr[1], cq[1], sq[1]); Fr[3] = frame_step<3>(Fr[2], cq[2], sq[2]);
+  Fr[4] = frame_step<4>(Fr[3], cq[3], sq[3]); Fr[5] = frame_step<5>(Fr[4], cq[4], sq[4]); Fr[6] = frame_step<6>(Fr[5], cq[5], sq[5]);
+  Fr[7] = frame_step<7>(Fr[6], cq[6], sq[6]);
+  const V3 ee = frame_point(Fr[7], pgm::kEEx, pgm::kEEy, pgm::kEEz);
+  ag[0] = ee.x; ag[1] = ee.y; ag[2] = ee.z;
+  const int nb = P.scene.nobs + P.scene.nstatic, np = 9 * nb;
+  float mybest = 999.0f;  // lanes 0..8: minimum of link `lane` over the obstacles (pyb_utils saturates at max_distance)
+  V3 mydir = v3(0.f, 0.f, 0.f);
+  for (int p0 = 0; p0 < np; p0 += 32) {
+    const int p = p0 + lane;
+    float best = 999.0f;
+    V3 dir = v3(0.f, 0.f, 0.f);
+    if (p < np) {
+      const int s = p / nb, j = p - s * nb;
+      Obst ob; V3 o;
+      if (j < P.scene.nobs) {
+        float bound;
+        ob = scene_obst(P.scene, j, e, n, bound);
+        o = v3(P.obs_pos_f[(size_t)(j * 3 + 0) * n + e], P.obs_pos_f[(size_t)(j * 3 + 1) * n + e], P.obs_pos_f[(size_t)(j * 3 + 2) * n + e]);
+      } else ob = static_obst(P.scene, j - P.scene.nobs, o);
+      const int k0 = slot_first(s), k1 = k0 + slot_count(s);
+      for (int k = k0; k < k1; k++) {
+        const PrimRT& pr = kPrimRT[k];
+        prim_vs_obstacle_rt(Fr[pr.frame], pr, o, ob, best, dir);
+      }
+    }
+    const int live = np - p0 < 32 ? np - p0 : 32;
+    for (int src = 0; src < live; src++) {  // pair p0 + src belongs to link (p0 + src) / nb: its lane takes it if it is closer
+      const float d = __shfl_sync(0xffffffffu, best, src);
+      const float dx = __shfl_sync(0xffffffffu, dir.x, src), dy = __shfl_sync(0xffffffffu, dir.y, src), dz = __shfl_sync(0xffffffffu, dir.z, src);
+      if ((p0 + src) / nb == lane && d < mybest) { mybest = d; mydir = v3(dx, dy, dz); }
+    }
+  }
+  float* o = P.obs + (size_t)e * P.obs_dim;
+  const int off = P.obs_js ? 20 : 6;
+  if (lane == 0) {
+    o[0] = ee.x; o[1] = ee.y; o[2] = ee.z; o[3] = 0.f; o[4] = 0.f; o[5] = 0.f;
+    if (P.obs_js) for (int d = 0; d < 7; d++) { o[6 + d] = q[d]; o[13 + d] = 0.f; }
+    for (int d = 0; d < 7; d++) P.q_dl[(size_t)d * n + e] = q[d];
+    float* a = P.achieved + (size_t)e * 3;
+    float* g = P.desired + (size_t)e * 3;
+    a[0] = ee.x; a[1] = ee.y; a[2] = ee.z;
+    g[0] = (float)P.goal[e]; g[1] = (float)P.goal[(size_t)n + e]; g[2] = (float)P.goal[(size_t)2 * n + e];
+  }
+  // utils.unit_vector(pA, pB) = nan_to_num((pB - pA) / |pB - pA|) with pB - pA = d * dir
+  const V3 u = mybest > 0.f ? mydir : (mybest < 0.f ? v3(-mydir.x, -mydir.y, -mydir.z) : v3(0.f, 0.f, 0.f));
+  float mn = lane < 9 ? mybest : 3.0e38f;
+  for (int k = 16; k > 0; k >>= 1) mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, k));
+  if (lane < 9) {
+    const int i = lane;
+    P.d_link[(size_t)i * n + e] = mybest;
+    if (P.obstacle_obs == 1) { o[off + i] = mybest; o[off + 9 + 3 * i] = u.x; o[off + 10 + 3 * i] = u.y; o[off + 11 + 3 * i] = u.z; }
+    else if (P.obstacle_obs == 2) { o[off + 3 * i] = u.x; o[off + 1 + 3 * i] = u.y; o[off + 2 + 3 * i] = u.z; }
+    else if (P.obstacle_obs == 3) o[off + i] = mybest;
+    else if (P.obstacle_obs == 5) {  // "vectors+past", first observation of the episode: the history is filled with it
+      const float cur[3] = {u.x, u.y, u.z};
+      for (int k = 0; k < 3; k++) {
+        const int c = 3 * i + k;
+        o[off + c] = cur[k]; o[off + 27 + c] = cur[k]; o[off + 54 + c] = cur[k];
+        P.past_vec[(size_t)c * n + e] = cur[k]; P.past_vec[(size_t)(27 + c) * n + e] = cur[k];
+      }
+    } else if (i == 0) o[off] = mn;
+  }
+  __syncwarp();
+}
+
 // RobotTaskEnv.reset (core.py:298-308) = Panda.reset (panda.py:290-298) + Reach.reset (reach.py:63-78) /
 // ReachAO.reset (reach_ao.py:965-1033) with its rejection-sampling helpers (:1101-1181)
 //

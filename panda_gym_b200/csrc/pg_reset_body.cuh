@@ -346,7 +346,8 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
   P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;
   if (status && leader) atomicAdd(&P.stats[6], 1.0);
   float ag[3], dg[3];
-  observe<true>(P, e, q, qd, q, cq, sq, ag, true);
+  if (WARP && P.task == 1 && P.obstacle_obs != 0 && P.scene.nobs + P.scene.nstatic > 0) observe_reset_warp(P, e, q, cq, sq, ag);
+  else observe<true>(P, e, q, qd, q, cq, sq, ag, true);
   dg[0] = (float)goal[0]; dg[1] = (float)goal[1]; dg[2] = (float)goal[2];
   bool succ = is_success(P, e, ag, dg);
   if (!AUTO) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }

