@@ -295,6 +295,26 @@ int pg_her_set_mt_state(pg_her_handle h, const uint32_t* key624_host, int pos);
 int pg_her_get_mt_state(pg_her_handle h, uint32_t* key624_host, int* pos);
 /* env: the simulator handle whose compute_reward relabels (reward terms read environment reward_env, SB3 uses 0) */
 int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, uint64_t fast_seed, int reward_env, pg_her_batch* out, void* stream);
+/* pg_her_sample for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * No counterpart in the reference.
+ * Same sampling, relabelling and reward recompute as pg_her_sample, same use of the buffer's MT19937 state / fast counter and of
+ * its cached valid list, but (1) the batch is written to the CALLER's device block packed_out_dev, [batch][row_stride] floats in
+ * the record's field order (row_stride and the column ranges are those pg_her_sample reports: observation | next observation |
+ * achieved | desired | next achieved | next desired | action | reward | done, row_stride = (2*obs_dim + act_dim + 16 + 15) / 16 * 16),
+ * and (2) every per-call scratch (index lists, compaction block counts, status word) lives in ONE file-scope static __device__
+ * array of the library (1.25 MiB, held by every GPU that loads the library until exit) instead of the buffer's own allocations.
+ * The call makes no cudaMalloc / cudaFree and calls no allocating routine; the first call on a device resolves the array's
+ * address (cudaGetSymbolAddress, no allocation) -- make that call outside a capture.
+ * Limits: batch <= PG_HER_STATIC_MAX_BATCH rows and buffer capacity (rows * n_envs) <= PG_HER_STATIC_MAX_TRANSITIONS; beyond
+ * either the call fails with PG_ERR_ARG and pg_last_error() names the limit.
+ * All calls on one GPU share the array and it keeps the last call's contents: calls that overlap on the GPU (different streams,
+ * different buffers) race; order them on one stream or with events.  The status word is cleared by every call.
+ * status_out_dev (device int, may be NULL) receives 0, or 1 when no episode has finished yet (the batch is then left untouched).
+ * pg_her_last_indices keeps reporting the last pg_her_sample call, not this one. */
+#define PG_HER_STATIC_MAX_BATCH 65536
+#define PG_HER_STATIC_MAX_TRANSITIONS 16777216
+int pg_her_sample_static(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, uint64_t fast_seed, int reward_env,
+                         float* packed_out_dev, int* status_out_dev, void* stream);
 /* (row, env, t) of the last sample() in SB3's draw order (virtual first), for parity tests; synchronises */
 int pg_her_last_indices(pg_her_handle h, int64_t batch, int* row_host, int* env_host, int* t_host, int* n_valid_host, int* status_host);
 int pg_her_info(pg_her_handle h, int* rows, int* pos, int* full, int64_t* launches);

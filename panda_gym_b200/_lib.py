@@ -108,6 +108,7 @@ SYMBOLS = [
     ("pg_her_set_mt_state", c_int, [P, P, c_int]),
     ("pg_her_get_mt_state", c_int, [P, P, P]),
     ("pg_her_sample", c_int, [P, P, c_i64, c_int, c_u64, c_int, P, P]),
+    ("pg_her_sample_static", c_int, [P, P, c_i64, c_int, c_u64, c_int, P, P, P]),
     ("pg_her_last_indices", c_int, [P, c_i64, P, P, P, P, P]),
     ("pg_her_info", c_int, [P, P, P, P, P]),
     ("pg_last_error", ctypes.c_char_p, []),

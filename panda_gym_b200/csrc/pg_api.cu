@@ -7,6 +7,7 @@
 #include <string.h>
 
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -908,6 +909,72 @@ int pg_her_sample(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, 
   out->next_achieved_goal = pk + 2 * od + 6; out->next_desired_goal = pk + 2 * od + 9;
   out->action = pk + 2 * od + 12; out->reward = pk + 2 * od + 12 + H.act_dim; out->done = out->reward + 1;
   out->batch = batch; out->n_virtual = nbv; out->row_stride = H.rec_w;
+  return PG_OK;
+}
+
+// ------------------------------------------------------------------------------------------ sample() without allocation
+// Scratch of pg_her_sample_static: the index lists the index kernel hands to the gather kernel, the per-block counts of the
+// valid-index compaction and the status word.  File-scope device memory: every GPU that loads the library holds these 1.25 MiB
+// until exit, ALL calls (of all buffers on that GPU) share it, and it keeps the last call's contents.  In host code the name
+// `g_her_static` is only the host-side stand-in of the symbol: its device address comes from cudaGetSymbolAddress, once per
+// device with that device current (static_scratch below).
+constexpr int kStaticMaxBatch = PG_HER_STATIC_MAX_BATCH;            // rows per call
+constexpr int kStaticMaxBlocks = PG_HER_STATIC_MAX_TRANSITIONS / pg::kHerBlock + 1;  // compaction blocks (buffer capacity / 256)
+constexpr int kStaticStatusAt = 4 * kStaticMaxBatch;               // [0] status, rest of the 256 B line unused
+constexpr int kStaticCountsAt = kStaticStatusAt + 64;
+constexpr int kStaticInts = kStaticCountsAt + (kStaticMaxBlocks + 63) / 64 * 64;
+static __device__ __align__(256) int g_her_static[kStaticInts];
+
+static std::mutex g_static_mu;
+static int* g_static_ptr[64] = {nullptr};
+// device address of g_her_static on `device` (which the caller has made current); resolved once per device
+static int static_scratch(int device, int** out) {
+  if (device < 0 || device >= 64) return fail(PG_ERR_ARG, "device index out of range");
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[device]) {
+    int* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_her_static);
+    if (e != cudaSuccess || !p) { cudaGetLastError(); return fail(PG_ERR_CUDA, std::string("cudaGetSymbolAddress(g_her_static): ") + cudaGetErrorString(e)); }
+    g_static_ptr[device] = p;
+  }
+  *out = g_static_ptr[device];
+  return PG_OK;
+}
+
+int pg_her_sample_static(pg_her_handle h, pg_handle env, int64_t batch, int exact_rng, uint64_t fast_seed, int reward_env,
+                         float* packed_out_dev, int* status_out_dev, void* stream) {
+  if (!h || !env || !packed_out_dev || batch <= 0) return fail(PG_ERR_ARG, "bad argument (NULL handle / output, or batch <= 0)");
+  if (batch > kStaticMaxBatch)
+    return fail(PG_ERR_ARG, "pg_her_sample_static: batch exceeds PG_HER_STATIC_MAX_BATCH (" + std::to_string(kStaticMaxBatch) + " rows): use pg_her_sample");
+  if (h->capacity > (int64_t)PG_HER_STATIC_MAX_TRANSITIONS)
+    return fail(PG_ERR_ARG, "pg_her_sample_static: buffer capacity exceeds PG_HER_STATIC_MAX_TRANSITIONS (" +
+                std::to_string(PG_HER_STATIC_MAX_TRANSITIONS) + "): use pg_her_sample");
+  if (reward_env < 0 || reward_env >= env->P.n) return fail(PG_ERR_ARG, "reward_env out of range");
+  PG_CUDA(cudaSetDevice(h->device));
+  int* scratch = nullptr;
+  int rc = static_scratch(h->device, &scratch);
+  if (rc != PG_OK) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  pg::HerParams H = h->H;  // the buffer's storage and valid list, with every per-call scratch pointer moved into g_her_static
+  H.s_row = scratch; H.s_env = scratch + kStaticMaxBatch; H.s_t = scratch + 2 * kStaticMaxBatch; H.s_trow = scratch + 3 * kStaticMaxBatch;
+  H.status = scratch + kStaticStatusAt;
+  H.block_counts = scratch + kStaticCountsAt;
+  const int total = (int)h->capacity;
+  const int B = (int)batch, nbv = (int)(h->her_ratio * (double)B);
+  // nothing here has to start at zero for the kernels (counts, index lists and status are fully written before they are read),
+  // but the status word is cleared anyway so that a call never reports the previous call's outcome
+  PG_CUDA(cudaMemsetAsync(H.status, 0, sizeof(int), s));
+  if (h->valid_stale) {  // same cache as pg_her_sample: the valid list belongs to the buffer, only the block counts are scratch
+    pg::launch_her_compact(H, total, s);
+    h->launches += 3;
+    h->valid_stale = false;
+  }
+  pg::launch_her_indices(H, B, nbv, exact_rng != 0, fast_seed, h->fast_counter++, s);
+  pg::HerBatch O; O.packed = packed_out_dev;
+  pg::launch_her_gather(H, env->P, O, B, nbv, reward_env, h->sm_count, s);
+  h->launches += 2;
+  if (status_out_dev) PG_CUDA(cudaMemcpyAsync(status_out_dev, H.status, sizeof(int), cudaMemcpyDeviceToDevice, s));
+  PG_CUDA(cudaGetLastError());
   return PG_OK;
 }
 
