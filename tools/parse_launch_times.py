@@ -12,4 +12,5 @@ for r in rows:
         except ValueError: continue
         u = d["Metric Unit"]; v.append(x / 1000 if u == "ns" else (x * 1000 if u == "ms" else x))
 v.sort()
+if not v: sys.exit("%s: no launch matches %r" % (sys.argv[1], flt))
 print(sys.argv[1], flt, "launches", len(v), "median us %.1f min %.1f max %.1f" % (v[len(v) // 2], v[0], v[-1]))
