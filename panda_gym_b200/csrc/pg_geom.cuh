@@ -220,7 +220,12 @@ template <typename T> __host__ __device__ __forceinline__ void tri_closest(V3T<T
 }
 
 // distance between the two CORES (0 when they touch / overlap); qa / qb = closest points on the cores
-template <typename T> __host__ __device__ __noinline__ T gjk_cyl_box(const GjkIn<T> g, V3T<T>* qa, V3T<T>* qb) {
+// DECIDE: the caller only wants to know on which side of `thr` the distance lies.  GJK carries both bounds at every iteration --
+// |v| from above (v is a point of the difference body), v.w / |v| from below (w supports it in direction -v) -- so it stops as
+// soon as one of them settles the question and returns that bound (<= thr, or > thr; qa / qb are then not set).  Against a
+// cylinder's curved surface fp64 GJK converges linearly and runs to its iteration cap for 1e-14; the reset's accept / reject
+// tests need a handful of iterations.
+template <typename T, bool DECIDE> __host__ __device__ __forceinline__ T gjk_cyl_box_impl(const GjkIn<T> g, V3T<T>* qa, V3T<T>* qb, T thr) {
   V3T<T> W[4], A[4], B[4];
   T lam[4] = {T(1), T(0), T(0), T(0)};
   int n = 0;
@@ -231,6 +236,11 @@ template <typename T> __host__ __device__ __noinline__ T gjk_cyl_box(const GjkIn
     gjk_support(g, v3t<T>(-v.x, -v.y, -v.z), sa, sb);
     V3T<T> w = sa - sb;
     T vv = dot(v, v);
+    if (DECIDE && n > 0) {
+      if (vv <= thr * thr) return tsqrt(vv);
+      const T vw = dot(v, w);
+      if (vw > T(0) && vw * vw > thr * thr * vv) return vw / tsqrt(vv);
+    }
     if (n > 0 && vv - dot(v, w) <= (sizeof(T) == 8 ? T(1e-14) : T(1e-5)) * vv + (sizeof(T) == 8 ? T(1e-22) : T(1e-12))) break;
     W[n] = w; A[n] = sa; B[n] = sb; n++;
     if (n == 1) { lam[0] = 1; }
@@ -282,6 +292,18 @@ template <typename T> __host__ __device__ __noinline__ T gjk_cyl_box(const GjkIn
   for (int k = 0; k < n; k++) { pa = pa + lam[k] * A[k]; pb = pb + lam[k] * B[k]; }
   *qa = pa; *qb = pb;
   return tnorm(v);
+}
+template <typename T> __host__ __device__ __noinline__ T gjk_cyl_box(const GjkIn<T> g, V3T<T>* qa, V3T<T>* qb) {
+  return gjk_cyl_box_impl<T, false>(g, qa, qb, T(0));
+}
+template <typename T> __host__ __device__ __noinline__ T gjk_cyl_box_decide(const GjkIn<T> g, T thr) {
+  V3T<T> qa, qb;
+  return gjk_cyl_box_impl<T, true>(g, &qa, &qb, thr);
+}
+// cyl_box(...).d for a caller that only compares it with `cutoff`: a value on the same side of `cutoff` as the distance
+template <typename T> __host__ __device__ __forceinline__ T cyl_box_decide(V3T<T> c, V3T<T> a, T r, T h, V3T<T> b, V3T<T> e, T m, T cutoff) {
+  GjkIn<T> g; g.c = c; g.a = a; g.b = b; g.e = e; g.r = r; g.h = h;
+  return gjk_cyl_box_decide<T>(g, cutoff + T(kHullMargin) + m) - T(kHullMargin) - m;
 }
 
 template <typename T> __host__ __device__ __forceinline__ ClosestT<T> cyl_box(V3T<T> c, V3T<T> a, T r, T h, V3T<T> b, V3T<T> e, T m) {

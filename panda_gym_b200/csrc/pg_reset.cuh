@@ -101,7 +101,7 @@ __device__ __noinline__ double robot_body_distance(const Params& P, const Body& 
         const double lb = bd.lb - (double)kHullMargin - m;
         if (lb > cutoff || lb >= best) continue;
         if (bd.exact) { best = lb; continue; }
-        d = cyl_box<double>(c, a, np.r, np.h, o, core, m).d;
+        d = cyl_box_decide<double>(c, a, np.r, np.h, o, core, m, cutoff);  // every caller only compares the result with `cutoff`
       }
     }
     best = fmin(best, d);

@@ -12,11 +12,29 @@
 // redoes the reset from its seed with the 32-tries-per-round forms: at a time-out wave (50 000 one-thread resets) the handful of
 // such environments no longer holds the step for 10 000 sequential inverse-kinematics solves.
 constexpr int kDeferTries = 64;
+// -DPG_RESET_TRACE (tools/trace_reset.py, variant build only): per reset, clock stamps of its phases, SM id and environment
+#ifdef PG_RESET_TRACE
+static __device__ unsigned long long g_trace[8 * 65536];
+static __device__ int g_trace_n;
+__device__ __forceinline__ unsigned long long trace_gt() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define PG_TRACE(k, v) do { if (tslot >= 0) g_trace[tslot * 8 + (k)] = (unsigned long long)(v); } while (0)
+#else
+#define PG_TRACE(k, v) do {} while (0)
+#endif
 template <bool WARP, bool GPOSE>
 __device__ __forceinline__ void reset_env(const Params& P, const int e, const uint64_t* __restrict__ seeds, const uint64_t first_env, const bool AUTO) {
   const int n = P.n;
   const bool leader = WARP ? (threadIdx.x & 31) == 0 : true;
   PG_CHECK(e >= 0 && e < n);
+#ifdef PG_RESET_TRACE
+  int tslot = -1;
+  if (leader) {
+    tslot = atomicAdd(&g_trace_n, 1);
+    if (tslot >= 65536) tslot = -1;
+    unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    PG_TRACE(0, trace_gt()); PG_TRACE(1, clock64()); PG_TRACE(7, ((unsigned long long)e << 32) | (smid << 8) | (WARP ? 1 : 0));
+  }
+#endif
   P.need_reset[e] = 0;
   uint32_t ep = P.episode[e];
   P.episode[e] = ep + 1;
@@ -121,6 +139,7 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
         if (!coll) break;
       }
     }
+    PG_TRACE(2, clock64());
     if (st.randomize_obstacles) {  // set_coll_free_obs(0.03)
       const double margin = 0.03;
       bool stop = false;  // StopIteration escapes set_coll_free_obs in the reference (reach_ao.py:1144-1145)
@@ -145,6 +164,7 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
         }
       }
     }
+    PG_TRACE(3, clock64());
     if (gpose && st.pose_kind == PG_POSE_IK_SPHERE)  // its check_collided (fp32 scene pass) must see the obstacles just sampled
       for (int k = 0; k < st.nobs * 3; k++) P.obs_pos_f[(size_t)k * n + e] = (float)P.obs_pos[(size_t)k * n + e];
     if (rbase || gpose) {  // set_coll_free_robot (reach_ao.py:1035-1060): per obstacle, re-draw the pose while the robot is within 0.05
@@ -346,11 +366,13 @@ __device__ __forceinline__ void reset_env(const Params& P, const int e, const ui
   P.rng[e] = g.s_hi; P.rng[(size_t)n + e] = g.s_lo; P.rng[(size_t)2 * n + e] = g.i_hi; P.rng[(size_t)3 * n + e] = g.i_lo;
   if (status && leader) atomicAdd(&P.stats[6], 1.0);
   float ag[3], dg[3];
+  PG_TRACE(4, clock64());
   if (WARP && P.task == 1 && P.obstacle_obs != 0 && P.scene.nobs + P.scene.nstatic > 0) observe_reset_warp(P, e, q, cq, sq, ag);
   else observe<true>(P, e, q, qd, q, cq, sq, ag, true);
   dg[0] = (float)goal[0]; dg[1] = (float)goal[1]; dg[2] = (float)goal[2];
   bool succ = is_success(P, e, ag, dg);
   if (!AUTO) { P.done[e] = 0; P.flags[e] = succ ? 1 : 0; P.reward[e] = 0.f; }
+  PG_TRACE(5, clock64()); PG_TRACE(6, trace_gt());
 }
 
 // LIST = false: every environment (or those of `mask`), one thread each.  LIST = true: the environments k_step appended to the

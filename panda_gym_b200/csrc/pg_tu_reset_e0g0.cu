@@ -6,4 +6,5 @@
 #define PG_RESET_LAUNCH launch_reset_e0g0
 #define PG_OBSERVE_KERNEL k_observe
 #define PG_OBSERVE_LAUNCH launch_observe_e0
+#define PG_RESET_TRACE_EXPORT
 #include "pg_reset_variant.inc"
