@@ -113,7 +113,14 @@ bool cyl_box_hits(V3 rel, V3 a, float r, float h, V3 core, float margin) {
   if (bd.exact) return true;
   V3 on;
   if (point_cylinder<float>(bd.pb, rel, a, r, h, on) <= thr) return true;  // the box's closest point already reaches the cylinder
+#ifndef PG_FLAG_FULL_GJK
+  // only the sign is wanted: GJK stops as soon as one of its two bounds crosses the threshold (gjk_cyl_box_decide) instead of
+  // converging (20 iterations + 4 polish projections) while the rest of the block waits at the pass's barriers
+  GjkIn<float> g; g.c = rel; g.a = a; g.b = v3(0.f, 0.f, 0.f); g.e = core; g.r = r; g.h = h;
+  return gjk_cyl_box_decide<float>(g, thr) <= thr;
+#else
   return cyl_box<float>(rel, a, r, h, v3(0.f, 0.f, 0.f), core, margin).d <= 0.f;
+#endif
 }
 
 template <int K>
