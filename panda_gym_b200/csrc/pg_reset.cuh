@@ -546,8 +546,10 @@ static __device__ __noinline__ void observe_reset_warp(const Params& P, int e, c
         o = v3(P.obs_pos_f[(size_t)(j * 3 + 0) * n + e], P.obs_pos_f[(size_t)(j * 3 + 1) * n + e], P.obs_pos_f[(size_t)(j * 3 + 2) * n + e]);
       } else ob = static_obst(P.scene, j - P.scene.nobs, o);
       const int k0 = slot_first(s), k1 = k0 + slot_count(s);
+      PG_CHECK(s >= 0 && s < 9 && k0 >= 0 && k1 <= pgm::kNumPrim);
       for (int k = k0; k < k1; k++) {
         const PrimRT& pr = kPrimRT[k];
+        PG_CHECK(pr.frame >= 0 && pr.frame < 8);
         prim_vs_obstacle_rt(Fr[pr.frame], pr, o, ob, best, dir);
       }
     }
