@@ -24,6 +24,8 @@ def geom():
     L.geom_cyl_box_bound_f64.argtypes = [P, P, D, D, P, P]
     L.geom_cyl_box_bound_f32.argtypes = [P, P, D, D, P, P]
     L.geom_seg_box_f64.argtypes = [P, P, D, P, P]
+    for f in (L.geom_gjk_decide_f64, L.geom_gjk_decide_f32):
+        f.argtypes = [P, P, D, D, P, D]; f.restype = D
     return L
 
 
@@ -76,3 +78,32 @@ def test_bounds_bracket_the_oracle_gjk(geom, oracle):
         if exact and out32[1] > 0:
             assert abs(out32[0] - d) < 2e-6
     assert n_exact > 500 and n_slanted > 500
+
+
+def test_thresholded_gjk_decides_like_the_converged_one(geom, oracle):
+    """gjk_cyl_box_decide (the reset's accept / reject tests in fp64, the flag pass's sign test in fp32) stops as soon as one of
+    GJK's two bounds settles `distance <= thr`: whatever it returns must lie on the same side of thr as the oracle's converged
+    fp64 GJK distance, for thresholds well inside, at and well outside the distance (ties within the arithmetic's resolution
+    excluded), and must itself be a valid bound (<= thr and >= d when within; > thr and <= d when beyond)."""
+    L = oracle.lib()
+    rng = np.random.default_rng(5)
+    pa = np.zeros(3); pb = np.zeros(3); zero = np.zeros(3)
+    n_in = n_out = 0
+    for c, a, r, h, e in _cases(rng, 2500):
+        d = L.pgo_gjk_cyl_box(_dp(c), _dp(a), float(r), float(h), _dp(zero), _dp(e), _dp(pa), _dp(pb))
+        for thr in (0.5 * d, d - 1e-6, d + 1e-6, 1.5 * d + 1e-3, 0.031, 0.051):
+            if thr <= 0:
+                continue
+            v = geom.geom_gjk_decide_f64(_dp(c), _dp(a), float(r), float(h), _dp(e), float(thr))
+            if abs(d - thr) > 1e-9:
+                assert (v <= thr) == (d <= thr), (d, thr, v)
+                if d <= thr:
+                    n_in += 1
+                    assert v >= d - 1e-9
+                else:
+                    n_out += 1
+                    assert v <= d + 1e-9
+            v32 = geom.geom_gjk_decide_f32(_dp(c), _dp(a), float(r), float(h), _dp(e), float(thr))
+            if abs(d - thr) > 2e-5 + 1e-4 * d:   # fp32 resolution of the inputs and of GJK's own stop rule
+                assert (v32 <= np.float32(thr)) == (d <= thr), (d, thr, v32)
+    assert n_in > 2000 and n_out > 2000
