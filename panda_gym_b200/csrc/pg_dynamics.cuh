@@ -389,6 +389,9 @@ __device__ __forceinline__ constexpr float motor_imp(int d) { return (d < 4 ? 87
 #define PG_SYNC_C ((PG_SYNC_MASK & 4) != 0)
 #define PG_SYNC_D ((PG_SYNC_MASK & 8) != 0)
 #define PG_SYNC_E ((PG_SYNC_MASK & 16) != 0)
+#ifdef PG_SWEEP_PROBE
+static __device__ int g_sweeps[148 * 512];
+#endif
 template <bool SYNC>
 __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_imp, float* q, float* qd, float* cq, float* sq,
                                         const float* tgt, int stride) {
@@ -457,6 +460,9 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
       float carry = 0.f;
       { float res = 0.f; PG_MOTOR_ROW(6) carry = res; }
       for (int it = 0; it < kSolverIters; it += 2) {
+#ifdef PG_SWEEP_PROBE  // variant build only (tools/sweep_probe.py): sweep pairs this environment ran, summed over the step
+        if (live) g_sweeps[blockIdx.x * blockDim.x + threadIdx.x]++;
+#endif
         if (live) {  // even iteration: backward sweep (row 6 done above / by the forward sweep before)
           float res = carry;
           PG_MOTOR_ROW(5) PG_MOTOR_ROW(4) PG_MOTOR_ROW(3) PG_MOTOR_ROW(2) PG_MOTOR_ROW(1) PG_MOTOR_ROW(0)
