@@ -390,7 +390,8 @@ __device__ __forceinline__ constexpr float motor_imp(int d) { return (d < 4 ? 87
 #define PG_SYNC_D ((PG_SYNC_MASK & 8) != 0)
 #define PG_SYNC_E ((PG_SYNC_MASK & 16) != 0)
 #ifdef PG_SWEEP_PROBE
-static __device__ int g_sweeps[148 * 512];
+static __device__ int g_sweeps[20 * 148 * 512];  // [substep of the step][thread]
+static __device__ int g_calls[148 * 512];
 #endif
 template <bool SYNC>
 __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_imp, float* q, float* qd, float* cq, float* sq,
@@ -461,7 +462,7 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
       { float res = 0.f; PG_MOTOR_ROW(6) carry = res; }
       for (int it = 0; it < kSolverIters; it += 2) {
 #ifdef PG_SWEEP_PROBE  // variant build only (tools/sweep_probe.py): sweep pairs this environment ran, summed over the step
-        if (live) g_sweeps[blockIdx.x * blockDim.x + threadIdx.x]++;
+        if (live) g_sweeps[(size_t)(g_calls[blockIdx.x * blockDim.x + threadIdx.x] % 20) * (148 * 512) + blockIdx.x * blockDim.x + threadIdx.x]++;
 #endif
         if (live) {  // even iteration: backward sweep (row 6 done above / by the forward sweep before)
           float res = carry;
@@ -478,6 +479,9 @@ __device__ __forceinline__ void substep(bool active, bool velocity, bool unit_im
       }
 #undef PG_MOTOR_ROW
     }
+#ifdef PG_SWEEP_PROBE
+    g_calls[blockIdx.x * blockDim.x + threadIdx.x]++;
+#endif
     // 4. apply, clamp, integrate
 #pragma unroll
     for (int d = 0; d < 7; d++) {

@@ -67,11 +67,11 @@ cudaError_t step_kernel_attrs(int* out) {
 }  // namespace pg
 
 #ifdef PG_SWEEP_PROBE
-// variant build only (tools/sweep_probe.py): read and clear the per-environment sweep-pair counters of k_step
-extern "C" int pg_debug_sweeps_read(int* out_host, int n) {
-  if (n > 148 * 512) n = 148 * 512;
-  if (cudaMemcpyFromSymbol(out_host, pg::g_sweeps, (size_t)n * sizeof(int)) != cudaSuccess) return -1;
-  static int zeros[148 * 512];
+// variant build only (tools/sweep_probe.py): read and clear the per-substep, per-environment sweep-pair counters of k_step
+// out_host: int [20][148 * 512]
+extern "C" int pg_debug_sweeps_read(int* out_host) {
+  if (cudaMemcpyFromSymbol(out_host, pg::g_sweeps, sizeof(int) * 20 * 148 * 512) != cudaSuccess) return -1;
+  static int zeros[20 * 148 * 512];
   return (int)cudaMemcpyToSymbol(pg::g_sweeps, zeros, sizeof zeros);
 }
 #endif

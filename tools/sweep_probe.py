@@ -1,43 +1,45 @@
-"""How well can a key known at the START of a step predict an environment's PGS work in that step?  Variant built with
--DPG_SWEEP_PROBE counts the sweep pairs every environment runs per step; this script compares, for several keys, the lane
-efficiency of the solver loop if the 443 environments of a block were sorted by the key before being dealt to warps
-(sum of per-warp maxima against the sum of the counts; the step total is a proxy for the per-substep maxima).
+"""How much of the idle-lane loss of k_step's PGS loop could a re-ordering of a block's environments recover?  A variant built
+with -DPG_SWEEP_PROBE counts the sweep pairs every environment runs in every substep; this script computes the lane efficiency
+of the loop (sum of counts / 32 x sum over substeps of per-warp maxima) for several orderings of the 448 threads of a block:
+keys known at the start of the step, the previous step's work, and the work of the step's own first substeps (what a
+re-binning inside the step could use).
 PANDA_B200_LIB=panda_gym_b200/variants/libpanda_b200_probe.so python tools/sweep_probe.py"""
 import ctypes, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from panda_gym_b200 import sim, _lib
 lib = _lib.load()
-N = 65536
+N, T = 65536, 148 * 512
 b = sim.PandaBatch(sim.make_config(1, N, scenario="reachao3", max_episode_steps=100, auto_reset=True)); b.seed(1234); b.reset()
 for k in range(160):
     b.step(b.random_actions(1234, k))
 torch.cuda.synchronize()
-buf = np.zeros(N, np.int32)
-lib.pg_debug_sweeps_read(buf.ctypes.data_as(ctypes.c_void_p), N)
-prev = None
-def eff(counts, key):
+buf = np.zeros((20, T), np.int32)
+lib.pg_debug_sweeps_read(buf.ctypes.data_as(ctypes.c_void_p))
+def eff(c, key, first=0):
+    """c [20][N]; order by key, efficiency over substeps first..19"""
     tot = 0.0; ideal = 0.0
     for blk in range(0, N, 448):
-        c = counts[blk:blk + 448]; k = key[blk:blk + 448]
-        c = c[np.argsort(k, kind="stable")]
-        pad = (-len(c)) % 32
-        c = np.concatenate([c, np.zeros(pad, c.dtype)]).reshape(-1, 32)
-        tot += c.max(1).sum() * 32; ideal += c.sum()
+        o = np.argsort(key[blk:blk + 448], kind="stable")
+        cc = c[first:, blk:blk + 448][:, o]
+        pad = (-cc.shape[1]) % 32
+        cc = np.concatenate([cc, np.zeros((cc.shape[0], pad), cc.dtype)], 1).reshape(cc.shape[0], -1, 32)
+        tot += cc.max(2).sum() * 32; ideal += cc.sum()
     return ideal / tot
-for k in range(160, 166):
+prev = None
+for k in range(160, 164):
     a = b.random_actions(1234, k)
-    q = b.view("q").clone(); qd = b.view("qd").clone()
     b.step(a); torch.cuda.synchronize()
-    lib.pg_debug_sweeps_read(buf.ctypes.data_as(ctypes.c_void_p), N)
-    c = buf.astype(np.float64).copy()
-    an = a.cpu().numpy(); qn = q.cpu().numpy(); qdn = qd.cpu().numpy()
-    if qn.shape[0] == 7: qn = qn.T; qdn = qdn.T
-    keys = {"none (env order)": np.arange(N), "oracle (the count itself)": c, "|a|_inf": np.abs(an).max(1), "|a|_1": np.abs(an).sum(1),
-            "|qd|_inf at start": np.abs(qdn).max(1), "|0.05 a - qd dt|_1": np.abs(0.05 * an - qdn * 0.04).sum(1)}
-    if prev is not None: keys["previous step's count"] = prev
-    print("step %d: pairs per env-step mean %.1f min %d max %d (of %d); corr with prev %s" % (
-        k, c.mean(), c.min(), c.max(), 25 * 20, "%.2f" % np.corrcoef(c, prev)[0, 1] if prev is not None else "-"))
-    for name, key in keys.items():
-        print("   sorted by %-28s lane efficiency %.3f   corr %.2f" % (name, eff(c, key), np.corrcoef(c, key)[0, 1] if name != "none (env order)" else 0))
-    prev = c
+    lib.pg_debug_sweeps_read(buf.ctypes.data_as(ctypes.c_void_p))
+    c = buf[:, :N].astype(np.float64).copy()
+    tot = c.sum(0)
+    print("step %d: pairs per env-substep mean %.1f of 25; per substep: %s" % (k, c.mean(), " ".join("%.0f" % x for x in c.mean(1))))
+    print("   share of env-substeps at the cap (25 pairs): %.2f; below 5 pairs: %.2f" % ((c >= 25).mean(), (c < 5).mean()))
+    keys = [("environment index (as built)", np.arange(N), 0), ("the step's total (unattainable)", tot, 0), ("|a|_inf", np.abs(a.cpu().numpy()).max(1), 0)]
+    if prev is not None: keys.append(("previous step's total", prev, 0))
+    for s in (1, 2, 4):
+        keys.append(("work of substeps 0..%d, applied from substep %d on" % (s - 1, s), c[:s].sum(0), s))
+        keys.append(("   (env order over the same substeps)", np.arange(N), s))
+    for name, key, first in keys:
+        print("   %-52s lane efficiency %.3f" % (name, eff(c, key, first)))
+    prev = tot
